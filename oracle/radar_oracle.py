@@ -1,0 +1,412 @@
+"""CPU oracle for the ADC-cube -> point-cloud path.   *** TEST INFRASTRUCTURE ONLY ***
+
+A plain-numpy (fp64) restatement of what the reference computes on this path, written as
+pure functions so it can be pinned and used as a checker.  Only ``tests/``,
+``__graft_entry__.smoke()`` and ``bench.py``'s CPU-baseline / ``--impl reference`` legs may
+import it; nothing under ``mmwave_radar_processing_b200/`` does (the product path fails
+loudly when the CUDA library is missing).
+
+Pinning: the reference's own tests hold no numeric golden vectors for this path
+(SURVEY.md section 8c).  The pin is ``tests/golden/*.npz``: outputs of the reference classes
+themselves, produced in the build container by ``tests/golden/make_golden.py`` (which
+imports ``/root/reference`` read-only) on seeded synthetic cubes; ``tests/test_oracle_golden.py``
+checks every function below against them.  The reference's two runnable known-answer checks
+(``tests/test_point_cloud_angles.py``, the CA/GO/SO part of ``tests/verify_detectors_manual.py``)
+are restated in ``tests/test_reference_known_answers.py``.
+
+Third-party arithmetic the reference leans on (numpy 1.26.4 pinned in its poetry.lock;
+pocketfft ``np.fft``, ``np.hanning``/``np.hamming``, ``np.partition``, ``sliding_window_view``)
+is re-expressed from the published definitions: forward DFT ``X[k]=sum x[n] e^{-2 pi i kn/N}``,
+``hanning(M)[n]=0.5-0.5cos(2 pi n/(M-1))``, ``hamming(M)[n]=0.54-0.46cos(2 pi n/(M-1))``,
+k-th order statistic = k-th entry of the sorted training set.
+
+Every function cites the reference lines it follows (paths relative to
+``/root/reference/mmwave_radar_processing/``).
+"""
+from __future__ import annotations
+
+import numpy as np
+from numpy.lib.stride_tricks import sliding_window_view
+
+C_M_S = 299792458.0
+
+
+# --------------------------------------------------------------------------------------
+# windows / small helpers
+# --------------------------------------------------------------------------------------
+def hann(m: int) -> np.ndarray:
+    """``np.hanning`` (symmetric, zero end points; hanning(1) == [1.])."""
+    if m < 1:
+        return np.zeros(0)
+    if m == 1:
+        return np.ones(1)
+    n = np.arange(m)
+    return 0.5 - 0.5 * np.cos(2.0 * np.pi * n / (m - 1))
+
+
+def hamm(m: int) -> np.ndarray:
+    """``np.hamming``."""
+    if m < 1:
+        return np.zeros(0)
+    if m == 1:
+        return np.ones(1)
+    n = np.arange(m)
+    return 0.54 - 0.46 * np.cos(2.0 * np.pi * n / (m - 1))
+
+
+def shift_index(n: int) -> np.ndarray:
+    """``fftshift`` as a gather: out[i] = in[(i - n//2) mod n]."""
+    return (np.arange(n) - n // 2) % n
+
+
+# --------------------------------------------------------------------------------------
+# a1: int16 I/Q -> complex cube, TDM virtual array
+# --------------------------------------------------------------------------------------
+def iq_to_cube(iq: np.ndarray) -> np.ndarray:
+    """Device ADC layout -> the reference's complex cube.
+
+    ``iq``: int16 ``[chirp][rx][sample][2]`` (I then Q), the layout the CUDA path ingests
+    (DESIGN.md "ADC layout").  Returns complex128 ``(rx, samples, chirps)`` - the array
+    ``CpslDS.get_radar_adc_data`` hands to processors (processors/_processor.py:58).
+    The cast int16 -> float64 is exact.
+    """
+    iq = np.asarray(iq)
+    assert iq.dtype == np.int16 and iq.ndim == 4 and iq.shape[-1] == 2
+    z = iq[..., 0].astype(np.float64) + 1j * iq[..., 1].astype(np.float64)   # (C, R, S)
+    return np.ascontiguousarray(z.transpose(1, 2, 0))                       # (R, S, C)
+
+
+def virtual_array(cube: np.ndarray, num_rx: int, cpl: int, loops: int) -> np.ndarray:
+    """TDM-MIMO regroup (processors/virtual_array_reformater.py:44-65).
+
+    virtual channel ``v = tx_slot*num_rx + rx`` takes chirps ``c = loop*cpl + tx_slot``.
+    """
+    s = cube.shape[1]
+    out = np.zeros((num_rx * cpl, s, loops), dtype=complex)
+    for slot in range(cpl):
+        out[slot * num_rx:(slot + 1) * num_rx] = cube[:num_rx, :, slot::cpl][:, :, :loops]
+    return out
+
+
+# --------------------------------------------------------------------------------------
+# a2-a5: range-Doppler
+# --------------------------------------------------------------------------------------
+def rd_axes(vel_max, vel_res, range_max, range_res):
+    """Bin axes of RangeDopplerProcessor.configure (processors/range_doppler_resp.py:33-47)."""
+    vel_bins = np.arange(start=-1 * vel_max, stop=vel_max - vel_res + 1e-3, step=vel_res)
+    range_bins = np.arange(start=0, step=range_res, stop=range_max - range_res / 2 + 1e-3)
+    return range_bins, vel_bins
+
+
+def range_doppler(cube_v: np.ndarray) -> np.ndarray:
+    """Complex RD cube for all antennas (processors/range_doppler_resp.py:49-103).
+
+    Hann over samples x Hann over chirps, unnormalised forward 2-D DFT over (S, L),
+    ``fftshift`` on the Doppler axis only.
+    """
+    _, s, l = cube_v.shape
+    w = hann(s)[None, :, None] * hann(l)[None, None, :]
+    spec = np.fft.fft(np.fft.fft(cube_v * w, axis=1), axis=2)
+    return spec[:, :, shift_index(l)]
+
+
+def rd_magnitude0(rd: np.ndarray) -> np.ndarray:
+    """CFAR input: |RD| of virtual antenna 0 only (range_doppler_detection/range_doppler_detector.py:72-80)."""
+    return np.abs(rd[0])
+
+
+def coarse_range_profile(cube_v: np.ndarray, chirp_idx: int = 0) -> np.ndarray:
+    """RangeProcessor.coarse_fft (processors/range_resp.py:32-57): one chirp, Hann(S), |FFT|, mean over antennas."""
+    x = cube_v[:, :, chirp_idx] * hann(cube_v.shape[1])
+    return np.mean(np.abs(np.fft.fft(x, axis=1)), axis=0)
+
+
+# --------------------------------------------------------------------------------------
+# a6-a9: CFAR family
+# --------------------------------------------------------------------------------------
+def ca_alpha(n_train_cells: int, pfa: float) -> float:
+    """alpha = N (pfa^(-1/N) - 1)  (detectors/base.py:155-169, :281-293)."""
+    return n_train_cells * (pfa ** (-1.0 / n_train_cells) - 1.0)
+
+
+def os_rank(rho: float, n_train_cells: int) -> int:
+    """k = clip(int(rho*N), 1, N)  (detectors/os_cfar.py:25-27, :131-132)."""
+    return max(1, min(int(rho * n_train_cells), n_train_cells))
+
+
+def _train_mask_1d(t: int, g: int) -> np.ndarray:
+    m = np.ones(2 * (t + g) + 1, dtype=bool)
+    m[t:t + 2 * g + 1] = False
+    return m
+
+
+def cfar_1d(x: np.ndarray, kind: str, num_train: int, num_guard: int, pfa: float = 0.0,
+            rho: float = 0.0, alpha: float = 0.0):
+    """1-D CFAR thresholds (detectors/ca_cfar.py:11-77, os_cfar.py:29-86, go_so_cfar.py:11-123).
+
+    Returns ``(thresholds, noise, mask)``; outside the valid interior thresholds = +inf, noise = 0.
+    ``kind`` in {"ca","go","so","os"}.  GO/SO use alpha computed with N = num_train (one side).
+    """
+    x = np.asarray(x, dtype=np.float64)
+    n = x.shape[0]
+    thr = np.full(n, np.inf)
+    noise = np.zeros(n)
+    t, g = int(num_train), int(num_guard)
+    win = 2 * (t + g) + 1
+    if n >= win:
+        w = sliding_window_view(x, win)                      # (n-win+1, win)
+        left, right = w[:, :t], w[:, t + 2 * g + 1:]
+        if kind == "ca":
+            est = np.mean(w[:, _train_mask_1d(t, g)], axis=1)
+            a = ca_alpha(2 * t, pfa)
+        elif kind == "go":
+            est = np.maximum(np.mean(left, axis=1), np.mean(right, axis=1))
+            a = ca_alpha(t, pfa)
+        elif kind == "so":
+            est = np.minimum(np.mean(left, axis=1), np.mean(right, axis=1))
+            a = ca_alpha(t, pfa)
+        elif kind == "os":
+            k = os_rank(rho, 2 * t)
+            est = np.sort(np.concatenate((left, right), axis=1), axis=1)[:, k - 1]
+            a = alpha
+        else:
+            raise ValueError(kind)
+        c = t + g
+        thr[c:c + est.shape[0]] = a * est
+        noise[c:c + est.shape[0]] = est
+    return thr, noise, x > thr
+
+
+def cfar_2d(x: np.ndarray, kind: str, num_train, num_guard, pfa: float = 0.0,
+            rho: float = 0.0, alpha: float = 0.0):
+    """2-D CFAR thresholds (detectors/ca_cfar.py:85-155, os_cfar.py:134-195; decision base.py:208-230).
+
+    Training set = outer (2(Tr+Gr)+1)x(2(Td+Gd)+1) rectangle minus the centre (2Gr+1)x(2Gd+1).
+    Returns ``(thresholds, noise, mask)``.
+    """
+    x = np.asarray(x, dtype=np.float64)
+    r, d = x.shape
+    tr, td = int(num_train[0]), int(num_train[1])
+    gr, gd = int(num_guard[0]), int(num_guard[1])
+    wr, wd = 2 * (tr + gr) + 1, 2 * (td + gd) + 1
+    thr = np.full((r, d), np.inf)
+    noise = np.zeros((r, d))
+    if r >= wr and d >= wd:
+        w = sliding_window_view(x, (wr, wd))                 # (r', d', wr, wd)
+        m = np.ones((wr, wd), dtype=bool)
+        m[tr:tr + 2 * gr + 1, td:td + 2 * gd + 1] = False
+        n_train = int(m.sum())
+        if kind == "ca":
+            est = (w * m).sum(axis=(2, 3)) / n_train
+            a = ca_alpha(n_train, pfa)
+        elif kind == "os":
+            k = os_rank(rho, n_train)
+            est = np.sort(w[..., m], axis=-1)[..., k - 1]
+            a = alpha
+        else:
+            raise ValueError(kind)
+        cr, cd = tr + gr, td + gd
+        thr[cr:cr + est.shape[0], cd:cd + est.shape[1]] = a * est
+        noise[cr:cr + est.shape[0], cd:cd + est.shape[1]] = est
+    return thr, noise, x > thr
+
+
+def mask_to_dets(mask: np.ndarray) -> np.ndarray:
+    """Row-major (range, Doppler) detection list, ``(0,2)`` int when empty
+    (detectors/base.py:226-230; range_doppler_detection/range_doppler_detector_2d.py:61-66)."""
+    rows, cols = np.nonzero(mask)
+    if rows.size == 0:
+        return np.empty((0, 2), dtype=int)
+    return np.stack((rows, cols), axis=1).astype(int)
+
+
+def detect_sequential(cube_v, rd_mag0, rng_kind, rng_params, vel_kind, vel_params) -> np.ndarray:
+    """RangeDopplerDetectorSequential.process (range_doppler_detection/range_doppler_detector_sequential.py:72-108)."""
+    prof = coarse_range_profile(cube_v, 0)
+    _, _, rmask = cfar_1d(prof, rng_kind, **rng_params)
+    out = []
+    for ri in np.nonzero(rmask)[0]:
+        _, _, vmask = cfar_1d(rd_mag0[ri], vel_kind, **vel_params)
+        out.extend((int(ri), int(di)) for di in np.nonzero(vmask)[0])
+    return np.array(out, dtype=int) if out else np.empty((0, 2), dtype=int)
+
+
+def detect_range_band(rd_mag0, range_bins, altitude_m, vel_kind, vel_params) -> np.ndarray:
+    """CFAR part of RangeDopplerGroundDetector.process
+    (range_doppler_detection/range_doppler_ground_detector.py:84-119) for a given altitude."""
+    lo = int(np.argmin(np.abs(range_bins - altitude_m)))
+    max_rng = min(np.max(range_bins), altitude_m / np.cos(np.deg2rad(60)))
+    hi = int(np.argmin(np.abs(range_bins - max_rng)))
+    rows = [lo] if hi == lo else list(range(lo, hi + 1))
+    out = []
+    for ri in rows:
+        _, _, vmask = cfar_1d(rd_mag0[ri], vel_kind, **vel_params)
+        out.extend((int(ri), int(di)) for di in np.nonzero(vmask)[0])
+    return np.array(out, dtype=int) if out else np.empty((0, 2), dtype=int)
+
+
+# --------------------------------------------------------------------------------------
+# a13-a15: angle estimation and point cloud
+# --------------------------------------------------------------------------------------
+def angle_axis(num_angle_bins: int):
+    """phase_shifts / angle_bins of PointCloudGenerator.configure and RangeAngleProcessor.configure
+    (processors/point_cloud_generator.py:89-105, range_angle_resp.py:38-48).  Length is A or A+1
+    depending on float rounding of ``np.arange`` - keep the identical expression."""
+    a = num_angle_bins
+    phase = np.arange(start=np.pi, stop=-np.pi - 2 * np.pi / (a - 1), step=-2 * np.pi / (a - 1))
+    phase[-1] = -1 * np.pi
+    return phase, np.arcsin(phase / np.pi)
+
+
+def angle_indices(rd: np.ndarray, r_idx, d_idx, ant_idxs, num_angle_bins: int, shift: bool) -> np.ndarray:
+    """Per-detection zero-padded angle FFT + first-max argmax
+    (processors/point_cloud_generator.py:143-214).  Returns the argmax indices (N,)."""
+    ant = np.asarray(ant_idxs, dtype=int)
+    n = len(r_idx)
+    if ant.size == 0:
+        return np.zeros(n, dtype=int)
+    snap = rd[ant][:, r_idx, d_idx].T                                       # (N, n_ant)
+    pad = np.zeros((n, num_angle_bins), dtype=complex)
+    pad[:, :ant.size] = snap
+    spec = np.fft.fft(pad, axis=1)
+    if shift:
+        spec = spec[:, shift_index(num_angle_bins)]
+    return np.argmax(np.abs(spec), axis=1)
+
+
+def point_cloud(rd, dets, range_bins, vel_bins, az_idxs, el_idxs, num_angle_bins=64,
+                shift_az=True, shift_el=False):
+    """PointCloudGenerator.process after detection (processors/point_cloud_generator.py:108-140,
+    :216-248).  Returns ``(points (N,4) f64, az_index (N,), el_index (N,))``."""
+    if dets.shape[0] == 0:
+        return np.empty((0, 4)), np.zeros(0, dtype=int), np.zeros(0, dtype=int)
+    r_idx = dets[:, 0].astype(int)
+    d_idx = dets[:, 1].astype(int)
+    _, bins = angle_axis(num_angle_bins)
+    az_i = angle_indices(rd, r_idx, d_idx, az_idxs, num_angle_bins, shift_az)
+    el_i = angle_indices(rd, r_idx, d_idx, el_idxs, num_angle_bins, shift_el)
+    az = bins[az_i] if len(az_idxs) else np.zeros(len(r_idx))
+    el = bins[el_i] if len(el_idxs) else np.zeros(len(r_idx))
+    rng = range_bins[r_idx]
+    vel = vel_bins[d_idx]
+    x = rng * np.cos(el) * np.cos(az)
+    y = rng * np.cos(el) * np.sin(az)
+    z = rng * np.sin(el)
+    return np.column_stack((x, y, z, vel)), az_i, el_i
+
+
+# --------------------------------------------------------------------------------------
+# a16: range-angle heat map
+# --------------------------------------------------------------------------------------
+def range_angle(cube_v, num_angle_bins=64, chirp_idx=0, rx_antennas=(), perform_windowing=True):
+    """RangeAngleProcessor.process (processors/range_angle_resp.py:68-122).
+
+    Hann over samples and over ALL antennas of the cube is applied BEFORE the antenna subset;
+    the subset's rank is the antenna's slot in the zero-padded angle FFT.
+    """
+    v, s, _ = cube_v.shape
+    x = cube_v[:, :, chirp_idx]
+    if perform_windowing:
+        x = x * hann(s)[None, :] * hann(v)[:, None]
+    ants = np.asarray(rx_antennas, dtype=int)
+    if ants.size > 0:
+        x = x[ants]
+    data = np.zeros((s, num_angle_bins), dtype=complex)
+    data[:, :x.shape[0]] = x.T
+    spec = np.fft.fft(np.fft.fft(data, axis=0), axis=1)
+    return np.abs(spec[:, shift_index(num_angle_bins)])
+
+
+# --------------------------------------------------------------------------------------
+# a17: Doppler beam sharpening
+# --------------------------------------------------------------------------------------
+def dbs_bin_selection(angle_bins_coarse, angle_bins_dbs, vel_bins, velocity_ned):
+    """Host-side (Doppler bin, coarse angle bin) choice per output angle
+    (processors/range_angle_resp_dbs_enhanced.py:200-258)."""
+    vel_bin = np.empty(len(angle_bins_dbs), dtype=int)
+    ang_bin = np.empty(len(angle_bins_dbs), dtype=int)
+    v = np.asarray(velocity_ned, dtype=float)
+    for i, th in enumerate(angle_bins_dbs):
+        rhat = np.array([np.cos(th), np.sin(th), 0])
+        dop = -1 * np.dot(rhat / np.linalg.norm(rhat), v)
+        vel_bin[i] = np.argmin(np.abs(vel_bins - dop))
+        ang_bin[i] = np.argmin(np.abs(angle_bins_coarse - th))
+    return vel_bin, ang_bin
+
+
+def dbs_enhanced(cube_v, velocity_ned, vel_bins, num_angle_bins=64, num_angle_bins_dbs=64, rx_antennas=()):
+    """RangeAngleProcessorDBSEnhanced.process_dbs_enhanced
+    (processors/range_angle_resp_dbs_enhanced.py:137-198, :216-304): antennas are subset FIRST,
+    then Hann over range, Doppler and the subset's antennas; 3-D FFT; pick one
+    (angle, Doppler) cell per output angle."""
+    ants = np.asarray(rx_antennas, dtype=int)
+    x = cube_v[ants] if ants.size > 0 else cube_v
+    n, s, l = x.shape
+    a = num_angle_bins
+    xr = np.fft.fft(x * hann(s)[None, :, None], axis=1)
+    xd = np.fft.fft(xr * hann(l)[None, None, :], axis=2)[:, :, shift_index(l)]
+    pad = np.zeros((a, s, l), dtype=complex)
+    pad[:n] = xd * hann(n)[:, None, None]
+    mag = np.abs(np.fft.fft(pad, axis=0)[shift_index(a)])
+    _, coarse = angle_axis(a)
+    fine = np.linspace(coarse[0], coarse[-1], num_angle_bins_dbs)
+    vb, ab = dbs_bin_selection(coarse, fine, vel_bins, velocity_ned)
+    return mag[ab, :, vb].T                                              # (S, A_dbs)
+
+
+# --------------------------------------------------------------------------------------
+# a18: multi-frame synthetic array (SAR)
+# --------------------------------------------------------------------------------------
+def sar_chirp_times_us(cpl, loops, chirp_period_us, chirp_cfg_idx=0, stride=1, start_index=0):
+    """Valid-chirp mask and (negative) chirp start times, last chirp of the frame at 0
+    (processors/simple_synthetic_array_beamformer_processor_multiFrame.py:207-234)."""
+    n = cpl * loops
+    cfg_of_chirp = np.tile(np.arange(start_index, start_index + cpl), loops)
+    valid = np.nonzero(cfg_of_chirp == chirp_cfg_idx)[0][::stride]
+    mask = np.zeros(n, dtype=bool)
+    mask[valid] = True
+    times = np.arange(n - 1, -1, -1) * -chirp_period_us
+    return mask, times[mask]
+
+
+def sar_geometry(history_vel, chirp_times_us, frame_period_ms):
+    """Element positions chained backwards over frames (…multiFrame.py:377-471).
+    ``history_vel`` (F,3) oldest->newest.  Returns (F,3,Lv)."""
+    f = history_vel.shape[0]
+    geo = np.zeros((f, 3, chirp_times_us.shape[0]))
+    p0 = np.zeros(3)
+    for i in range(f - 1, -1, -1):
+        vel = history_vel[i]
+        geo[i] = 2 * chirp_times_us[None, :] * 1e-6 * vel[:, None] + p0[:, None]
+        p0 = p0 + 2 * vel * (-1 * frame_period_ms * 1e-3)
+    return geo
+
+
+def sar_velocity_gate(history_vel, min_vel, max_vel, max_vel_stdev) -> bool:
+    """Validity gate of _update_vel_history (…multiFrame.py:352-375)."""
+    h = np.asarray(history_vel, dtype=float)
+    ok = np.all((min_vel <= np.abs(h)) & (np.abs(h) <= max_vel))
+    ok = ok and np.all(np.std(h, axis=0) <= max_vel_stdev)
+    d = h / (np.linalg.norm(h, axis=1, keepdims=True) + 1e-6)
+    return bool(ok and np.all(d @ d.T > 0.95))
+
+
+def sar_steering(az_rad, el_rad):
+    """Unit pointing vectors d[(x,y,z), az, el] (…multiFrame.py:474-488)."""
+    th, ph = np.meshgrid(np.asarray(az_rad), np.asarray(el_rad), indexing="ij")
+    return np.array([np.cos(th) * np.cos(ph), np.sin(th) * np.cos(ph), np.sin(ph)])
+
+
+def sar_response(history, geometry, d, lambda_m):
+    """compute_synthetic_response (…multiFrame.py:499-585).
+
+    ``history`` (F,S,Lv) complex oldest->newest, ``geometry`` (F,3,Lv), ``d`` (3,A,E).
+    out[:,a,e] = FFT_S( hann(S) * sum_n hamming(N)[n] x[s,n] e^{+2 pi i d.p_n / lambda} ).
+    """
+    f, s, lv = history.shape
+    x = history.transpose(1, 0, 2).reshape(s, f * lv) * hamm(f * lv)[None, :]
+    p = geometry.transpose(1, 0, 2).reshape(3, f * lv)
+    _, na, ne = d.shape
+    steer = np.exp(1j * 2 * np.pi * np.einsum("cae,cn->nae", d, p) / lambda_m)      # (N, A, E)
+    beams = np.einsum("sn,nae->sae", x, steer)
+    return np.fft.fft(beams * hann(s)[:, None, None], axis=0)
