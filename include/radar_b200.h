@@ -1,0 +1,189 @@
+/*
+ * radar_b200.h - C ABI of libradar_b200.so: the B200 (sm_100a) ADC-cube -> point-cloud path.
+ *
+ * This is the drop-in boundary.  The reference is pure Python/numpy and has
+ * no FFI today; each entry point below names the reference method whose arithmetic it replaces
+ * (paths relative to mmwave_radar_processing/ in the reference tree).  INTEGRATION.md shows the
+ * ctypes stub a maintainer of the reference would add.
+ *
+ * Conventions
+ *  - every function returns 0 on success, a negative RADAR_E_* code otherwise; nothing throws or
+ *    aborts across the boundary; radar_last_error() returns the message of the last failure;
+ *  - all data pointers are DEVICE pointers unless the parameter name starts with "h_";
+ *  - `stream` is a cudaStream_t passed as void* (NULL = default stream); calls are asynchronous
+ *    with respect to the host and ordered on that stream;
+ *  - one ctx per (radar shape, device); calls on one ctx must be serialised by the caller;
+ *  - complex values are interleaved float pairs (re, im) = numpy complex64;
+ *  - ADC ingest layouts (`in_kind`):
+ *        RADAR_IN_IQ16    int16  [frame][chirp][rx][sample][2]   (I,Q)  - raw capture order
+ *        RADAR_IN_CUBE64  float2 [frame][virtual_antenna][sample][loop] - the reference's
+ *                         complex cube after VirtualArrayReformatter (cast to complex64)
+ *    with chirp = loop*chirps_per_loop + tx_slot and virtual_antenna = tx_slot*num_rx + rx
+ *    (processors/virtual_array_reformater.py:44-65).
+ */
+#ifndef RADAR_B200_H
+#define RADAR_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RADAR_B200_ABI_VERSION 1
+
+#define RADAR_OK              0
+#define RADAR_E_INVALID      -1   /* bad argument */
+#define RADAR_E_UNSUPPORTED  -2   /* shape outside what the kernels handle (e.g. tile exceeds shared memory) */
+#define RADAR_E_CUDA         -3   /* CUDA runtime error, see radar_last_error */
+#define RADAR_E_NOMEM        -4
+
+#define RADAR_IN_IQ16    0
+#define RADAR_IN_CUBE64  1
+
+#define RADAR_WIN_RANGE    1      /* Hann over ADC samples */
+#define RADAR_WIN_DOPPLER  2      /* Hann over chirp loops */
+#define RADAR_WIN_ANTENNA  4      /* Hann over antennas (range-angle / DBS) */
+
+#define RADAR_CFAR_CA 0
+#define RADAR_CFAR_OS 1
+#define RADAR_CFAR_GO 2
+#define RADAR_CFAR_SO 3
+
+typedef struct radar_ctx radar_ctx;
+
+typedef struct radar_shape {
+    int32_t num_rx;            /* R   enabled RX antennas                      (cfgManager.py:266-278) */
+    int32_t num_samples;       /* S   ADC samples per chirp = range FFT length                       */
+    int32_t chirps_per_loop;   /* cpl TDM TX slots = frameCfg end-start+1      (cfgManager.py:160-169) */
+    int32_t num_loops;         /* L   frameCfg loops = Doppler FFT length                            */
+} radar_shape;
+
+/* CFAR configuration (detectors/base.py, ca_cfar.py, os_cfar.py, go_so_cfar.py).
+ * 2-D detectors use (train_r, guard_r) along range rows and (train_d, guard_d) along Doppler columns;
+ * 1-D detectors use train_d / guard_d along the processed axis.
+ * alpha: OS uses it as given.  CA/GO/SO: if alpha <= 0 it is derived from pfa exactly like the reference
+ * (alpha = N*(pfa^(-1/N)-1), N = all training cells for CA, ONE side for GO/SO).
+ * os_rank: 1-based k of the k-th smallest training cell; if <= 0 it is derived as clip(int(rho*N),1,N). */
+typedef struct radar_cfar_params {
+    int32_t kind;
+    int32_t train_r, train_d;
+    int32_t guard_r, guard_d;
+    int32_t os_rank;
+    double  pfa;
+    double  rho;
+    double  alpha;
+} radar_cfar_params;
+
+/* ---- context ------------------------------------------------------------------------------- */
+int radar_abi_version(void);
+int radar_ctx_create(const radar_shape* shape, int device, radar_ctx** out_ctx);
+int radar_ctx_destroy(radar_ctx* ctx);
+/* message of the last failed call on ctx (ctx == NULL: last failure of radar_ctx_create in this thread) */
+const char* radar_last_error(const radar_ctx* ctx);
+
+/* Bin axes looked up by radar_point_cloud (host pointers, copied).  They must be produced with the
+ * reference's numpy expressions (processors/range_doppler_resp.py:33-47, point_cloud_generator.py:89-105)
+ * by the host layer so float-arange quirks match bit for bit. */
+int radar_ctx_set_axes(radar_ctx* ctx, const double* h_range_bins, int n_range,
+                       const double* h_vel_bins, int n_vel);
+int radar_ctx_set_angle_bins(radar_ctx* ctx, const double* h_angle_bins, int n_bins);
+
+/* ---- K1+K2: range-Doppler ------------------------------------------------------------------ *
+ * Replaces VirtualArrayReformatter.process + RangeDopplerProcessor.process
+ * (processors/virtual_array_reformater.py:44-65, processors/range_doppler_resp.py:49-110) and the
+ * magnitude of RangeDopplerDetector._compute_range_doppler_response
+ * (processors/range_doppler_detection/range_doppler_detector.py:62-80).
+ *   rd_out  : float2 [frame][n_ant_out][S][L], Doppler axis fftshift-ed, or NULL
+ *   mag_out : float; mag_antenna >= 0 -> [frame][S][L] = |RD[mag_antenna]|,
+ *             mag_antenna == -1 -> [frame][n_ant_out][S][L]; or NULL
+ *   ant_list: optional device int32[n_ant] subset of virtual antennas (NULL -> all V, n_ant ignored)
+ *   window_flags: RADAR_WIN_RANGE | RADAR_WIN_DOPPLER is the reference behaviour; 0 = un-windowed
+ *             (StripMapSARProcessor / MicroDopplerProcessor use that). */
+int radar_range_doppler(radar_ctx* ctx, const void* adc, int in_kind, int n_frames,
+                        const int32_t* ant_list, int n_ant, int window_flags,
+                        void* rd_out, float* mag_out, int mag_antenna, void* stream);
+
+/* ---- a10: coarse range profile ------------------------------------------------------------- *
+ * RangeProcessor.coarse_fft (processors/range_resp.py:32-57): chirp `loop_idx` of the virtual cube,
+ * Hann(S), |FFT|, mean over all V antennas.   profile_out: float [frame][S]. */
+int radar_range_profile(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx,
+                        float* profile_out, void* stream);
+
+/* ---- K4: CFAR + ordered compaction ---------------------------------------------------------- *
+ * 2-D: BaseCFAR2D.detect with CaCFAR2D / OsCFAR2D (detectors/base.py:208-230, ca_cfar.py:85-155,
+ * os_cfar.py:94-195) on n_maps maps float [n_maps][rows][cols].
+ *   noise_out : double [n_maps][rows][cols] noise estimate (0 outside the valid interior) or NULL;
+ *               thresholds = alpha*noise inside, +inf outside: the host layer forms them with the same fp64
+ *               product the kernel compares against
+ *   mask_out  : uint8 [n_maps][rows][cols] (x > alpha*noise, compared in fp64) or NULL
+ *   dets_out  : int32 [n_maps][max_dets][2] (row, col) in row-major order (np.where order) or NULL
+ *   count_out : int32 [n_maps] number of detections (may exceed max_dets: list truncated) or NULL */
+int radar_cfar_2d(radar_ctx* ctx, const float* maps, int n_maps, int rows, int cols,
+                  const radar_cfar_params* params, double* noise_out, uint8_t* mask_out,
+                  int32_t* dets_out, int32_t* count_out, int max_dets, void* stream);
+
+/* 1-D CFAR along the columns of every selected row: BaseCFAR1D.detect with Ca/Os/Go/So
+ * (detectors/base.py:38-65, ca_cfar.py:11-77, os_cfar.py:11-86, go_so_cfar.py:11-123); used on the
+ * range profile (rows = 1) and per range bin along Doppler by the sequential and ground detectors
+ * (processors/range_doppler_detection/range_doppler_detector_sequential.py:72-108,
+ *  range_doppler_ground_detector.py:84-119).
+ *   row_select: optional uint8 [n_maps][rows]; rows with 0 are skipped (no detections, noise 0). */
+int radar_cfar_1d_rows(radar_ctx* ctx, const float* maps, int n_maps, int rows, int cols,
+                       const radar_cfar_params* params, const uint8_t* row_select,
+                       double* noise_out, uint8_t* mask_out,
+                       int32_t* dets_out, int32_t* count_out, int max_dets, void* stream);
+
+/* alpha = N*(pfa^(-1/N)-1) (detectors/base.py:155-169) - host helper so callers print the same number */
+double radar_cfar_ca_alpha(int n_train_cells, double pfa);
+
+/* ---- K3b: per-detection angle FFT + point cloud --------------------------------------------- *
+ * PointCloudGenerator._compute_angle_estimation + _convert_to_cartesian
+ * (processors/point_cloud_generator.py:143-248).
+ *   rd       : float2 [frame][V][S][L] from radar_range_doppler (all V antennas)
+ *   dets     : int32 [frame][max_dets][2], counts int32 [frame]
+ *   az_idx/el_idx : device int32 antenna lists (n == 0 -> angle 0, as the reference)
+ *   points_out : double [frame][max_dets][4] (x, y, z, velocity), FLU frame (fp64 like the reference)
+ *   az_bin_out / el_bin_out : int32 [frame][max_dets] argmax bins (for bit-exact checks) or NULL
+ * Needs radar_ctx_set_axes and radar_ctx_set_angle_bins (n_bins >= num_angle_bins). */
+int radar_point_cloud(radar_ctx* ctx, const void* rd, int n_frames,
+                      const int32_t* dets, const int32_t* counts, int max_dets,
+                      const int32_t* az_idx, int n_az, const int32_t* el_idx, int n_el,
+                      int shift_az, int shift_el, int num_angle_bins,
+                      double* points_out, int32_t* az_bin_out, int32_t* el_bin_out, void* stream);
+
+/* ---- K3a: range-angle heat map --------------------------------------------------------------- *
+ * RangeAngleProcessor.process (processors/range_angle_resp.py:68-122).
+ *   ant_list: device int32[n_ant] (NULL -> all V antennas in order); window_flags: RADAR_WIN_RANGE |
+ *   RADAR_WIN_ANTENNA = perform_windowing True (the antenna Hann spans ALL V antennas and is indexed by
+ *   the ORIGINAL antenna number, applied before the subset).   out: float [frame][S][num_angle_bins]. */
+int radar_range_angle(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx,
+                      const int32_t* ant_list, int n_ant, int num_angle_bins, int window_flags,
+                      float* out, void* stream);
+
+/* ---- K5b: Doppler beam sharpening ------------------------------------------------------------ *
+ * RangeAngleProcessorDBSEnhanced.process_dbs_enhanced (processors/range_angle_resp_dbs_enhanced.py:
+ * 137-304).  The host layer selects, per output angle i, the Doppler bin vel_bin[i] and the coarse angle
+ * bin ang_bin[i] (fp64 argmins, :239-258) and passes them as device int32[n_out].
+ *   out: float [frame][S][n_out]. */
+int radar_dbs(radar_ctx* ctx, const void* adc, int in_kind, int n_frames,
+              const int32_t* ant_list, int n_ant, int num_angle_bins,
+              const int32_t* vel_bin, const int32_t* ang_bin, int n_out,
+              float* out, void* stream);
+
+/* ---- K5a: multi-frame synthetic-array beamformer ---------------------------------------------- *
+ * SyntheticArrayBeamformerProcessor.compute_synthetic_response
+ * (processors/simple_synthetic_array_beamformer_processor_multiFrame.py:499-585).
+ *   aperture : float2 [S][N]  history reshaped (frame-major, valid chirps), NOT yet Hamming-weighted
+ *   positions: double [3][N]  element positions (x,y,z rows)
+ *   dirs     : double [3][G]  unit pointing vectors, g = az*E + el
+ *   [g_begin, g_end) : voxel slice computed by this call (multi-GPU sharding)
+ *   out      : float2 [S][g_end-g_begin] (range bin major), complex response */
+int radar_sar_image(radar_ctx* ctx, const void* aperture, int num_samples, int n_elems,
+                    const double* positions, const double* dirs, int n_dirs, double lambda_m,
+                    int g_begin, int g_end, void* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RADAR_B200_H */

@@ -1,0 +1,256 @@
+// C-ABI layer of libradar_b200.so: context life cycle, host-built tables, argument checks, and the
+// extern "C" entry points declared in include/radar_b200.h.  No torch types cross this boundary.
+#include <cmath>
+#include <cstdarg>
+#include <cstring>
+#include <new>
+#include "radar_internal.h"
+
+namespace rb {
+
+static thread_local char g_create_error[512] = {0};
+
+int set_error(radar_ctx* ctx, int code, const char* fmt, ...) {
+    char* dst = ctx ? ctx->err : g_create_error;
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(dst, 512, fmt, ap);
+    va_end(ap);
+    return code;
+}
+
+template <typename T>
+static int upload(radar_ctx* ctx, const std::vector<T>& host, T** dev) {
+    RB_CUDA_OK(ctx, cudaMalloc(reinterpret_cast<void**>(dev), host.size() * sizeof(T)));
+    RB_CUDA_OK(ctx, cudaMemcpy(*dev, host.data(), host.size() * sizeof(T), cudaMemcpyHostToDevice));
+    return RADAR_OK;
+}
+
+static std::vector<float> hann_window(int n) {
+    // np.hanning: 0.5 - 0.5 cos(2 pi k/(n-1)), zero end points, hanning(1) = [1]
+    std::vector<float> w((size_t)n);
+    for (int k = 0; k < n; ++k)
+        w[(size_t)k] = n == 1 ? 1.0f : (float)(0.5 - 0.5 * std::cos(2.0 * M_PI * (double)k / (double)(n - 1)));
+    return w;
+}
+
+static int build_fft_tables(radar_ctx* ctx, int n, FftTables* t) {
+    if (n > 65535) return set_error(ctx, RADAR_E_UNSUPPORTED, "FFT length %d exceeds 65535", n);
+    if (!make_plan(n, &t->plan))
+        return set_error(ctx, RADAR_E_UNSUPPORTED, "FFT length %d has a prime factor above %d", n, kMaxGenericRadix);
+    std::vector<cf> tw((size_t)n);
+    for (int j = 0; j < n; ++j) {
+        const double ang = -2.0 * M_PI * (double)j / (double)n;
+        tw[(size_t)j] = cmake((float)std::cos(ang), (float)std::sin(ang));
+    }
+    std::vector<uint16_t> pos((size_t)n);
+    plan_positions(t->plan, pos.data());
+    std::vector<float> ones((size_t)n, 1.0f);
+    if (int rc = upload(ctx, tw, &t->tw)) return rc;
+    if (int rc = upload(ctx, pos, &t->pos)) return rc;
+    if (int rc = upload(ctx, hann_window(n), &t->hann)) return rc;
+    if (int rc = upload(ctx, ones, &t->ones)) return rc;
+    return RADAR_OK;
+}
+
+static void free_fft_tables(FftTables* t) {
+    cudaFree(t->tw); cudaFree(t->pos); cudaFree(t->hann); cudaFree(t->ones);
+    *t = FftTables{};
+}
+
+int ensure_scratch(radar_ctx* ctx, size_t bytes) {
+    if (bytes <= ctx->scratch_bytes) return RADAR_OK;
+    if (ctx->scratch) { RB_CUDA_OK(ctx, cudaFree(ctx->scratch)); ctx->scratch = nullptr; ctx->scratch_bytes = 0; }
+    RB_CUDA_OK(ctx, cudaMalloc(&ctx->scratch, bytes));
+    ctx->scratch_bytes = bytes;
+    return RADAR_OK;
+}
+
+int get_angle_tables(radar_ctx* ctx, int num_angle_bins, AngleTables* out) {
+    auto it = ctx->angle_tabs.find(num_angle_bins);
+    if (it != ctx->angle_tabs.end()) { *out = it->second; return RADAR_OK; }
+    const int n = num_angle_bins;
+    std::vector<cf> tw((size_t)n);
+    std::vector<double2> tw64((size_t)n);
+    for (int j = 0; j < n; ++j) {
+        const double ang = -2.0 * M_PI * (double)j / (double)n;
+        tw64[(size_t)j] = make_double2(std::cos(ang), std::sin(ang));
+        tw[(size_t)j] = cmake((float)std::cos(ang), (float)std::sin(ang));
+    }
+    AngleTables t;
+    if (int rc = upload(ctx, tw, &t.tw)) return rc;
+    if (int rc = upload(ctx, tw64, &t.tw64)) return rc;
+    ctx->angle_tabs[n] = t;
+    *out = t;
+    return RADAR_OK;
+}
+
+// n > 0: np.hanning(n);  n < 0: all-ones table of length -n
+int get_hann(radar_ctx* ctx, int n, float** out) {
+    auto it = ctx->hann_by_len.find(n);
+    if (it != ctx->hann_by_len.end()) { *out = it->second; return RADAR_OK; }
+    std::vector<float> w = n > 0 ? hann_window(n) : std::vector<float>((size_t)(-n), 1.0f);
+    float* dev = nullptr;
+    if (int rc = upload(ctx, w, &dev)) return rc;
+    ctx->hann_by_len[n] = dev;
+    *out = dev;
+    return RADAR_OK;
+}
+
+static int upload_doubles(radar_ctx* ctx, const double* h, int n, double** dev, int* n_dev) {
+    if (!h || n <= 0) return set_error(ctx, RADAR_E_INVALID, "empty axis");
+    if (*dev) { RB_CUDA_OK(ctx, cudaFree(*dev)); *dev = nullptr; }
+    RB_CUDA_OK(ctx, cudaMalloc(reinterpret_cast<void**>(dev), (size_t)n * sizeof(double)));
+    RB_CUDA_OK(ctx, cudaMemcpy(*dev, h, (size_t)n * sizeof(double), cudaMemcpyHostToDevice));
+    *n_dev = n;
+    return RADAR_OK;
+}
+
+struct DeviceGuard {
+    int prev = -1;
+    explicit DeviceGuard(int dev) { cudaGetDevice(&prev); if (prev != dev) cudaSetDevice(dev); else prev = -1; }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+
+}  // namespace rb
+
+using namespace rb;
+
+#define RB_ENTER(ctx)                                                          \
+    if (!(ctx)) return rb::set_error(nullptr, RADAR_E_INVALID, "null ctx");    \
+    rb::DeviceGuard _guard((ctx)->device)
+
+extern "C" {
+
+int radar_abi_version(void) { return RADAR_B200_ABI_VERSION; }
+
+const char* radar_last_error(const radar_ctx* ctx) { return ctx ? ctx->err : g_create_error; }
+
+double radar_cfar_ca_alpha(int n_train_cells, double pfa) {
+    return (double)n_train_cells * (std::pow(pfa, -1.0 / (double)n_train_cells) - 1.0);
+}
+
+int radar_ctx_create(const radar_shape* shape, int device, radar_ctx** out_ctx) {
+    if (!shape || !out_ctx) return set_error(nullptr, RADAR_E_INVALID, "null argument");
+    *out_ctx = nullptr;
+    if (shape->num_rx < 1 || shape->num_samples < 1 || shape->chirps_per_loop < 1 || shape->num_loops < 1)
+        return set_error(nullptr, RADAR_E_INVALID, "radar_shape fields must be >= 1");
+    int n_dev = 0;
+    cudaError_t e = cudaGetDeviceCount(&n_dev);
+    if (e != cudaSuccess || n_dev == 0)
+        return set_error(nullptr, RADAR_E_CUDA, "no CUDA device available: %s", cudaGetErrorString(e));
+    if (device < 0 || device >= n_dev) return set_error(nullptr, RADAR_E_INVALID, "device %d out of range (0..%d)", device, n_dev - 1);
+    radar_ctx* ctx = new (std::nothrow) radar_ctx();
+    if (!ctx) return set_error(nullptr, RADAR_E_NOMEM, "out of host memory");
+    ctx->device = device;
+    ctx->shape = *shape;
+    ctx->V = shape->num_rx * shape->chirps_per_loop;
+    ctx->C = shape->chirps_per_loop * shape->num_loops;
+    DeviceGuard guard(device);
+    int rc = RADAR_OK;
+    do {
+        cudaDeviceProp prop;
+        if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { rc = set_error(ctx, RADAR_E_CUDA, "cudaGetDeviceProperties failed"); break; }
+        ctx->sm_count = prop.multiProcessorCount;
+        ctx->max_smem_optin = (int)prop.sharedMemPerBlockOptin;
+        if ((rc = build_fft_tables(ctx, shape->num_samples, &ctx->fftS))) break;
+        if ((rc = build_fft_tables(ctx, shape->num_loops, &ctx->fftL))) break;
+        if ((rc = get_hann(ctx, ctx->V, &ctx->hannV))) break;
+    } while (0);
+    if (rc != RADAR_OK) {
+        std::memcpy(g_create_error, ctx->err, sizeof(g_create_error));
+        radar_ctx_destroy(ctx);
+        return rc;
+    }
+    *out_ctx = ctx;
+    return RADAR_OK;
+}
+
+int radar_ctx_destroy(radar_ctx* ctx) {
+    if (!ctx) return RADAR_OK;
+    DeviceGuard guard(ctx->device);
+    free_fft_tables(&ctx->fftS);
+    free_fft_tables(&ctx->fftL);
+    for (auto& kv : ctx->hann_by_len) cudaFree(kv.second);
+    for (auto& kv : ctx->angle_tabs) { cudaFree(kv.second.tw); cudaFree(kv.second.tw64); }
+    cudaFree(ctx->range_bins); cudaFree(ctx->vel_bins); cudaFree(ctx->angle_bins); cudaFree(ctx->scratch);
+    delete ctx;
+    return RADAR_OK;
+}
+
+int radar_ctx_set_axes(radar_ctx* ctx, const double* h_range_bins, int n_range, const double* h_vel_bins, int n_vel) {
+    RB_ENTER(ctx);
+    if (n_range < ctx->shape.num_samples || n_vel < ctx->shape.num_loops)
+        return set_error(ctx, RADAR_E_INVALID, "axes shorter than the map (%d x %d)", ctx->shape.num_samples, ctx->shape.num_loops);
+    if (int rc = upload_doubles(ctx, h_range_bins, n_range, &ctx->range_bins, &ctx->n_range_bins)) return rc;
+    return upload_doubles(ctx, h_vel_bins, n_vel, &ctx->vel_bins, &ctx->n_vel_bins);
+}
+
+int radar_ctx_set_angle_bins(radar_ctx* ctx, const double* h_angle_bins, int n_bins) {
+    RB_ENTER(ctx);
+    return upload_doubles(ctx, h_angle_bins, n_bins, &ctx->angle_bins, &ctx->n_angle_bins);
+}
+
+int radar_range_doppler(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, const int32_t* ant_list, int n_ant,
+                        int window_flags, void* rd_out, float* mag_out, int mag_antenna, void* stream) {
+    RB_ENTER(ctx);
+    if (!adc || n_frames < 0) return set_error(ctx, RADAR_E_INVALID, "null adc or negative frame count");
+    if (!rd_out && !mag_out) return set_error(ctx, RADAR_E_INVALID, "no output requested");
+    return launch_range_doppler(ctx, adc, in_kind, n_frames, ant_list, n_ant, nullptr, window_flags,
+                                reinterpret_cast<cf*>(rd_out), mag_out, mag_antenna, (cudaStream_t)stream);
+}
+
+int radar_range_profile(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx, float* profile_out, void* stream) {
+    RB_ENTER(ctx);
+    if (!adc || !profile_out || n_frames < 0) return set_error(ctx, RADAR_E_INVALID, "null pointer or negative frame count");
+    return launch_range_profile(ctx, adc, in_kind, n_frames, loop_idx, profile_out, (cudaStream_t)stream);
+}
+
+int radar_cfar_2d(radar_ctx* ctx, const float* maps, int n_maps, int rows, int cols, const radar_cfar_params* params,
+                  double* noise_out, uint8_t* mask_out, int32_t* dets_out, int32_t* count_out, int max_dets, void* stream) {
+    RB_ENTER(ctx);
+    if (!maps || !params || n_maps < 0) return set_error(ctx, RADAR_E_INVALID, "null pointer or negative map count");
+    return launch_cfar_2d(ctx, maps, n_maps, rows, cols, *params, noise_out, mask_out, dets_out, count_out, max_dets, (cudaStream_t)stream);
+}
+
+int radar_cfar_1d_rows(radar_ctx* ctx, const float* maps, int n_maps, int rows, int cols, const radar_cfar_params* params,
+                       const uint8_t* row_select, double* noise_out, uint8_t* mask_out, int32_t* dets_out, int32_t* count_out,
+                       int max_dets, void* stream) {
+    RB_ENTER(ctx);
+    if (!maps || !params || n_maps < 0) return set_error(ctx, RADAR_E_INVALID, "null pointer or negative map count");
+    return launch_cfar_1d_rows(ctx, maps, n_maps, rows, cols, *params, row_select, noise_out, mask_out, dets_out, count_out, max_dets, (cudaStream_t)stream);
+}
+
+int radar_point_cloud(radar_ctx* ctx, const void* rd, int n_frames, const int32_t* dets, const int32_t* counts, int max_dets,
+                      const int32_t* az_idx, int n_az, const int32_t* el_idx, int n_el, int shift_az, int shift_el,
+                      int num_angle_bins, double* points_out, int32_t* az_bin_out, int32_t* el_bin_out, void* stream) {
+    RB_ENTER(ctx);
+    if (!rd || !dets || !counts || !points_out || n_frames < 0) return set_error(ctx, RADAR_E_INVALID, "null pointer or negative frame count");
+    if ((n_az > 0 && !az_idx) || (n_el > 0 && !el_idx)) return set_error(ctx, RADAR_E_INVALID, "antenna list missing");
+    return launch_point_cloud(ctx, reinterpret_cast<const cf*>(rd), n_frames, dets, counts, max_dets, az_idx, n_az, el_idx, n_el,
+                              shift_az, shift_el, num_angle_bins, points_out, az_bin_out, el_bin_out, (cudaStream_t)stream);
+}
+
+int radar_range_angle(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx, const int32_t* ant_list, int n_ant,
+                      int num_angle_bins, int window_flags, float* out, void* stream) {
+    RB_ENTER(ctx);
+    if (!adc || !out || n_frames < 0) return set_error(ctx, RADAR_E_INVALID, "null pointer or negative frame count");
+    return launch_range_angle(ctx, adc, in_kind, n_frames, loop_idx, ant_list, n_ant, num_angle_bins, window_flags, out, (cudaStream_t)stream);
+}
+
+int radar_dbs(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, const int32_t* ant_list, int n_ant, int num_angle_bins,
+              const int32_t* vel_bin, const int32_t* ang_bin, int n_out, float* out, void* stream) {
+    RB_ENTER(ctx);
+    if (!adc || !vel_bin || !ang_bin || !out || n_frames < 0) return set_error(ctx, RADAR_E_INVALID, "null pointer or negative frame count");
+    return launch_dbs(ctx, adc, in_kind, n_frames, ant_list, n_ant, num_angle_bins, vel_bin, ang_bin, n_out, out, (cudaStream_t)stream);
+}
+
+int radar_sar_image(radar_ctx* ctx, const void* aperture, int num_samples, int n_elems, const double* positions, const double* dirs,
+                    int n_dirs, double lambda_m, int g_begin, int g_end, void* out, void* stream) {
+    RB_ENTER(ctx);
+    if (!aperture || !positions || !dirs || !out) return set_error(ctx, RADAR_E_INVALID, "null pointer");
+    return launch_sar_image(ctx, reinterpret_cast<const cf*>(aperture), num_samples, n_elems, positions, dirs, n_dirs, lambda_m,
+                            g_begin, g_end, reinterpret_cast<cf*>(out), (cudaStream_t)stream);
+}
+
+}  // extern "C"

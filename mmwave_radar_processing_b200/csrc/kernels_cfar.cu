@@ -1,0 +1,266 @@
+// CFAR family + ordered detection compaction: one CTA per map, the map resident in shared memory.
+//
+// Reference arithmetic reproduced (paths relative to mmwave_radar_processing/ in the reference):
+//   detectors/base.py:38-65, :208-230 (strict x > threshold, np.where order),
+//   detectors/ca_cfar.py:11-155, detectors/os_cfar.py:11-195, detectors/go_so_cfar.py:11-123.
+//
+// * CA / GO / SO: one thread per cell under test, training sums accumulated in fp64.
+// * OS: one warp per cell under test; every lane keeps its share of the training window in registers
+//   and the exact k-th order statistic is built bit by bit (MSB->LSB) from warp-wide counts
+//   (__reduce_add_sync), which is an exact selection on the fp32 bit patterns (non-negative floats order
+//   like their unsigned encodings).
+// * decision in fp64: (double)x > alpha*(double)noise - the same expression the host layer uses to publish
+//   `thresholds`.
+// * compaction: warp ballots + popcounts, an exclusive scan over the warps' totals, then an ordered
+//   scatter - row-major (range, Doppler) like np.where, one global counter write per map.
+#include "radar_internal.h"
+#include "rd_core.cuh"
+
+namespace rb {
+
+constexpr int kCfarThreads = 256;
+constexpr int kCfarWarps = kCfarThreads / 32;
+
+struct CfarArgs {
+    const float* maps;
+    int rows, cols;
+    int kind, tr, td, gr, gd;
+    int n_train;          // cells entering the estimate (CA/OS: all; GO/SO: one side)
+    int k_rank;           // OS: 1-based rank
+    double alpha;
+    const uint8_t* row_select;
+    double* noise_out;
+    uint8_t* mask_out;
+    int32_t* dets_out;
+    int32_t* count_out;
+    int max_dets;
+    FastDiv div_cols, div_vd, div_wd;
+};
+
+template <int MAXV>
+__device__ __forceinline__ void os_cells(const CfarArgs& a, const float* map, uint8_t* mask, double* noise_dst) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int cr = a.tr + a.gr, cd = a.td + a.gd;
+    const int wr = 2 * cr + 1, wd = 2 * cd + 1;
+    const int nvr = a.rows - 2 * cr, nvd = a.cols - 2 * cd;
+    // per-lane window offsets, identical for every cell under test
+    int off[MAXV];
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+        const int w = lane + 32 * i;
+        off[i] = -1;
+        if (w < wr * wd) {
+            const int y = (int)a.div_wd.div((uint32_t)w);
+            const int x = w - y * wd;
+            const bool guard = (y >= a.tr && y <= a.tr + 2 * a.gr) && (x >= a.td && x <= a.td + 2 * a.gd);
+            if (!guard) off[i] = y * a.cols + x;
+        }
+    }
+    const int n_cut = nvr * nvd;
+    for (int c = warp; c < n_cut; c += kCfarWarps) {
+        const int vr = (int)a.div_vd.div((uint32_t)c);
+        const int vd = c - vr * nvd;
+        const int r = vr + cr, d = vd + cd;
+        if (a.row_select && !a.row_select[r]) continue;
+        const int base = vr * a.cols + vd;      // top-left corner of the window
+        unsigned vals[MAXV];
+#pragma unroll
+        for (int i = 0; i < MAXV; ++i) vals[i] = off[i] >= 0 ? __float_as_uint(map[base + off[i]]) : 0xffffffffu;
+        unsigned res = 0;
+#pragma unroll 1
+        for (int bit = 30; bit >= 0; --bit) {
+            const unsigned cand = res | (1u << bit);
+            int cnt = 0;
+#pragma unroll
+            for (int i = 0; i < MAXV; ++i) cnt += (vals[i] < cand) ? 1 : 0;
+            cnt = __reduce_add_sync(0xffffffffu, cnt);
+            if (cnt < a.k_rank) res = cand;     // fewer than k cells below cand: the k-th smallest is >= cand
+        }
+        if (lane == 0) {
+            const int cell = r * a.cols + d;
+            const double noise = (double)__uint_as_float(res);
+            mask[cell] = ((double)map[cell] > a.alpha * noise) ? 1 : 0;
+            if (noise_dst) noise_dst[cell] = noise;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(kCfarThreads) cfar_kernel(const __grid_constant__ CfarArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ int warp_counts[kCfarWarps];
+    const int n_cells = a.rows * a.cols;
+    SmemArena ar(smem_raw);
+    float* map = ar.take<float>(n_cells);
+    uint8_t* mask = ar.take<uint8_t>(n_cells);
+    const long long m = blockIdx.x;
+    const float* src = a.maps + m * n_cells;
+    double* noise_dst = a.noise_out ? a.noise_out + m * n_cells : nullptr;
+    const uint8_t* rsel = a.row_select ? a.row_select + m * a.rows : nullptr;
+    CfarArgs la = a;
+    la.row_select = rsel;
+    for (int i = threadIdx.x; i < n_cells; i += blockDim.x) {
+        map[i] = src[i];
+        mask[i] = 0;
+        if (noise_dst) noise_dst[i] = 0.0;
+    }
+    __syncthreads();
+
+    const int cr = a.tr + a.gr, cd = a.td + a.gd;
+    const int nvr = a.rows - 2 * cr, nvd = a.cols - 2 * cd;
+    if (nvr > 0 && nvd > 0) {      // window larger than the map: no valid cell (reference swallows the ValueError)
+        if (a.kind == RADAR_CFAR_OS) {
+            const int wcells = (2 * cr + 1) * (2 * cd + 1);
+            if (wcells <= 32 * 8) os_cells<8>(la, map, mask, noise_dst);
+            else if (wcells <= 32 * 16) os_cells<16>(la, map, mask, noise_dst);
+            else os_cells<32>(la, map, mask, noise_dst);
+        } else {
+            const int n_cut = nvr * nvd;
+            for (int c = threadIdx.x; c < n_cut; c += blockDim.x) {
+                const int vr = (int)a.div_vd.div((uint32_t)c);
+                const int vd = c - vr * nvd;
+                const int r = vr + cr, d = vd + cd;
+                if (rsel && !rsel[r]) continue;
+                double noise;
+                if (a.kind == RADAR_CFAR_CA) {
+                    double sum = 0.0;
+                    for (int y = r - cr; y <= r + cr; ++y) {
+                        const float* row = map + y * a.cols;
+                        const bool inner = (y >= r - a.gr && y <= r + a.gr);
+                        if (inner) {
+                            for (int x = d - cd; x < d - a.gd; ++x) sum += (double)row[x];
+                            for (int x = d + a.gd + 1; x <= d + cd; ++x) sum += (double)row[x];
+                        } else {
+                            for (int x = d - cd; x <= d + cd; ++x) sum += (double)row[x];
+                        }
+                    }
+                    noise = sum / (double)a.n_train;
+                } else {                            // GO / SO: 1-D only (tr == gr == 0)
+                    const float* row = map + r * a.cols;
+                    double left = 0.0, right = 0.0;
+                    for (int x = d - cd; x < d - a.gd; ++x) left += (double)row[x];
+                    for (int x = d + a.gd + 1; x <= d + cd; ++x) right += (double)row[x];
+                    left /= (double)a.td;
+                    right /= (double)a.td;
+                    noise = (a.kind == RADAR_CFAR_GO) ? fmax(left, right) : fmin(left, right);
+                }
+                const int cell = r * a.cols + d;
+                mask[cell] = ((double)map[cell] > a.alpha * noise) ? 1 : 0;
+                if (noise_dst) noise_dst[cell] = noise;
+            }
+        }
+    }
+    __syncthreads();
+
+    if (a.mask_out) {
+        uint8_t* dst = a.mask_out + m * n_cells;
+        for (int i = threadIdx.x; i < n_cells; i += blockDim.x) dst[i] = mask[i];
+    }
+    if (!a.dets_out && !a.count_out) return;
+
+    // ordered compaction: each warp owns a contiguous, 32-aligned span of cells
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int span = (((n_cells + kCfarWarps - 1) / kCfarWarps) + 31) & ~31;
+    const int begin = warp * span;
+    const int end = min(begin + span, n_cells);
+    int cnt = 0;
+    for (int i = begin + lane; i < begin + span; i += 32) {
+        const bool hit = (i < end) && mask[i];
+        cnt += __popc(__ballot_sync(0xffffffffu, hit));
+    }
+    if (lane == 0) warp_counts[warp] = cnt;
+    __syncthreads();
+    int offset = 0, total = 0;
+    for (int w = 0; w < kCfarWarps; ++w) {
+        if (w < warp) offset += warp_counts[w];
+        total += warp_counts[w];
+    }
+    if (threadIdx.x == 0 && a.count_out) a.count_out[m] = total;
+    if (!a.dets_out) return;
+    int32_t* dets = a.dets_out + m * (long long)a.max_dets * 2;
+    for (int i = begin + lane; i < begin + span; i += 32) {
+        const bool hit = (i < end) && mask[i];
+        const unsigned ballot = __ballot_sync(0xffffffffu, hit);
+        if (hit) {
+            const int slot = offset + __popc(ballot & ((1u << lane) - 1u));
+            if (slot < a.max_dets) {
+                const int r = (int)a.div_cols.div((uint32_t)i);
+                dets[2 * slot] = r;
+                dets[2 * slot + 1] = i - r * a.cols;
+            }
+        }
+        offset += __popc(ballot);
+    }
+}
+
+static int resolve_params(radar_ctx* ctx, const radar_cfar_params& p, bool one_d, CfarArgs* a) {
+    a->kind = p.kind;
+    a->tr = one_d ? 0 : p.train_r;  a->gr = one_d ? 0 : p.guard_r;
+    a->td = p.train_d;              a->gd = p.guard_d;
+    if (a->tr < 0 || a->td < 0 || a->gr < 0 || a->gd < 0) return set_error(ctx, RADAR_E_INVALID, "negative CFAR window");
+    const int wr = 2 * (a->tr + a->gr) + 1, wd = 2 * (a->td + a->gd) + 1;
+    const int n_all = wr * wd - (2 * a->gr + 1) * (2 * a->gd + 1);
+    if (n_all <= 0) return set_error(ctx, RADAR_E_INVALID, "CFAR window has no training cells");
+    switch (p.kind) {
+        case RADAR_CFAR_CA:
+            a->n_train = n_all;
+            a->alpha = p.alpha > 0 ? p.alpha : radar_cfar_ca_alpha(n_all, p.pfa);
+            break;
+        case RADAR_CFAR_GO: case RADAR_CFAR_SO:
+            if (!one_d) return set_error(ctx, RADAR_E_INVALID, "GO/SO-CFAR exist only in 1-D (reference go_so_cfar.py)");
+            a->n_train = a->td;
+            a->alpha = p.alpha > 0 ? p.alpha : radar_cfar_ca_alpha(a->td, p.pfa);
+            break;
+        case RADAR_CFAR_OS: {
+            a->n_train = n_all;
+            int k = p.os_rank > 0 ? p.os_rank : (int)(p.rho * (double)n_all);
+            if (p.os_rank <= 0) k = k < 1 ? 1 : (k > n_all ? n_all : k);
+            if (k < 1 || k > n_all) return set_error(ctx, RADAR_E_INVALID, "k_rank must be between 1 and %d, got %d", n_all, k);
+            if (wr * wd > 32 * 32) return set_error(ctx, RADAR_E_UNSUPPORTED, "OS-CFAR window of %d cells exceeds 1024", wr * wd);
+            a->k_rank = k;
+            a->alpha = p.alpha;
+            break;
+        }
+        default:
+            return set_error(ctx, RADAR_E_INVALID, "unknown CFAR kind %d", p.kind);
+    }
+    a->div_wd = make_fastdiv((uint32_t)wd);
+    return RADAR_OK;
+}
+
+static int launch_cfar(radar_ctx* ctx, const float* maps, int n_maps, int rows, int cols, const radar_cfar_params& p,
+                       bool one_d, const uint8_t* row_select, double* noise_out, uint8_t* mask_out,
+                       int32_t* dets_out, int32_t* count_out, int max_dets, cudaStream_t st) {
+    if (rows <= 0 || cols <= 0) return set_error(ctx, RADAR_E_INVALID, "empty map");
+    if (dets_out && max_dets <= 0) return set_error(ctx, RADAR_E_INVALID, "max_dets must be positive");
+    if (n_maps <= 0) return RADAR_OK;
+    CfarArgs a{};
+    if (int rc = resolve_params(ctx, p, one_d, &a)) return rc;
+    a.maps = maps; a.rows = rows; a.cols = cols;
+    a.row_select = row_select;
+    a.noise_out = noise_out; a.mask_out = mask_out; a.dets_out = dets_out; a.count_out = count_out; a.max_dets = max_dets;
+    a.div_cols = make_fastdiv((uint32_t)cols);
+    const int nvd = cols - 2 * (a.td + a.gd);
+    a.div_vd = make_fastdiv((uint32_t)(nvd > 0 ? nvd : 1));
+    const size_t n_cells = (size_t)rows * cols;
+    const size_t smem = arena_bytes(n_cells, 4) + arena_bytes(n_cells, 1);
+    if (smem > (size_t)ctx->max_smem_optin)
+        return set_error(ctx, RADAR_E_UNSUPPORTED, "CFAR map of %d x %d cells exceeds shared memory", rows, cols);
+    RB_CUDA_OK(ctx, cudaFuncSetAttribute(cfar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cfar_kernel<<<(unsigned)n_maps, kCfarThreads, smem, st>>>(a);
+    RB_CUDA_OK(ctx, cudaGetLastError());
+    return RADAR_OK;
+}
+
+int launch_cfar_2d(radar_ctx* ctx, const float* maps, int n_maps, int rows, int cols, const radar_cfar_params& p,
+                   double* noise_out, uint8_t* mask_out, int32_t* dets_out, int32_t* count_out, int max_dets,
+                   cudaStream_t st) {
+    return launch_cfar(ctx, maps, n_maps, rows, cols, p, false, nullptr, noise_out, mask_out, dets_out, count_out, max_dets, st);
+}
+
+int launch_cfar_1d_rows(radar_ctx* ctx, const float* maps, int n_maps, int rows, int cols, const radar_cfar_params& p,
+                        const uint8_t* row_select, double* noise_out, uint8_t* mask_out, int32_t* dets_out,
+                        int32_t* count_out, int max_dets, cudaStream_t st) {
+    return launch_cfar(ctx, maps, n_maps, rows, cols, p, true, row_select, noise_out, mask_out, dets_out, count_out, max_dets, st);
+}
+
+}  // namespace rb

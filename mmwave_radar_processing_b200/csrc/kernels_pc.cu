@@ -1,0 +1,129 @@
+// K3b: per-detection zero-padded angle DFT + first-max argmax (azimuth and elevation antenna sets) and the
+// spherical -> cartesian conversion; one warp per detection.
+//
+// Reference arithmetic reproduced: processors/point_cloud_generator.py:143-248 (gather raw[ant][r][d],
+// zero-pad to num_angle_bins, FFT, optional fftshift, abs, np.argmax (first maximum), angle_bins[idx],
+// x = r cos(el) cos(az), y = r cos(el) sin(az), z = r sin(el)).
+//
+// The DFT, the magnitude (hypot) and the trigonometry run in fp64 on the fp32 RD samples: the work is a few
+// hundred FMAs per detection and the argmax index has to be bit-exact against the fp64 reference.
+#include "radar_internal.h"
+
+namespace rb {
+
+constexpr int kPcThreads = 128;
+constexpr int kPcWarps = kPcThreads / 32;
+constexpr int kPcMaxAnt = 32;
+
+struct PcArgs {
+    const cf* rd;
+    int V, S, L;
+    const int32_t* dets; const int32_t* counts; int max_dets;
+    const int32_t* az_idx; int n_az;
+    const int32_t* el_idx; int n_el;
+    int shift_az, shift_el, A;
+    const double2* tw64;
+    const double* range_bins; const double* vel_bins; const double* angle_bins;
+    double* points; int32_t* az_bin; int32_t* el_bin;
+};
+
+// argmax_a | sum_j z[j] W_A^{j a'} |,  a' = (a - A/2) mod A when shifted; first maximum wins.
+// zs: this warp's staging row in shared memory (kPcMaxAnt complex doubles).
+__device__ __forceinline__ int angle_argmax(const PcArgs& a, const cf* tile, const int32_t* ant, int n, bool shift,
+                                            int lane, double2* zs) {
+    __syncwarp();
+    if (lane < n) {
+        const cf z = tile[(long long)ant[lane] * a.S * a.L];
+        zs[lane] = make_double2((double)z.x, (double)z.y);
+    }
+    __syncwarp();
+    double best = -1.0;
+    int best_a = 0x7fffffff;
+    for (int ao = lane; ao < a.A; ao += 32) {
+        int ap = ao;
+        if (shift) { ap = ao - a.A / 2; if (ap < 0) ap += a.A; }
+        double sr = 0.0, si = 0.0;
+        int e = 0;
+        for (int j = 0; j < n; ++j) {
+            const double2 x = zs[j];
+            const double2 w = a.tw64[e];
+            sr += x.x * w.x - x.y * w.y;
+            si += x.x * w.y + x.y * w.x;
+            e += ap; if (e >= a.A) e -= a.A;
+        }
+        const double mag = hypot(sr, si);
+        if (mag > best) { best = mag; best_a = ao; }      // ascending ao per lane: strict > keeps the first
+    }
+    // warp argmax, ties -> smaller index (all 32 lanes take part; idle lanes carry best = -1)
+    for (int s = 16; s > 0; s >>= 1) {
+        const double ob = __shfl_xor_sync(0xffffffffu, best, s);
+        const int oa = __shfl_xor_sync(0xffffffffu, best_a, s);
+        if (ob > best || (ob == best && oa < best_a)) { best = ob; best_a = oa; }
+    }
+    return best_a;
+}
+
+__global__ void __launch_bounds__(kPcThreads) point_cloud_kernel(const __grid_constant__ PcArgs a, int n_frames) {
+    const int lane = threadIdx.x & 31;
+    const long long gw = (long long)blockIdx.x * kPcWarps + (threadIdx.x >> 5);
+    const long long total = (long long)n_frames * a.max_dets;
+    if (gw >= total) return;
+    const int frame = (int)(gw / a.max_dets);
+    const int slot = (int)(gw - (long long)frame * a.max_dets);
+    int n = a.counts[frame];
+    if (n > a.max_dets) n = a.max_dets;
+    if (slot >= n) return;
+    const int r = a.dets[2 * gw], d = a.dets[2 * gw + 1];
+    const cf* tile = a.rd + (long long)frame * a.V * a.S * a.L + (long long)r * a.L + d;
+    __shared__ double2 zs_all[kPcWarps][kPcMaxAnt];
+    double2* zs = zs_all[threadIdx.x >> 5];
+    int az_i = 0, el_i = 0;
+    if (a.n_az > 0) az_i = angle_argmax(a, tile, a.az_idx, a.n_az, a.shift_az != 0, lane, zs);
+    if (a.n_el > 0) el_i = angle_argmax(a, tile, a.el_idx, a.n_el, a.shift_el != 0, lane, zs);
+    if (lane == 0) {
+        const double az = a.n_az > 0 ? a.angle_bins[az_i] : 0.0;
+        const double el = a.n_el > 0 ? a.angle_bins[el_i] : 0.0;
+        const double rng = a.range_bins[r], vel = a.vel_bins[d];
+        double4 p;
+        p.x = rng * cos(el) * cos(az);
+        p.y = rng * cos(el) * sin(az);
+        p.z = rng * sin(el);
+        p.w = vel;
+        reinterpret_cast<double4*>(a.points)[gw] = p;
+        if (a.az_bin) a.az_bin[gw] = az_i;
+        if (a.el_bin) a.el_bin[gw] = el_i;
+    }
+}
+
+int launch_point_cloud(radar_ctx* ctx, const cf* rd, int n_frames, const int32_t* dets, const int32_t* counts,
+                       int max_dets, const int32_t* az_idx, int n_az, const int32_t* el_idx, int n_el, int shift_az,
+                       int shift_el, int num_angle_bins, double* points_out, int32_t* az_bin_out, int32_t* el_bin_out,
+                       cudaStream_t st) {
+    if (n_az < 0 || n_el < 0 || n_az > kPcMaxAnt || n_el > kPcMaxAnt)
+        return set_error(ctx, RADAR_E_INVALID, "antenna sets must hold 0..%d indices", kPcMaxAnt);
+    if (num_angle_bins < 1 || num_angle_bins > 8192 || num_angle_bins < n_az || num_angle_bins < n_el)
+        return set_error(ctx, RADAR_E_INVALID, "num_angle_bins %d invalid", num_angle_bins);
+    if (!ctx->range_bins || !ctx->vel_bins) return set_error(ctx, RADAR_E_INVALID, "radar_ctx_set_axes not called");
+    if ((n_az > 0 || n_el > 0) && (!ctx->angle_bins || ctx->n_angle_bins < num_angle_bins))
+        return set_error(ctx, RADAR_E_INVALID, "radar_ctx_set_angle_bins not called with >= %d bins", num_angle_bins);
+    if (max_dets <= 0) return set_error(ctx, RADAR_E_INVALID, "max_dets must be positive");
+    if (n_frames <= 0) return RADAR_OK;
+    AngleTables at;
+    if (int rc = get_angle_tables(ctx, num_angle_bins, &at)) return rc;
+    PcArgs a;
+    a.rd = rd; a.V = ctx->V; a.S = ctx->shape.num_samples; a.L = ctx->shape.num_loops;
+    a.dets = dets; a.counts = counts; a.max_dets = max_dets;
+    a.az_idx = az_idx; a.n_az = n_az; a.el_idx = el_idx; a.n_el = n_el;
+    a.shift_az = shift_az; a.shift_el = shift_el; a.A = num_angle_bins;
+    a.tw64 = at.tw64;
+    a.range_bins = ctx->range_bins; a.vel_bins = ctx->vel_bins; a.angle_bins = ctx->angle_bins;
+    a.points = points_out; a.az_bin = az_bin_out; a.el_bin = el_bin_out;
+    const long long warps = (long long)n_frames * max_dets;
+    const long long grid = (warps + kPcWarps - 1) / kPcWarps;
+    if (grid > 0x7fffffffLL) return set_error(ctx, RADAR_E_INVALID, "too many detection slots in one call");
+    point_cloud_kernel<<<(unsigned)grid, kPcThreads, 0, st>>>(a, n_frames);
+    RB_CUDA_OK(ctx, cudaGetLastError());
+    return RADAR_OK;
+}
+
+}  // namespace rb

@@ -1,0 +1,453 @@
+// Range-Doppler family: fused int16-deinterleave + TDM virtual-array gather + Hann windows + range FFT +
+// Doppler FFT (+fftshift, +magnitude) with the whole (S x L) antenna tile resident in shared memory;
+// the coarse range profile; the range-angle heat map; Doppler beam sharpening.
+//
+// Reference arithmetic reproduced (paths relative to mmwave_radar_processing/ in the reference):
+//   processors/virtual_array_reformater.py:44-65, processors/range_doppler_resp.py:49-110,
+//   processors/range_resp.py:32-57, processors/range_angle_resp.py:55-122,
+//   processors/range_angle_resp_dbs_enhanced.py:137-304.
+#include "radar_internal.h"
+#include "rd_core.cuh"
+
+namespace rb {
+
+constexpr int kRdThreads = 256;
+
+// ------------------------------------------------------------------------------------------------
+// ADC element fetch for the two ingest layouts (see include/radar_b200.h)
+// ------------------------------------------------------------------------------------------------
+struct AdcView {
+    const void* base;
+    int in_kind;
+    int R, S, cpl, L, V, C;
+};
+
+// x[v][s][l] of frame f as complex float (exact for int16).
+__device__ __forceinline__ cf adc_fetch(const AdcView& a, long long frame, int v, int s, int l) {
+    if (a.in_kind == RADAR_IN_IQ16) {
+        const int tx = v / a.R, rx = v - tx * a.R;
+        const long long row = ((frame * a.C + (long long)l * a.cpl + tx) * a.R + rx) * a.S + s;
+        const unsigned w = __ldg(reinterpret_cast<const unsigned*>(a.base) + row);
+        return cmake((float)(short)(w & 0xffffu), (float)(short)(w >> 16));
+    } else {
+        const long long idx = ((frame * a.V + v) * a.S + s) * (long long)a.L + l;
+        return __ldg(reinterpret_cast<const cf*>(a.base) + idx);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1+K2 fused range-Doppler: one CTA per (frame, output antenna)
+// ------------------------------------------------------------------------------------------------
+struct RdArgs {
+    AdcView adc;
+    int n_out_ant;
+    const int32_t* ant_list;
+    const float* ant_weight;
+    const float* winS;
+    const float* winL;
+    const cf* twS;
+    const cf* twL;
+    const uint16_t* posS;
+    const uint16_t* posL;
+    cf* rd_out;
+    float* mag_out;
+    int mag_antenna;
+    FftPlan planS, planL;
+    FastDiv divS, divL;
+};
+
+struct RdSmem {
+    cf* tile; cf* twS; cf* twL; float* winS; float* winL; uint16_t* posS; uint16_t* srcL;
+};
+
+__device__ __forceinline__ RdSmem rd_carve(unsigned char* raw, int S, int L) {
+    SmemArena ar(raw);
+    RdSmem sm;
+    sm.tile = ar.take<cf>(S * odd_pitch(L));
+    sm.twS = ar.take<cf>(S);
+    sm.twL = ar.take<cf>(L);
+    sm.winS = ar.take<float>(S);
+    sm.winL = ar.take<float>(L);
+    sm.posS = ar.take<uint16_t>(S);
+    sm.srcL = ar.take<uint16_t>(L);
+    return sm;
+}
+__host__ __device__ static inline size_t rd_smem_bytes(int S, int L) {
+    return arena_bytes((size_t)S * (L | 1), sizeof(cf)) + arena_bytes(S, sizeof(cf)) + arena_bytes(L, sizeof(cf)) +
+           arena_bytes(S, 4) + arena_bytes(L, 4) + arena_bytes(S, 2) + arena_bytes(L, 2);
+}
+
+__device__ __forceinline__ void rd_load_tables(const RdSmem& sm, const RdArgs& a) {
+    const int S = a.adc.S, L = a.adc.L;
+    load_table(sm.twS, a.twS, S);
+    load_table(sm.twL, a.twL, L);
+    load_table(sm.winS, a.winS, S);
+    load_table(sm.winL, a.winL, L);
+    load_table(sm.posS, a.posS, S);
+    // fftshift folded into the gather: output column d holds frequency bin (d - L/2) mod L
+    for (int d = threadIdx.x; d < L; d += blockDim.x) {
+        int f = d - L / 2;
+        if (f < 0) f += L;
+        sm.srcL[d] = a.posL[f];
+    }
+}
+
+// Load one antenna's (S x L) samples with the separable window, run both FFTs in place.
+// On return tile[posS[k]*Lp + srcL[d]] = RD[k][d].
+__device__ __forceinline__ void rd_compute_tile(const RdSmem& sm, const RdArgs& a, long long frame, int v, float weight) {
+    const int S = a.adc.S, L = a.adc.L, Lp = odd_pitch(L);
+    const int total = S * L;
+    if (a.adc.in_kind == RADAR_IN_IQ16) {
+        for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+            const int l = (int)a.divS.div((uint32_t)idx);
+            const int s = idx - l * S;
+            const cf x = adc_fetch(a.adc, frame, v, s, l);
+            const float w = sm.winS[s] * sm.winL[l] * weight;
+            sm.tile[s * Lp + l] = cmake(x.x * w, x.y * w);
+        }
+    } else {
+        for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+            const int s = (int)a.divL.div((uint32_t)idx);
+            const int l = idx - s * L;
+            const cf x = adc_fetch(a.adc, frame, v, s, l);
+            const float w = sm.winS[s] * sm.winL[l] * weight;
+            sm.tile[s * Lp + l] = cmake(x.x * w, x.y * w);
+        }
+    }
+    __syncthreads();
+    fft_axis(sm.tile, /*strideF=*/Lp, /*strideO=*/1, /*O=*/L, a.divL, a.planS, sm.twS);   // range
+    fft_axis(sm.tile, /*strideF=*/1, /*strideO=*/Lp, /*O=*/S, a.divS, a.planL, sm.twL);   // Doppler
+}
+
+__global__ void __launch_bounds__(kRdThreads) rd_fused_kernel(const __grid_constant__ RdArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int S = a.adc.S, L = a.adc.L, Lp = odd_pitch(L);
+    RdSmem sm = rd_carve(smem_raw, S, L);
+    rd_load_tables(sm, a);
+    const long long frame = blockIdx.x / a.n_out_ant;
+    const int vo = blockIdx.x - (int)frame * a.n_out_ant;
+    const int v = a.ant_list ? a.ant_list[vo] : vo;
+    const float weight = a.ant_weight ? a.ant_weight[vo] : 1.0f;
+    __syncthreads();
+    rd_compute_tile(sm, a, frame, v, weight);
+
+    const int total = S * L;
+    const long long tile_base = ((long long)frame * a.n_out_ant + vo) * total;
+    const bool want_mag_all = a.mag_out && a.mag_antenna < 0;
+    const bool want_mag_one = a.mag_out && a.mag_antenna == vo;
+    float* mag_dst = want_mag_all ? a.mag_out + tile_base : (want_mag_one ? a.mag_out + frame * total : nullptr);
+    for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+        const int k = (int)a.divL.div((uint32_t)idx);
+        const int d = idx - k * L;
+        const cf val = sm.tile[sm.posS[k] * Lp + sm.srcL[d]];
+        if (a.rd_out) a.rd_out[tile_base + idx] = val;
+        if (mag_dst) mag_dst[idx] = sqrtf(val.x * val.x + val.y * val.y);
+    }
+}
+
+static int check_in_kind(radar_ctx* ctx, int in_kind) {
+    if (in_kind != RADAR_IN_IQ16 && in_kind != RADAR_IN_CUBE64)
+        return set_error(ctx, RADAR_E_INVALID, "unknown in_kind %d", in_kind);
+    return RADAR_OK;
+}
+
+static AdcView make_view(const radar_ctx* ctx, const void* adc, int in_kind) {
+    AdcView v;
+    v.base = adc; v.in_kind = in_kind;
+    v.R = ctx->shape.num_rx; v.S = ctx->shape.num_samples; v.cpl = ctx->shape.chirps_per_loop;
+    v.L = ctx->shape.num_loops; v.V = ctx->V; v.C = ctx->C;
+    return v;
+}
+
+template <typename K>
+static int opt_in_smem(radar_ctx* ctx, K kernel, size_t bytes, const char* what) {
+    if (bytes > (size_t)ctx->max_smem_optin)
+        return set_error(ctx, RADAR_E_UNSUPPORTED, "%s needs %zu bytes of shared memory per CTA (device limit %d)",
+                         what, bytes, ctx->max_smem_optin);
+    RB_CUDA_OK(ctx, cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    return RADAR_OK;
+}
+
+int launch_range_doppler(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, const int32_t* ant_list,
+                         int n_ant, const float* ant_weight, int window_flags, cf* rd_out, float* mag_out,
+                         int mag_antenna, cudaStream_t st) {
+    if (int rc = check_in_kind(ctx, in_kind)) return rc;
+    if (n_frames <= 0) return RADAR_OK;
+    RdArgs a;
+    a.adc = make_view(ctx, adc, in_kind);
+    a.n_out_ant = ant_list ? n_ant : ctx->V;
+    if (a.n_out_ant <= 0) return set_error(ctx, RADAR_E_INVALID, "empty antenna list");
+    if (mag_out && mag_antenna >= a.n_out_ant) return set_error(ctx, RADAR_E_INVALID, "mag_antenna %d out of range", mag_antenna);
+    a.ant_list = ant_list;
+    a.ant_weight = ant_weight;
+    a.winS = (window_flags & RADAR_WIN_RANGE) ? ctx->fftS.hann : ctx->fftS.ones;
+    a.winL = (window_flags & RADAR_WIN_DOPPLER) ? ctx->fftL.hann : ctx->fftL.ones;
+    a.twS = ctx->fftS.tw; a.twL = ctx->fftL.tw;
+    a.posS = ctx->fftS.pos; a.posL = ctx->fftL.pos;
+    a.rd_out = rd_out; a.mag_out = mag_out; a.mag_antenna = mag_antenna;
+    a.planS = ctx->fftS.plan; a.planL = ctx->fftL.plan;
+    a.divS = make_fastdiv((uint32_t)a.adc.S); a.divL = make_fastdiv((uint32_t)a.adc.L);
+    const size_t smem = rd_smem_bytes(a.adc.S, a.adc.L);
+    if (int rc = opt_in_smem(ctx, rd_fused_kernel, smem, "range-Doppler tile")) return rc;
+    const long long grid = (long long)n_frames * a.n_out_ant;
+    if (grid > 0x7fffffffLL) return set_error(ctx, RADAR_E_INVALID, "too many frames in one call");
+    rd_fused_kernel<<<(unsigned)grid, kRdThreads, smem, st>>>(a);
+    RB_CUDA_OK(ctx, cudaGetLastError());
+    return RADAR_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// a10: coarse range profile - one CTA per frame, tile [s][v]
+// ------------------------------------------------------------------------------------------------
+struct ProfArgs {
+    AdcView adc;
+    int loop_idx;
+    const float* winS; const cf* twS; const uint16_t* posS;
+    float* out;
+    FftPlan planS; FastDiv divS, divV;
+};
+
+__global__ void __launch_bounds__(kRdThreads) range_profile_kernel(const __grid_constant__ ProfArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int S = a.adc.S, V = a.adc.V, Vp = odd_pitch(V);
+    SmemArena ar(smem_raw);
+    cf* tile = ar.take<cf>(S * Vp);
+    cf* tw = ar.take<cf>(S);
+    float* win = ar.take<float>(S);
+    uint16_t* pos = ar.take<uint16_t>(S);
+    load_table(tw, a.twS, S);
+    load_table(win, a.winS, S);
+    load_table(pos, a.posS, S);
+    __syncthreads();
+    const long long frame = blockIdx.x;
+    for (int idx = threadIdx.x; idx < S * V; idx += blockDim.x) {
+        const int v = (int)a.divS.div((uint32_t)idx);
+        const int s = idx - v * S;
+        const cf x = adc_fetch(a.adc, frame, v, s, a.loop_idx);
+        tile[s * Vp + v] = cscale(x, win[s]);
+    }
+    __syncthreads();
+    fft_axis(tile, Vp, 1, V, a.divV, a.planS, tw);
+    for (int k = threadIdx.x; k < S; k += blockDim.x) {
+        const cf* row = tile + pos[k] * Vp;
+        double acc = 0.0;
+        for (int v = 0; v < V; ++v) acc += (double)sqrtf(row[v].x * row[v].x + row[v].y * row[v].y);
+        a.out[frame * S + k] = (float)(acc / (double)V);
+    }
+}
+
+int launch_range_profile(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx, float* out,
+                         cudaStream_t st) {
+    if (int rc = check_in_kind(ctx, in_kind)) return rc;
+    if (loop_idx < 0 || loop_idx >= ctx->shape.num_loops) return set_error(ctx, RADAR_E_INVALID, "loop_idx %d out of range", loop_idx);
+    if (n_frames <= 0) return RADAR_OK;
+    ProfArgs a;
+    a.adc = make_view(ctx, adc, in_kind);
+    a.loop_idx = loop_idx;
+    a.winS = ctx->fftS.hann; a.twS = ctx->fftS.tw; a.posS = ctx->fftS.pos;
+    a.out = out;
+    a.planS = ctx->fftS.plan;
+    a.divS = make_fastdiv((uint32_t)a.adc.S); a.divV = make_fastdiv((uint32_t)a.adc.V);
+    const int S = a.adc.S, V = a.adc.V;
+    const size_t smem = arena_bytes((size_t)S * (V | 1), sizeof(cf)) + arena_bytes(S, sizeof(cf)) + arena_bytes(S, 4) + arena_bytes(S, 2);
+    if (int rc = opt_in_smem(ctx, range_profile_kernel, smem, "range profile tile")) return rc;
+    range_profile_kernel<<<(unsigned)n_frames, kRdThreads, smem, st>>>(a);
+    RB_CUDA_OK(ctx, cudaGetLastError());
+    return RADAR_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3a: range-angle heat map - one CTA per frame; range FFT of one chirp per antenna, then a
+// zero-padded angle DFT evaluated directly (K = n_ant <= V terms per output cell)
+// ------------------------------------------------------------------------------------------------
+struct RaArgs {
+    AdcView adc;
+    int loop_idx;
+    const int32_t* ant_list; int n_ant;
+    int A;
+    const float* winS; const float* winV;     // winV indexed by ORIGINAL antenna (may be all-ones)
+    const cf* twS; const uint16_t* posS; const cf* twA;
+    float* out;
+    FftPlan planS; FastDiv divS, divN, divA;
+};
+
+__global__ void __launch_bounds__(kRdThreads) range_angle_kernel(const __grid_constant__ RaArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int S = a.adc.S, N = a.n_ant, Np = odd_pitch(N), A = a.A;
+    SmemArena ar(smem_raw);
+    cf* tile = ar.take<cf>(S * Np);
+    cf* tw = ar.take<cf>(S);
+    cf* twA = ar.take<cf>(A);
+    float* win = ar.take<float>(S);
+    uint16_t* pos = ar.take<uint16_t>(S);
+    load_table(tw, a.twS, S);
+    load_table(twA, a.twA, A);
+    load_table(win, a.winS, S);
+    load_table(pos, a.posS, S);
+    __syncthreads();
+    const long long frame = blockIdx.x;
+    for (int idx = threadIdx.x; idx < S * N; idx += blockDim.x) {
+        const int j = (int)a.divS.div((uint32_t)idx);
+        const int s = idx - j * S;
+        const int v = a.ant_list ? a.ant_list[j] : j;
+        const cf x = adc_fetch(a.adc, frame, v, s, a.loop_idx);
+        tile[s * Np + j] = cscale(x, win[s] * a.winV[v]);
+    }
+    __syncthreads();
+    fft_axis(tile, Np, 1, N, a.divN, a.planS, tw);
+    float* dst = a.out + frame * (long long)S * A;
+    const int total = S * A;
+    for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+        const int k = (int)a.divA.div((uint32_t)idx);
+        const int ao = idx - k * A;
+        int ap = ao - A / 2;                 // fftshift: column ao holds bin (ao - A/2) mod A
+        if (ap < 0) ap += A;
+        const cf* row = tile + pos[k] * Np;
+        cf acc = row[0];
+        int e = 0;
+        for (int j = 1; j < N; ++j) {
+            e += ap; if (e >= A) e -= A;
+            const cf w = twA[e];
+            acc.x = fmaf(row[j].x, w.x, fmaf(-row[j].y, w.y, acc.x));
+            acc.y = fmaf(row[j].x, w.y, fmaf(row[j].y, w.x, acc.y));
+        }
+        dst[idx] = sqrtf(acc.x * acc.x + acc.y * acc.y);
+    }
+}
+
+int launch_range_angle(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx,
+                       const int32_t* ant_list, int n_ant, int num_angle_bins, int window_flags, float* out,
+                       cudaStream_t st) {
+    if (int rc = check_in_kind(ctx, in_kind)) return rc;
+    if (loop_idx < 0 || loop_idx >= ctx->shape.num_loops) return set_error(ctx, RADAR_E_INVALID, "loop_idx %d out of range", loop_idx);
+    const int N = ant_list ? n_ant : ctx->V;
+    if (N <= 0) return set_error(ctx, RADAR_E_INVALID, "empty antenna list");
+    if (num_angle_bins < N || num_angle_bins > 8192)
+        return set_error(ctx, RADAR_E_INVALID, "num_angle_bins %d must be in [n_ant=%d, 8192]", num_angle_bins, N);
+    if (n_frames <= 0) return RADAR_OK;
+    AngleTables at;
+    if (int rc = get_angle_tables(ctx, num_angle_bins, &at)) return rc;
+    float* onesV = nullptr;
+    if (int rc = get_hann(ctx, -ctx->V, &onesV)) return rc;     // negative length = all-ones table
+    RaArgs a;
+    a.adc = make_view(ctx, adc, in_kind);
+    a.loop_idx = loop_idx;
+    a.ant_list = ant_list; a.n_ant = N; a.A = num_angle_bins;
+    a.winS = (window_flags & RADAR_WIN_RANGE) ? ctx->fftS.hann : ctx->fftS.ones;
+    a.winV = (window_flags & RADAR_WIN_ANTENNA) ? ctx->hannV : onesV;
+    a.twS = ctx->fftS.tw; a.posS = ctx->fftS.pos; a.twA = at.tw;
+    a.out = out;
+    a.planS = ctx->fftS.plan;
+    a.divS = make_fastdiv((uint32_t)a.adc.S); a.divN = make_fastdiv((uint32_t)N); a.divA = make_fastdiv((uint32_t)num_angle_bins);
+    const int S = a.adc.S;
+    const size_t smem = arena_bytes((size_t)S * (N | 1), sizeof(cf)) + arena_bytes(S, sizeof(cf)) +
+                        arena_bytes(num_angle_bins, sizeof(cf)) + arena_bytes(S, 4) + arena_bytes(S, 2);
+    if (int rc = opt_in_smem(ctx, range_angle_kernel, smem, "range-angle tile")) return rc;
+    range_angle_kernel<<<(unsigned)n_frames, kRdThreads, smem, st>>>(a);
+    RB_CUDA_OK(ctx, cudaGetLastError());
+    return RADAR_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K5b: Doppler beam sharpening - one CTA per frame.  For each antenna of the subset the full RD tile is
+// formed in shared memory (same code as K1+K2) and only the selected (range, Doppler-bin) cells are
+// combined with the angle steering coefficient of each output angle.
+// ------------------------------------------------------------------------------------------------
+struct DbsArgs {
+    RdArgs rd;
+    int A, n_out;
+    const int32_t* vel_bin; const int32_t* ang_bin;
+    const cf* twA;
+    cf* acc_global;      // used when the accumulator does not fit in shared memory
+    int acc_in_smem;
+    float* out;
+    FastDiv divOut;
+};
+
+__global__ void __launch_bounds__(kRdThreads) dbs_kernel(const __grid_constant__ DbsArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int S = a.rd.adc.S, L = a.rd.adc.L, Lp = odd_pitch(L);
+    RdSmem sm = rd_carve(smem_raw, S, L);
+    unsigned char* after = smem_raw + rd_smem_bytes(S, L);
+    SmemArena ar(after);
+    cf* twA = ar.take<cf>(a.A);
+    int* selL = ar.take<int>(a.n_out);       // tile column holding Doppler bin vel_bin[i]
+    int* selA = ar.take<int>(a.n_out);       // shifted angle frequency of ang_bin[i]
+    const long long frame = blockIdx.x;
+    const int total = S * a.n_out;
+    cf* acc = a.acc_in_smem ? ar.take<cf>(total) : a.acc_global + frame * (long long)total;
+    rd_load_tables(sm, a.rd);
+    load_table(twA, a.twA, a.A);
+    __syncthreads();
+    for (int i = threadIdx.x; i < a.n_out; i += blockDim.x) {
+        selL[i] = sm.srcL[a.vel_bin[i]];
+        int f = a.ang_bin[i] - a.A / 2;
+        if (f < 0) f += a.A;
+        selA[i] = f;
+    }
+    for (int idx = threadIdx.x; idx < total; idx += blockDim.x) acc[idx] = cmake(0.f, 0.f);
+    __syncthreads();
+    for (int j = 0; j < a.rd.n_out_ant; ++j) {
+        const int v = a.rd.ant_list ? a.rd.ant_list[j] : j;
+        const float weight = a.rd.ant_weight ? a.rd.ant_weight[j] : 1.0f;
+        rd_compute_tile(sm, a.rd, frame, v, weight);
+        for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+            const int k = (int)a.divOut.div((uint32_t)idx);
+            const int i = idx - k * a.n_out;
+            const cf x = sm.tile[sm.posS[k] * Lp + selL[i]];
+            const cf w = twA[(int)(((long long)j * selA[i]) % a.A)];
+            cf c = acc[idx];
+            c.x = fmaf(x.x, w.x, fmaf(-x.y, w.y, c.x));
+            c.y = fmaf(x.x, w.y, fmaf(x.y, w.x, c.y));
+            acc[idx] = c;
+        }
+        __syncthreads();
+    }
+    float* dst = a.out + frame * (long long)total;
+    for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
+        const cf c = acc[idx];
+        dst[idx] = sqrtf(c.x * c.x + c.y * c.y);
+    }
+}
+
+int launch_dbs(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, const int32_t* ant_list, int n_ant,
+               int num_angle_bins, const int32_t* vel_bin, const int32_t* ang_bin, int n_out, float* out,
+               cudaStream_t st) {
+    if (int rc = check_in_kind(ctx, in_kind)) return rc;
+    const int N = ant_list ? n_ant : ctx->V;
+    if (N <= 0 || n_out <= 0) return set_error(ctx, RADAR_E_INVALID, "empty antenna list or output grid");
+    if (num_angle_bins < N || num_angle_bins > 8192)
+        return set_error(ctx, RADAR_E_INVALID, "num_angle_bins %d must be in [n_ant=%d, 8192]", num_angle_bins, N);
+    if (n_frames <= 0) return RADAR_OK;
+    AngleTables at;
+    if (int rc = get_angle_tables(ctx, num_angle_bins, &at)) return rc;
+    float* hannN = nullptr;
+    if (int rc = get_hann(ctx, N, &hannN)) return rc;           // Hann over the SUBSET's length (ref :176-177)
+    DbsArgs a;
+    a.rd.adc = make_view(ctx, adc, in_kind);
+    a.rd.n_out_ant = N; a.rd.ant_list = ant_list; a.rd.ant_weight = hannN;
+    a.rd.winS = ctx->fftS.hann; a.rd.winL = ctx->fftL.hann;
+    a.rd.twS = ctx->fftS.tw; a.rd.twL = ctx->fftL.tw; a.rd.posS = ctx->fftS.pos; a.rd.posL = ctx->fftL.pos;
+    a.rd.rd_out = nullptr; a.rd.mag_out = nullptr; a.rd.mag_antenna = 0;
+    a.rd.planS = ctx->fftS.plan; a.rd.planL = ctx->fftL.plan;
+    a.rd.divS = make_fastdiv((uint32_t)a.rd.adc.S); a.rd.divL = make_fastdiv((uint32_t)a.rd.adc.L);
+    a.A = num_angle_bins; a.n_out = n_out;
+    a.vel_bin = vel_bin; a.ang_bin = ang_bin; a.twA = at.tw; a.out = out;
+    a.divOut = make_fastdiv((uint32_t)n_out);
+    const int S = a.rd.adc.S, L = a.rd.adc.L;
+    const size_t base = rd_smem_bytes(S, L) + arena_bytes(num_angle_bins, sizeof(cf)) + 2 * arena_bytes(n_out, 4);
+    const size_t acc_bytes = arena_bytes((size_t)S * n_out, sizeof(cf));
+    size_t smem = base + acc_bytes;
+    a.acc_in_smem = 1; a.acc_global = nullptr;
+    if (smem > (size_t)ctx->max_smem_optin) {
+        smem = base; a.acc_in_smem = 0;
+        if (int rc = ensure_scratch(ctx, (size_t)n_frames * S * n_out * sizeof(cf))) return rc;
+        a.acc_global = reinterpret_cast<cf*>(ctx->scratch);
+    }
+    if (int rc = opt_in_smem(ctx, dbs_kernel, smem, "DBS tile")) return rc;
+    dbs_kernel<<<(unsigned)n_frames, kRdThreads, smem, st>>>(a);
+    RB_CUDA_OK(ctx, cudaGetLastError());
+    return RADAR_OK;
+}
+
+}  // namespace rb

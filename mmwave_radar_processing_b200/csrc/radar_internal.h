@@ -1,0 +1,87 @@
+// Internal declarations shared by the kernel translation units and the C-ABI layer.
+#pragma once
+#include <cstdint>
+#include <cstdio>
+#include <map>
+#include <vector>
+#include <cuda_runtime.h>
+#include "../../include/radar_b200.h"
+#include "fft_plan.h"
+
+namespace rb {
+
+// Device-resident FFT tables for one transform length.
+struct FftTables {
+    FftPlan plan{};
+    cf* tw = nullptr;          // [N] W_N^j
+    uint16_t* pos = nullptr;   // [N] natural bin -> in-place position
+    float* hann = nullptr;     // [N] np.hanning(N)
+    float* ones = nullptr;     // [N] all-ones window (window disabled)
+};
+
+struct AngleTables {           // zero-padded angle DFT of length A
+    cf* tw = nullptr;          // [A] W_A^j as float
+    double2* tw64 = nullptr;   // [A] W_A^j in fp64 (per-detection angle estimate)
+};
+
+}  // namespace rb
+
+struct radar_ctx {
+    int device = 0;
+    radar_shape shape{};
+    int V = 0, C = 0;
+    int sm_count = 0;
+    int max_smem_optin = 0;
+    rb::FftTables fftS, fftL;
+    float* hannV = nullptr;                       // [V] np.hanning(V)
+    std::map<int, float*> hann_by_len;            // extra Hann windows (DBS subset length)
+    std::map<int, rb::AngleTables> angle_tabs;    // per num_angle_bins
+    double* range_bins = nullptr; int n_range_bins = 0;
+    double* vel_bins = nullptr;   int n_vel_bins = 0;
+    double* angle_bins = nullptr; int n_angle_bins = 0;
+    void* scratch = nullptr; size_t scratch_bytes = 0;
+    char err[512] = {0};
+};
+
+namespace rb {
+
+int set_error(radar_ctx* ctx, int code, const char* fmt, ...);
+int ensure_scratch(radar_ctx* ctx, size_t bytes);
+int get_angle_tables(radar_ctx* ctx, int num_angle_bins, AngleTables* out);
+int get_hann(radar_ctx* ctx, int n, float** out);
+
+#define RB_CUDA_OK(ctx, expr)                                                                   \
+    do {                                                                                        \
+        cudaError_t _e = (expr);                                                                \
+        if (_e != cudaSuccess)                                                                  \
+            return rb::set_error((ctx), RADAR_E_CUDA, "%s failed: %s (%s:%d)", #expr,           \
+                                 cudaGetErrorString(_e), __FILE__, __LINE__);                   \
+    } while (0)
+
+// ---- launchers (kernels_*.cu) ------------------------------------------------------------------
+int launch_range_doppler(radar_ctx* ctx, const void* adc, int in_kind, int n_frames,
+                         const int32_t* ant_list, int n_ant, const float* ant_weight, int window_flags,
+                         cf* rd_out, float* mag_out, int mag_antenna, cudaStream_t st);
+int launch_range_profile(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx,
+                         float* profile_out, cudaStream_t st);
+int launch_range_angle(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx,
+                       const int32_t* ant_list, int n_ant, int num_angle_bins, int window_flags,
+                       float* out, cudaStream_t st);
+int launch_dbs(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, const int32_t* ant_list, int n_ant,
+               int num_angle_bins, const int32_t* vel_bin, const int32_t* ang_bin, int n_out, float* out,
+               cudaStream_t st);
+int launch_cfar_2d(radar_ctx* ctx, const float* maps, int n_maps, int rows, int cols,
+                   const radar_cfar_params& p, double* noise_out, uint8_t* mask_out, int32_t* dets_out,
+                   int32_t* count_out, int max_dets, cudaStream_t st);
+int launch_cfar_1d_rows(radar_ctx* ctx, const float* maps, int n_maps, int rows, int cols,
+                        const radar_cfar_params& p, const uint8_t* row_select, double* noise_out,
+                        uint8_t* mask_out, int32_t* dets_out, int32_t* count_out, int max_dets, cudaStream_t st);
+int launch_point_cloud(radar_ctx* ctx, const cf* rd, int n_frames, const int32_t* dets, const int32_t* counts,
+                       int max_dets, const int32_t* az_idx, int n_az, const int32_t* el_idx, int n_el,
+                       int shift_az, int shift_el, int num_angle_bins, double* points_out, int32_t* az_bin_out,
+                       int32_t* el_bin_out, cudaStream_t st);
+int launch_sar_image(radar_ctx* ctx, const cf* aperture, int num_samples, int n_elems, const double* positions,
+                     const double* dirs, int n_dirs, double lambda_m, int g_begin, int g_end, cf* out,
+                     cudaStream_t st);
+
+}  // namespace rb

@@ -1,0 +1,246 @@
+"""Device-level wrapper over the C ABI: one ``RadarEngine`` per (radar shape, CUDA device).
+
+PyTorch is plumbing here (device buffers + streams); every computation is a call into
+``libradar_b200.so``.  All methods take and return CUDA tensors and enqueue on the current torch stream.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional, Sequence
+
+import numpy as np
+import torch
+
+from . import _native as nat
+
+
+def _stream_ptr():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def cfar_params(kind: str, num_train, num_guard, pfa: float = 0.0, rho: float = 0.0, alpha: float = 0.0,
+                os_rank: int = 0) -> nat.CfarParams:
+    """Build the C struct.  2-D detectors pass (range, doppler) pairs, 1-D detectors pass ints."""
+    p = nat.CfarParams()
+    p.kind = nat.CFAR_KIND[kind]
+    if isinstance(num_train, (tuple, list, np.ndarray)):
+        p.train_r, p.train_d = int(num_train[0]), int(num_train[1])
+        p.guard_r, p.guard_d = int(num_guard[0]), int(num_guard[1])
+    else:
+        p.train_r, p.train_d = 0, int(num_train)
+        p.guard_r, p.guard_d = 0, int(num_guard)
+    p.os_rank = int(os_rank)
+    p.pfa, p.rho, p.alpha = float(pfa), float(rho), float(alpha)
+    return p
+
+
+class RadarEngine:
+    """Owns a ``radar_ctx``.  Shapes: R rx, S samples, cpl TX slots, L loops; V = R*cpl, C = cpl*L."""
+
+    def __init__(self, num_rx: int, num_samples: int, chirps_per_loop: int, num_loops: int, device=None):
+        if not torch.cuda.is_available():
+            raise RuntimeError("mmwave_radar_processing_b200 needs a CUDA device (no CPU fallback)")
+        self.lib = nat.load_library()
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
+        self.R, self.S, self.cpl, self.L = int(num_rx), int(num_samples), int(chirps_per_loop), int(num_loops)
+        self.V, self.C = self.R * self.cpl, self.cpl * self.L
+        shape = nat.RadarShape(self.R, self.S, self.cpl, self.L)
+        handle = C.c_void_p()
+        nat.check(self.lib.radar_ctx_create(C.byref(shape), self.device.index, C.byref(handle)), None)
+        self.ctx = handle
+        self._int_cache = {}
+        self._axes_key = None
+        self._angle_key = None
+
+    @classmethod
+    def for_config(cls, cfg, device=None) -> "RadarEngine":
+        key = (cfg.num_rx_antennas, cfg.get_num_adc_samples(0), cfg.chirp_cfgs_per_loop, cfg.frameCfg_loops,
+               str(device) if device is not None else f"cuda:{torch.cuda.current_device()}")
+        eng = _ENGINES.get(key)
+        if eng is None:
+            eng = cls(*key[:4], device=device)
+            _ENGINES[key] = eng
+        return eng
+
+    def __del__(self):
+        try:
+            if getattr(self, "ctx", None):
+                self.lib.radar_ctx_destroy(self.ctx)
+                self.ctx = None
+        except Exception:  # noqa: BLE001 - interpreter shutdown
+            pass
+
+    # ------------------------------------------------------------------ helpers
+    def _ints(self, values: Optional[Sequence[int]]):
+        """Small int32 device array, cached by content (antenna lists, bin selections)."""
+        if values is None:
+            return None
+        key = tuple(int(v) for v in values)
+        t = self._int_cache.get(key)
+        if t is None:
+            t = torch.tensor(key, dtype=torch.int32, device=self.device) if key else \
+                torch.zeros(1, dtype=torch.int32, device=self.device)
+            self._int_cache[key] = t
+        return t
+
+    def _in_kind(self, adc: torch.Tensor) -> int:
+        if adc.dtype == torch.int16:
+            exp = (self.C, self.R, self.S, 2)
+            kind = nat.RADAR_IN_IQ16
+        elif adc.dtype == torch.complex64:
+            exp = (self.V, self.S, self.L)
+            kind = nat.RADAR_IN_CUBE64
+        else:
+            raise ValueError(f"ADC tensor must be int16 IQ or complex64 cube, got {adc.dtype}")
+        if tuple(adc.shape[-len(exp):]) != exp or adc.dim() != len(exp) + 1:
+            raise ValueError(f"ADC tensor shape {tuple(adc.shape)} != (frames,)+{exp}")
+        if not adc.is_contiguous() or adc.device != self.device:
+            raise ValueError("ADC tensor must be contiguous and on the engine's device")
+        return kind
+
+    def set_axes(self, range_bins: np.ndarray, vel_bins: np.ndarray):
+        rb = np.ascontiguousarray(range_bins, dtype=np.float64)
+        vb = np.ascontiguousarray(vel_bins, dtype=np.float64)
+        key = (rb.tobytes(), vb.tobytes())
+        if key != self._axes_key:
+            dp = C.POINTER(C.c_double)
+            nat.check(self.lib.radar_ctx_set_axes(self.ctx, rb.ctypes.data_as(dp), rb.shape[0],
+                                                  vb.ctypes.data_as(dp), vb.shape[0]), self.ctx)
+            self._axes_key = key
+
+    def set_angle_bins(self, angle_bins: np.ndarray):
+        ab = np.ascontiguousarray(angle_bins, dtype=np.float64)
+        key = ab.tobytes()
+        if key != self._angle_key:
+            nat.check(self.lib.radar_ctx_set_angle_bins(self.ctx, ab.ctypes.data_as(C.POINTER(C.c_double)),
+                                                        ab.shape[0]), self.ctx)
+            self._angle_key = key
+
+    # ------------------------------------------------------------------ kernels
+    def range_doppler(self, adc: torch.Tensor, ant_list=None, window_flags: int = 3, want_rd: bool = True,
+                      mag_antenna: Optional[int] = None, rd_out=None, mag_out=None):
+        """-> (rd complex64 [F, n_ant, S, L] or None, mag float32 [F,S,L] / [F,n_ant,S,L] or None)."""
+        kind = self._in_kind(adc)
+        f = adc.shape[0]
+        n_ant = len(ant_list) if ant_list is not None else self.V
+        ants = self._ints(ant_list)
+        if want_rd and rd_out is None:
+            rd_out = torch.empty((f, n_ant, self.S, self.L), dtype=torch.complex64, device=self.device)
+        if mag_antenna is not None and mag_out is None:
+            shape = (f, self.S, self.L) if mag_antenna >= 0 else (f, n_ant, self.S, self.L)
+            mag_out = torch.empty(shape, dtype=torch.float32, device=self.device)
+        nat.check(self.lib.radar_range_doppler(
+            self.ctx, nat.ptr(adc), kind, f, nat.ptr(ants), n_ant, int(window_flags),
+            nat.ptr(rd_out if want_rd else None), nat.ptr(mag_out), int(mag_antenna if mag_antenna is not None else 0),
+            _stream_ptr()), self.ctx)
+        return (rd_out if want_rd else None), mag_out
+
+    def range_profile(self, adc: torch.Tensor, loop_idx: int = 0, out=None) -> torch.Tensor:
+        kind = self._in_kind(adc)
+        f = adc.shape[0]
+        if out is None:
+            out = torch.empty((f, self.S), dtype=torch.float32, device=self.device)
+        nat.check(self.lib.radar_range_profile(self.ctx, nat.ptr(adc), kind, f, int(loop_idx), nat.ptr(out),
+                                               _stream_ptr()), self.ctx)
+        return out
+
+    def cfar(self, maps: torch.Tensor, params: nat.CfarParams, one_d: bool = False, row_select=None,
+             want_noise: bool = False, want_mask: bool = False, max_dets: Optional[int] = None,
+             dets_out=None, count_out=None):
+        """CFAR + ordered compaction on float32 maps [n, rows, cols].
+
+        -> dict(noise=f64 or None, mask=u8 or None, dets=int32 [n,max_dets,2], counts=int32 [n])."""
+        if maps.dtype != torch.float32 or maps.dim() != 3 or not maps.is_contiguous():
+            raise ValueError("maps must be a contiguous float32 [n, rows, cols] tensor")
+        n, rows, cols = maps.shape
+        if max_dets is None:
+            max_dets = rows * cols
+        noise = torch.empty((n, rows, cols), dtype=torch.float64, device=self.device) if want_noise else None
+        mask = torch.empty((n, rows, cols), dtype=torch.uint8, device=self.device) if want_mask else None
+        if dets_out is None:
+            dets_out = torch.empty((n, max_dets, 2), dtype=torch.int32, device=self.device)
+        if count_out is None:
+            count_out = torch.empty((n,), dtype=torch.int32, device=self.device)
+        if one_d:
+            nat.check(self.lib.radar_cfar_1d_rows(self.ctx, nat.ptr(maps), n, rows, cols, C.byref(params),
+                                                  nat.ptr(row_select), nat.ptr(noise), nat.ptr(mask), nat.ptr(dets_out),
+                                                  nat.ptr(count_out), int(max_dets), _stream_ptr()), self.ctx)
+        else:
+            nat.check(self.lib.radar_cfar_2d(self.ctx, nat.ptr(maps), n, rows, cols, C.byref(params), nat.ptr(noise),
+                                             nat.ptr(mask), nat.ptr(dets_out), nat.ptr(count_out), int(max_dets),
+                                             _stream_ptr()), self.ctx)
+        return dict(noise=noise, mask=mask, dets=dets_out, counts=count_out)
+
+    def point_cloud(self, rd: torch.Tensor, dets: torch.Tensor, counts: torch.Tensor, az_idx, el_idx,
+                    shift_az: bool = True, shift_el: bool = False, num_angle_bins: int = 64,
+                    points_out=None, want_bins: bool = True):
+        """-> (points float64 [F,max_dets,4], az_bin int32 [F,max_dets] | None, el_bin | None)."""
+        f, max_dets = dets.shape[0], dets.shape[1]
+        if rd.dtype != torch.complex64 or tuple(rd.shape) != (f, self.V, self.S, self.L):
+            raise ValueError("rd must be complex64 [F, V, S, L] for all V antennas")
+        if points_out is None:
+            points_out = torch.zeros((f, max_dets, 4), dtype=torch.float64, device=self.device)
+        az_bin = torch.zeros((f, max_dets), dtype=torch.int32, device=self.device) if want_bins else None
+        el_bin = torch.zeros((f, max_dets), dtype=torch.int32, device=self.device) if want_bins else None
+        az, el = self._ints(az_idx), self._ints(el_idx)
+        nat.check(self.lib.radar_point_cloud(
+            self.ctx, nat.ptr(rd), f, nat.ptr(dets), nat.ptr(counts), max_dets,
+            nat.ptr(az), len(az_idx), nat.ptr(el), len(el_idx), int(bool(shift_az)), int(bool(shift_el)),
+            int(num_angle_bins), nat.ptr(points_out), nat.ptr(az_bin), nat.ptr(el_bin), _stream_ptr()), self.ctx)
+        return points_out, az_bin, el_bin
+
+    def range_angle(self, adc: torch.Tensor, loop_idx: int = 0, ant_list=None, num_angle_bins: int = 64,
+                    windowing: bool = True, out=None) -> torch.Tensor:
+        kind = self._in_kind(adc)
+        f = adc.shape[0]
+        n_ant = len(ant_list) if ant_list is not None else self.V
+        if out is None:
+            out = torch.empty((f, self.S, num_angle_bins), dtype=torch.float32, device=self.device)
+        flags = (nat.RADAR_WIN_RANGE | nat.RADAR_WIN_ANTENNA) if windowing else 0
+        nat.check(self.lib.radar_range_angle(self.ctx, nat.ptr(adc), kind, f, int(loop_idx), nat.ptr(self._ints(ant_list)),
+                                             n_ant, int(num_angle_bins), flags, nat.ptr(out), _stream_ptr()), self.ctx)
+        return out
+
+    def dbs(self, adc: torch.Tensor, vel_bin, ang_bin, ant_list=None, num_angle_bins: int = 64, out=None) -> torch.Tensor:
+        kind = self._in_kind(adc)
+        f = adc.shape[0]
+        n_ant = len(ant_list) if ant_list is not None else self.V
+        n_out = len(vel_bin)
+        if out is None:
+            out = torch.empty((f, self.S, n_out), dtype=torch.float32, device=self.device)
+        nat.check(self.lib.radar_dbs(self.ctx, nat.ptr(adc), kind, f, nat.ptr(self._ints(ant_list)), n_ant,
+                                     int(num_angle_bins), nat.ptr(self._ints(vel_bin)), nat.ptr(self._ints(ang_bin)),
+                                     n_out, nat.ptr(out), _stream_ptr()), self.ctx)
+        return out
+
+    def sar_image(self, aperture: torch.Tensor, positions: torch.Tensor, dirs: torch.Tensor, lambda_m: float,
+                  g_begin: int = 0, g_end: Optional[int] = None, out=None) -> torch.Tensor:
+        """aperture complex64 [S,N], positions float64 [3,N], dirs float64 [3,G] -> complex64 [S, g_end-g_begin]."""
+        s, n = aperture.shape
+        g = dirs.shape[1]
+        g_end = g if g_end is None else g_end
+        if aperture.dtype != torch.complex64 or positions.dtype != torch.float64 or dirs.dtype != torch.float64:
+            raise ValueError("aperture complex64, positions/dirs float64 expected")
+        if tuple(positions.shape) != (3, n) or dirs.shape[0] != 3:
+            raise ValueError("positions must be [3,N], dirs [3,G]")
+        if out is None:
+            out = torch.empty((s, g_end - g_begin), dtype=torch.complex64, device=self.device)
+        nat.check(self.lib.radar_sar_image(self.ctx, nat.ptr(aperture.contiguous()), s, n, nat.ptr(positions.contiguous()),
+                                           nat.ptr(dirs.contiguous()), g, float(lambda_m), int(g_begin), int(g_end),
+                                           nat.ptr(out), _stream_ptr()), self.ctx)
+        return out
+
+
+_ENGINES = {}
+
+
+def utility_engine(device=None) -> RadarEngine:
+    """Shape-independent engine used by the stand-alone CFAR detector classes."""
+    key = ("util", str(device) if device is not None else f"cuda:{torch.cuda.current_device()}")
+    eng = _ENGINES.get(key)
+    if eng is None:
+        eng = RadarEngine(1, 1, 1, 1, device=device)
+        _ENGINES[key] = eng
+    return eng

@@ -1,0 +1,363 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the numpy oracle and the reference-generated
+golden fixtures, on the same seeded inputs.
+
+Tolerances (BASELINE.json north_star): bin / peak indices bit-exact; RD and RA magnitudes <= 1e-4 relative
+L2 (fp32 device arithmetic vs fp64 reference); CFAR masks identical except cells within 1e-5 (relative) of
+the threshold, which are counted and reported.
+"""
+import numpy as np
+import pytest
+
+from conftest import (CFAR1D_SETS, CFAR2D_SETS, GOLDEN_CASES, GROUND_VEL, SEQ_PARAMS, ant_sets, frame_iq, golden,
+                      load_cfg, rel_l2)
+
+pytestmark = pytest.mark.gpu
+
+RD_TOL = 1e-4
+NEAR_THR = 1e-5
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    torch = pytest.importorskip("torch")
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    return torch
+
+
+def _engine(cm):
+    from mmwave_radar_processing_b200.engine import RadarEngine
+    return RadarEngine.for_config(cm)
+
+
+def _oracle_frame(cm, seed):
+    from oracle import radar_oracle as orc
+    iq = frame_iq(cm, seed)
+    cube = orc.virtual_array(orc.iq_to_cube(iq), cm.num_rx_antennas, cm.chirp_cfgs_per_loop, cm.frameCfg_loops)
+    return iq, cube, orc.range_doppler(cube)
+
+
+def _mask_diff_report(x, thr, mask_dev, mask_ref):
+    """Cells where the masks differ must all be within NEAR_THR of the threshold."""
+    diff = np.nonzero(mask_dev != mask_ref)
+    if diff[0].size == 0:
+        return 0
+    rel = np.abs(x[diff] - thr[diff]) / np.abs(thr[diff])
+    assert np.all(rel < NEAR_THR), f"mask differs away from the threshold: rel distances {rel}"
+    return int(diff[0].size)
+
+
+# ------------------------------------------------------------------------------------------------ RD
+@pytest.mark.parametrize("name,seed", GOLDEN_CASES)
+def test_range_doppler_both_layouts(torch_cuda, name, seed):
+    torch = torch_cuda
+    cm = load_cfg(name)
+    g = golden(name, seed)
+    iq, cube, rd_ref = _oracle_frame(cm, seed)
+    eng = _engine(cm)
+    rd, mag = eng.range_doppler(torch.from_numpy(iq[None]).cuda(), want_rd=True, mag_antenna=0)
+    rd = rd[0].cpu().numpy()
+    assert rel_l2(rd, rd_ref) < RD_TOL
+    assert rel_l2(mag[0].cpu().numpy(), np.abs(rd_ref[0])) < RD_TOL
+    assert rel_l2(mag[0].cpu().numpy(), g["rd_mag_rx0"]) < RD_TOL
+    if "rd" in g:
+        assert rel_l2(rd, g["rd"]) < RD_TOL
+    # complex64 cube layout (the reference's host cube)
+    from mmwave_radar_processing_b200.processors._device import engine_for_cube_shape
+    e2 = engine_for_cube_shape(*cube.shape)
+    rd2, mag_all = e2.range_doppler(torch.from_numpy(cube.astype(np.complex64)[None]).cuda(), want_rd=True, mag_antenna=-1)
+    assert rel_l2(rd2[0].cpu().numpy(), rd_ref) < RD_TOL
+    assert rel_l2(mag_all[0].cpu().numpy(), np.abs(rd_ref)) < RD_TOL
+    # the two ingest layouts run the same arithmetic on the same values
+    assert np.array_equal(rd2[0].cpu().numpy(), rd)
+    # antenna subset + un-windowed variant
+    sub = [cube.shape[0] - 1, 0]
+    rd3, _ = eng.range_doppler(torch.from_numpy(iq[None]).cuda(), ant_list=sub, window_flags=0)
+    ref3 = np.fft.fftshift(np.fft.fft2(cube[sub], axes=(-2, -1)), axes=-1)
+    assert rel_l2(rd3[0].cpu().numpy(), ref3) < RD_TOL
+
+
+@pytest.mark.parametrize("name", ["1843_RadVel_10Hz", "1843_RadVel_5Hz", "1843_vel_nav", "1843_RaGNNarok_UAV_5m",
+                                  "1843_RaGNNarok_UAV_10m", "6843_vel_sr", "RadSAR_lr", "6843_hand_ods_30Hz",
+                                  "1843_RadVel_10Hz_lr_SAR", "RadCloud_original", "1843_RaGNNarok"])
+def test_range_doppler_every_fft_length(torch_cuda, name):
+    """All (S, L) pairs of the 25 cfgs incl. odd tile sizes (63x115), primes (127, 23, 13) and 512-point FFTs."""
+    torch = torch_cuda
+    cm = load_cfg(name)
+    iq, cube, rd_ref = _oracle_frame(cm, 7)
+    eng = _engine(cm)
+    rd, mag = eng.range_doppler(torch.from_numpy(iq[None]).cuda(), want_rd=True, mag_antenna=0)
+    assert rel_l2(rd[0].cpu().numpy(), rd_ref) < RD_TOL
+    assert rel_l2(mag[0].cpu().numpy(), np.abs(rd_ref[0])) < RD_TOL
+
+
+def test_range_profile(torch_cuda):
+    torch = torch_cuda
+    from oracle import radar_oracle as orc
+    for name, seed in GOLDEN_CASES:
+        cm = load_cfg(name)
+        g = golden(name, seed)
+        iq, cube, _ = _oracle_frame(cm, seed)
+        eng = _engine(cm)
+        dev = torch.from_numpy(iq[None]).cuda()
+        assert rel_l2(eng.range_profile(dev, 0)[0].cpu().numpy(), g["range_profile"]) < RD_TOL
+        assert rel_l2(eng.range_profile(dev, 3)[0].cpu().numpy(), orc.coarse_range_profile(cube, 3)) < RD_TOL
+
+
+# ------------------------------------------------------------------------------------------------ CFAR
+@pytest.mark.parametrize("name,seed", GOLDEN_CASES)
+def test_cfar2d_and_point_cloud(torch_cuda, name, seed):
+    torch = torch_cuda
+    from oracle import radar_oracle as orc
+    from mmwave_radar_processing_b200.engine import cfar_params
+    from mmwave_radar_processing_b200.pipeline import reference_axes
+    cm = load_cfg(name)
+    g = golden(name, seed)
+    iq, cube, rd_ref = _oracle_frame(cm, seed)
+    eng = _engine(cm)
+    rb, vb, ab = reference_axes(cm, 64)
+    eng.set_axes(rb, vb)
+    eng.set_angle_bins(ab)
+    rd, mag = eng.range_doppler(torch.from_numpy(iq[None]).cuda(), want_rd=True, mag_antenna=0)
+    mag_h = mag[0].cpu().numpy().astype(np.float64)
+    sets = ant_sets(cube.shape[0])
+    near = 0
+    for tag, (kind, params) in CFAR2D_SETS.items():
+        p = cfar_params(kind, params["num_train"], params["num_guard"], pfa=params.get("pfa", 0.0),
+                        rho=params.get("rho", 0.0), alpha=params.get("alpha", 0.0))
+        res = eng.cfar(mag, p, want_noise=True, want_mask=True)
+        noise = res["noise"][0].cpu().numpy()
+        mask = res["mask"][0].cpu().numpy().astype(bool)
+        # (1) exact against the oracle evaluated on the SAME fp32 map: isolates the CFAR kernel
+        thr_o, noise_o, mask_o = orc.cfar_2d(mag_h, kind, **params)
+        assert np.allclose(noise, noise_o, rtol=1e-12, atol=0)
+        assert np.array_equal(mask, mask_o)
+        n = int(res["counts"][0])
+        dets = res["dets"][0, :n].cpu().numpy()
+        assert np.array_equal(dets, orc.mask_to_dets(mask_o))
+        # (2) against the fp64 reference run: identical except cells within 1e-5 of the threshold
+        gthr = g[f"thr2d_{tag}"]
+        ref_mask = np.zeros_like(mask)
+        gd = g[f"dets2d_{tag}"]
+        ref_mask[gd[:, 0], gd[:, 1]] = True
+        fin = np.isfinite(gthr)
+        assert rel_l2(noise[fin], g[f"noise2d_{tag}"][fin]) < RD_TOL
+        flips = _mask_diff_report(g["rd_mag_rx0"], gthr, mask, ref_mask)
+        near += flips
+        if flips == 0:
+            assert np.array_equal(dets, gd)
+            for ab_tag in ("a", "b"):
+                az, el = sets["az_" + ab_tag], sets["el_" + ab_tag]
+                pts, az_bin, el_bin = eng.point_cloud(rd, res["dets"], res["counts"], az, el, True, False, 64)
+                gp = g[f"pc_{tag}_{ab_tag}"]
+                assert pts[0, :n].shape == gp.shape
+                if n:
+                    _, az_o, el_o = orc.point_cloud(rd_ref, gd, rb, vb, az, el)
+                    if az:
+                        assert np.array_equal(az_bin[0, :n].cpu().numpy(), az_o)        # bit-exact indices
+                    if el:
+                        assert np.array_equal(el_bin[0, :n].cpu().numpy(), el_o)
+                    assert np.allclose(pts[0, :n].cpu().numpy(), gp, rtol=1e-12, atol=1e-12)
+    print(f"{name} seed {seed}: {near} CFAR cells within {NEAR_THR} of threshold flipped")
+
+
+def test_cfar_edge_cases(torch_cuda):
+    torch = torch_cuda
+    from oracle import radar_oracle as orc
+    from mmwave_radar_processing_b200.engine import cfar_params, utility_engine
+    eng = utility_engine()
+    rng = np.random.default_rng(3)
+    # window larger than the map -> no detections, noise 0 (reference swallows the ValueError)
+    x = rng.exponential(1.0, (9, 40)).astype(np.float32)
+    res = eng.cfar(torch.from_numpy(x[None]).cuda(), cfar_params("os", (8, 4), (2, 1), rho=0.75, alpha=3.5),
+                   want_noise=True, want_mask=True)
+    assert int(res["counts"][0]) == 0 and not res["mask"].any() and not res["noise"].any()
+    # heavy-detection map with truncation: count reports the true number, list holds the first max_dets in order
+    x = rng.exponential(1.0, (40, 50)).astype(np.float32)
+    p = cfar_params("ca", (3, 3), (1, 1), alpha=0.9)
+    full = eng.cfar(torch.from_numpy(x[None]).cuda(), p, want_mask=True)
+    n = int(full["counts"][0])
+    _, _, mask_o = orc.cfar_2d(x.astype(np.float64), "ca", (3, 3), (1, 1), pfa=0.5)   # alpha overridden below
+    cut = eng.cfar(torch.from_numpy(x[None]).cuda(), p, max_dets=17)
+    assert int(cut["counts"][0]) == n > 17
+    assert np.array_equal(cut["dets"][0].cpu().numpy(), full["dets"][0, :17].cpu().numpy())
+    d = full["dets"][0, :n].cpu().numpy()
+    lin = d[:, 0] * 50 + d[:, 1]
+    assert np.all(np.diff(lin) > 0)                                     # row-major, strictly increasing
+    assert np.array_equal(np.nonzero(full["mask"][0].cpu().numpy().ravel())[0], lin)
+    # ties: constant map -> nothing exceeds alpha*noise for alpha >= 1, everything for alpha < 1 (strict >)
+    c = np.full((1, 30, 30), 2.0, dtype=np.float32)
+    for kind, kw in (("ca", dict(alpha=1.0)), ("os", dict(rho=0.5, alpha=1.0))):
+        r = eng.cfar(torch.from_numpy(c).cuda(), cfar_params(kind, (2, 2), (1, 1), **kw))
+        assert int(r["counts"][0]) == 0
+    r = eng.cfar(torch.from_numpy(c).cuda(), cfar_params("os", (2, 2), (1, 1), rho=0.5, alpha=0.999))
+    assert int(r["counts"][0]) == 24 * 24
+    # OS rank extremes: rho -> k=1 (minimum) and k=N (maximum)
+    x = rng.exponential(1.0, (25, 31)).astype(np.float32)
+    for rho in (0.0, 1.0, 0.33):
+        r = eng.cfar(torch.from_numpy(x[None]).cuda(), cfar_params("os", (3, 2), (1, 1), rho=rho, alpha=1.0), want_noise=True)
+        _, noise_o, _ = orc.cfar_2d(x.astype(np.float64), "os", (3, 2), (1, 1), rho=rho, alpha=1.0)
+        assert np.array_equal(r["noise"][0].cpu().numpy(), noise_o)
+    # large OS window (> 256 and > 512 cells) exercises the wider per-lane register files
+    x = rng.exponential(1.0, (64, 64)).astype(np.float32)
+    for tr, gr in (((9, 9), (2, 2)), ((12, 12), (3, 3))):
+        r = eng.cfar(torch.from_numpy(x[None]).cuda(), cfar_params("os", tr, gr, rho=0.7, alpha=2.0), want_noise=True)
+        _, noise_o, _ = orc.cfar_2d(x.astype(np.float64), "os", tr, gr, rho=0.7, alpha=2.0)
+        assert np.array_equal(r["noise"][0].cpu().numpy(), noise_o)
+
+
+@pytest.mark.parametrize("name,seed", GOLDEN_CASES)
+def test_cfar1d_family_and_detectors(torch_cuda, name, seed):
+    torch = torch_cuda
+    from oracle import radar_oracle as orc
+    from mmwave_radar_processing_b200.engine import cfar_params
+    cm = load_cfg(name)
+    g = golden(name, seed)
+    iq, cube, rd_ref = _oracle_frame(cm, seed)
+    eng = _engine(cm)
+    dev = torch.from_numpy(iq[None]).cuda()
+    _, mag = eng.range_doppler(dev, want_rd=False, mag_antenna=0)
+    prof = eng.range_profile(dev, 0)
+    mag_h = mag[0].cpu().numpy().astype(np.float64)
+    prof_h = prof[0].cpu().numpy().astype(np.float64)
+    for tag, (kind, params) in CFAR1D_SETS.items():
+        p = cfar_params(kind, params["num_train"], params["num_guard"], pfa=params.get("pfa", 0.0),
+                        rho=params.get("rho", 0.0), alpha=params.get("alpha", 0.0))
+        # all rows of the RD map at once + the profile as a 1-row map
+        res = eng.cfar(mag, p, one_d=True, want_noise=True, want_mask=True)
+        noise = res["noise"][0].cpu().numpy()
+        mask = res["mask"][0].cpu().numpy().astype(bool)
+        for r in range(mag_h.shape[0]):
+            _, n_o, m_o = orc.cfar_1d(mag_h[r], kind, **params)
+            assert np.allclose(noise[r], n_o, rtol=1e-12, atol=0)
+            assert np.array_equal(mask[r], m_o), (tag, r)
+        resp = eng.cfar(prof[:, None, :].contiguous(), p, one_d=True, want_noise=True, want_mask=True)
+        _, n_o, m_o = orc.cfar_1d(prof_h, kind, **params)
+        assert np.allclose(resp["noise"][0, 0].cpu().numpy(), n_o, rtol=1e-12, atol=0)
+        assert np.array_equal(resp["mask"][0, 0].cpu().numpy().astype(bool), m_o)
+        # against the reference run (fp64 inputs): same indices unless a cell sits on the threshold
+        gm = np.zeros_like(m_o)
+        gm[g[f"c1_prof_{tag}_idx"]] = True
+        _mask_diff_report(g["range_profile"], g[f"c1_prof_{tag}_thr"], m_o, gm)
+
+
+# ------------------------------------------------------------------------------------------------ RA / DBS / SAR
+@pytest.mark.parametrize("name,seed", GOLDEN_CASES)
+def test_range_angle(torch_cuda, name, seed):
+    torch = torch_cuda
+    cm = load_cfg(name)
+    g = golden(name, seed)
+    iq, cube, _ = _oracle_frame(cm, seed)
+    eng = _engine(cm)
+    dev = torch.from_numpy(iq[None]).cuda()
+    sets = ant_sets(cube.shape[0])
+    for a in (64, 256):
+        assert rel_l2(eng.range_angle(dev, 0, sets["ra"], a)[0].cpu().numpy(), g[f"ra_{a}_sub"]) < RD_TOL
+        assert rel_l2(eng.range_angle(dev, 2, None, a)[0].cpu().numpy(), g[f"ra_{a}_all_c2"]) < RD_TOL
+    assert rel_l2(eng.range_angle(dev, 1, sets["ra"], 64, windowing=False)[0].cpu().numpy(), g["ra_64_nowin"]) < RD_TOL
+
+
+@pytest.mark.parametrize("name", ["RadSAR_1843_official", "6843_RadVel_ods_20Hz"])
+def test_dbs(torch_cuda, name):
+    torch = torch_cuda
+    from oracle import radar_oracle as orc
+    cm = load_cfg(name)
+    g = golden(name, 0)
+    iq, cube, _ = _oracle_frame(cm, 0)
+    eng = _engine(cm)
+    dev = torch.from_numpy(iq[None]).cuda()
+    _, vb = orc.rd_axes(cm.vel_max_m_s, cm.vel_res_m_s, cm.range_max_m, cm.range_res_m)
+    _, coarse = orc.angle_axis(64)
+    fine = np.linspace(coarse[0], coarse[-1], 100)
+    vbin, abin = orc.dbs_bin_selection(coarse, fine, vb, g["dbs_velocity"])
+    out = eng.dbs(dev, vbin.tolist(), abin.tolist(), ant_list=[0, 3, 4, 7], num_angle_bins=64)
+    assert rel_l2(out[0].cpu().numpy(), g["dbs_sub"]) < RD_TOL
+    out = eng.dbs(dev, vbin.tolist(), abin.tolist(), ant_list=None, num_angle_bins=64)
+    assert rel_l2(out[0].cpu().numpy(), g["dbs_all"]) < RD_TOL
+
+
+def test_sar(torch_cuda):
+    torch = torch_cuda
+    from oracle import radar_oracle as orc
+    from mmwave_radar_processing_b200.synthetic import synth_frame_iq
+    from mmwave_radar_processing_b200.processors._device import engine_for_cube_shape
+    name = "RadSAR_1843_official"
+    cm = load_cfg(name)
+    g = golden(name, 0)
+    r, s, cpl, l = cm.num_rx_antennas, cm.get_num_adc_samples(0), cm.chirp_cfgs_per_loop, cm.frameCfg_loops
+    prof = cm.profile_cfgs[0]
+    eng = engine_for_cube_shape(1, s, 1)
+    for tag in ("a", "b"):
+        rx, cfg_idx, nf, stride = [int(v) for v in g[f"sar_{tag}_params"]]
+        mask, _ = orc.sar_chirp_times_us(cpl, l, prof["idleTime_us"] + prof["rampEndTime_us"], cfg_idx, stride)
+        hist = np.stack([orc.iq_to_cube(synth_frame_iq(r, s, cpl, l, 1000 + f))[rx][:, mask] for f in range(nf)])
+        geo = g[f"sar_{tag}_geometry"]
+        d = orc.sar_steering(g[f"sar_{tag}_az"], g[f"sar_{tag}_el"])
+        ap = torch.from_numpy(np.ascontiguousarray(hist.transpose(1, 0, 2).reshape(s, -1), dtype=np.complex64)).cuda()
+        pos = torch.from_numpy(np.ascontiguousarray(geo.transpose(1, 0, 2).reshape(3, -1))).cuda()
+        dirs = torch.from_numpy(np.ascontiguousarray(d.reshape(3, -1))).cuda()
+        ref = g[f"sar_{tag}_resp"].reshape(s, -1)
+        out = eng.sar_image(ap, pos, dirs, float(g[f"sar_{tag}_lambda"]))
+        assert rel_l2(out.cpu().numpy(), ref) < RD_TOL
+        # voxel sharding: any slice equals the same columns of the full image
+        gtot = ref.shape[1]
+        lo, hi = gtot // 3, gtot - 5
+        part = eng.sar_image(ap, pos, dirs, float(g[f"sar_{tag}_lambda"]), lo, hi)
+        assert np.array_equal(part.cpu().numpy(), out[:, lo:hi].cpu().numpy())
+
+
+# ------------------------------------------------------------------------------------------------ batch properties
+def test_batch_properties_full_size(torch_cuda):
+    """Size-independent properties at bench batch size: every frame of a batch equals the same frame processed
+    alone; linearity of the RD transform; permuting frames permutes results."""
+    torch = torch_cuda
+    from mmwave_radar_processing_b200.pipeline import DetectorSpec, FramePipeline
+    from mmwave_radar_processing_b200.synthetic import synth_batch_for_cfg
+    cm = load_cfg("1843_RadVel")
+    base = synth_batch_for_cfg(cm, range(16))
+    reps = 64
+    iq = np.concatenate([base] * reps)                       # 1024 frames
+    perm = np.random.default_rng(0).permutation(iq.shape[0])
+    pipe = FramePipeline(cm, detector=DetectorSpec("os", (8, 4), (2, 1), rho=0.75, alpha=3.5), max_dets=256)
+    dev = torch.from_numpy(iq[perm]).cuda()
+    out = pipe.run(dev)
+    counts = out["counts"].cpu().numpy()
+    pts = out["points"].cpu().numpy()
+    single = FramePipeline(cm, detector=DetectorSpec("os", (8, 4), (2, 1), rho=0.75, alpha=3.5), max_dets=256)
+    ref = single.run(torch.from_numpy(base).cuda())
+    rc, rp = ref["counts"].cpu().numpy(), ref["points"].cpu().numpy()
+    assert counts.min() > 0
+    for i, src in enumerate(perm):
+        j = src % 16
+        assert counts[i] == rc[j]
+        assert np.array_equal(pts[i, :counts[i]], rp[j, :rc[j]])
+    # linearity: RD(a*x) == a*RD(x) up to fp32 rounding, RD(x+y) == RD(x)+RD(y)
+    eng = pipe.engine
+    x = torch.from_numpy(base[:2]).cuda()
+    half = torch.from_numpy((base[:2] // 2 * 2)).cuda()
+    rd_full, _ = eng.range_doppler(half)
+    rd_half, _ = eng.range_doppler(torch.from_numpy(base[:2] // 2).cuda())
+    assert rel_l2((2 * rd_half).cpu().numpy(), rd_full.cpu().numpy()) < 1e-6
+    s = torch.from_numpy((base[0:1].astype(np.int32) // 2 + base[1:2].astype(np.int32) // 2).astype(np.int16)).cuda()
+    a, _ = eng.range_doppler(torch.from_numpy(base[0:1] // 2).cuda())
+    b, _ = eng.range_doppler(torch.from_numpy(base[1:2] // 2).cuda())
+    c, _ = eng.range_doppler(s)
+    assert rel_l2((a + b).cpu().numpy(), c.cpu().numpy()) < 1e-6
+    del x
+
+
+def test_error_paths(torch_cuda):
+    torch = torch_cuda
+    from mmwave_radar_processing_b200 import _native as nat
+    from mmwave_radar_processing_b200.engine import RadarEngine, cfar_params, utility_engine
+    eng = utility_engine()
+    x = torch.zeros((1, 8, 8), dtype=torch.float32, device="cuda")
+    with pytest.raises(nat.RadarError):
+        eng.cfar(x, cfar_params("go", (1, 1), (1, 1), pfa=1e-3))          # GO/SO are 1-D only
+    with pytest.raises(nat.RadarError):
+        eng.cfar(x, cfar_params("os", (1, 1), (0, 0), rho=0.5, alpha=2.0, os_rank=99))
+    with pytest.raises(nat.RadarError):
+        RadarEngine(4, 257 * 3, 1, 8)                                     # prime factor 257 > 128
+    e = RadarEngine(4, 64, 1, 8)
+    with pytest.raises(ValueError):
+        e.range_doppler(torch.zeros((1, 8, 4, 63, 2), dtype=torch.int16, device="cuda"))
