@@ -143,14 +143,24 @@ double radar_cfar_ca_alpha(int n_train_cells, double pfa);
  *   rd       : float2 [frame][V][S][L] from radar_range_doppler (all V antennas)
  *   dets     : int32 [frame][max_dets][2], counts int32 [frame]
  *   az_idx/el_idx : device int32 antenna lists (n == 0 -> angle 0, as the reference)
- *   points_out : double [frame][max_dets][4] (x, y, z, velocity), FLU frame (fp64 like the reference)
- *   az_bin_out / el_bin_out : int32 [frame][max_dets] argmax bins (for bit-exact checks) or NULL
+ *   offsets  : NULL -> padded output: row of detection i of frame f is f*max_dets + i;
+ *              else int32 [frame+1] from radar_det_offsets -> packed output: row offsets[f] + i
+ *              (frame after frame, np.where order inside a frame - what the NCCL allgather and the
+ *              host download move)
+ *   points_out : double [rows][4] (x, y, z, velocity), FLU frame (fp64 like the reference)
+ *   az_bin_out / el_bin_out : int32 [rows] argmax bins (for bit-exact checks) or NULL
  * Needs radar_ctx_set_axes and radar_ctx_set_angle_bins (n_bins >= num_angle_bins). */
 int radar_point_cloud(radar_ctx* ctx, const void* rd, int n_frames,
                       const int32_t* dets, const int32_t* counts, int max_dets,
                       const int32_t* az_idx, int n_az, const int32_t* el_idx, int n_el,
-                      int shift_az, int shift_el, int num_angle_bins,
+                      int shift_az, int shift_el, int num_angle_bins, const int32_t* offsets,
                       double* points_out, int32_t* az_bin_out, int32_t* el_bin_out, void* stream);
+
+/* Exclusive scan of min(counts[f], max_dets): offsets_out int32 [n_frames+1], offsets_out[n_frames] = total
+ * number of points of the batch (the per-frame list lengths of PointCloudGenerator.process,
+ * processors/point_cloud_generator.py:108-140, laid end to end). */
+int radar_det_offsets(radar_ctx* ctx, const int32_t* counts, int n_frames, int max_dets,
+                      int32_t* offsets_out, void* stream);
 
 /* ---- K3a: range-angle heat map --------------------------------------------------------------- *
  * RangeAngleProcessor.process (processors/range_angle_resp.py:68-122).

@@ -47,7 +47,8 @@ SIGNATURES = {
     "radar_cfar_2d": (_I, [_P, _P, _I, _I, _I, C.POINTER(CfarParams), _P, _P, _P, _P, _I, _P]),
     "radar_cfar_1d_rows": (_I, [_P, _P, _I, _I, _I, C.POINTER(CfarParams), _P, _P, _P, _P, _P, _I, _P]),
     "radar_cfar_ca_alpha": (C.c_double, [_I, C.c_double]),
-    "radar_point_cloud": (_I, [_P, _P, _I, _P, _P, _I, _P, _I, _P, _I, _I, _I, _I, _P, _P, _P, _P]),
+    "radar_point_cloud": (_I, [_P, _P, _I, _P, _P, _I, _P, _I, _P, _I, _I, _I, _I, _P, _P, _P, _P, _P]),
+    "radar_det_offsets": (_I, [_P, _P, _I, _I, _P, _P]),
     "radar_range_angle": (_I, [_P, _P, _I, _I, _I, _P, _I, _I, _I, _P, _P]),
     "radar_dbs": (_I, [_P, _P, _I, _I, _P, _I, _I, _P, _P, _I, _P, _P]),
     "radar_sar_image": (_I, [_P, _P, _I, _I, _P, _P, _I, C.c_double, _I, _I, _P, _P]),

@@ -223,12 +223,19 @@ int radar_cfar_1d_rows(radar_ctx* ctx, const float* maps, int n_maps, int rows, 
 
 int radar_point_cloud(radar_ctx* ctx, const void* rd, int n_frames, const int32_t* dets, const int32_t* counts, int max_dets,
                       const int32_t* az_idx, int n_az, const int32_t* el_idx, int n_el, int shift_az, int shift_el,
-                      int num_angle_bins, double* points_out, int32_t* az_bin_out, int32_t* el_bin_out, void* stream) {
+                      int num_angle_bins, const int32_t* offsets, double* points_out, int32_t* az_bin_out, int32_t* el_bin_out,
+                      void* stream) {
     RB_ENTER(ctx);
     if (!rd || !dets || !counts || !points_out || n_frames < 0) return set_error(ctx, RADAR_E_INVALID, "null pointer or negative frame count");
     if ((n_az > 0 && !az_idx) || (n_el > 0 && !el_idx)) return set_error(ctx, RADAR_E_INVALID, "antenna list missing");
     return launch_point_cloud(ctx, reinterpret_cast<const cf*>(rd), n_frames, dets, counts, max_dets, az_idx, n_az, el_idx, n_el,
-                              shift_az, shift_el, num_angle_bins, points_out, az_bin_out, el_bin_out, (cudaStream_t)stream);
+                              shift_az, shift_el, num_angle_bins, offsets, points_out, az_bin_out, el_bin_out, (cudaStream_t)stream);
+}
+
+int radar_det_offsets(radar_ctx* ctx, const int32_t* counts, int n_frames, int max_dets, int32_t* offsets_out, void* stream) {
+    RB_ENTER(ctx);
+    if (!counts || !offsets_out || n_frames < 0) return set_error(ctx, RADAR_E_INVALID, "null pointer or negative frame count");
+    return launch_det_offsets(ctx, counts, n_frames, max_dets, offsets_out, (cudaStream_t)stream);
 }
 
 int radar_range_angle(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx, const int32_t* ant_list, int n_ant,

@@ -25,6 +25,7 @@ struct PcArgs {
     const double2* tw64;
     const double* range_bins; const double* vel_bins; const double* angle_bins;
     double* points; int32_t* az_bin; int32_t* el_bin;
+    const int32_t* offsets;      // optional exclusive scan of the clamped counts: packed output rows
 };
 
 // argmax_a | sum_j z[j] W_A^{j a'} |,  a' = (a - A/2) mod A when shifted; first maximum wins.
@@ -89,16 +90,17 @@ __global__ void __launch_bounds__(kPcThreads) point_cloud_kernel(const __grid_co
         p.y = rng * cos(el) * sin(az);
         p.z = rng * sin(el);
         p.w = vel;
-        reinterpret_cast<double4*>(a.points)[gw] = p;
-        if (a.az_bin) a.az_bin[gw] = az_i;
-        if (a.el_bin) a.el_bin[gw] = el_i;
+        const long long row = a.offsets ? (long long)a.offsets[frame] + slot : gw;
+        reinterpret_cast<double4*>(a.points)[row] = p;
+        if (a.az_bin) a.az_bin[row] = az_i;
+        if (a.el_bin) a.el_bin[row] = el_i;
     }
 }
 
 int launch_point_cloud(radar_ctx* ctx, const cf* rd, int n_frames, const int32_t* dets, const int32_t* counts,
                        int max_dets, const int32_t* az_idx, int n_az, const int32_t* el_idx, int n_el, int shift_az,
-                       int shift_el, int num_angle_bins, double* points_out, int32_t* az_bin_out, int32_t* el_bin_out,
-                       cudaStream_t st) {
+                       int shift_el, int num_angle_bins, const int32_t* offsets, double* points_out, int32_t* az_bin_out,
+                       int32_t* el_bin_out, cudaStream_t st) {
     if (n_az < 0 || n_el < 0 || n_az > kPcMaxAnt || n_el > kPcMaxAnt)
         return set_error(ctx, RADAR_E_INVALID, "antenna sets must hold 0..%d indices", kPcMaxAnt);
     if (num_angle_bins < 1 || num_angle_bins > 8192 || num_angle_bins < n_az || num_angle_bins < n_el)
@@ -118,10 +120,60 @@ int launch_point_cloud(radar_ctx* ctx, const cf* rd, int n_frames, const int32_t
     a.tw64 = at.tw64;
     a.range_bins = ctx->range_bins; a.vel_bins = ctx->vel_bins; a.angle_bins = ctx->angle_bins;
     a.points = points_out; a.az_bin = az_bin_out; a.el_bin = el_bin_out;
+    a.offsets = offsets;
     const long long warps = (long long)n_frames * max_dets;
     const long long grid = (warps + kPcWarps - 1) / kPcWarps;
     if (grid > 0x7fffffffLL) return set_error(ctx, RADAR_E_INVALID, "too many detection slots in one call");
     point_cloud_kernel<<<(unsigned)grid, kPcThreads, 0, st>>>(a, n_frames);
+    RB_CUDA_OK(ctx, cudaGetLastError());
+    return RADAR_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Exclusive scan of the per-frame detection counts (clamped to max_dets): offsets[f] is the first row of
+// frame f in the packed point list, offsets[n_frames] the total.  One CTA; every thread scans a contiguous
+// chunk of frames, the chunk totals go through a shared-memory block scan.
+// ------------------------------------------------------------------------------------------------
+constexpr int kScanThreads = 1024;
+
+__global__ void __launch_bounds__(kScanThreads) det_offsets_kernel(const int32_t* __restrict__ counts, int n_frames,
+                                                                   int max_dets, int32_t* __restrict__ offsets) {
+    __shared__ int warp_tot[kScanThreads / 32];
+    const int chunk = (n_frames + kScanThreads - 1) / kScanThreads;
+    const int begin = min(threadIdx.x * chunk, n_frames), end = min(begin + chunk, n_frames);
+    int sum = 0;
+    for (int f = begin; f < end; ++f) sum += min(max(counts[f], 0), max_dets);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int incl = sum;
+    for (int s = 1; s < 32; s <<= 1) {
+        const int o = __shfl_up_sync(0xffffffffu, incl, s);
+        if (lane >= s) incl += o;
+    }
+    if (lane == 31) warp_tot[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        int w = warp_tot[lane];
+        for (int s = 1; s < 32; s <<= 1) {
+            const int o = __shfl_up_sync(0xffffffffu, w, s);
+            if (lane >= s) w += o;
+        }
+        warp_tot[lane] = w;
+    }
+    __syncthreads();
+    int run = incl - sum + (warp > 0 ? warp_tot[warp - 1] : 0);
+    for (int f = begin; f < end; ++f) {
+        offsets[f] = run;
+        run += min(max(counts[f], 0), max_dets);
+    }
+    if (threadIdx.x == kScanThreads - 1) offsets[n_frames] = warp_tot[kScanThreads / 32 - 1];
+}
+
+int launch_det_offsets(radar_ctx* ctx, const int32_t* counts, int n_frames, int max_dets, int32_t* offsets_out,
+                       cudaStream_t st) {
+    if (max_dets <= 0) return set_error(ctx, RADAR_E_INVALID, "max_dets must be positive");
+    if ((long long)n_frames * max_dets > 0x7fffffffLL)
+        return set_error(ctx, RADAR_E_INVALID, "n_frames*max_dets overflows the int32 offsets");
+    det_offsets_kernel<<<1, kScanThreads, 0, st>>>(counts, n_frames, max_dets, offsets_out);
     RB_CUDA_OK(ctx, cudaGetLastError());
     return RADAR_OK;
 }

@@ -78,8 +78,10 @@ int launch_cfar_1d_rows(radar_ctx* ctx, const float* maps, int n_maps, int rows,
                         uint8_t* mask_out, int32_t* dets_out, int32_t* count_out, int max_dets, cudaStream_t st);
 int launch_point_cloud(radar_ctx* ctx, const cf* rd, int n_frames, const int32_t* dets, const int32_t* counts,
                        int max_dets, const int32_t* az_idx, int n_az, const int32_t* el_idx, int n_el,
-                       int shift_az, int shift_el, int num_angle_bins, double* points_out, int32_t* az_bin_out,
-                       int32_t* el_bin_out, cudaStream_t st);
+                       int shift_az, int shift_el, int num_angle_bins, const int32_t* offsets, double* points_out,
+                       int32_t* az_bin_out, int32_t* el_bin_out, cudaStream_t st);
+int launch_det_offsets(radar_ctx* ctx, const int32_t* counts, int n_frames, int max_dets, int32_t* offsets_out,
+                       cudaStream_t st);
 int launch_sar_image(radar_ctx* ctx, const cf* aperture, int num_samples, int n_elems, const double* positions,
                      const double* dirs, int n_dirs, double lambda_m, int g_begin, int g_end, cf* out,
                      cudaStream_t st);

@@ -1,0 +1,140 @@
+"""Multi-GPU plumbing: one process per GPU, ``torch.distributed`` (NCCL over NVLink on the GPU box, gloo in
+the CPU tests).  Only the two exchange steps the path really has:
+
+  * streaming frames are sharded by contiguous frame blocks; the variable-length per-rank point clouds are
+    exchanged with a counts all-gather followed by a fixed-capacity all-gather of the packed rows;
+  * SAR / DBS image grids are sharded by voxel (direction) after a broadcast of the aperture cube and the
+    element geometry; the image tiles are all-gathered when every rank wants the full image.
+
+There is no data-path collective inside the kernels: frames and voxels are independent.
+"""
+from __future__ import annotations
+
+import os
+from typing import Callable, List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+
+def init_from_env(backend: Optional[str] = None) -> Tuple[int, int, int]:
+    """Join the process group described by RANK / LOCAL_RANK / WORLD_SIZE / MASTER_* (torchrun).
+    Returns (rank, local_rank, world).  A single process (no WORLD_SIZE or 1) does not create a group."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29531")
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        kw = {}
+        if backend == "nccl":
+            torch.cuda.set_device(local_rank)
+            kw["device_id"] = torch.device("cuda", local_rank)
+        dist.init_process_group(backend=backend, rank=rank, world_size=world, **kw)
+    elif torch.cuda.is_available():
+        torch.cuda.set_device(local_rank)
+    return rank, local_rank, world
+
+
+def world_size() -> int:
+    return dist.get_world_size() if dist.is_initialized() else 1
+
+
+def shard_range(n: int, rank: int, world: int) -> Tuple[int, int]:
+    """Contiguous block [lo, hi) of ``n`` items owned by ``rank``; the first ``n % world`` ranks get one extra.
+    Contiguous so a cross-frame recurrence (the ground detector's altimeter) stays inside a block."""
+    base, extra = divmod(n, world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+# -------------------------------------------------------------------------------------------- streaming frames
+def allgather_point_clouds(points_packed: torch.Tensor, counts: torch.Tensor, total: torch.Tensor, cap_rows: int,
+                           out_points: Optional[torch.Tensor] = None, out_counts: Optional[torch.Tensor] = None,
+                           out_totals: Optional[torch.Tensor] = None):
+    """Exchange the per-rank point clouds of one batch.
+
+    points_packed [>=cap_rows, 4] f64: this rank's packed rows (frame after frame); counts int32 [F_local];
+    total int32 [1] = number of valid rows.  Every rank contributes exactly ``cap_rows`` rows (NCCL has no
+    all-gather-v): rows beyond ``total`` are padding.  Returns (points [W, cap_rows, 4], counts [W, F_local],
+    totals [W]) - all device tensors, no host synchronisation.  The caller checks ``totals.max() <= cap_rows``
+    when it next touches the host (``check_capacity``) and re-gathers with a larger capacity if not.
+    Equal F_local on every rank is required (pad the last block with empty frames otherwise)."""
+    w = world_size()
+    f = counts.shape[0]
+    dev = points_packed.device
+    if out_points is None:
+        out_points = torch.empty((w, cap_rows, 4), dtype=points_packed.dtype, device=dev)
+    if out_counts is None:
+        out_counts = torch.empty((w, f), dtype=counts.dtype, device=dev)
+    if out_totals is None:
+        out_totals = torch.empty((w,), dtype=total.dtype, device=dev)
+    if w == 1:
+        out_points[0].copy_(points_packed[:cap_rows])
+        out_counts[0].copy_(counts)
+        out_totals.copy_(total)
+        return out_points, out_counts, out_totals
+    dist.all_gather_into_tensor(out_counts.view(-1), counts.contiguous())
+    dist.all_gather_into_tensor(out_totals, total.contiguous())
+    dist.all_gather_into_tensor(out_points.view(-1), points_packed[:cap_rows].contiguous().view(-1))
+    return out_points, out_counts, out_totals
+
+
+def check_capacity(totals: torch.Tensor, cap_rows: int) -> int:
+    """Host-side check after a batch: largest per-rank total; raises if the gather truncated a rank."""
+    m = int(totals.max().item())
+    if m > cap_rows:
+        raise RuntimeError(f"a rank produced {m} points but the all-gather capacity is {cap_rows} rows")
+    return m
+
+
+def split_gathered(points: torch.Tensor, counts: torch.Tensor, max_dets: int) -> List:
+    """[W, cap, 4], [W, F] -> list over the global frame order of (N_i, 4) numpy arrays."""
+    pts = points.cpu().numpy()
+    cnt = counts.cpu().numpy().clip(max=max_dets)
+    clouds = []
+    for r in range(cnt.shape[0]):
+        row = 0
+        for c in cnt[r]:
+            clouds.append(pts[r, row:row + int(c)])
+            row += int(c)
+    return clouds
+
+
+# -------------------------------------------------------------------------------------------- SAR / DBS grids
+def sar_image_sharded(compute_slice: Callable[[torch.Tensor, torch.Tensor, torch.Tensor, int, int], torch.Tensor],
+                      aperture: torch.Tensor, positions: torch.Tensor, dirs: torch.Tensor, src: int = 0,
+                      gather: bool = True):
+    """Voxel-sharded synthetic-array image.
+
+    Rank ``src`` holds the aperture cube [S, N] c64 and the geometry [3, N] f64; they are broadcast, every rank
+    computes directions [g_lo, g_hi) with ``compute_slice(aperture, positions, dirs, g_lo, g_hi)`` -> [S, g_hi-g_lo]
+    and, if ``gather``, the tiles are all-gathered into the full [S, G] image on every rank (tiles are padded to
+    the widest shard for the collective)."""
+    w = world_size()
+    rank = dist.get_rank() if dist.is_initialized() else 0
+    if w > 1:
+        dist.broadcast(aperture, src=src)
+        dist.broadcast(positions, src=src)
+    g = dirs.shape[1]
+    lo, hi = shard_range(g, rank, w)
+    tile = compute_slice(aperture, positions, dirs, lo, hi)
+    if not gather or w == 1:
+        return tile, (lo, hi)
+    s = tile.shape[0]
+    widest = shard_range(g, 0, w)[1]
+    pad = torch.zeros((widest, s), dtype=tile.dtype, device=tile.device)
+    pad[:hi - lo] = tile.transpose(0, 1)
+    allt = torch.empty((w, widest, s), dtype=tile.dtype, device=tile.device)
+    # complex tensors travel as their real view (NCCL / gloo have no complex all-gather)
+    if tile.is_complex():
+        dist.all_gather_into_tensor(torch.view_as_real(allt).view(-1), torch.view_as_real(pad).reshape(-1))
+    else:
+        dist.all_gather_into_tensor(allt.view(-1), pad.view(-1))
+    cols = []
+    for r in range(w):
+        rlo, rhi = shard_range(g, r, w)
+        cols.append(allt[r, :rhi - rlo])
+    return torch.cat(cols, dim=0).transpose(0, 1).contiguous(), (lo, hi)

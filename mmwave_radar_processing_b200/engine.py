@@ -173,22 +173,39 @@ class RadarEngine:
                                              _stream_ptr()), self.ctx)
         return dict(noise=noise, mask=mask, dets=dets_out, counts=count_out)
 
+    def det_offsets(self, counts: torch.Tensor, max_dets: int, out=None) -> torch.Tensor:
+        """Exclusive scan of min(counts, max_dets) -> int32 [F+1]; out[F] is the batch's number of points."""
+        f = counts.shape[0]
+        if out is None:
+            out = torch.empty((f + 1,), dtype=torch.int32, device=self.device)
+        nat.check(self.lib.radar_det_offsets(self.ctx, nat.ptr(counts), f, int(max_dets), nat.ptr(out), _stream_ptr()),
+                  self.ctx)
+        return out
+
     def point_cloud(self, rd: torch.Tensor, dets: torch.Tensor, counts: torch.Tensor, az_idx, el_idx,
                     shift_az: bool = True, shift_el: bool = False, num_angle_bins: int = 64,
-                    points_out=None, want_bins: bool = True):
-        """-> (points float64 [F,max_dets,4], az_bin int32 [F,max_dets] | None, el_bin | None)."""
+                    points_out=None, want_bins: bool = True, offsets=None):
+        """-> (points float64, az_bin int32 | None, el_bin | None).
+
+        offsets None: padded layout, points [F,max_dets,4], bins [F,max_dets].
+        offsets int32 [F+1] (``det_offsets``): packed layout, points [rows,4] with rows >= offsets[F]."""
         f, max_dets = dets.shape[0], dets.shape[1]
         if rd.dtype != torch.complex64 or tuple(rd.shape) != (f, self.V, self.S, self.L):
             raise ValueError("rd must be complex64 [F, V, S, L] for all V antennas")
         if points_out is None:
+            if offsets is not None:
+                raise ValueError("packed output needs a caller-sized points_out")
             points_out = torch.zeros((f, max_dets, 4), dtype=torch.float64, device=self.device)
-        az_bin = torch.zeros((f, max_dets), dtype=torch.int32, device=self.device) if want_bins else None
-        el_bin = torch.zeros((f, max_dets), dtype=torch.int32, device=self.device) if want_bins else None
+        rows = points_out.numel() // 4
+        az_bin = torch.zeros((rows,) if offsets is not None else (f, max_dets), dtype=torch.int32,
+                             device=self.device) if want_bins else None
+        el_bin = torch.zeros_like(az_bin) if want_bins else None
         az, el = self._ints(az_idx), self._ints(el_idx)
         nat.check(self.lib.radar_point_cloud(
             self.ctx, nat.ptr(rd), f, nat.ptr(dets), nat.ptr(counts), max_dets,
             nat.ptr(az), len(az_idx), nat.ptr(el), len(el_idx), int(bool(shift_az)), int(bool(shift_el)),
-            int(num_angle_bins), nat.ptr(points_out), nat.ptr(az_bin), nat.ptr(el_bin), _stream_ptr()), self.ctx)
+            int(num_angle_bins), nat.ptr(offsets), nat.ptr(points_out), nat.ptr(az_bin), nat.ptr(el_bin),
+            _stream_ptr()), self.ctx)
         return points_out, az_bin, el_bin
 
     def range_angle(self, adc: torch.Tensor, loop_idx: int = 0, ant_list=None, num_angle_bins: int = 64,

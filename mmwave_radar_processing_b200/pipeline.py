@@ -1,17 +1,24 @@
 """Batched streaming front-end (our extension of the reference API): int16 ADC frames -> point clouds.
 
-``FramePipeline`` chains the three device stages of ``PointCloudGenerator.process`` for a whole batch of
-frames with preallocated buffers:
+``FramePipeline`` chains the device stages of ``PointCloudGenerator.process`` (and, optionally, the
+``RangeAngleProcessor`` heat map) for a whole batch of frames with preallocated buffers:
 
-    radar_range_doppler (K1+K2)  ->  radar_cfar_2d / radar_cfar_1d_rows (K4, K4c)  ->  radar_point_cloud (K3b)
+    radar_range_doppler (K1+K2) -> [radar_range_angle (K3a)] -> radar_cfar_2d (K4, K4c)
+        -> radar_det_offsets (scan) -> radar_point_cloud (K3b, packed rows)
 
 Frames are independent, so a batch is just the leading axis of every buffer and the
 multi-GPU path shards that axis (``distributed.py``).
+
+Two entry points:
+  * ``run(iq_dev)``      - inputs already resident in HBM, everything on the current stream;
+  * ``run_host(iq_host)``- the end-to-end call: pinned host int16 batch in, host point clouds out.  The batch
+    is cut into chunks that ping-pong over two CUDA streams so the H2D copy of chunk i+1 overlaps the kernels
+    of chunk i and the D2H copy of chunk i-1.
 """
 from __future__ import annotations
 
 from dataclasses import dataclass, field
-from typing import Optional, Sequence
+from typing import Callable, List, Optional, Sequence
 
 import numpy as np
 import torch
@@ -50,6 +57,23 @@ class DetectorSpec:
         raise ValueError(f"unknown detector kind {self.kind}")
 
 
+class _Buffers:
+    """Device buffers of one in-flight chunk."""
+
+    def __init__(self, pipe: "FramePipeline", n_frames: int, with_iq: bool):
+        e, dev = pipe.engine, pipe.engine.device
+        self.cap = n_frames
+        self.rd = torch.empty((n_frames, e.V, e.S, e.L), dtype=torch.complex64, device=dev)
+        self.mag = torch.empty((n_frames, e.S, e.L), dtype=torch.float32, device=dev)
+        self.ra = (torch.empty((n_frames, e.S, pipe.ra_angle_bins), dtype=torch.float32, device=dev)
+                   if pipe.with_range_angle else None)
+        self.dets = torch.zeros((n_frames, pipe.max_dets, 2), dtype=torch.int32, device=dev)
+        self.counts = torch.zeros((n_frames,), dtype=torch.int32, device=dev)
+        self.offsets = torch.zeros((n_frames + 1,), dtype=torch.int32, device=dev)
+        self.points = torch.zeros((n_frames * pipe.max_dets, 4), dtype=torch.float64, device=dev)
+        self.iq = (torch.empty((n_frames, e.C, e.R, e.S, 2), dtype=torch.int16, device=dev) if with_iq else None)
+
+
 @dataclass
 class FramePipeline:
     cfg: object
@@ -60,6 +84,10 @@ class FramePipeline:
     shift_el_resp: bool = False
     num_angle_bins: int = 64
     max_dets: int = 256
+    with_range_angle: bool = False          # also produce the RangeAngleProcessor heat map of every frame
+    ra_antennas: Sequence[int] = ()
+    ra_angle_bins: int = 64
+    ra_chirp_idx: int = 0
     device: Optional[object] = None
 
     def __post_init__(self):
@@ -69,49 +97,129 @@ class FramePipeline:
         self.engine.set_axes(rb, vb)
         self.engine.set_angle_bins(ab)
         self._params = self.detector.c_params()
-        self._cap = 0
-        self.launches_per_batch = 3          # rd_fused_kernel, cfar_kernel, point_cloud_kernel
+        self._main: Optional[_Buffers] = None
+        self._chunks: List[_Buffers] = []
+        self._streams: List[torch.cuda.Stream] = []
+        # rd_fused, [range_angle], cfar, det_offsets, point_cloud
+        self.launches_per_batch = 4 + (1 if self.with_range_angle else 0)
 
-    def _ensure(self, n_frames: int):
-        if n_frames <= self._cap:
-            return
-        e, dev = self.engine, self.engine.device
-        self.rd = torch.empty((n_frames, e.V, e.S, e.L), dtype=torch.complex64, device=dev)
-        self.mag = torch.empty((n_frames, e.S, e.L), dtype=torch.float32, device=dev)
-        self.dets = torch.zeros((n_frames, self.max_dets, 2), dtype=torch.int32, device=dev)
-        self.counts = torch.zeros((n_frames,), dtype=torch.int32, device=dev)
-        self.points = torch.zeros((n_frames, self.max_dets, 4), dtype=torch.float64, device=dev)
-        self._cap = n_frames
-
-    def run(self, iq_dev: torch.Tensor):
-        """iq_dev: int16 [F][chirp][rx][sample][2] on the device -> dict of device tensors (views of the
-        pipeline's buffers): points f64 [F,max_dets,4], counts int32 [F], dets int32 [F,max_dets,2]."""
+    # ------------------------------------------------------------------ device-resident path
+    def _stages(self, iq_dev: torch.Tensor, buf: _Buffers, mark: Optional[Callable[[str], None]] = None):
         f = iq_dev.shape[0]
-        self._ensure(f)
         e = self.engine
-        rd, mag = self.rd[:f], self.mag[:f]
+        rd, mag = buf.rd[:f], buf.mag[:f]
         e.range_doppler(iq_dev, want_rd=True, mag_antenna=0, rd_out=rd, mag_out=mag)
-        res = e.cfar(mag, self._params, one_d=False, max_dets=self.max_dets, dets_out=self.dets[:f], count_out=self.counts[:f])
-        pts, _, _ = e.point_cloud(rd, res["dets"], res["counts"], list(self.az_antenna_idxs), list(self.el_antenna_idxs),
+        if mark:
+            mark("range_doppler")
+        ra = None
+        if self.with_range_angle:
+            ra = e.range_angle(iq_dev, loop_idx=self.ra_chirp_idx, ant_list=list(self.ra_antennas) or None,
+                               num_angle_bins=self.ra_angle_bins, out=buf.ra[:f])
+            if mark:
+                mark("range_angle")
+        dets, counts = buf.dets[:f], buf.counts[:f]
+        e.cfar(mag, self._params, one_d=False, max_dets=self.max_dets, dets_out=dets, count_out=counts)
+        if mark:
+            mark("cfar")
+        offsets = e.det_offsets(counts, self.max_dets, out=buf.offsets[:f + 1])
+        pts, _, _ = e.point_cloud(rd, dets, counts, list(self.az_antenna_idxs), list(self.el_antenna_idxs),
                                   shift_az=self.shift_az_resp, shift_el=self.shift_el_resp,
-                                  num_angle_bins=self.num_angle_bins, points_out=self.points[:f], want_bins=False)
-        return dict(points=pts, counts=res["counts"], dets=res["dets"], rd=rd, mag=mag)
+                                  num_angle_bins=self.num_angle_bins, points_out=buf.points, want_bins=False,
+                                  offsets=offsets)
+        if mark:
+            mark("point_cloud")
+        return dict(points=pts, counts=counts, offsets=offsets, dets=dets, rd=rd, mag=mag, ra=ra)
 
-    def run_host(self, iq_host: torch.Tensor, points_host: torch.Tensor, counts_host: torch.Tensor):
-        """End-to-end step: pinned int16 host batch -> device -> pipeline -> pinned host results.
-        Everything is enqueued on the current stream; the caller synchronises."""
+    def run(self, iq_dev: torch.Tensor, mark: Optional[Callable[[str], None]] = None):
+        """iq_dev: int16 [F][chirp][rx][sample][2] on the device -> dict of device tensors (views of the
+        pipeline's buffers): points f64 [F*max_dets,4] packed (frame f owns rows offsets[f]:offsets[f+1]),
+        counts int32 [F], offsets int32 [F+1], dets int32 [F,max_dets,2], rd, mag, ra."""
+        f = iq_dev.shape[0]
+        if self._main is None or self._main.cap < f:
+            self._main = _Buffers(self, f, with_iq=False)
+        return self._stages(iq_dev, self._main, mark)
+
+    # ------------------------------------------------------------------ host (end-to-end) path
+    def host_buffers(self, n_frames: int, points_per_frame: int = 64):
+        """Pinned host staging for ``run_host``: (iq int16, counts int32, offsets int32, points f64)."""
+        e = self.engine
+        iq = torch.empty((n_frames, e.C, e.R, e.S, 2), dtype=torch.int16).pin_memory()
+        counts = torch.zeros((n_frames,), dtype=torch.int32).pin_memory()
+        points = torch.zeros((n_frames * points_per_frame, 4), dtype=torch.float64).pin_memory()
+        return iq, counts, points
+
+    def run_host(self, iq_host: torch.Tensor, counts_host: torch.Tensor, points_host: torch.Tensor,
+                 chunk_frames: int = 512):
+        """End-to-end batch: pinned host int16 frames -> point clouds in pinned host memory.
+
+        ``points_host`` [rows,4] is cut into equal per-chunk regions; a chunk's packed points land at the start
+        of its region.  Returns ``(totals, regions, h2d_bytes, d2h_bytes)`` after synchronising: per-chunk
+        point totals and region starts (rows).  If a chunk produced more points than its region holds the
+        remainder is fetched into a spill tensor (returned in ``self.spill``)."""
         f = iq_host.shape[0]
-        if not hasattr(self, "_iq_dev") or self._iq_dev.shape[0] < f:
-            self._iq_dev = torch.empty(iq_host.shape, dtype=torch.int16, device=self.engine.device)
-        iq_dev = self._iq_dev[:f]
-        iq_dev.copy_(iq_host, non_blocking=True)
-        out = self.run(iq_dev)
-        points_host[:f].copy_(out["points"], non_blocking=True)
-        counts_host[:f].copy_(out["counts"], non_blocking=True)
-        return out
+        n_chunks = (f + chunk_frames - 1) // chunk_frames
+        if len(self._streams) < 2:
+            self._streams = [torch.cuda.Stream(device=self.engine.device) for _ in range(2)]
+        while len(self._chunks) < 2 or self._chunks[0].cap < chunk_frames:
+            self._chunks = [_Buffers(self, chunk_frames, with_iq=True) for _ in range(2)]
+        if getattr(self, "_tot_host", None) is None or self._tot_host.shape[0] < n_chunks:
+            self._tot_host = torch.zeros((n_chunks,), dtype=torch.int32).pin_memory()
+        region = points_host.shape[0] // n_chunks
+        cur = torch.cuda.current_stream()
+        start = torch.cuda.Event()
+        start.record(cur)
+        outs = []
+        h2d = d2h = 0
+        for c in range(n_chunks):
+            st, buf = self._streams[c % 2], self._chunks[c % 2]
+            lo, hi = c * chunk_frames, min(f, (c + 1) * chunk_frames)
+            n = hi - lo
+            with torch.cuda.stream(st):
+                if c < 2:
+                    st.wait_event(start)
+                buf.iq[:n].copy_(iq_host[lo:hi], non_blocking=True)
+                out = self._stages(buf.iq[:n], buf)
+                counts_host[lo:hi].copy_(out["counts"], non_blocking=True)
+                self._tot_host[c:c + 1].copy_(out["offsets"][n:n + 1], non_blocking=True)
+                rows = min(region, n * self.max_dets)
+                points_host[c * region:c * region + rows].copy_(out["points"][:rows], non_blocking=True)
+            h2d += iq_host[lo:hi].numel() * 2
+            d2h += n * 4 + 4 + rows * 32
+            outs.append((out, n))
+        for st in self._streams:
+            cur.wait_stream(st)
+        cur.synchronize()
+        totals = self._tot_host[:n_chunks].tolist()
+        self.spill = {}
+        # only the last two chunks still own their device buffers; an overflowing earlier chunk means the
+        # caller's points_per_frame estimate was too small: report it instead of returning a truncated cloud
+        for c, tot in enumerate(totals):
+            if tot > region:
+                if c >= n_chunks - 2:
+                    self.spill[c] = outs[c][0]["points"][region:tot].cpu()
+                    d2h += (tot - region) * 32
+                else:
+                    raise RuntimeError(f"chunk {c} produced {tot} points but its host region holds {region}; "
+                                       "size points_host with a larger points_per_frame")
+        return totals, [c * region for c in range(n_chunks)], h2d, d2h
 
+    # ------------------------------------------------------------------ host views
     def gather_host(self, out) -> list:
         """List of per-frame (N_i, 4) float64 numpy point clouds (what the reference returns per frame)."""
-        counts = out["counts"].cpu().numpy()
-        pts = out["points"].cpu().numpy()
-        return [pts[i, :min(int(c), self.max_dets)].copy() for i, c in enumerate(counts)]
+        offs = out["offsets"].cpu().numpy()
+        pts = out["points"][:int(offs[-1])].cpu().numpy()
+        return [pts[offs[i]:offs[i + 1]].copy() for i in range(len(offs) - 1)]
+
+    @staticmethod
+    def split_host(points_host, counts_host, totals, regions, chunk_frames, max_dets) -> list:
+        """Per-frame point clouds from ``run_host`` results (numpy views)."""
+        pts = points_host.numpy()
+        cnt = np.minimum(counts_host.numpy(), max_dets)
+        clouds = []
+        for c, (tot, start) in enumerate(zip(totals, regions)):
+            lo = c * chunk_frames
+            row = start
+            for i in range(lo, min(lo + chunk_frames, cnt.shape[0])):
+                clouds.append(pts[row:row + int(cnt[i])])
+                row += int(cnt[i])
+        return clouds

@@ -167,7 +167,7 @@ def cfar_1d(x: np.ndarray, kind: str, num_train: int, num_guard: int, pfa: float
             a = ca_alpha(t, pfa)
         elif kind == "os":
             k = os_rank(rho, 2 * t)
-            est = np.sort(np.concatenate((left, right), axis=1), axis=1)[:, k - 1]
+            est = np.partition(np.concatenate((left, right), axis=1), k - 1, axis=1)[:, k - 1]
             a = alpha
         else:
             raise ValueError(kind)
@@ -201,7 +201,7 @@ def cfar_2d(x: np.ndarray, kind: str, num_train, num_guard, pfa: float = 0.0,
             a = ca_alpha(n_train, pfa)
         elif kind == "os":
             k = os_rank(rho, n_train)
-            est = np.sort(w[..., m], axis=-1)[..., k - 1]
+            est = np.partition(w[..., m], k - 1, axis=-1)[..., k - 1]
             a = alpha
         else:
             raise ValueError(kind)

@@ -322,15 +322,26 @@ def test_batch_properties_full_size(torch_cuda):
     dev = torch.from_numpy(iq[perm]).cuda()
     out = pipe.run(dev)
     counts = out["counts"].cpu().numpy()
-    pts = out["points"].cpu().numpy()
+    offs = out["offsets"].cpu().numpy()
+    assert offs[0] == 0 and np.array_equal(np.diff(offs), np.minimum(counts, 256))
+    clouds = pipe.gather_host(out)
     single = FramePipeline(cm, detector=DetectorSpec("os", (8, 4), (2, 1), rho=0.75, alpha=3.5), max_dets=256)
     ref = single.run(torch.from_numpy(base).cuda())
-    rc, rp = ref["counts"].cpu().numpy(), ref["points"].cpu().numpy()
+    rc, rp = ref["counts"].cpu().numpy(), single.gather_host(ref)
     assert counts.min() > 0
     for i, src in enumerate(perm):
         j = src % 16
         assert counts[i] == rc[j]
-        assert np.array_equal(pts[i, :counts[i]], rp[j, :rc[j]])
+        assert np.array_equal(clouds[i], rp[j])
+    # end-to-end host path (chunks ping-ponging over two streams) returns the same clouds
+    iq_h, cnt_h, pts_h = pipe.host_buffers(iq.shape[0], points_per_frame=int(counts.max()))
+    iq_h.copy_(torch.from_numpy(iq[perm]))
+    totals, regions, h2d, d2h = pipe.run_host(iq_h, cnt_h, pts_h, chunk_frames=96)   # ragged last chunk
+    assert h2d == iq.nbytes and sum(totals) == offs[-1]
+    host_clouds = FramePipeline.split_host(pts_h, cnt_h, totals, regions, 96, 256)
+    assert len(host_clouds) == len(clouds)
+    for a, b in zip(host_clouds, clouds):
+        assert np.array_equal(a, b)
     # linearity: RD(a*x) == a*RD(x) up to fp32 rounding, RD(x+y) == RD(x)+RD(y)
     eng = pipe.engine
     x = torch.from_numpy(base[:2]).cuda()
