@@ -5,7 +5,9 @@
 //   detectors/ca_cfar.py:11-155, detectors/os_cfar.py:11-195, detectors/go_so_cfar.py:11-123.
 //
 // * CA / GO / SO: one thread per cell under test, training sums accumulated in fp64.
-// * OS: one warp per cell under test; every lane keeps its share of the training window in registers
+// * OS, mask only (the streaming path): one thread per cell under test counts the training cells below a per-cell bound
+//   and stops as soon as the decision is fixed (see os_count_cells).
+// * OS with noise estimates requested: one warp per cell under test; every lane keeps its share of the training window in registers
 //   and the exact k-th order statistic is built bit by bit (MSB->LSB) from warp-wide counts
 //   (__reduce_add_sync), which is an exact selection on the fp32 bit patterns (non-negative floats order
 //   like their unsigned encodings).
@@ -85,6 +87,64 @@ __device__ __forceinline__ void os_cells(const CfarArgs& a, const float* map, ui
     }
 }
 
+
+// ---- OS-CFAR decision without the order statistic ---------------------------------------------------------------
+// The detector only needs  x > alpha * v_k  (v_k = k-th smallest training cell).  Rounded multiplication by a positive
+// constant is monotone, so that holds iff at least k training cells c satisfy  alpha*(double)c < (double)x.  For
+// non-negative floats that predicate is a plain threshold  c < T  with T the smallest float for which it fails, found
+// from x/alpha by stepping at most a couple of ulps.  The count needs no selection at all and can stop as soon as the
+// outcome is fixed (count >= k: detection; count + cells still unseen < k: none) - for noise cells that is after about a
+// third of the window.  The mask is identical to the one the exact order statistic produces (tests compare both paths).
+__device__ __forceinline__ float os_compare_bound(float x, double alpha) {
+    const double xd = (double)x;
+    float q = (float)(xd / alpha);
+    if (!(q >= 0.0f)) q = 0.0f;                                   // negative or NaN cell under test: nothing is below it
+    while (q < __int_as_float(0x7f800000) && alpha * (double)q < xd) q = __uint_as_float(__float_as_uint(q) + 1u);
+    while (q > 0.0f) {
+        const float p = __uint_as_float(__float_as_uint(q) - 1u);
+        if (alpha * (double)p < xd) break;
+        q = p;
+    }
+    return q;
+}
+
+__device__ __forceinline__ int count_below(const float* __restrict__ row, int begin, int end, float t) {
+    int n = 0;
+#pragma unroll 4
+    for (int i = begin; i < end; ++i) n += (row[i] < t) ? 1 : 0;
+    return n;
+}
+
+__device__ __forceinline__ void os_count_cells(const CfarArgs& a, const float* map, uint8_t* mask) {
+    const int cr = a.tr + a.gr, cd = a.td + a.gd;
+    const int wr = 2 * cr + 1, wd = 2 * cd + 1;
+    const int nvr = a.rows - 2 * cr, nvd = a.cols - 2 * cd;
+    const int n_cut = nvr * nvd;
+    const int g_lo = a.tr, g_hi = a.tr + 2 * a.gr;                 // window rows crossing the guard band
+    const int seg2 = a.td + 2 * a.gd + 1;
+    for (int c = threadIdx.x; c < n_cut; c += blockDim.x) {
+        const int vr = (int)a.div_vd.div((uint32_t)c);
+        const int vd = c - vr * nvd;
+        const int r = vr + cr;
+        if (a.row_select && !a.row_select[r]) continue;
+        const int cell = r * a.cols + vd + cd;
+        const float t = os_compare_bound(map[cell], a.alpha);
+        const float* row = map + vr * a.cols + vd;                // top-left corner of the window
+        int cnt = 0, unseen = a.n_train;
+        for (int y = 0; y < wr; ++y, row += a.cols) {
+            if (y < g_lo || y > g_hi) {
+                cnt += count_below(row, 0, wd, t);
+                unseen -= wd;
+            } else {
+                cnt += count_below(row, 0, a.td, t) + count_below(row, seg2, wd, t);
+                unseen -= 2 * a.td;
+            }
+            if (cnt >= a.k_rank || cnt + unseen < a.k_rank) break;
+        }
+        mask[cell] = cnt >= a.k_rank ? 1 : 0;
+    }
+}
+
 __global__ void __launch_bounds__(kCfarThreads) cfar_kernel(const __grid_constant__ CfarArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ int warp_counts[kCfarWarps];
@@ -108,7 +168,9 @@ __global__ void __launch_bounds__(kCfarThreads) cfar_kernel(const __grid_constan
     const int cr = a.tr + a.gr, cd = a.td + a.gd;
     const int nvr = a.rows - 2 * cr, nvd = a.cols - 2 * cd;
     if (nvr > 0 && nvd > 0) {      // window larger than the map: no valid cell (reference swallows the ValueError)
-        if (a.kind == RADAR_CFAR_OS) {
+        if (a.kind == RADAR_CFAR_OS && !noise_dst && a.alpha > 0.0) {
+            os_count_cells(la, map, mask);
+        } else if (a.kind == RADAR_CFAR_OS) {
             const int wcells = (2 * cr + 1) * (2 * cd + 1);
             if (wcells <= 32 * 8) os_cells<8>(la, map, mask, noise_dst);
             else if (wcells <= 32 * 16) os_cells<16>(la, map, mask, noise_dst);

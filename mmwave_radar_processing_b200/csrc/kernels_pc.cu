@@ -1,5 +1,5 @@
 // K3b: per-detection zero-padded angle DFT + first-max argmax (azimuth and elevation antenna sets) and the
-// spherical -> cartesian conversion; one warp per detection.
+// spherical -> cartesian conversion; one warp per detection, one CTA per frame.
 //
 // Reference arithmetic reproduced: processors/point_cloud_generator.py:143-248 (gather raw[ant][r][d],
 // zero-pad to num_angle_bins, FFT, optional fftshift, abs, np.argmax (first maximum), angle_bins[idx],
@@ -64,36 +64,40 @@ __device__ __forceinline__ int angle_argmax(const PcArgs& a, const cf* tile, con
     return best_a;
 }
 
+// One CTA per frame (grid-stride); its warps walk the frame's detection list.
 __global__ void __launch_bounds__(kPcThreads) point_cloud_kernel(const __grid_constant__ PcArgs a, int n_frames) {
-    const int lane = threadIdx.x & 31;
-    const long long gw = (long long)blockIdx.x * kPcWarps + (threadIdx.x >> 5);
-    const long long total = (long long)n_frames * a.max_dets;
-    if (gw >= total) return;
-    const int frame = (int)(gw / a.max_dets);
-    const int slot = (int)(gw - (long long)frame * a.max_dets);
-    int n = a.counts[frame];
-    if (n > a.max_dets) n = a.max_dets;
-    if (slot >= n) return;
-    const int r = a.dets[2 * gw], d = a.dets[2 * gw + 1];
-    const cf* tile = a.rd + (long long)frame * a.V * a.S * a.L + (long long)r * a.L + d;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     __shared__ double2 zs_all[kPcWarps][kPcMaxAnt];
-    double2* zs = zs_all[threadIdx.x >> 5];
-    int az_i = 0, el_i = 0;
-    if (a.n_az > 0) az_i = angle_argmax(a, tile, a.az_idx, a.n_az, a.shift_az != 0, lane, zs);
-    if (a.n_el > 0) el_i = angle_argmax(a, tile, a.el_idx, a.n_el, a.shift_el != 0, lane, zs);
-    if (lane == 0) {
-        const double az = a.n_az > 0 ? a.angle_bins[az_i] : 0.0;
-        const double el = a.n_el > 0 ? a.angle_bins[el_i] : 0.0;
-        const double rng = a.range_bins[r], vel = a.vel_bins[d];
-        double4 p;
-        p.x = rng * cos(el) * cos(az);
-        p.y = rng * cos(el) * sin(az);
-        p.z = rng * sin(el);
-        p.w = vel;
-        const long long row = a.offsets ? (long long)a.offsets[frame] + slot : gw;
-        reinterpret_cast<double4*>(a.points)[row] = p;
-        if (a.az_bin) a.az_bin[row] = az_i;
-        if (a.el_bin) a.el_bin[row] = el_i;
+    double2* zs = zs_all[warp];
+    for (int frame = blockIdx.x; frame < n_frames; frame += gridDim.x) {
+        const int n = min(a.counts[frame], a.max_dets);
+        const long long slot0 = (long long)frame * a.max_dets;
+        const long long row0 = a.offsets ? (long long)a.offsets[frame] : slot0;
+        const cf* cube = a.rd + (long long)frame * a.V * a.S * a.L;
+        for (int slot = warp; slot < n; slot += kPcWarps) {
+            const int r = a.dets[2 * (slot0 + slot)], d = a.dets[2 * (slot0 + slot) + 1];
+            const cf* tile = cube + (long long)r * a.L + d;
+            int az_i = 0, el_i = 0;
+            if (a.n_az > 0) az_i = angle_argmax(a, tile, a.az_idx, a.n_az, a.shift_az != 0, lane, zs);
+            if (a.n_el > 0) el_i = angle_argmax(a, tile, a.el_idx, a.n_el, a.shift_el != 0, lane, zs);
+            if (lane == 0) {
+                const double az = a.n_az > 0 ? a.angle_bins[az_i] : 0.0;
+                const double el = a.n_el > 0 ? a.angle_bins[el_i] : 0.0;
+                const double rng = a.range_bins[r], vel = a.vel_bins[d];
+                double sa, ca, se, ce;
+                sincos(az, &sa, &ca);
+                sincos(el, &se, &ce);
+                double4 p;
+                p.x = rng * ce * ca;
+                p.y = rng * ce * sa;
+                p.z = rng * se;
+                p.w = vel;
+                const long long row = row0 + slot;
+                reinterpret_cast<double4*>(a.points)[row] = p;
+                if (a.az_bin) a.az_bin[row] = az_i;
+                if (a.el_bin) a.el_bin[row] = el_i;
+            }
+        }
     }
 }
 
@@ -121,9 +125,7 @@ int launch_point_cloud(radar_ctx* ctx, const cf* rd, int n_frames, const int32_t
     a.range_bins = ctx->range_bins; a.vel_bins = ctx->vel_bins; a.angle_bins = ctx->angle_bins;
     a.points = points_out; a.az_bin = az_bin_out; a.el_bin = el_bin_out;
     a.offsets = offsets;
-    const long long warps = (long long)n_frames * max_dets;
-    const long long grid = (warps + kPcWarps - 1) / kPcWarps;
-    if (grid > 0x7fffffffLL) return set_error(ctx, RADAR_E_INVALID, "too many detection slots in one call");
+    const int grid = n_frames < ctx->sm_count * 64 ? n_frames : ctx->sm_count * 64;
     point_cloud_kernel<<<(unsigned)grid, kPcThreads, 0, st>>>(a, n_frames);
     RB_CUDA_OK(ctx, cudaGetLastError());
     return RADAR_OK;

@@ -135,6 +135,10 @@ def test_cfar2d_and_point_cloud(torch_cuda, name, seed):
         n = int(res["counts"][0])
         dets = res["dets"][0, :n].cpu().numpy()
         assert np.array_equal(dets, orc.mask_to_dets(mask_o))
+        # mask-only call (streaming path: OS-CFAR decides by counting, no order statistic): same mask, same list
+        res2 = eng.cfar(mag, p, want_noise=False, want_mask=True)
+        assert np.array_equal(res2["mask"][0].cpu().numpy().astype(bool), mask_o)
+        assert int(res2["counts"][0]) == n and np.array_equal(res2["dets"][0, :n].cpu().numpy(), dets)
         # (2) against the fp64 reference run: identical except cells within 1e-5 of the threshold
         gthr = g[f"thr2d_{tag}"]
         ref_mask = np.zeros_like(mask)
@@ -355,6 +359,39 @@ def test_batch_properties_full_size(torch_cuda):
     c, _ = eng.range_doppler(s)
     assert rel_l2((a + b).cpu().numpy(), c.cpu().numpy()) < 1e-6
     del x
+
+
+def test_os_cfar_counting_path_ties_and_edges(torch_cuda):
+    """The counting OS-CFAR decision equals the order-statistic decision on maps full of ties, zeros, huge
+    dynamic range and thresholds that land exactly on cell values (alpha a power of two), 1-D and 2-D."""
+    torch = torch_cuda
+    from oracle import radar_oracle as orc
+    from mmwave_radar_processing_b200.engine import cfar_params, utility_engine
+    eng = utility_engine()
+    rng = np.random.default_rng(7)
+    maps = []
+    maps.append(rng.integers(0, 6, (40, 33)).astype(np.float32))                       # heavy ties
+    maps.append((2.0 ** rng.integers(-20, 20, (40, 33))).astype(np.float32))            # powers of two
+    maps.append(rng.exponential(1.0, (40, 33)).astype(np.float32))
+    m = rng.exponential(1.0, (40, 33)).astype(np.float32); m[::3] = 0.0; maps.append(m)  # zero rows
+    m = rng.exponential(1e30, (40, 33)).astype(np.float32); m[5, 5] = np.float32(3e38); maps.append(m)
+    x = torch.from_numpy(np.stack(maps)).cuda()
+    for alpha in (0.5, 1.0, 2.0, 3.5, 1e-3):
+        for rho in (0.01, 0.5, 0.75, 1.0):
+            for (t2, g2) in (((3, 2), (1, 1)), ((8, 4), (2, 1)), ((1, 1), (0, 0))):
+                p = cfar_params("os", t2, g2, rho=rho, alpha=alpha)
+                a = eng.cfar(x, p, want_noise=True, want_mask=True)
+                b = eng.cfar(x, p, want_noise=False, want_mask=True)
+                assert torch.equal(a["mask"], b["mask"]) and torch.equal(a["counts"], b["counts"])
+                for i, mp in enumerate(maps):
+                    _, _, mo = orc.cfar_2d(mp.astype(np.float64), "os", t2, g2, rho=rho, alpha=alpha)
+                    assert np.array_equal(b["mask"][i].cpu().numpy().astype(bool), mo), (alpha, rho, t2, i)
+            p1 = cfar_params("os", 6, 2, rho=rho, alpha=alpha)
+            a = eng.cfar(x, p1, one_d=True, want_noise=True, want_mask=True)
+            b = eng.cfar(x, p1, one_d=True, want_noise=False, want_mask=True)
+            assert torch.equal(a["mask"], b["mask"])
+            _, _, mo = orc.cfar_1d(maps[0][3].astype(np.float64), "os", 6, 2, rho=rho, alpha=alpha)
+            assert np.array_equal(b["mask"][0, 3].cpu().numpy().astype(bool), mo)
 
 
 def test_error_paths(torch_cuda):
