@@ -2,6 +2,7 @@
 // extern "C" entry points declared in include/radar_b200.h.  No torch types cross this boundary.
 #include <cmath>
 #include <cstdarg>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include "radar_internal.h"
@@ -146,6 +147,7 @@ int radar_ctx_create(const radar_shape* shape, int device, radar_ctx** out_ctx) 
     ctx->shape = *shape;
     ctx->V = shape->num_rx * shape->chirps_per_loop;
     ctx->C = shape->chirps_per_loop * shape->num_loops;
+    { const char* g = std::getenv("RADAR_B200_GENERIC"); ctx->force_generic = (g && g[0] == '1') ? 1 : 0; }
     DeviceGuard guard(device);
     int rc = RADAR_OK;
     do {

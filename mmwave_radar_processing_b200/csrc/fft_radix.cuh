@@ -18,12 +18,26 @@ namespace rb {
 typedef float2 cf;
 
 RB_HD cf cmake(float re, float im) { cf r; r.x = re; r.y = im; return r; }
-RB_HD cf cadd(cf a, cf b) { return cmake(a.x + b.x, a.y + b.y); }
-RB_HD cf csub(cf a, cf b) { return cmake(a.x - b.x, a.y - b.y); }
-RB_HD cf cscale(cf a, float s) { return cmake(a.x * s, a.y * s); }
-RB_HD cf cmul(cf a, cf b) { return cmake(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
+#if defined(__CUDA_ARCH__)
+// sm_100a packed fp32 pairs: one FADD2 / FMUL2 / FFMA2 per complex add / real scale / real-coefficient FMA.  They retire the
+// same flops per clock as the scalar forms but take half the issue slots (profiles/ubench_fma_pipe.txt), which is what
+// the issue-bound FFT kernels need; ptxas folds the (s,s) broadcast of a constant coefficient into an immediate.
+typedef unsigned long long pk64;
+__device__ __forceinline__ pk64 pk(cf a) { pk64 r; asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(a.x), "f"(a.y)); return r; }
+__device__ __forceinline__ cf unpk(pk64 v) { cf a; asm("mov.b64 {%0,%1}, %2;" : "=f"(a.x), "=f"(a.y) : "l"(v)); return a; }
+__device__ __forceinline__ cf cadd(cf a, cf b) { pk64 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk(a)), "l"(pk(b))); return unpk(r); }
+__device__ __forceinline__ cf csub(cf a, cf b) { pk64 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk(a)), "l"(pk(b))); return unpk(r); }
+__device__ __forceinline__ cf cscale(cf a, float s) { pk64 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk(a)), "l"(pk(cmake(s, s)))); return unpk(r); }
 // a + s*b (real s)
-RB_HD cf cfma(float s, cf b, cf a) { return cmake(fmaf(s, b.x, a.x), fmaf(s, b.y, a.y)); }
+__device__ __forceinline__ cf cfma(float s, cf b, cf a) { pk64 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(pk(cmake(s, s))), "l"(pk(b)), "l"(pk(a))); return unpk(r); }
+#else
+inline cf cadd(cf a, cf b) { return cmake(a.x + b.x, a.y + b.y); }
+inline cf csub(cf a, cf b) { return cmake(a.x - b.x, a.y - b.y); }
+inline cf cscale(cf a, float s) { return cmake(a.x * s, a.y * s); }
+// a + s*b (real s); fused like the device form so the host self-check rounds identically
+inline cf cfma(float s, cf b, cf a) { return cmake(fmaf(s, b.x, a.x), fmaf(s, b.y, a.y)); }
+#endif
+RB_HD cf cmul(cf a, cf b) { return cmake(a.x * b.x - a.y * b.y, a.x * b.y + a.y * b.x); }
 // multiply by -i : (x + iy)(-i) = y - ix
 RB_HD cf cmul_mi(cf a) { return cmake(a.y, -a.x); }
 // out = m - i*n  and  m + i*n

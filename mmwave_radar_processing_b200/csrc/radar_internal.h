@@ -40,6 +40,7 @@ struct radar_ctx {
     double* vel_bins = nullptr;   int n_vel_bins = 0;
     double* angle_bins = nullptr; int n_angle_bins = 0;
     void* scratch = nullptr; size_t scratch_bytes = 0;
+    int force_generic = 0;                        // RADAR_B200_GENERIC=1: skip the shape-specialised kernels (tests)
     char err[512] = {0};
 };
 
@@ -62,6 +63,8 @@ int get_hann(radar_ctx* ctx, int n, float** out);
 int launch_range_doppler(radar_ctx* ctx, const void* adc, int in_kind, int n_frames,
                          const int32_t* ant_list, int n_ant, const float* ant_weight, int window_flags,
                          cf* rd_out, float* mag_out, int mag_antenna, cudaStream_t st);
+int launch_range_doppler_spec(radar_ctx* ctx, const void* adc, int n_frames, const int32_t* ant_list, int n_ant,
+                              int window_flags, cf* rd_out, float* mag_out, int mag_antenna, cudaStream_t st);
 int launch_range_profile(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx,
                          float* profile_out, cudaStream_t st);
 int launch_range_angle(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx,

@@ -79,6 +79,6 @@ struct SmemArena {
         return r;
     }
 };
-__host__ __device__ inline size_t arena_bytes(size_t count, size_t elem) { return (count * elem + 15) & ~(size_t)15; }
+__host__ __device__ constexpr size_t arena_bytes(size_t count, size_t elem) { return (count * elem + 15) & ~(size_t)15; }
 
 }  // namespace rb
