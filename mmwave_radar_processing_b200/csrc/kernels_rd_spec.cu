@@ -5,13 +5,17 @@
 // transform lengths, their radix splits and the CTA size as template parameters, so every index computation folds
 // into immediates, every loop unrolls and the butterflies run on packed FFMA2/FADD2 (fft_radix.cuh).
 //
-// One CTA per (frame, virtual antenna).  Tile A[s][l] (complex64, odd row pitch) lives in shared memory:
-//   load : int16 I/Q words, lanes along s (coalesced rows of 4*S bytes), exact int->float, Hann(S)*Hann(L), STS
-//   R0   : radix RS1 over s (decimation in frequency, in place), twiddles W_S^(n2*k1); lanes along l
-//   R1   : radix RS2 over s, in place; range bin k = k1 + RS1*k2 ends in row RS2*k1 + k2
-//   D0   : radix RL1 over l, in place, twiddles W_L^(n2*k1); lanes along l inside a row
-//   D1   : radix RL2 over l; results leave the registers straight to global memory at [k][fftshift(d)]
-//          (+ |.| for the CFAR map of one antenna)
+// One CTA per (frame, virtual antenna).  Shared memory holds the raw int16 words of the antenna (raw[l][s], 4 B per
+// sample) and the complex tile A[s][l] (odd row pitch):
+//   load : cp.async of the antenna's L rows (4*S bytes each, 16/8/4-byte pieces by alignment) - no register round trip
+//   R0   : radix RS1 over s straight from the raw words: exact int->float, Hann(S)*Hann(L), butterfly, twiddles
+//          W_S^(n2*k1); lanes along n2 (raw reads contiguous, tile writes at the odd pitch: conflict free)
+//   R1   : radix RS2 over s, in place, lanes along l; range bin k = k1 + RS1*k2 ends in row RS2*k1 + k2
+//   D0   : radix RL1 over l, in place, twiddles W_L^(n2*k1); lanes along the rows (odd pitch: conflict free)
+//   D1   : radix RL2 over l; lanes along the Doppler bins so the results leave the registers straight to global
+//          memory as runs of RL1 consecutive bins at [k][fftshift(d)] (+ |.| for the CFAR map of one antenna)
+// Shared-memory traffic is 56 B per sample (the data path of the SM, not the FMA pipe, is what this kernel fills next
+// to HBM), so the layout work above is about keeping every one of those accesses conflict free.
 // Two-factor splits cover every length <= 256 whose factors have a hand-written butterfly; other shapes use the
 // generic kernel.
 #include "radar_internal.h"
@@ -19,14 +23,23 @@
 
 namespace rb {
 
+// pitch (in 32-bit words) of a raw row: multiple of the copy vector, and congruent to about RS2 modulo the 32 banks so
+// the RS2 consecutive words that the lanes of neighbouring rows read land in different banks
+constexpr int raw_pitch(int S, int RS2, int VEC) {
+    for (int sp = S;; ++sp)
+        if (sp % VEC == 0 && (sp % 32) >= (RS2 % 32) && (sp % 32) <= (RS2 % 32) + 3) return sp;
+}
+
 template <int S_, int L_, int RS1_, int RS2_, int RL1_, int RL2_, int NT_>
 struct RdShape {
     static constexpr int S = S_, L = L_, RS1 = RS1_, RS2 = RS2_, RL1 = RL1_, RL2 = RL2_, NT = NT_;
     static constexpr int Lp = L | 1;
+    static constexpr int VEC = S % 4 == 0 ? 4 : (S % 2 == 0 ? 2 : 1);     // words per cp.async
+    static constexpr int SP = raw_pitch(S, RS2, VEC);
     static_assert(RS1 * RS2 == S && RL1 * RL2 == L, "radix split must multiply to the length");
     static constexpr size_t smem_bytes() {
-        return arena_bytes((size_t)S * Lp, sizeof(cf)) + arena_bytes(S, sizeof(cf)) + arena_bytes(L, sizeof(cf)) +
-               arena_bytes(S, 4) + arena_bytes(L, 4);
+        return arena_bytes((size_t)S * Lp, sizeof(cf)) + arena_bytes((size_t)L * SP, 4) + arena_bytes(S, sizeof(cf)) +
+               arena_bytes(L, sizeof(cf)) + arena_bytes(S, 4) + arena_bytes(L, 4);
     }
 };
 
@@ -59,20 +72,26 @@ __device__ __forceinline__ void dif_task(cf* p, int stride_m, const cf* tw, int 
     for (int k = 0; k < R; ++k) p[k * stride_m] = v[k];
 }
 
+template <int BYTES>
+__device__ __forceinline__ void cp_async(void* smem_dst, const void* gmem_src) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    if constexpr (BYTES == 16) asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gmem_src) : "memory");
+    else asm volatile("cp.async.ca.shared.global [%0], [%1], %2;" ::"r"(d), "l"(gmem_src), "n"(BYTES) : "memory");
+}
+
 template <class C>
 __global__ void __launch_bounds__(C::NT) rd_spec_kernel(const __grid_constant__ RdSpecArgs a) {
-    constexpr int S = C::S, L = C::L, Lp = C::Lp, NT = C::NT;
+    constexpr int S = C::S, L = C::L, Lp = C::Lp, NT = C::NT, SP = C::SP, VEC = C::VEC;
     constexpr int RS1 = C::RS1, RS2 = C::RS2, RL1 = C::RL1, RL2 = C::RL2;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     SmemArena ar(smem_raw);
     cf* tile = ar.take<cf>(S * Lp);
+    uint32_t* raw = ar.take<uint32_t>(L * SP);
     cf* twS = ar.take<cf>(S);
     cf* twL = ar.take<cf>(L);
     float* winS = ar.take<float>(S);
     float* winL = ar.take<float>(L);
     const int tid = threadIdx.x;
-    for (int i = tid; i < S; i += NT) { twS[i] = a.twS[i]; winS[i] = a.winS[i]; }
-    for (int i = tid; i < L; i += NT) { twL[i] = a.twL[i]; winL[i] = a.winL[i]; }
 
     const int frame = blockIdx.x / a.n_out_ant;
     const int vo = blockIdx.x - frame * a.n_out_ant;
@@ -80,49 +99,46 @@ __global__ void __launch_bounds__(C::NT) rd_spec_kernel(const __grid_constant__ 
     const int tx = v / a.R, rx = v - tx * a.R;
     // word index of (loop l, sample s): ((frame*C + l*cpl + tx)*R + rx)*S + s
     const long long row0 = ((long long)frame * (a.cpl * L) + tx) * a.R + rx;
-    const int row_stride = a.cpl * a.R;                 // rows between consecutive loops
+    const long long row_stride_words = (long long)a.cpl * a.R * S;      // between consecutive loops
     const uint32_t* src = a.iq + row0 * S;
-    __syncthreads();
 
-    // ---- load + window ------------------------------------------------------------------------------------------
-    if constexpr (S % 4 == 0) {
-        constexpr int VPR = S / 4;                      // 16-byte vectors per row
+    // ---- raw rows -> shared memory (asynchronous), tables meanwhile ----------------------------------------------
+    {
+        constexpr int VPR = S / VEC;                    // copies per row
         constexpr int NV = VPR * L;
-#pragma unroll 4
         for (int i = tid; i < NV; i += NT) {
             const int l = i / VPR, q = i - l * VPR;
-            const uint4 w = __ldg(reinterpret_cast<const uint4*>(src + (long long)l * row_stride * S) + q);
-            const float4 ws = *reinterpret_cast<const float4*>(winS + 4 * q);
-            const float wl = winL[l];
-            cf* dst = tile + (4 * q) * Lp + l;
-            dst[0] = cscale(iq_word_to_cf(w.x), ws.x * wl);
-            dst[Lp] = cscale(iq_word_to_cf(w.y), ws.y * wl);
-            dst[2 * Lp] = cscale(iq_word_to_cf(w.z), ws.z * wl);
-            dst[3 * Lp] = cscale(iq_word_to_cf(w.w), ws.w * wl);
+            cp_async<4 * VEC>(raw + l * SP + VEC * q, src + l * row_stride_words + VEC * q);
         }
-    } else {
-        constexpr int NW = S * L;
-#pragma unroll 8
-        for (int i = tid; i < NW; i += NT) {
-            const int l = i / S, s = i - l * S;
-            const uint32_t w = __ldg(src + (long long)l * row_stride * S + s);
-            tile[s * Lp + l] = cscale(iq_word_to_cf(w), winS[s] * winL[l]);
-        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
     }
+    for (int i = tid; i < S; i += NT) { twS[i] = a.twS[i]; winS[i] = a.winS[i]; }
+    for (int i = tid; i < L; i += NT) { twL[i] = a.twL[i]; winL[i] = a.winL[i]; }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     __syncthreads();
 
-    // ---- range FFT (axis s, element stride Lp), lanes along l -----------------------------------------------------
+    // ---- range FFT stage 0: raw words -> window -> radix RS1 -> tile; lanes along n2 -------------------------------
     {
         constexpr int T0 = RS2 * L;
-#pragma unroll
         for (int t = tid; t < T0; t += NT) {
-            const int n2 = t / L, l = t - n2 * L;
-            dif_task<RS1, (RS2 > 1)>(tile + n2 * Lp + l, RS2 * Lp, twS, n2);
+            const int l = t / RS2, n2 = t - l * RS2;
+            const uint32_t* rsrc = raw + l * SP + n2;
+            const float wl = winL[l];
+            cf vv[RS1];
+#pragma unroll
+            for (int i = 0; i < RS1; ++i) vv[i] = cscale(iq_word_to_cf(rsrc[RS2 * i]), winS[n2 + RS2 * i] * wl);
+            Dft<RS1>::run(vv);
+            if constexpr (RS2 > 1) {
+#pragma unroll
+                for (int k = 1; k < RS1; ++k) vv[k] = cmul(vv[k], twS[n2 * k]);
+            }
+            cf* dst = tile + n2 * Lp + l;
+#pragma unroll
+            for (int k = 0; k < RS1; ++k) dst[k * RS2 * Lp] = vv[k];
         }
         __syncthreads();
         if constexpr (RS2 > 1) {
             constexpr int T1 = RS1 * L;
-#pragma unroll
             for (int t = tid; t < T1; t += NT) {
                 const int k1 = t / L, l = t - k1 * L;
                 dif_task<RS2, false>(tile + (RS2 * k1) * Lp + l, Lp, twS, 0);
@@ -131,12 +147,12 @@ __global__ void __launch_bounds__(C::NT) rd_spec_kernel(const __grid_constant__ 
         }
     }
 
-    // ---- Doppler FFT (axis l, contiguous inside a row) ------------------------------------------------------------
+    // ---- Doppler FFT (axis l): stage 0 lanes along the rows, last stage lanes along the output bins ------------------------------------------------------------
     if constexpr (RL2 > 1) {
         constexpr int T0 = S * RL2;
 #pragma unroll
         for (int t = tid; t < T0; t += NT) {
-            const int p = t / RL2, n2 = t - p * RL2;
+            const int n2 = t / S, p = t - n2 * S;
             dif_task<RL1, true>(tile + p * Lp + n2, RL2, twL, n2);
         }
         __syncthreads();
@@ -198,6 +214,7 @@ static int launch_spec(radar_ctx* ctx, const RdSpecArgs& a, int n_frames, cudaSt
 // Returns RADAR_OK when a specialised kernel was launched, 1 when the shape has no specialisation (caller falls back).
 int launch_range_doppler_spec(radar_ctx* ctx, const void* adc, int n_frames, const int32_t* ant_list, int n_ant,
                               int window_flags, cf* rd_out, float* mag_out, int mag_antenna, cudaStream_t st) {
+    if (reinterpret_cast<uintptr_t>(adc) % 16 != 0) return 1;      // cp.async pieces assume a 16-byte aligned batch
     RdSpecArgs a;
     a.iq = reinterpret_cast<const uint32_t*>(adc);
     a.R = ctx->shape.num_rx; a.cpl = ctx->shape.chirps_per_loop;
