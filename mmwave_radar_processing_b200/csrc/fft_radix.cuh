@@ -195,20 +195,33 @@ template <> struct Dft<13> : DftOddPrime<13> {};
 
 // ---- composites via in-register Cooley-Tukey ------------------------------------------------
 
-template <> struct Dft<6> {
+// Coprime composites by the prime-factor (Good-Thomas) map: no internal twiddles.  With N = N1*N2,
+// input n = (N2*n1 + N1*n2) mod N and output k = (E1*k1 + E2*k2) mod N where E1 = 1 (mod N1), 0 (mod N2) and
+// E2 = 0 (mod N1), 1 (mod N2); every index is a compile-time constant after unrolling, so the permutations cost nothing.
+constexpr int pfa_inv(int a, int m) { for (int x = 1; x < m; ++x) if ((a * x) % m == 1) return x; return 1; }
+template <int N1, int N2> struct DftPfa {
     RB_HD static void run(cf* v) {
-        const float H = 0.5f, S = 0.86602540378443864676f;
-        cf e[3] = {v[0], v[2], v[4]};
-        cf o[3] = {v[1], v[3], v[5]};
-        Dft<3>::run(e);
-        Dft<3>::run(o);
-        cf o1 = cmul(o[1], cmake(H, -S));     // W6^1
-        cf o2 = cmul(o[2], cmake(-H, -S));    // W6^2
-        v[0] = cadd(e[0], o[0]);  v[3] = csub(e[0], o[0]);
-        v[1] = cadd(e[1], o1);    v[4] = csub(e[1], o1);
-        v[2] = cadd(e[2], o2);    v[5] = csub(e[2], o2);
+        constexpr int N = N1 * N2;
+        constexpr int E1 = N2 * pfa_inv(N2 % N1, N1), E2 = N1 * pfa_inv(N1 % N2, N2);
+        cf a[N2][N1];
+#pragma unroll
+        for (int n2 = 0; n2 < N2; ++n2) {
+#pragma unroll
+            for (int n1 = 0; n1 < N1; ++n1) a[n2][n1] = v[(N2 * n1 + N1 * n2) % N];
+            Dft<N1>::run(a[n2]);
+        }
+#pragma unroll
+        for (int k1 = 0; k1 < N1; ++k1) {
+            cf b[N2];
+#pragma unroll
+            for (int n2 = 0; n2 < N2; ++n2) b[n2] = a[n2][k1];
+            Dft<N2>::run(b);
+#pragma unroll
+            for (int k2 = 0; k2 < N2; ++k2) v[(E1 * k1 + E2 * k2) % N] = b[k2];
+        }
     }
 };
+template <> struct Dft<6> : DftPfa<3, 2> {};
 
 template <> struct Dft<8> {
     RB_HD static void run(cf* v) {
@@ -252,27 +265,12 @@ template <> struct Dft<9> {
     }
 };
 
-template <> struct Dft<10> {
-    RB_HD static void run(cf* v) {
-        const cf W1 = cmake(0.80901699437494742410f, -0.58778525229247312917f);   // W10^1
-        const cf W2 = cmake(0.30901699437494742410f, -0.95105651629515357212f);   // W10^2
-        const cf W3 = cmake(-0.30901699437494742410f, -0.95105651629515357212f);  // W10^3
-        const cf W4 = cmake(-0.80901699437494742410f, -0.58778525229247312917f);  // W10^4
-        cf e[5] = {v[0], v[2], v[4], v[6], v[8]};
-        cf o[5] = {v[1], v[3], v[5], v[7], v[9]};
-        Dft<5>::run(e);
-        Dft<5>::run(o);
-        o[1] = cmul(o[1], W1);
-        o[2] = cmul(o[2], W2);
-        o[3] = cmul(o[3], W3);
-        o[4] = cmul(o[4], W4);
-#pragma unroll
-        for (int k = 0; k < 5; ++k) {
-            v[k] = cadd(e[k], o[k]);
-            v[k + 5] = csub(e[k], o[k]);
-        }
-    }
-};
+template <> struct Dft<10> : DftPfa<5, 2> {};
+template <> struct Dft<12> : DftPfa<3, 4> {};
+template <> struct Dft<14> : DftPfa<7, 2> {};
+template <> struct Dft<15> : DftPfa<5, 3> {};
+template <> struct Dft<20> : DftPfa<5, 4> {};
+template <> struct Dft<30> : DftPfa<5, 6> {};
 
 template <> struct Dft<16> {
     RB_HD static void run(cf* v) {

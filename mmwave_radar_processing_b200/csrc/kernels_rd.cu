@@ -178,7 +178,11 @@ int launch_range_doppler(radar_ctx* ctx, const void* adc, int in_kind, int n_fra
     a.n_out_ant = ant_list ? n_ant : ctx->V;
     if (a.n_out_ant <= 0) return set_error(ctx, RADAR_E_INVALID, "empty antenna list");
     if (mag_out && mag_antenna >= a.n_out_ant) return set_error(ctx, RADAR_E_INVALID, "mag_antenna %d out of range", mag_antenna);
-    if (in_kind == RADAR_IN_IQ16 && !ant_weight && !ctx->force_generic) {
+    if (in_kind == RADAR_IN_IQ16 && !ant_weight && !ant_list && ctx->force_generic == 0) {
+        const int rc = launch_range_doppler_stream(ctx, adc, n_frames, window_flags, rd_out, mag_out, mag_antenna, st);
+        if (rc <= 0) return rc;            // launched (0) or failed (<0); 1 = no streaming instantiation for this shape
+    }
+    if (in_kind == RADAR_IN_IQ16 && !ant_weight && ctx->force_generic != 1) {
         const int rc = launch_range_doppler_spec(ctx, adc, n_frames, ant_list, n_ant, window_flags, rd_out, mag_out, mag_antenna, st);
         if (rc <= 0) return rc;            // launched (0) or failed (<0); 1 = no specialisation for this shape
     }

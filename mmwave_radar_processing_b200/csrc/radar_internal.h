@@ -40,7 +40,8 @@ struct radar_ctx {
     double* vel_bins = nullptr;   int n_vel_bins = 0;
     double* angle_bins = nullptr; int n_angle_bins = 0;
     void* scratch = nullptr; size_t scratch_bytes = 0;
-    int force_generic = 0;                        // RADAR_B200_GENERIC=1: skip the shape-specialised kernels (tests)
+    int force_generic = 0;                        // RADAR_B200_GENERIC=1: generic range-Doppler kernel only, =2: skip the streaming kernel (tests)
+    int stream_variant = 0;                       // RADAR_B200_STREAM_VARIANT: tuning candidate of the streaming kernel
     char err[512] = {0};
 };
 
@@ -65,6 +66,8 @@ int launch_range_doppler(radar_ctx* ctx, const void* adc, int in_kind, int n_fra
                          cf* rd_out, float* mag_out, int mag_antenna, cudaStream_t st);
 int launch_range_doppler_spec(radar_ctx* ctx, const void* adc, int n_frames, const int32_t* ant_list, int n_ant,
                               int window_flags, cf* rd_out, float* mag_out, int mag_antenna, cudaStream_t st);
+int launch_range_doppler_stream(radar_ctx* ctx, const void* adc, int n_frames, int window_flags, cf* rd_out,
+                                float* mag_out, int mag_antenna, cudaStream_t st);
 int launch_range_profile(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx,
                          float* profile_out, cudaStream_t st);
 int launch_range_angle(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx,
