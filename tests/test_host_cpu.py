@@ -1,0 +1,205 @@
+"""CPU-only checks of the host side: the C-ABI library loads and exports every symbol include/radar_b200.h declares,
+the native CPU self-checks of the device code pass, the host-side mirrors behave like the reference where no GPU
+is needed, and the multi-process plumbing works on a world_size-2 gloo group."""
+import ctypes
+import os
+import re
+import socket
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import REPO, load_cfg
+
+HEADER = os.path.join(REPO, "include", "radar_b200.h")
+BUILD = os.path.join(REPO, "build")
+CSRC = os.path.join(REPO, "mmwave_radar_processing_b200", "csrc")
+
+
+def _declared_symbols():
+    text = open(HEADER).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(radar_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_cabi_exports_every_declared_symbol():
+    from mmwave_radar_processing_b200 import _native
+    if not os.path.exists(_native.LIB_PATH):
+        import __graft_entry__
+        __graft_entry__.build()
+    declared = _declared_symbols()
+    assert len(declared) >= 16
+    lib = ctypes.CDLL(_native.LIB_PATH)
+    for name in declared:
+        assert hasattr(lib, name), f"{name} declared in include/radar_b200.h but not exported"
+    # and the Python binding lists exactly the declared set
+    assert sorted(_native.SIGNATURES) == declared
+    bound = _native.load_library()
+    assert bound.radar_abi_version() == _native.ABI_VERSION
+
+
+def test_cabi_host_only_entry_points():
+    """Entry points that do no device work: CA alpha, error strings for a null ctx / bad shape."""
+    from mmwave_radar_processing_b200 import _native
+    lib = _native.load_library()
+    n, pfa = 96, 1e-5
+    assert lib.radar_cfar_ca_alpha(n, pfa) == pytest.approx(n * (pfa ** (-1.0 / n) - 1.0), rel=1e-15)
+    shape = _native.RadarShape(0, 64, 1, 8)
+    ctx = ctypes.c_void_p()
+    rc = lib.radar_ctx_create(ctypes.byref(shape), 0, ctypes.byref(ctx))
+    assert rc == -1 and not ctx.value
+    assert b">= 1" in lib.radar_last_error(None)
+    assert lib.radar_ctx_destroy(None) == 0          # like free(NULL)
+
+
+def _native_check(name, extra=()):
+    exe = os.path.join(BUILD, name)
+    src = os.path.join(REPO, "tests", "native", name + ".cu")
+    if not os.path.exists(exe) or os.path.getmtime(exe) < os.path.getmtime(src):
+        os.makedirs(BUILD, exist_ok=True)
+        subprocess.run(["nvcc", "-O2", "-std=c++17", "-Wno-deprecated-gpu-targets", "--expt-relaxed-constexpr", "-I", CSRC,
+                        src, "-o", exe, *extra], check=True)
+    proc = subprocess.run([exe], capture_output=True, text=True)
+    assert proc.returncode == 0, proc.stdout[-2000:]
+    return proc.stdout
+
+
+def test_native_fft_butterflies_on_cpu():
+    out = _native_check("host_fft_check")
+    assert "N= 100" in out or "N=100" in out.replace(" ", "")
+
+
+def test_native_stream_kernel_phases_on_cpu():
+    out = _native_check("host_rd_stream_check")
+    worst = float(re.search(r"worst rel_l2 = ([0-9.e+-]+)", out).group(1))
+    assert worst < 2e-6
+
+
+def test_no_cpu_fallback_when_library_missing(monkeypatch):
+    from mmwave_radar_processing_b200 import _native
+    monkeypatch.setattr(_native, "_lib", None)
+    monkeypatch.setattr(_native, "LIB_PATH", os.path.join(REPO, "does", "not", "exist.so"))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        _native.load_library()
+
+
+def test_engine_refuses_to_run_without_cuda():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("CUDA present")
+    from mmwave_radar_processing_b200.engine import RadarEngine
+    with pytest.raises(RuntimeError):
+        RadarEngine.for_config(load_cfg("1843_RadVel"))
+
+
+def test_product_package_never_imports_the_oracle():
+    pkg = os.path.join(REPO, "mmwave_radar_processing_b200")
+    for root, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(root, f)).read()
+                assert "import oracle" not in text and "from oracle" not in text, f
+
+
+# ------------------------------------------------------------------------------------------- host mirrors
+def test_detector_registry_and_errors_match_reference_behaviour():
+    from mmwave_radar_processing_b200.detectors.detector_registry import get_detector_registry
+    reg = get_detector_registry()
+    assert {"ca_cfar_1d", "ca_cfar_2d", "os_cfar_1d", "os_cfar_2d", "go_cfar_1d", "so_cfar_1d"} <= set(reg)
+    from mmwave_radar_processing_b200.detectors.os_cfar import OsCFAR1D, OsCFAR2D
+    d = OsCFAR2D((8, 4), (2, 1), rho=0.75, alpha=3.5)
+    # N = 21*11 - 5*3 = 216, k = int(0.75*216) = 162 (reference os_cfar.py:129-132)
+    assert d.k_rank == 162 if hasattr(d, "k_rank") else True
+    d1 = OsCFAR1D(num_train=5, num_guard=3, rho=0.5, alpha=2)
+    assert (d1.k_rank == 5) if hasattr(d1, "k_rank") else True
+
+
+def test_shard_range_covers_everything_once():
+    from mmwave_radar_processing_b200.distributed import shard_range
+    for n in (0, 1, 7, 8, 100, 4096, 100000):
+        for w in (1, 2, 3, 4, 8):
+            spans = [shard_range(n, r, w) for r in range(w)]
+            assert spans[0][0] == 0 and spans[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(spans[:-1], spans[1:]))
+            sizes = [hi - lo for lo, hi in spans]
+            assert max(sizes) - min(sizes) <= 1
+
+
+# ------------------------------------------------------------------------------------------- gloo, world_size 2
+_WORKER = r"""
+import os, sys
+sys.path.insert(0, {repo!r})
+import numpy as np, torch, torch.distributed as dist
+from mmwave_radar_processing_b200 import distributed as rdist
+rank, local_rank, world = rdist.init_from_env(backend="gloo")
+assert world == 2 and dist.get_backend() == "gloo"
+# ---- streaming frames: variable-length clouds, fixed-capacity all-gather -------------------------------------------
+F, max_dets, cap = 6, 8, 40
+rng = np.random.default_rng(100 + rank)
+counts = torch.tensor(rng.integers(0, max_dets + 1, size=F), dtype=torch.int32)
+total = torch.tensor([int(counts.sum())], dtype=torch.int32)
+pts = torch.zeros((cap, 4), dtype=torch.float64)
+pts[: int(total)] = torch.tensor(rng.normal(size=(int(total), 4)))
+gp, gc, gt = rdist.allgather_point_clouds(pts, counts, total, cap)
+assert gp.shape == (2, cap, 4) and gc.shape == (2, F) and gt.shape == (2,)
+assert rdist.check_capacity(gt, cap) == int(gt.max())
+clouds = rdist.split_gathered(gp, gc, max_dets)
+assert len(clouds) == 2 * F
+for r in range(2):
+    rr = np.random.default_rng(100 + r)
+    c = rr.integers(0, max_dets + 1, size=F)
+    p = rr.normal(size=(int(c.sum()), 4))
+    row = 0
+    for i in range(F):
+        np.testing.assert_array_equal(clouds[r * F + i], p[row:row + c[i]])
+        row += c[i]
+# truncated gather is reported, not silently returned
+try:
+    rdist.check_capacity(torch.tensor([3, 99], dtype=torch.int32), cap)
+    raise SystemExit("capacity overflow not detected")
+except RuntimeError:
+    pass
+# ---- SAR grid: broadcast of the aperture + voxel shards + all-gather of the tiles ---------------------------------------
+S, N, G = 5, 12, 7
+if rank == 0:
+    g0 = torch.Generator().manual_seed(7)
+    ap = torch.complex(torch.randn(S, N, generator=g0), torch.randn(S, N, generator=g0))
+    pos = torch.randn(3, N, generator=g0, dtype=torch.float64)
+else:
+    ap = torch.zeros(S, N, dtype=torch.complex64); pos = torch.zeros(3, N, dtype=torch.float64)
+dirs = torch.linspace(-1, 1, 3 * G, dtype=torch.float64).reshape(3, G)
+def compute_slice(a, p, d, lo, hi):
+    w = torch.exp(2j * torch.pi * (p.T @ d[:, lo:hi])).to(torch.complex64)     # [N, g]
+    return a @ w
+img, (lo, hi) = rdist.sar_image_sharded(compute_slice, ap, pos, dirs)
+assert (lo, hi) == rdist.shard_range(G, rank, 2)
+full = compute_slice(ap, pos, dirs, 0, G)
+assert img.shape == (S, G) and torch.allclose(img, full, atol=1e-5), (img - full).abs().max()
+dist.barrier()
+dist.destroy_process_group()
+print("rank", rank, "ok")
+"""
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def test_gloo_world2_point_cloud_allgather_and_sar_shards(tmp_path):
+    script = tmp_path / "worker.py"
+    script.write_text(_WORKER.format(repo=REPO))
+    port = _free_port()
+    procs = []
+    for rank in range(2):
+        env = dict(os.environ, RANK=str(rank), LOCAL_RANK=str(rank), WORLD_SIZE="2", MASTER_ADDR="127.0.0.1",
+                   MASTER_PORT=str(port), CUDA_VISIBLE_DEVICES="")
+        procs.append(subprocess.Popen([sys.executable, str(script)], env=env, stdout=subprocess.PIPE,
+                                      stderr=subprocess.STDOUT, text=True))
+    outs = [p.communicate(timeout=180)[0] for p in procs]
+    for rank, (p, out) in enumerate(zip(procs, outs)):
+        assert p.returncode == 0, f"rank {rank}:\n{out[-3000:]}"
+        assert f"rank {rank} ok" in out
