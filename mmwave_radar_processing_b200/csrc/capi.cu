@@ -176,7 +176,7 @@ int radar_ctx_destroy(radar_ctx* ctx) {
     free_fft_tables(&ctx->fftL);
     for (auto& kv : ctx->hann_by_len) cudaFree(kv.second);
     for (auto& kv : ctx->angle_tabs) { cudaFree(kv.second.tw); cudaFree(kv.second.tw64); }
-    cudaFree(ctx->range_bins); cudaFree(ctx->vel_bins); cudaFree(ctx->angle_bins); cudaFree(ctx->scratch);
+    cudaFree(ctx->range_bins); cudaFree(ctx->vel_bins); cudaFree(ctx->angle_bins); cudaFree(ctx->angle_cos); cudaFree(ctx->angle_sin); cudaFree(ctx->scratch);
     delete ctx;
     return RADAR_OK;
 }
@@ -191,7 +191,14 @@ int radar_ctx_set_axes(radar_ctx* ctx, const double* h_range_bins, int n_range, 
 
 int radar_ctx_set_angle_bins(radar_ctx* ctx, const double* h_angle_bins, int n_bins) {
     RB_ENTER(ctx);
-    return upload_doubles(ctx, h_angle_bins, n_bins, &ctx->angle_bins, &ctx->n_angle_bins);
+    if (int rc = upload_doubles(ctx, h_angle_bins, n_bins, &ctx->angle_bins, &ctx->n_angle_bins)) return rc;
+    // x = r cos(el) cos(az), y = r cos(el) sin(az), z = r sin(el) (point_cloud_generator.py:216-248): the trigonometry of the
+    // bin centres is tabulated once in fp64 on the host instead of per detection on the device
+    std::vector<double> c((size_t)n_bins), s((size_t)n_bins);
+    for (int i = 0; i < n_bins; ++i) { c[(size_t)i] = std::cos(h_angle_bins[i]); s[(size_t)i] = std::sin(h_angle_bins[i]); }
+    int n_tmp = 0;
+    if (int rc = upload_doubles(ctx, c.data(), n_bins, &ctx->angle_cos, &n_tmp)) return rc;
+    return upload_doubles(ctx, s.data(), n_bins, &ctx->angle_sin, &n_tmp);
 }
 
 int radar_range_doppler(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, const int32_t* ant_list, int n_ant,

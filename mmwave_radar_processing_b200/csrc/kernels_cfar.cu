@@ -114,14 +114,28 @@ __device__ __forceinline__ int count_below(const float* __restrict__ row, int be
     for (int i = begin; i < end; ++i) n += (row[i] < t) ? 1 : 0;
     return n;
 }
+// compile-time span: every load is base + immediate and the whole row is in flight at once
+template <int BEGIN, int END>
+__device__ __forceinline__ int count_below_fixed(const float* __restrict__ row, float t) {
+    float v[END - BEGIN > 0 ? END - BEGIN : 1];
+#pragma unroll
+    for (int i = BEGIN; i < END; ++i) v[i - BEGIN] = row[i];
+    int n = 0;
+#pragma unroll
+    for (int i = BEGIN; i < END; ++i) n += (v[i - BEGIN] < t) ? 1 : 0;
+    return n;
+}
 
+// TD, GD > 0: Doppler-axis window compiled in (the common detector settings); TD == 0: run-time widths.
+template <int TD, int GD>
 __device__ __forceinline__ void os_count_cells(const CfarArgs& a, const float* map, uint8_t* mask) {
-    const int cr = a.tr + a.gr, cd = a.td + a.gd;
+    const int td = TD > 0 ? TD : a.td, gd = TD > 0 ? GD : a.gd;
+    const int cr = a.tr + a.gr, cd = td + gd;
     const int wr = 2 * cr + 1, wd = 2 * cd + 1;
     const int nvr = a.rows - 2 * cr, nvd = a.cols - 2 * cd;
     const int n_cut = nvr * nvd;
     const int g_lo = a.tr, g_hi = a.tr + 2 * a.gr;                 // window rows crossing the guard band
-    const int seg2 = a.td + 2 * a.gd + 1;
+    const int seg2 = td + 2 * gd + 1;
     for (int c = threadIdx.x; c < n_cut; c += blockDim.x) {
         const int vr = (int)a.div_vd.div((uint32_t)c);
         const int vd = c - vr * nvd;
@@ -133,11 +147,13 @@ __device__ __forceinline__ void os_count_cells(const CfarArgs& a, const float* m
         int cnt = 0, unseen = a.n_train;
         for (int y = 0; y < wr; ++y, row += a.cols) {
             if (y < g_lo || y > g_hi) {
-                cnt += count_below(row, 0, wd, t);
+                if (TD > 0) cnt += count_below_fixed<0, 2 * (TD + GD) + 1>(row, t);
+                else cnt += count_below(row, 0, wd, t);
                 unseen -= wd;
             } else {
-                cnt += count_below(row, 0, a.td, t) + count_below(row, seg2, wd, t);
-                unseen -= 2 * a.td;
+                if (TD > 0) cnt += count_below_fixed<0, TD>(row, t) + count_below_fixed<TD + 2 * GD + 1, 2 * (TD + GD) + 1>(row, t);
+                else cnt += count_below(row, 0, td, t) + count_below(row, seg2, wd, t);
+                unseen -= 2 * td;
             }
             if (cnt >= a.k_rank || cnt + unseen < a.k_rank) break;
         }
@@ -145,7 +161,17 @@ __device__ __forceinline__ void os_count_cells(const CfarArgs& a, const float* m
     }
 }
 
-__global__ void __launch_bounds__(kCfarThreads) cfar_kernel(const __grid_constant__ CfarArgs a) {
+__device__ __forceinline__ void os_count_dispatch(const CfarArgs& a, const float* map, uint8_t* mask) {
+    // Doppler-axis (train, guard) of the reference's detector settings (tests/verify_processors.py:121-143,
+    // gui_configs/processor_params.yaml:41-88)
+    if (a.td == 4 && a.gd == 1) os_count_cells<4, 1>(a, map, mask);
+    else if (a.td == 5 && a.gd == 2) os_count_cells<5, 2>(a, map, mask);
+    else if (a.td == 5 && a.gd == 3) os_count_cells<5, 3>(a, map, mask);
+    else if (a.td == 12 && a.gd == 4) os_count_cells<12, 4>(a, map, mask);
+    else os_count_cells<0, 0>(a, map, mask);
+}
+
+__global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_constant__ CfarArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ int warp_counts[kCfarWarps];
     const int n_cells = a.rows * a.cols;
@@ -169,7 +195,7 @@ __global__ void __launch_bounds__(kCfarThreads) cfar_kernel(const __grid_constan
     const int nvr = a.rows - 2 * cr, nvd = a.cols - 2 * cd;
     if (nvr > 0 && nvd > 0) {      // window larger than the map: no valid cell (reference swallows the ValueError)
         if (a.kind == RADAR_CFAR_OS && !noise_dst && a.alpha > 0.0) {
-            os_count_cells(la, map, mask);
+            os_count_dispatch(la, map, mask);
         } else if (a.kind == RADAR_CFAR_OS) {
             const int wcells = (2 * cr + 1) * (2 * cd + 1);
             if (wcells <= 32 * 8) os_cells<8>(la, map, mask, noise_dst);

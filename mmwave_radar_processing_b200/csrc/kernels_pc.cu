@@ -14,6 +14,8 @@ namespace rb {
 constexpr int kPcThreads = 128;
 constexpr int kPcWarps = kPcThreads / 32;
 constexpr int kPcMaxAnt = 32;
+constexpr int kPcGather = 2048;      // RD samples staged per chunk of detections (16 KB)
+constexpr int kPcTwMax = 256;        // angle DFT tables up to this length are staged in shared memory
 
 struct PcArgs {
     const cf* rd;
@@ -23,36 +25,31 @@ struct PcArgs {
     const int32_t* el_idx; int n_el;
     int shift_az, shift_el, A;
     const double2* tw64;
-    const double* range_bins; const double* vel_bins; const double* angle_bins;
+    const double* range_bins; const double* vel_bins;
+    const double* angle_cos; const double* angle_sin;     // cos / sin of angle_bins (host fp64, uploaded with the bins)
     double* points; int32_t* az_bin; int32_t* el_bin;
     const int32_t* offsets;      // optional exclusive scan of the clamped counts: packed output rows
 };
 
-// argmax_a | sum_j z[j] W_A^{j a'} |,  a' = (a - A/2) mod A when shifted; first maximum wins.
-// zs: this warp's staging row in shared memory (kPcMaxAnt complex doubles).
-__device__ __forceinline__ int angle_argmax(const PcArgs& a, const cf* tile, const int32_t* ant, int n, bool shift,
-                                            int lane, double2* zs) {
-    __syncwarp();
-    if (lane < n) {
-        const cf z = tile[(long long)ant[lane] * a.S * a.L];
-        zs[lane] = make_double2((double)z.x, (double)z.y);
-    }
-    __syncwarp();
+// argmax_a | sum_j z[j] W_A^{j a'} |,  a' = (a - A/2) mod A when shifted; first maximum wins.  z: this detection's n gathered
+// RD samples (shared memory), tw: W_A^e in fp64.  |.|^2 is compared (sqrt is monotone, so the ordering is the one of |.|).
+__device__ __forceinline__ int angle_argmax(const cf* z, int n, int A, bool shift, int lane, const double2* tw) {
     double best = -1.0;
     int best_a = 0x7fffffff;
-    for (int ao = lane; ao < a.A; ao += 32) {
+    for (int ao = lane; ao < A; ao += 32) {
         int ap = ao;
-        if (shift) { ap = ao - a.A / 2; if (ap < 0) ap += a.A; }
+        if (shift) { ap = ao - A / 2; if (ap < 0) ap += A; }
         double sr = 0.0, si = 0.0;
         int e = 0;
         for (int j = 0; j < n; ++j) {
-            const double2 x = zs[j];
-            const double2 w = a.tw64[e];
-            sr += x.x * w.x - x.y * w.y;
-            si += x.x * w.y + x.y * w.x;
-            e += ap; if (e >= a.A) e -= a.A;
+            const cf xf = z[j];
+            const double xr = (double)xf.x, xi = (double)xf.y;
+            const double2 w = tw[e];
+            sr += xr * w.x - xi * w.y;
+            si += xr * w.y + xi * w.x;
+            e += ap; if (e >= A) e -= A;
         }
-        const double mag = hypot(sr, si);
+        const double mag = sr * sr + si * si;
         if (mag > best) { best = mag; best_a = ao; }      // ascending ao per lane: strict > keeps the first
     }
     // warp argmax, ties -> smaller index (all 32 lanes take part; idle lanes carry best = -1)
@@ -64,38 +61,55 @@ __device__ __forceinline__ int angle_argmax(const PcArgs& a, const cf* tile, con
     return best_a;
 }
 
-// One CTA per frame (grid-stride); its warps walk the frame's detection list.
+// One CTA per frame (grid-stride).  The scattered RD samples of a whole chunk of detections are gathered into shared
+// memory first - every thread issues independent loads, so the chunk pays ONE memory latency instead of one per
+// detection - then the warps walk the chunk, one detection each.
 __global__ void __launch_bounds__(kPcThreads) point_cloud_kernel(const __grid_constant__ PcArgs a, int n_frames) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    __shared__ double2 zs_all[kPcWarps][kPcMaxAnt];
-    double2* zs = zs_all[warp];
+    __shared__ cf zs[kPcGather];
+    __shared__ double2 tw_s[kPcTwMax];
+    const bool tw_in_smem = a.A <= kPcTwMax;
+    if (tw_in_smem)
+        for (int i = threadIdx.x; i < a.A; i += kPcThreads) tw_s[i] = a.tw64[i];
+    const double2* tw = tw_in_smem ? tw_s : a.tw64;
+    const int nant = a.n_az + a.n_el;
+    const int chunk = nant > 0 ? kPcGather / nant : a.max_dets;
+    const long long plane = (long long)a.S * a.L;
     for (int frame = blockIdx.x; frame < n_frames; frame += gridDim.x) {
         const int n = min(a.counts[frame], a.max_dets);
         const long long slot0 = (long long)frame * a.max_dets;
         const long long row0 = a.offsets ? (long long)a.offsets[frame] : slot0;
-        const cf* cube = a.rd + (long long)frame * a.V * a.S * a.L;
-        for (int slot = warp; slot < n; slot += kPcWarps) {
-            const int r = a.dets[2 * (slot0 + slot)], d = a.dets[2 * (slot0 + slot) + 1];
-            const cf* tile = cube + (long long)r * a.L + d;
-            int az_i = 0, el_i = 0;
-            if (a.n_az > 0) az_i = angle_argmax(a, tile, a.az_idx, a.n_az, a.shift_az != 0, lane, zs);
-            if (a.n_el > 0) el_i = angle_argmax(a, tile, a.el_idx, a.n_el, a.shift_el != 0, lane, zs);
-            if (lane == 0) {
-                const double az = a.n_az > 0 ? a.angle_bins[az_i] : 0.0;
-                const double el = a.n_el > 0 ? a.angle_bins[el_i] : 0.0;
-                const double rng = a.range_bins[r], vel = a.vel_bins[d];
-                double sa, ca, se, ce;
-                sincos(az, &sa, &ca);
-                sincos(el, &se, &ce);
-                double4 p;
-                p.x = rng * ce * ca;
-                p.y = rng * ce * sa;
-                p.z = rng * se;
-                p.w = vel;
-                const long long row = row0 + slot;
-                reinterpret_cast<double4*>(a.points)[row] = p;
-                if (a.az_bin) a.az_bin[row] = az_i;
-                if (a.el_bin) a.el_bin[row] = el_i;
+        const cf* cube = a.rd + (long long)frame * a.V * plane;
+        for (int c0 = 0; c0 < n; c0 += chunk) {
+            const int m = min(chunk, n - c0);
+            __syncthreads();                                  // previous chunk consumed (and tw_s written, first time)
+            for (int i = threadIdx.x; i < m * nant; i += kPcThreads) {
+                const int slot = i / nant, j = i - slot * nant;
+                const int2 rdx = reinterpret_cast<const int2*>(a.dets)[slot0 + c0 + slot];
+                const int ant = j < a.n_az ? a.az_idx[j] : a.el_idx[j - a.n_az];
+                zs[i] = __ldg(cube + ant * plane + (long long)rdx.x * a.L + rdx.y);
+            }
+            __syncthreads();
+            for (int slot = warp; slot < m; slot += kPcWarps) {
+                const cf* z = zs + slot * nant;
+                int az_i = 0, el_i = 0;
+                if (a.n_az > 0) az_i = angle_argmax(z, a.n_az, a.A, a.shift_az != 0, lane, tw);
+                if (a.n_el > 0) el_i = angle_argmax(z + a.n_az, a.n_el, a.A, a.shift_el != 0, lane, tw);
+                if (lane == 0) {
+                    const int2 rdx = reinterpret_cast<const int2*>(a.dets)[slot0 + c0 + slot];
+                    const double ca = a.n_az > 0 ? a.angle_cos[az_i] : 1.0, sa = a.n_az > 0 ? a.angle_sin[az_i] : 0.0;
+                    const double ce = a.n_el > 0 ? a.angle_cos[el_i] : 1.0, se = a.n_el > 0 ? a.angle_sin[el_i] : 0.0;
+                    const double rng = a.range_bins[rdx.x], vel = a.vel_bins[rdx.y];
+                    double4 p;
+                    p.x = rng * ce * ca;
+                    p.y = rng * ce * sa;
+                    p.z = rng * se;
+                    p.w = vel;
+                    const long long row = row0 + c0 + slot;
+                    reinterpret_cast<double4*>(a.points)[row] = p;
+                    if (a.az_bin) a.az_bin[row] = az_i;
+                    if (a.el_bin) a.el_bin[row] = el_i;
+                }
             }
         }
     }
@@ -122,7 +136,8 @@ int launch_point_cloud(radar_ctx* ctx, const cf* rd, int n_frames, const int32_t
     a.az_idx = az_idx; a.n_az = n_az; a.el_idx = el_idx; a.n_el = n_el;
     a.shift_az = shift_az; a.shift_el = shift_el; a.A = num_angle_bins;
     a.tw64 = at.tw64;
-    a.range_bins = ctx->range_bins; a.vel_bins = ctx->vel_bins; a.angle_bins = ctx->angle_bins;
+    a.range_bins = ctx->range_bins; a.vel_bins = ctx->vel_bins;
+    a.angle_cos = ctx->angle_cos; a.angle_sin = ctx->angle_sin;
     a.points = points_out; a.az_bin = az_bin_out; a.el_bin = el_bin_out;
     a.offsets = offsets;
     const int grid = n_frames < ctx->sm_count * 64 ? n_frames : ctx->sm_count * 64;

@@ -39,6 +39,7 @@ struct radar_ctx {
     double* range_bins = nullptr; int n_range_bins = 0;
     double* vel_bins = nullptr;   int n_vel_bins = 0;
     double* angle_bins = nullptr; int n_angle_bins = 0;
+    double* angle_cos = nullptr; double* angle_sin = nullptr;   // cos / sin of angle_bins (host fp64)
     void* scratch = nullptr; size_t scratch_bytes = 0;
     int force_generic = 0;                        // RADAR_B200_GENERIC=1: generic range-Doppler kernel only, =2: skip the streaming kernel (tests)
     int stream_variant = 0;                       // RADAR_B200_STREAM_VARIANT: tuning candidate of the streaming kernel
