@@ -31,34 +31,63 @@ struct PcArgs {
     const int32_t* offsets;      // optional exclusive scan of the clamped counts: packed output rows
 };
 
-// argmax_a | sum_j z[j] W_A^{j a'} |,  a' = (a - A/2) mod A when shifted; first maximum wins.  z: this detection's n gathered
-// RD samples (shared memory), tw: W_A^e in fp64.  |.|^2 is compared (sqrt is monotone, so the ordering is the one of |.|).
-__device__ __forceinline__ int angle_argmax(const cf* z, int n, int A, bool shift, int lane, const double2* tw) {
+// argmax_a | sum_j z[j] w^j |, w = W_A^{a'}, a' = (a - A/2) mod A when shifted; first maximum wins.  z: this detection's n
+// gathered RD samples (shared memory), tw: W_A^e in fp64.  The sum is evaluated by Horner's rule in fp64 (one twiddle per
+// bin) and |.|^2 is compared (sqrt is monotone, so the ordering is the one of |.|).  NC > 0: antenna count compiled in, the
+// samples are converted to fp64 once and stay in registers.
+template <int NC>
+__device__ __forceinline__ int angle_argmax(const cf* z, int n_rt, int A, bool shift, int lane, const double2* tw) {
+    const int n = NC > 0 ? NC : n_rt;
+    double zr[NC > 0 ? NC : 1], zi[NC > 0 ? NC : 1];
+    if (NC > 0) {
+#pragma unroll
+        for (int j = 0; j < NC; ++j) { const cf v = z[j]; zr[j] = (double)v.x; zi[j] = (double)v.y; }
+    }
     double best = -1.0;
     int best_a = 0x7fffffff;
     for (int ao = lane; ao < A; ao += 32) {
         int ap = ao;
         if (shift) { ap = ao - A / 2; if (ap < 0) ap += A; }
-        double sr = 0.0, si = 0.0;
-        int e = 0;
-        for (int j = 0; j < n; ++j) {
-            const cf xf = z[j];
-            const double xr = (double)xf.x, xi = (double)xf.y;
-            const double2 w = tw[e];
-            sr += xr * w.x - xi * w.y;
-            si += xr * w.y + xi * w.x;
-            e += ap; if (e >= A) e -= A;
+        const double2 w = tw[ap];
+        double sr, si;
+        if (NC > 0) {
+            sr = zr[NC - 1]; si = zi[NC - 1];
+#pragma unroll
+            for (int j = NC - 2; j >= 0; --j) {
+                const double nr = fma(sr, w.x, fma(-si, w.y, zr[j]));
+                si = fma(sr, w.y, fma(si, w.x, zi[j]));
+                sr = nr;
+            }
+        } else {
+            sr = (double)z[n - 1].x; si = (double)z[n - 1].y;
+            for (int j = n - 2; j >= 0; --j) {
+                const cf v = z[j];
+                const double nr = fma(sr, w.x, fma(-si, w.y, (double)v.x));
+                si = fma(sr, w.y, fma(si, w.x, (double)v.y));
+                sr = nr;
+            }
         }
         const double mag = sr * sr + si * si;
         if (mag > best) { best = mag; best_a = ao; }      // ascending ao per lane: strict > keeps the first
     }
-    // warp argmax, ties -> smaller index (all 32 lanes take part; idle lanes carry best = -1)
-    for (int s = 16; s > 0; s >>= 1) {
-        const double ob = __shfl_xor_sync(0xffffffffu, best, s);
-        const int oa = __shfl_xor_sync(0xffffffffu, best_a, s);
-        if (ob > best || (ob == best && oa < best_a)) { best = ob; best_a = oa; }
+    // warp argmax, ties -> smaller index: non-negative doubles order like their bit patterns, so three warp reductions
+    // (high word, low word, index) replace a shuffle tree on 96-bit keys.  Idle lanes (A < 32) carry -1 -> key 0.
+    const unsigned long long bits = best >= 0.0 ? (unsigned long long)__double_as_longlong(best) : 0ull;
+    const unsigned hi = (unsigned)(bits >> 32), lo = (unsigned)bits;
+    const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
+    const unsigned ml = __reduce_max_sync(0xffffffffu, hi == mh ? lo : 0u);
+    return (int)__reduce_min_sync(0xffffffffu, (hi == mh && lo == ml) ? (unsigned)best_a : 0x7fffffffu);
+}
+
+__device__ __forceinline__ int angle_argmax_any(const cf* z, int n, int A, bool shift, int lane, const double2* tw) {
+    switch (n) {
+        case 1: return angle_argmax<1>(z, n, A, shift, lane, tw);
+        case 2: return angle_argmax<2>(z, n, A, shift, lane, tw);
+        case 3: return angle_argmax<3>(z, n, A, shift, lane, tw);
+        case 4: return angle_argmax<4>(z, n, A, shift, lane, tw);
+        case 8: return angle_argmax<8>(z, n, A, shift, lane, tw);
+        default: return angle_argmax<0>(z, n, A, shift, lane, tw);
     }
-    return best_a;
 }
 
 // One CTA per frame (grid-stride).  The scattered RD samples of a whole chunk of detections are gathered into shared
@@ -93,8 +122,8 @@ __global__ void __launch_bounds__(kPcThreads) point_cloud_kernel(const __grid_co
             for (int slot = warp; slot < m; slot += kPcWarps) {
                 const cf* z = zs + slot * nant;
                 int az_i = 0, el_i = 0;
-                if (a.n_az > 0) az_i = angle_argmax(z, a.n_az, a.A, a.shift_az != 0, lane, tw);
-                if (a.n_el > 0) el_i = angle_argmax(z + a.n_az, a.n_el, a.A, a.shift_el != 0, lane, tw);
+                if (a.n_az > 0) az_i = angle_argmax_any(z, a.n_az, a.A, a.shift_az != 0, lane, tw);
+                if (a.n_el > 0) el_i = angle_argmax_any(z + a.n_az, a.n_el, a.A, a.shift_el != 0, lane, tw);
                 if (lane == 0) {
                     const int2 rdx = reinterpret_cast<const int2*>(a.dets)[slot0 + c0 + slot];
                     const double ca = a.n_az > 0 ? a.angle_cos[az_i] : 1.0, sa = a.n_az > 0 ? a.angle_sin[az_i] : 0.0;

@@ -279,6 +279,44 @@ struct RaArgs {
     FftPlan planS; FastDiv divS, divN, divA;
 };
 
+// Zero-padded angle DFT of one range row + fftshift + magnitude: out[k][ao] = | sum_j row[j] w^j |, w = W_A^((ao - A/2) mod A),
+// evaluated by Horner's rule (one twiddle load per output).  One warp per range bin: the row is read once (broadcast) and
+// kept in registers, lanes run along the angle bin so the stores are coalesced.  NC > 0: antenna count compiled in.
+template <int NC>
+__device__ __forceinline__ void ra_angle_stage(const cf* tile, int Np, const uint16_t* pos, const cf* twA, int S, int A,
+                                               float* dst, int n_rt = 0) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const int N = NC > 0 ? NC : n_rt;
+    for (int k = warp; k < S; k += nw) {
+        const cf* row = tile + pos[k] * Np;
+        cf r[NC > 0 ? NC : 1];
+        if (NC > 0) {
+#pragma unroll
+            for (int j = 0; j < NC; ++j) r[j] = row[j];
+        }
+        float* out = dst + (long long)k * A;
+        for (int ao = lane; ao < A; ao += 32) {
+            int ap = ao - A / 2;                 // fftshift: column ao holds bin (ao - A/2) mod A
+            if (ap < 0) ap += A;
+            const cf w = twA[ap];
+            cf acc;
+            if (NC > 0) {
+                acc = r[NC - 1];
+#pragma unroll
+                for (int j = NC - 2; j >= 0; --j)
+                    acc = cmake(fmaf(acc.x, w.x, fmaf(-acc.y, w.y, r[j].x)), fmaf(acc.x, w.y, fmaf(acc.y, w.x, r[j].y)));
+            } else {
+                acc = row[N - 1];
+                for (int j = N - 2; j >= 0; --j) {
+                    const cf x = row[j];
+                    acc = cmake(fmaf(acc.x, w.x, fmaf(-acc.y, w.y, x.x)), fmaf(acc.x, w.y, fmaf(acc.y, w.x, x.y)));
+                }
+            }
+            out[ao] = sqrtf(acc.x * acc.x + acc.y * acc.y);
+        }
+    }
+}
+
 __global__ void __launch_bounds__(kRdThreads) range_angle_kernel(const __grid_constant__ RaArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int S = a.adc.S, N = a.n_ant, Np = odd_pitch(N), A = a.A;
@@ -304,22 +342,14 @@ __global__ void __launch_bounds__(kRdThreads) range_angle_kernel(const __grid_co
     __syncthreads();
     fft_axis(tile, Np, 1, N, a.divN, a.planS, tw);
     float* dst = a.out + frame * (long long)S * A;
-    const int total = S * A;
-    for (int idx = threadIdx.x; idx < total; idx += blockDim.x) {
-        const int k = (int)a.divA.div((uint32_t)idx);
-        const int ao = idx - k * A;
-        int ap = ao - A / 2;                 // fftshift: column ao holds bin (ao - A/2) mod A
-        if (ap < 0) ap += A;
-        const cf* row = tile + pos[k] * Np;
-        cf acc = row[0];
-        int e = 0;
-        for (int j = 1; j < N; ++j) {
-            e += ap; if (e >= A) e -= A;
-            const cf w = twA[e];
-            acc.x = fmaf(row[j].x, w.x, fmaf(-row[j].y, w.y, acc.x));
-            acc.y = fmaf(row[j].x, w.y, fmaf(row[j].y, w.x, acc.y));
-        }
-        dst[idx] = sqrtf(acc.x * acc.x + acc.y * acc.y);
+    switch (N) {
+        case 1: ra_angle_stage<1>(tile, Np, pos, twA, S, A, dst); break;
+        case 2: ra_angle_stage<2>(tile, Np, pos, twA, S, A, dst); break;
+        case 3: ra_angle_stage<3>(tile, Np, pos, twA, S, A, dst); break;
+        case 4: ra_angle_stage<4>(tile, Np, pos, twA, S, A, dst); break;
+        case 8: ra_angle_stage<8>(tile, Np, pos, twA, S, A, dst); break;
+        case 12: ra_angle_stage<12>(tile, Np, pos, twA, S, A, dst); break;
+        default: ra_angle_stage<0>(tile, Np, pos, twA, S, A, dst, N); break;
     }
 }
 
