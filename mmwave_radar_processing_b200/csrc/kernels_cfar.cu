@@ -36,6 +36,8 @@ struct CfarArgs {
     int32_t* dets_out;
     int32_t* count_out;
     int max_dets;
+    int pitch;            // row pitch of the map in shared memory: == nvd (mod 32) so consecutive cells under test, which run
+                          // across valid rows, read consecutive banks (>= cols)
     FastDiv div_cols, div_vd, div_wd;
 };
 
@@ -55,7 +57,7 @@ __device__ __forceinline__ void os_cells(const CfarArgs& a, const float* map, ui
             const int y = (int)a.div_wd.div((uint32_t)w);
             const int x = w - y * wd;
             const bool guard = (y >= a.tr && y <= a.tr + 2 * a.gr) && (x >= a.td && x <= a.td + 2 * a.gd);
-            if (!guard) off[i] = y * a.cols + x;
+            if (!guard) off[i] = y * a.pitch + x;
         }
     }
     const int n_cut = nvr * nvd;
@@ -64,7 +66,7 @@ __device__ __forceinline__ void os_cells(const CfarArgs& a, const float* map, ui
         const int vd = c - vr * nvd;
         const int r = vr + cr, d = vd + cd;
         if (a.row_select && !a.row_select[r]) continue;
-        const int base = vr * a.cols + vd;      // top-left corner of the window
+        const int base = vr * a.pitch + vd;     // top-left corner of the window
         unsigned vals[MAXV];
 #pragma unroll
         for (int i = 0; i < MAXV; ++i) vals[i] = off[i] >= 0 ? __float_as_uint(map[base + off[i]]) : 0xffffffffu;
@@ -81,7 +83,7 @@ __device__ __forceinline__ void os_cells(const CfarArgs& a, const float* map, ui
         if (lane == 0) {
             const int cell = r * a.cols + d;
             const double noise = (double)__uint_as_float(res);
-            mask[cell] = ((double)map[cell] > a.alpha * noise) ? 1 : 0;
+            mask[cell] = ((double)map[r * a.pitch + d] > a.alpha * noise) ? 1 : 0;
             if (noise_dst) noise_dst[cell] = noise;
         }
     }
@@ -122,7 +124,8 @@ __device__ __forceinline__ int count_below_fixed(const float* __restrict__ row, 
     for (int i = BEGIN; i < END; ++i) v[i - BEGIN] = row[i];
     int n = 0;
 #pragma unroll
-    for (int i = BEGIN; i < END; ++i) n += (v[i - BEGIN] < t) ? 1 : 0;
+    for (int i = BEGIN; i < END; ++i)       // one compare + one predicated add per cell (the compiler's select form takes three)
+        asm("{.reg .pred p; setp.lt.f32 p, %1, %2; @p add.s32 %0, %0, 1;}" : "+r"(n) : "f"(v[i - BEGIN]), "f"(t));
     return n;
 }
 
@@ -142,10 +145,10 @@ __device__ __forceinline__ void os_count_cells(const CfarArgs& a, const float* m
         const int r = vr + cr;
         if (a.row_select && !a.row_select[r]) continue;
         const int cell = r * a.cols + vd + cd;
-        const float t = os_compare_bound(map[cell], a.alpha);
-        const float* row = map + vr * a.cols + vd;                // top-left corner of the window
+        const float* row = map + vr * a.pitch + vd;               // top-left corner of the window
+        const float t = os_compare_bound(row[cr * a.pitch + cd], a.alpha);
         int cnt = 0, unseen = a.n_train;
-        for (int y = 0; y < wr; ++y, row += a.cols) {
+        for (int y = 0; y < wr; ++y, row += a.pitch) {
             if (y < g_lo || y > g_hi) {
                 if (TD > 0) cnt += count_below_fixed<0, 2 * (TD + GD) + 1>(row, t);
                 else cnt += count_below(row, 0, wd, t);
@@ -176,7 +179,7 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
     __shared__ int warp_counts[kCfarWarps];
     const int n_cells = a.rows * a.cols;
     SmemArena ar(smem_raw);
-    float* map = ar.take<float>(n_cells);
+    float* map = ar.take<float>(a.rows * a.pitch);
     uint8_t* mask = ar.take<uint8_t>(n_cells);
     const long long m = blockIdx.x;
     const float* src = a.maps + m * n_cells;
@@ -185,7 +188,7 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
     CfarArgs la = a;
     la.row_select = rsel;
     for (int i = threadIdx.x; i < n_cells; i += blockDim.x) {
-        map[i] = src[i];
+        { const int y = (int)a.div_cols.div((uint32_t)i); map[y * a.pitch + (i - y * a.cols)] = src[i]; }
         mask[i] = 0;
         if (noise_dst) noise_dst[i] = 0.0;
     }
@@ -212,7 +215,7 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
                 if (a.kind == RADAR_CFAR_CA) {
                     double sum = 0.0;
                     for (int y = r - cr; y <= r + cr; ++y) {
-                        const float* row = map + y * a.cols;
+                        const float* row = map + y * a.pitch;
                         const bool inner = (y >= r - a.gr && y <= r + a.gr);
                         if (inner) {
                             for (int x = d - cd; x < d - a.gd; ++x) sum += (double)row[x];
@@ -223,7 +226,7 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
                     }
                     noise = sum / (double)a.n_train;
                 } else {                            // GO / SO: 1-D only (tr == gr == 0)
-                    const float* row = map + r * a.cols;
+                    const float* row = map + r * a.pitch;
                     double left = 0.0, right = 0.0;
                     for (int x = d - cd; x < d - a.gd; ++x) left += (double)row[x];
                     for (int x = d + a.gd + 1; x <= d + cd; ++x) right += (double)row[x];
@@ -232,7 +235,7 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
                     noise = (a.kind == RADAR_CFAR_GO) ? fmax(left, right) : fmin(left, right);
                 }
                 const int cell = r * a.cols + d;
-                mask[cell] = ((double)map[cell] > a.alpha * noise) ? 1 : 0;
+                mask[cell] = ((double)map[r * a.pitch + d] > a.alpha * noise) ? 1 : 0;
                 if (noise_dst) noise_dst[cell] = noise;
             }
         }
@@ -330,7 +333,9 @@ static int launch_cfar(radar_ctx* ctx, const float* maps, int n_maps, int rows, 
     const int nvd = cols - 2 * (a.td + a.gd);
     a.div_vd = make_fastdiv((uint32_t)(nvd > 0 ? nvd : 1));
     const size_t n_cells = (size_t)rows * cols;
-    const size_t smem = arena_bytes(n_cells, 4) + arena_bytes(n_cells, 1);
+    a.pitch = cols;
+    if (nvd > 0) while ((a.pitch - nvd) % 32 != 0) ++a.pitch;
+    const size_t smem = arena_bytes((size_t)rows * a.pitch, 4) + arena_bytes(n_cells, 1);
     if (smem > (size_t)ctx->max_smem_optin)
         return set_error(ctx, RADAR_E_UNSUPPORTED, "CFAR map of %d x %d cells exceeds shared memory", rows, cols);
     RB_CUDA_OK(ctx, cudaFuncSetAttribute(cfar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

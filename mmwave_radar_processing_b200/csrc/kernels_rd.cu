@@ -276,17 +276,28 @@ struct RaArgs {
     const float* winS; const float* winV;     // winV indexed by ORIGINAL antenna (may be all-ones)
     const cf* twS; const uint16_t* posS; const cf* twA;
     float* out;
-    FftPlan planS; FastDiv divS, divN, divA;
+    long long n_frames; int frames_per_pass;
+    FftPlan planS; FastDiv divS, divN, divW;
 };
 
 // Zero-padded angle DFT of one range row + fftshift + magnitude: out[k][ao] = | sum_j row[j] w^j |, w = W_A^((ao - A/2) mod A),
-// evaluated by Horner's rule (one twiddle load per output).  One warp per range bin: the row is read once (broadcast) and
-// kept in registers, lanes run along the angle bin so the stores are coalesced.  NC > 0: antenna count compiled in.
-template <int NC>
+// evaluated by Horner's rule.  One warp per range bin: the row is read once (broadcast) and kept in registers, lanes run
+// along the angle bin so the stores are coalesced.  NC > 0: antenna count compiled in.  NB > 0: A == 32*NB, every lane keeps
+// the NB twiddles of its angle bins in registers for the whole kernel.
+template <int NC, int NB>
 __device__ __forceinline__ void ra_angle_stage(const cf* tile, int Np, const uint16_t* pos, const cf* twA, int S, int A,
                                                float* dst, int n_rt = 0) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
     const int N = NC > 0 ? NC : n_rt;
+    cf wreg[NB > 0 ? NB : 1];
+    if (NB > 0) {
+#pragma unroll
+        for (int b = 0; b < NB; ++b) {
+            int ap = lane + 32 * b - A / 2;          // fftshift: column ao holds bin (ao - A/2) mod A
+            if (ap < 0) ap += A;
+            wreg[b] = twA[ap];
+        }
+    }
     for (int k = warp; k < S; k += nw) {
         const cf* row = tile + pos[k] * Np;
         cf r[NC > 0 ? NC : 1];
@@ -294,11 +305,8 @@ __device__ __forceinline__ void ra_angle_stage(const cf* tile, int Np, const uin
 #pragma unroll
             for (int j = 0; j < NC; ++j) r[j] = row[j];
         }
-        float* out = dst + (long long)k * A;
-        for (int ao = lane; ao < A; ao += 32) {
-            int ap = ao - A / 2;                 // fftshift: column ao holds bin (ao - A/2) mod A
-            if (ap < 0) ap += A;
-            const cf w = twA[ap];
+        float* out = dst + k * A + lane;
+        auto one = [&](cf w) {
             cf acc;
             if (NC > 0) {
                 acc = r[NC - 1];
@@ -312,16 +320,39 @@ __device__ __forceinline__ void ra_angle_stage(const cf* tile, int Np, const uin
                     acc = cmake(fmaf(acc.x, w.x, fmaf(-acc.y, w.y, x.x)), fmaf(acc.x, w.y, fmaf(acc.y, w.x, x.y)));
                 }
             }
-            out[ao] = sqrtf(acc.x * acc.x + acc.y * acc.y);
+            return sqrtf(acc.x * acc.x + acc.y * acc.y);
+        };
+        if (NB > 0) {
+            float m[NB > 0 ? NB : 1];
+#pragma unroll
+            for (int b = 0; b < NB; ++b) m[b] = one(wreg[b]);
+#pragma unroll
+            for (int b = 0; b < NB; ++b) out[32 * b] = m[b];
+        } else {
+            for (int ao = lane; ao < A; ao += 32) {
+                int ap = ao - A / 2;
+                if (ap < 0) ap += A;
+                out[ao - lane] = one(twA[ap]);
+            }
         }
     }
 }
+template <int NC>
+__device__ __forceinline__ void ra_angle_stage_any(const cf* tile, int Np, const uint16_t* pos, const cf* twA, int S, int A,
+                                                   float* dst, int n_rt = 0) {
+    if (A == 64) ra_angle_stage<NC, 2>(tile, Np, pos, twA, S, A, dst, n_rt);
+    else if (A == 128) ra_angle_stage<NC, 4>(tile, Np, pos, twA, S, A, dst, n_rt);
+    else if (A == 32) ra_angle_stage<NC, 1>(tile, Np, pos, twA, S, A, dst, n_rt);
+    else ra_angle_stage<NC, 0>(tile, Np, pos, twA, S, A, dst, n_rt);
+}
 
+// FC frames per CTA pass: the range FFT runs over FC*N columns at once (the generic stage executor puts lanes along the
+// columns, so a single frame's 4 antennas would leave most of the CTA idle) and the tables are staged once per CTA.
 __global__ void __launch_bounds__(kRdThreads) range_angle_kernel(const __grid_constant__ RaArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int S = a.adc.S, N = a.n_ant, Np = odd_pitch(N), A = a.A;
+    const int S = a.adc.S, N = a.n_ant, FC = a.frames_per_pass, W = FC * N, P = odd_pitch(W), A = a.A;
     SmemArena ar(smem_raw);
-    cf* tile = ar.take<cf>(S * Np);
+    cf* tile = ar.take<cf>(S * P);
     cf* tw = ar.take<cf>(S);
     cf* twA = ar.take<cf>(A);
     float* win = ar.take<float>(S);
@@ -330,26 +361,34 @@ __global__ void __launch_bounds__(kRdThreads) range_angle_kernel(const __grid_co
     load_table(twA, a.twA, A);
     load_table(win, a.winS, S);
     load_table(pos, a.posS, S);
+    for (int i = threadIdx.x; i < S * P; i += blockDim.x) tile[i] = cmake(0.f, 0.f);
     __syncthreads();
-    const long long frame = blockIdx.x;
-    for (int idx = threadIdx.x; idx < S * N; idx += blockDim.x) {
-        const int j = (int)a.divS.div((uint32_t)idx);
-        const int s = idx - j * S;
-        const int v = a.ant_list ? a.ant_list[j] : j;
-        const cf x = adc_fetch(a.adc, frame, v, s, a.loop_idx);
-        tile[s * Np + j] = cscale(x, win[s] * a.winV[v]);
-    }
-    __syncthreads();
-    fft_axis(tile, Np, 1, N, a.divN, a.planS, tw);
-    float* dst = a.out + frame * (long long)S * A;
-    switch (N) {
-        case 1: ra_angle_stage<1>(tile, Np, pos, twA, S, A, dst); break;
-        case 2: ra_angle_stage<2>(tile, Np, pos, twA, S, A, dst); break;
-        case 3: ra_angle_stage<3>(tile, Np, pos, twA, S, A, dst); break;
-        case 4: ra_angle_stage<4>(tile, Np, pos, twA, S, A, dst); break;
-        case 8: ra_angle_stage<8>(tile, Np, pos, twA, S, A, dst); break;
-        case 12: ra_angle_stage<12>(tile, Np, pos, twA, S, A, dst); break;
-        default: ra_angle_stage<0>(tile, Np, pos, twA, S, A, dst, N); break;
+    for (long long f0 = (long long)blockIdx.x * FC; f0 < a.n_frames; f0 += (long long)gridDim.x * FC) {
+        const int nf = (int)min((long long)FC, a.n_frames - f0);
+        for (int idx = threadIdx.x; idx < S * N * nf; idx += blockDim.x) {
+            const int c = (int)a.divS.div((uint32_t)idx);          // column = f*N + j
+            const int s = idx - c * S;
+            const int f = (int)a.divN.div((uint32_t)c), j = c - f * N;
+            const int v = a.ant_list ? a.ant_list[j] : j;
+            const cf x = adc_fetch(a.adc, f0 + f, v, s, a.loop_idx);
+            tile[s * P + c] = cscale(x, win[s] * a.winV[v]);
+        }
+        __syncthreads();
+        fft_axis(tile, P, 1, W, a.divW, a.planS, tw);
+        for (int f = 0; f < nf; ++f) {
+            float* dst = a.out + (f0 + f) * (long long)S * A;
+            const cf* t = tile + f * N;
+            switch (N) {
+                case 1: ra_angle_stage_any<1>(t, P, pos, twA, S, A, dst); break;
+                case 2: ra_angle_stage_any<2>(t, P, pos, twA, S, A, dst); break;
+                case 3: ra_angle_stage_any<3>(t, P, pos, twA, S, A, dst); break;
+                case 4: ra_angle_stage_any<4>(t, P, pos, twA, S, A, dst); break;
+                case 8: ra_angle_stage_any<8>(t, P, pos, twA, S, A, dst); break;
+                case 12: ra_angle_stage_any<12>(t, P, pos, twA, S, A, dst); break;
+                default: ra_angle_stage_any<0>(t, P, pos, twA, S, A, dst, N); break;
+            }
+        }
+        __syncthreads();
     }
 }
 
@@ -376,12 +415,20 @@ int launch_range_angle(radar_ctx* ctx, const void* adc, int in_kind, int n_frame
     a.twS = ctx->fftS.tw; a.posS = ctx->fftS.pos; a.twA = at.tw;
     a.out = out;
     a.planS = ctx->fftS.plan;
-    a.divS = make_fastdiv((uint32_t)a.adc.S); a.divN = make_fastdiv((uint32_t)N); a.divA = make_fastdiv((uint32_t)num_angle_bins);
     const int S = a.adc.S;
-    const size_t smem = arena_bytes((size_t)S * (N | 1), sizeof(cf)) + arena_bytes(S, sizeof(cf)) +
+    // frames per pass: up to a warp's worth of FFT columns, tile under 64 KB, and about 3 passes per SM
+    int fc = 32 / N; if (fc < 1) fc = 1; if (fc > 8) fc = 8;
+    while (fc > 1 && (long long)n_frames / fc < (long long)ctx->sm_count * 3) fc >>= 1;     // enough passes to fill the GPU
+    while (fc > 1 && (size_t)S * ((fc * N) | 1) * sizeof(cf) > 64 * 1024) --fc;
+    if (fc > n_frames) fc = n_frames;
+    a.n_frames = n_frames; a.frames_per_pass = fc;
+    a.divS = make_fastdiv((uint32_t)S); a.divN = make_fastdiv((uint32_t)N); a.divW = make_fastdiv((uint32_t)(fc * N));
+    const size_t smem = arena_bytes((size_t)S * ((fc * N) | 1), sizeof(cf)) + arena_bytes(S, sizeof(cf)) +
                         arena_bytes(num_angle_bins, sizeof(cf)) + arena_bytes(S, 4) + arena_bytes(S, 2);
     if (int rc = opt_in_smem(ctx, range_angle_kernel, smem, "range-angle tile")) return rc;
-    range_angle_kernel<<<(unsigned)n_frames, kRdThreads, smem, st>>>(a);
+    const long long passes = ((long long)n_frames + fc - 1) / fc;
+    const long long grid = passes < (long long)ctx->sm_count * 4 ? passes : (long long)ctx->sm_count * 4;
+    range_angle_kernel<<<(unsigned)grid, kRdThreads, smem, st>>>(a);
     RB_CUDA_OK(ctx, cudaGetLastError());
     return RADAR_OK;
 }

@@ -225,7 +225,12 @@ RB_HD void rd_stream_for_rows(int tid, int n_q, F f) {
         if (lane < C::L)
             for (int q = warp; q < n_q; q += C::NW) f(q, lane);
     } else {
-        for (int u = tid; u < n_q * C::L; u += C::NT) { const int q = u / C::L; f(q, u - q * C::L); }
+        // flattened over PADDED rows (pitch Lp, one idle lane per row): consecutive lanes touch consecutive tile elements
+        // even across a row boundary, so no shared-memory access of phase B has a bank conflict
+        for (int u = tid; u < n_q * C::Lp; u += C::NT) {
+            const int q = u / C::Lp, c = u - q * C::Lp;
+            if (c < C::L) f(q, c);
+        }
     }
 }
 
