@@ -41,20 +41,32 @@ __global__ void __launch_bounds__(C::NT, C::MINB) rd_stream_kernel(const __grid_
     unsigned item = blockIdx.x;
     int buf = 0;
     if constexpr (C::DF > 1) {
-        uint32_t w0[C::DL1], w1[C::DL1];
-        if (item < n_items) rd_stream_load_half<C, 0>(tid, rd_stream_item_src<C>(a, item), w0);
+        // Class 0 is loaded at the top of the item, class 1 as soon as class 0 is converted (it lands while class 0 is
+        // transformed); what travels one item ahead is an L2 prefetch, which costs no registers - holding next-item words
+        // across phase B made ptxas spill them right after their load, i.e. wait for them (long-scoreboard stall on an STL).
+        if (item < n_items) {
+            rd_stream_prefetch_half<C, 0>(tid, rd_stream_item_src<C>(a, item));
+            rd_stream_prefetch_half<C, 1>(tid, rd_stream_item_src<C>(a, item));
+        }
         __syncthreads();
         for (; item < n_items; item += gridDim.x) {
             cf* tile = tiles + buf * (C::G * C::TILE);
-            rd_stream_load_half<C, 1>(tid, rd_stream_item_src<C>(a, item), w1);    // lands while class 0 is transformed
-            rd_stream_doppler_half<C, 0>(a, tid, w0, tile, winS_s);
-            rd_stream_doppler_half<C, 1>(a, tid, w1, tile, winS_s);
-            const unsigned next = item + gridDim.x;                                // class 0 of the NEXT item travels during phase B
+            uint32_t w[C::DL1];
+            cf v[C::DL1];
+            const uint32_t* src = rd_stream_item_src<C>(a, item);
+            rd_stream_load_half<C, 0>(tid, src, w);
+            const unsigned next = item + gridDim.x;
             if (next < n_items) {
                 const uint32_t* nsrc = rd_stream_item_src<C>(a, next);
-                rd_stream_load_half<C, 0>(tid, nsrc, w0);
-                rd_stream_prefetch_half<C, 1>(tid, nsrc);                            // class 1 of it is pulled into L2 meanwhile
+                rd_stream_prefetch_half<C, 0>(tid, nsrc);
+                rd_stream_prefetch_half<C, 1>(tid, nsrc);
             }
+            rd_stream_convert_half<C, 0>(a, tid, w, v);
+            asm volatile("" ::: "memory");                  // class 1 is requested only now, into the registers class 0 just freed
+            rd_stream_load_half<C, 1>(tid, src, w);
+            rd_stream_transform_half<C, 0>(tid, v, tile, winS_s);
+            rd_stream_convert_half<C, 1>(a, tid, w, v);
+            rd_stream_transform_half<C, 1>(tid, v, tile, winS_s);
             __syncthreads();
             rd_stream_range_s0_fused<C>(a, tid, tile);
             __syncthreads();

@@ -172,18 +172,28 @@ RB_HD void rd_stream_prefetch_half(int tid, const uint32_t* src) {
 #endif
 }
 template <class C, int H>
-RB_HD void rd_stream_doppler_half(const RdStreamParams<C>& a, int tid, const uint32_t (&w)[C::DL1], cf* tile, const float* winS_s) {
+RB_HD void rd_stream_convert_half(const RdStreamParams<C>& a, int tid, const uint32_t (&w)[C::DL1], cf (&v)[C::DL1]) {
+    if (tid < C::COLS) {
+#pragma unroll
+        for (int n1 = 0; n1 < C::DL1; ++n1) v[n1] = cscale(iq_word(w[n1]), a.winL[(C::DF * n1 + C::DL1 * H) % C::L]);
+    }
+}
+template <class C, int H>
+RB_HD void rd_stream_transform_half(int tid, cf (&v)[C::DL1], cf* tile, const float* winS_s) {
     constexpr int DL1 = C::DL1;
     if (tid < C::COLS) {
-        cf v[DL1];
-#pragma unroll
-        for (int n1 = 0; n1 < DL1; ++n1) v[n1] = cscale(iq_word(w[n1]), a.winL[(C::DF * n1 + DL1 * H) % C::L]);
         Dft<DL1>::run(v);
         const float ws = winS_s[tid % C::S];
         cf* dst = tile + tid * C::Lp + H * DL1;
 #pragma unroll
         for (int k = 0; k < DL1; ++k) dst[k] = cscale(v[k], ws);
     }
+}
+template <class C, int H>
+RB_HD void rd_stream_doppler_half(const RdStreamParams<C>& a, int tid, const uint32_t (&w)[C::DL1], cf* tile, const float* winS_s) {
+    cf v[C::DL1];
+    rd_stream_convert_half<C, H>(a, tid, w, v);
+    rd_stream_transform_half<C, H>(tid, v, tile, winS_s);
 }
 // first range stage with the radix-2 Doppler combine in front: a thread owns partial columns k1 and DL1 + k1 of the rows
 // n2 + RS2*i; DL1 lanes per (antenna, n2) row group, 32/DL1 row groups per warp.
