@@ -2,7 +2,7 @@
 # One GPU-box session: parity tests, bench lines, ncu launch list and a full capture of the top kernel.
 # usage (under gpurun): bash tools/gpu_round.sh <tag> [kernel-regex]
 TAG=${1:-r1}
-KREGEX=${2:-rd_fused}
+KREGEX=${2:-rd_stream}
 OUT=gpurun_out/$TAG
 mkdir -p $OUT
 nvidia-smi --query-gpu=name,clocks.max.sm,clocks.max.mem,power.limit --format=csv > $OUT/gpu.txt
