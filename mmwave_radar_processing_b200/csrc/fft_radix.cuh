@@ -44,6 +44,10 @@ RB_HD cf cmul_mi(cf a) { return cmake(a.y, -a.x); }
 RB_HD cf c_m_minus_i_n(cf m, cf n) { return cmake(m.x + n.y, m.y - n.x); }
 RB_HD cf c_m_plus_i_n(cf m, cf n) { return cmake(m.x - n.y, m.y + n.x); }
 
+// -i*(a - b) = (a.y - b.y, b.x - a.x): the odd parts of the symmetric butterflies are formed already rotated, so the
+// conjugate output pairs m -/+ i*n become one packed add and one packed subtract instead of four scalar adds
+RB_HD cf csub_mi(cf a, cf b) { return cmake(a.y - b.y, b.x - a.x); }
+
 template <int R> struct Dft;
 
 template <> struct Dft<1> { RB_HD static void run(cf*) {} };
@@ -60,11 +64,11 @@ template <> struct Dft<3> {
     RB_HD static void run(cf* v) {
         const float S3 = 0.86602540378443864676f;   // sin(2pi/3)
         cf t = cadd(v[1], v[2]);
-        cf u = cscale(csub(v[1], v[2]), S3);
+        cf u = cscale(csub_mi(v[1], v[2]), S3);       // -i * S3 * (v1 - v2)
         cf m = cfma(-0.5f, t, v[0]);
         v[0] = cadd(v[0], t);
-        v[1] = c_m_minus_i_n(m, u);
-        v[2] = c_m_plus_i_n(m, u);
+        v[1] = cadd(m, u);
+        v[2] = csub(m, u);
     }
 };
 
@@ -86,16 +90,16 @@ template <> struct Dft<5> {
         const float S1 = 0.95105651629515357212f;    // sin(2pi/5)
         const float S2 = 0.58778525229247312917f;    // sin(4pi/5)
         cf t1 = cadd(v[1], v[4]), t2 = cadd(v[2], v[3]);
-        cf u1 = csub(v[1], v[4]), u2 = csub(v[2], v[3]);
+        cf u1 = csub_mi(v[1], v[4]), u2 = csub_mi(v[2], v[3]);      // already multiplied by -i
         cf m1 = cfma(C2, t2, cfma(C1, t1, v[0]));
         cf m2 = cfma(C1, t2, cfma(C2, t1, v[0]));
         cf n1 = cfma(S2, u2, cscale(u1, S1));
         cf n2 = cfma(-S1, u2, cscale(u1, S2));
         v[0] = cadd(v[0], cadd(t1, t2));
-        v[1] = c_m_minus_i_n(m1, n1);
-        v[4] = c_m_plus_i_n(m1, n1);
-        v[2] = c_m_minus_i_n(m2, n2);
-        v[3] = c_m_plus_i_n(m2, n2);
+        v[1] = cadd(m1, n1);
+        v[4] = csub(m1, n1);
+        v[2] = cadd(m2, n2);
+        v[3] = csub(m2, n2);
     }
 };
 
@@ -108,7 +112,7 @@ template <> struct Dft<7> {
         const float S2 = 0.97492791218182360702f;    // sin(4pi/7)
         const float S3 = 0.43388373911755812048f;    // sin(6pi/7)
         cf t1 = cadd(v[1], v[6]), t2 = cadd(v[2], v[5]), t3 = cadd(v[3], v[4]);
-        cf u1 = csub(v[1], v[6]), u2 = csub(v[2], v[5]), u3 = csub(v[3], v[4]);
+        cf u1 = csub_mi(v[1], v[6]), u2 = csub_mi(v[2], v[5]), u3 = csub_mi(v[3], v[4]);   // already multiplied by -i
         // cos(2pi jk/7): k=1: C1 C2 C3 ; k=2: C2 C3 C1 ; k=3: C3 C1 C2
         cf m1 = cfma(C3, t3, cfma(C2, t2, cfma(C1, t1, v[0])));
         cf m2 = cfma(C1, t3, cfma(C3, t2, cfma(C2, t1, v[0])));
@@ -118,12 +122,12 @@ template <> struct Dft<7> {
         cf n2 = cfma(-S1, u3, cfma(-S3, u2, cscale(u1, S2)));
         cf n3 = cfma(S2, u3, cfma(-S1, u2, cscale(u1, S3)));
         v[0] = cadd(v[0], cadd(t1, cadd(t2, t3)));
-        v[1] = c_m_minus_i_n(m1, n1);
-        v[6] = c_m_plus_i_n(m1, n1);
-        v[2] = c_m_minus_i_n(m2, n2);
-        v[5] = c_m_plus_i_n(m2, n2);
-        v[3] = c_m_minus_i_n(m3, n3);
-        v[4] = c_m_plus_i_n(m3, n3);
+        v[1] = cadd(m1, n1);
+        v[6] = csub(m1, n1);
+        v[2] = cadd(m2, n2);
+        v[5] = csub(m2, n2);
+        v[3] = cadd(m3, n3);
+        v[4] = csub(m3, n3);
     }
 };
 
@@ -169,7 +173,7 @@ template <int P> struct DftOddPrime {
 #pragma unroll
         for (int j = 0; j < H; ++j) {
             t[j] = cadd(v[j + 1], v[P - 1 - j]);
-            u[j] = csub(v[j + 1], v[P - 1 - j]);
+            u[j] = csub_mi(v[j + 1], v[P - 1 - j]);      // already multiplied by -i
         }
         cf x0 = v[0];
         cf sum = x0;
@@ -185,8 +189,8 @@ template <int P> struct DftOddPrime {
                 m = cfma(OddPrimeTables<P>::c(idx), t[j - 1], m);
                 n = cfma(OddPrimeTables<P>::s(idx), u[j - 1], n);
             }
-            v[k] = c_m_minus_i_n(m, n);
-            v[P - k] = c_m_plus_i_n(m, n);
+            v[k] = cadd(m, n);
+            v[P - k] = csub(m, n);
         }
     }
 };

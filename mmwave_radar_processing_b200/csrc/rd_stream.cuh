@@ -75,9 +75,9 @@ struct RdStreamParams {
 // u = x + 32768 for the sign-flipped half word, so subtracting 2^23 + 32768 leaves x (every step is exact).
 RB_HD cf iq_word(uint32_t w) {
 #ifdef __CUDA_ARCH__
-    const uint32_t x = w ^ 0x80008000u;
-    const float lo = __uint_as_float((x & 0xffffu) | 0x4B000000u);
-    const float hi = __uint_as_float(__byte_perm(x, 0x4B000000u, 0x7632));
+    // (w & 0xffff) ^ 0x4B008000 flips the sign bit of the low half and sets the exponent in one LOP3 (the fields do not overlap)
+    const float lo = __uint_as_float((w & 0xffffu) ^ 0x4B008000u);
+    const float hi = __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7632) ^ 0x8000u);
     return cadd(cmake(lo, hi), cmake(-8421376.0f, -8421376.0f));
 #else
     return cmake((float)(short)(w & 0xffffu), (float)(short)(w >> 16));
