@@ -110,6 +110,29 @@ int radar_range_doppler(radar_ctx* ctx, const void* adc, int in_kind, int n_fram
 int radar_range_profile(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx,
                         float* profile_out, void* stream);
 
+/* ---- a10b: zoom range profile ------------------------------------------------ *
+ * RangeProcessor.zoom_fft (processors/range_resp.py:59-103): chirp `loop_idx`, Hann(S), then
+ * scipy.signal.ZoomFFT(S, [f0, f1], fs) with m = S points and endpoint=False, i.e.
+ *   X[v][k] = sum_s hann[s] x[v][s] exp(-2 pi i s r_k / range_max_m),  r_k = start + k (stop - start)/S,
+ * |.|, mean over all V antennas.  start_m / stop_m: DEVICE double [n_frames] (one window per frame: the altimeter
+ * centres it on the frame's coarse ground peak).   zoom_out: float [frame][S]; its range axis is
+ * linspace(start, stop, S) as in the reference. */
+int radar_range_zoom(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx,
+                     const double* start_m, const double* stop_m, double range_max_m,
+                     float* zoom_out, void* stream);
+
+/* ---- prominence peak picking ------------------------------------------------ *
+ * RangeProcessor.find_peaks (processors/range_resp.py:105-150): scipy.signal.find_peaks(resp_db,
+ * prominence=prominence_db) (local maxima with plateau midpoints, prominence over the whole signal), keep the peaks
+ * within threshold_db of the strongest, strongest first, at most max_peaks.
+ *   profiles   : float [n_profiles][n]; in_db == 0: linear magnitudes, 20*log10 is taken in fp64 on the device
+ *                (Altimeter._get_coarse_peaks, altimeter.py:69-76); in_db != 0: already in dB
+ *   peak_idx_out: int32 [n_profiles][max_peaks] sample indices, -1 padded;  peak_db_out: double, same shape, or NULL
+ *   count_out  : int32 [n_profiles] or NULL */
+int radar_find_peaks(radar_ctx* ctx, const float* profiles, int n_profiles, int n, int in_db,
+                     double prominence_db, double threshold_db, int max_peaks,
+                     int32_t* peak_idx_out, double* peak_db_out, int32_t* count_out, void* stream);
+
 /* ---- K4: CFAR + ordered compaction ---------------------------------------------------------- *
  * 2-D: BaseCFAR2D.detect with CaCFAR2D / OsCFAR2D (detectors/base.py:208-230, ca_cfar.py:85-155,
  * os_cfar.py:94-195) on n_maps maps float [n_maps][rows][cols].

@@ -44,6 +44,8 @@ SIGNATURES = {
     "radar_ctx_set_angle_bins": (_I, [_P, C.POINTER(C.c_double), _I]),
     "radar_range_doppler": (_I, [_P, _P, _I, _I, _P, _I, _I, _P, _P, _I, _P]),
     "radar_range_profile": (_I, [_P, _P, _I, _I, _I, _P, _P]),
+    "radar_range_zoom": (_I, [_P, _P, _I, _I, _I, _P, _P, C.c_double, _P, _P]),
+    "radar_find_peaks": (_I, [_P, _P, _I, _I, _I, C.c_double, C.c_double, _I, _P, _P, _P, _P]),
     "radar_cfar_2d": (_I, [_P, _P, _I, _I, _I, C.POINTER(CfarParams), _P, _P, _P, _P, _I, _P]),
     "radar_cfar_1d_rows": (_I, [_P, _P, _I, _I, _I, C.POINTER(CfarParams), _P, _P, _P, _P, _P, _I, _P]),
     "radar_cfar_ca_alpha": (C.c_double, [_I, C.c_double]),

@@ -216,6 +216,22 @@ int radar_range_profile(radar_ctx* ctx, const void* adc, int in_kind, int n_fram
     return launch_range_profile(ctx, adc, in_kind, n_frames, loop_idx, profile_out, (cudaStream_t)stream);
 }
 
+int radar_range_zoom(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx, const double* start_m,
+                     const double* stop_m, double range_max_m, float* zoom_out, void* stream) {
+    RB_ENTER(ctx);
+    if (n_frames > 0 && (!adc || !start_m || !stop_m || !zoom_out)) return set_error(ctx, RADAR_E_INVALID, "null pointer");
+    return launch_range_zoom(ctx, adc, in_kind, n_frames, loop_idx, start_m, stop_m, range_max_m, zoom_out, (cudaStream_t)stream);
+}
+
+int radar_find_peaks(radar_ctx* ctx, const float* profiles, int n_profiles, int n, int in_db, double prominence_db,
+                     double threshold_db, int max_peaks, int32_t* peak_idx_out, double* peak_db_out, int32_t* count_out,
+                     void* stream) {
+    RB_ENTER(ctx);
+    if (n_profiles > 0 && !profiles) return set_error(ctx, RADAR_E_INVALID, "null profiles");
+    return launch_find_peaks(ctx, profiles, n_profiles, n, in_db, prominence_db, threshold_db, max_peaks, peak_idx_out,
+                             peak_db_out, count_out, (cudaStream_t)stream);
+}
+
 int radar_cfar_2d(radar_ctx* ctx, const float* maps, int n_maps, int rows, int cols, const radar_cfar_params* params,
                   double* noise_out, uint8_t* mask_out, int32_t* dets_out, int32_t* count_out, int max_dets, void* stream) {
     RB_ENTER(ctx);

@@ -71,6 +71,11 @@ int launch_range_doppler_stream(radar_ctx* ctx, const void* adc, int n_frames, i
                                 float* mag_out, int mag_antenna, cudaStream_t st);
 int launch_range_profile(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx,
                          float* profile_out, cudaStream_t st);
+int launch_range_zoom(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx, const double* start_m,
+                      const double* stop_m, double range_max_m, float* out, cudaStream_t st);
+int launch_find_peaks(radar_ctx* ctx, const float* profiles, int n_profiles, int n, int in_db, double prominence,
+                      double threshold_db, int max_peaks, int32_t* idx_out, double* db_out, int32_t* count_out,
+                      cudaStream_t st);
 int launch_range_angle(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx,
                        const int32_t* ant_list, int n_ant, int num_angle_bins, int window_flags,
                        float* out, cudaStream_t st);

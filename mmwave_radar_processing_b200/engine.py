@@ -146,6 +146,44 @@ class RadarEngine:
                                                _stream_ptr()), self.ctx)
         return out
 
+    def range_zoom(self, adc: torch.Tensor, start_m, stop_m, range_max_m: float, loop_idx: int = 0, out=None) -> torch.Tensor:
+        """Zoom range profile of every frame (RangeProcessor.zoom_fft): float32 [F, S].  start_m / stop_m: scalars or
+        per-frame sequences / device float64 tensors."""
+        kind = self._in_kind(adc)
+        f = adc.shape[0]
+
+        def per_frame(v):
+            if isinstance(v, torch.Tensor):
+                t = v.to(device=self.device, dtype=torch.float64).reshape(-1)
+            else:
+                t = torch.as_tensor(v, dtype=torch.float64).reshape(-1).to(self.device)
+            if t.numel() == 1:
+                t = t.expand(f)
+            if t.numel() != f:
+                raise ValueError(f"zoom window must hold 1 or {f} values, got {t.numel()}")
+            return t.contiguous()
+        lo, hi = per_frame(start_m), per_frame(stop_m)
+        if out is None:
+            out = torch.empty((f, self.S), dtype=torch.float32, device=self.device)
+        nat.check(self.lib.radar_range_zoom(self.ctx, nat.ptr(adc), kind, f, int(loop_idx), nat.ptr(lo), nat.ptr(hi),
+                                            float(range_max_m), nat.ptr(out), _stream_ptr()), self.ctx)
+        return out
+
+    def find_peaks(self, profiles: torch.Tensor, in_db: bool = False, prominence_db: float = 6.0,
+                   threshold_db: float = 20.0, max_peaks: int = 3):
+        """Prominence peak picking (RangeProcessor.find_peaks) on float32 profiles [n, len] ->
+        (idx int32 [n, max_peaks] (-1 padded), db float64 [n, max_peaks], counts int32 [n])."""
+        if profiles.dtype != torch.float32 or profiles.dim() != 2 or not profiles.is_contiguous():
+            raise ValueError("profiles must be a contiguous float32 [n, len] tensor")
+        n, m = profiles.shape
+        idx = torch.empty((n, max_peaks), dtype=torch.int32, device=self.device)
+        db = torch.empty((n, max_peaks), dtype=torch.float64, device=self.device)
+        cnt = torch.empty((n,), dtype=torch.int32, device=self.device)
+        nat.check(self.lib.radar_find_peaks(self.ctx, nat.ptr(profiles), n, m, 1 if in_db else 0, float(prominence_db),
+                                            float(threshold_db), int(max_peaks), nat.ptr(idx), nat.ptr(db), nat.ptr(cnt),
+                                            _stream_ptr()), self.ctx)
+        return idx, db, cnt
+
     def cfar(self, maps: torch.Tensor, params: nat.CfarParams, one_d: bool = False, row_select=None,
              want_noise: bool = False, want_mask: bool = False, max_dets: Optional[int] = None,
              dets_out=None, count_out=None):

@@ -1,8 +1,8 @@
 """Ground-return detector (reference: processors/range_doppler_detection/range_doppler_ground_detector.py:13-121):
 altimeter -> range band [altitude, min(max range, altitude/cos 60deg)] -> 1-D Doppler CFAR per range bin.
 
-The CFAR over the band runs on the device (row-selected 1-D kernel).  The altimeter's peak logic is
-SURVEY 8f next-1 and stays host-side on the device-computed coarse profile."""
+The CFAR over the band runs on the device (row-selected 1-D kernel) and so do the altimeter's profiles and peak picking
+(processors/altimeter.py); a device batch gets one band per frame from the altitude recurrence."""
 from typing import Dict
 
 import numpy as np
@@ -43,14 +43,16 @@ class RangeDopplerGroundDetector(RangeDopplerDetector):
 
     def process(self, adc_cube, **kwargs):
         import torch
-        altitude_m = self.altimeter.process(adc_cube=adc_cube, **self.altimeter_params)
-        lo, hi = self.range_band(altitude_m)
+        altitudes = np.atleast_1d(self.altimeter.process(adc_cube=adc_cube, **self.altimeter_params))
         self._compute_range_doppler_response(adc_cube)
         eng = self._eng
         f, rows = self._mag_dev.shape[0], self._mag_dev.shape[1]
-        rsel = torch.zeros((f, rows), dtype=torch.uint8, device=eng.device)
-        if hi >= lo:
-            rsel[:, lo:hi + 1] = 1
+        sel = np.zeros((f, rows), dtype=np.uint8)
+        for i in range(f):
+            lo, hi = self.range_band(float(altitudes[min(i, altitudes.shape[0] - 1)]))
+            if hi >= lo:
+                sel[i, lo:hi + 1] = 1
+        rsel = torch.from_numpy(sel).to(eng.device)
         vp, _ = self.vel_detector._c_params()
         res = eng.cfar(self._mag_dev, vp, one_d=True, row_select=rsel)
         self.dets = self._finish_dets(res)

@@ -1,15 +1,19 @@
-"""Coarse range profile (reference: processors/range_resp.py:8-164).
+"""Range profiles (reference: processors/range_resp.py:8-164).
 
-``coarse_fft`` (one chirp, Hann over samples, |FFT|, mean over antennas) runs on the device
-(``radar_range_profile``).  ``zoom_fft`` / ``find_peaks`` are SURVEY section 8f "next-1": they act on one
-63..512-sample profile and stay host-side (scipy) until the chirp-Z kernel lands; they are not on the
-measured hot path.
+``coarse_fft`` (one chirp, Hann over samples, |FFT|, mean over antennas) is ``radar_range_profile``; ``zoom_fft``
+(scipy ZoomFFT in the reference) is ``radar_range_zoom`` - the direct evaluation of the same sum; ``find_peaks``
+(scipy ``find_peaks(prominence=6)`` + 20 dB gate + strongest-N) is ``radar_find_peaks``.  All three run on the device;
+host numpy inputs are staged through the compatibility path like every other processor.
 """
 import numpy as np
 
 from ..config_managers.cfgManager import ConfigManager
-from ._device import stage_cube, to_host_f64
+from ._device import is_device_tensor, stage_cube, to_host_f64
 from ._processor import _Processor
+
+
+def _to_numpy(x):
+    return x.detach().cpu().numpy() if is_device_tensor(x) else x
 
 
 class RangeProcessor(_Processor):
@@ -33,28 +37,41 @@ class RangeProcessor(_Processor):
             return prof
         return to_host_f64(prof[0])
 
-    def zoom_fft(self, adc_cube: np.ndarray, range_start_m: float, range_stop_m: float, chirp_idx: int = 0):
-        from scipy.signal import ZoomFFT          # next-1: host side
-        x = np.asarray(adc_cube)[:, :, chirp_idx]
-        n = x.shape[1]
-        xw = x * np.hanning(n)
-        fs = 1 / self.config_manager.range_res_m
-        f0 = range_start_m * fs / self.config_manager.range_max_m
-        f1 = range_stop_m * fs / self.config_manager.range_max_m
-        zoom = ZoomFFT(n, [f0, f1], fs=fs)
-        avg = np.mean(np.abs(zoom(xw, axis=1)), axis=0)
-        return avg, np.linspace(range_start_m, range_stop_m, len(avg))
+    def zoom_fft(self, adc_cube, range_start_m, range_stop_m, chirp_idx: int = 0):
+        """-> (zoom magnitude averaged over antennas, zoom range bins).  Host cube in: fp64 (S,) arrays out, as the
+        reference.  Device batch in (extension): float32 [F, S] tensor out, ``range_start_m`` / ``range_stop_m`` may be
+        per-frame sequences and the bins are returned as a float64 [F, S] numpy array."""
+        eng, dev, squeeze = stage_cube(adc_cube, self.config_manager)
+        loop = int(chirp_idx) % eng.L if int(chirp_idx) < 0 else int(chirp_idx)
+        zoom = eng.range_zoom(dev, range_start_m, range_stop_m, self.config_manager.range_max_m, loop_idx=loop)
+        if squeeze:
+            return to_host_f64(zoom[0]), np.linspace(float(range_start_m), float(range_stop_m), eng.S)
+        lo = np.broadcast_to(np.asarray(_to_numpy(range_start_m), dtype=np.float64).reshape(-1), (dev.shape[0],))
+        hi = np.broadcast_to(np.asarray(_to_numpy(range_stop_m), dtype=np.float64).reshape(-1), (dev.shape[0],))
+        return zoom, np.linspace(lo, hi, eng.S, axis=1)
 
-    def find_peaks(self, rng_resp_db: np.ndarray, rng_bins: np.ndarray, max_peaks: int = 3, threshold_dB: int = 20):
-        from scipy.signal import find_peaks        # next-1: host side
-        peaks, _ = find_peaks(rng_resp_db, prominence=6)
-        if len(peaks) == 0:
+    def find_peaks(self, rng_resp_db, rng_bins, max_peaks: int = 3, threshold_dB: int = 20):
+        """Strongest prominent peaks of a range response in dB -> (range values, dB values), strongest first."""
+        import torch
+        eng = self._any_engine()
+        if is_device_tensor(rng_resp_db):
+            prof = rng_resp_db.to(device=eng.device, dtype=torch.float32)
+        else:
+            prof = torch.from_numpy(np.ascontiguousarray(rng_resp_db, dtype=np.float32)).to(eng.device)
+        batch = prof.dim() == 2
+        idx, db, cnt = eng.find_peaks(prof.reshape(-1, prof.shape[-1]).contiguous(), in_db=True, prominence_db=6.0,
+                                      threshold_db=float(threshold_dB), max_peaks=int(max_peaks))
+        if batch:
+            return idx, db, cnt
+        n = int(cnt[0].item())
+        if n == 0:
             return np.array([]), np.array([])
-        vals = rng_resp_db[peaks]
-        keep = vals >= (np.max(vals) - threshold_dB)
-        peaks, vals = peaks[keep], vals[keep]
-        top = peaks[np.argsort(vals)[::-1]][:max_peaks]
-        return rng_bins[top], rng_resp_db[top]
+        sel = idx[0, :n].cpu().numpy()
+        return np.asarray(rng_bins)[sel], np.asarray(_to_numpy(rng_resp_db), dtype=np.float64)[sel]
+
+    def _any_engine(self):
+        from ..engine import RadarEngine
+        return RadarEngine.for_config(self.config_manager)
 
     def process(self, adc_cube, chirp_idx: int = 0, **kwargs):
         return self.coarse_fft(adc_cube, chirp_idx)

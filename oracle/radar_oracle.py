@@ -410,3 +410,111 @@ def sar_response(history, geometry, d, lambda_m):
     steer = np.exp(1j * 2 * np.pi * np.einsum("cae,cn->nae", d, p) / lambda_m)      # (N, A, E)
     beams = np.einsum("sn,nae->sae", x, steer)
     return np.fft.fft(beams * hann(s)[:, None, None], axis=0)
+
+
+# ------------------------------------------------------------------------------------------------
+# zoom range profile, prominence peak picking, altimeter recurrence
+# ------------------------------------------------------------------------------------------------
+def zoom_range_profile(cube_v: np.ndarray, range_start_m: float, range_stop_m: float, range_max_m: float,
+                       chirp_idx: int = 0):
+    """RangeProcessor.zoom_fft (reference processors/range_resp.py:59-103).  scipy.signal.ZoomFFT(n, [f0, f1], fs=fs)
+    with m = n output points and endpoint=False evaluates X[k] = sum_s x[s] exp(-2 pi i s f_k / fs),
+    f_k = f0 + k (f1 - f0)/m (scipy 1.14 _czt.py: a = exp(2 pi i f0/fs), w = exp(-2 pi i (f1-f0)/(m fs))); with the
+    reference's f = range * fs / range_max that is a phase of s * r_k / range_max turns, r_k = start + k (stop-start)/n.
+    Restated as the direct sum (no chirp-Z convolution).  Returns (mean_v |X|, linspace(start, stop, n))."""
+    x = np.asarray(cube_v)[:, :, chirp_idx].astype(np.complex128)
+    n = x.shape[1]
+    xw = x * hann(n)
+    k = np.arange(n)
+    r_k = range_start_m + k * (range_stop_m - range_start_m) / n
+    s = np.arange(n)
+    phase = np.outer(r_k / range_max_m, s)                      # turns, [k, s]
+    kern = np.exp(-2j * np.pi * phase)
+    zoom = xw @ kern.T                                           # [v, k]
+    return np.mean(np.abs(zoom), axis=0), np.linspace(range_start_m, range_stop_m, n)
+
+
+def local_maxima_1d(x: np.ndarray) -> np.ndarray:
+    """scipy.signal._peak_finding_utils._local_maxima_1d (scipy 1.14): strict rise, plateau, strict fall -> the
+    plateau's midpoint (left + right)//2; the first and last samples are never peaks."""
+    x = np.asarray(x, dtype=np.float64)
+    peaks = []
+    i, i_max = 1, x.shape[0] - 1
+    while i < i_max:
+        if x[i - 1] < x[i]:
+            i_ahead = i + 1
+            while i_ahead < i_max and x[i_ahead] == x[i]:
+                i_ahead += 1
+            if x[i_ahead] < x[i]:
+                peaks.append((i + i_ahead - 1) // 2)
+                i = i_ahead
+        i += 1
+    return np.asarray(peaks, dtype=np.intp)
+
+
+def peak_prominences(x: np.ndarray, peaks: np.ndarray) -> np.ndarray:
+    """scipy.signal.peak_prominences with wlen=None (scipy 1.14 _peak_prominences): walk left / right from the peak
+    until a sample is HIGHER than it (or the signal ends), keeping the minimum; prominence = peak - max(left min, right min)."""
+    x = np.asarray(x, dtype=np.float64)
+    out = np.empty(len(peaks), dtype=np.float64)
+    for j, p in enumerate(peaks):
+        i, left_min = p, x[p]
+        while 0 <= i and x[i] <= x[p]:
+            left_min = min(left_min, x[i])
+            i -= 1
+        i, right_min = p, x[p]
+        while i <= x.shape[0] - 1 and x[i] <= x[p]:
+            right_min = min(right_min, x[i])
+            i += 1
+        out[j] = x[p] - max(left_min, right_min)
+    return out
+
+
+def find_range_peaks(resp_db: np.ndarray, bins: np.ndarray, max_peaks: int = 3, threshold_db: float = 20.0,
+                     prominence: float = 6.0):
+    """RangeProcessor.find_peaks (reference processors/range_resp.py:105-150): scipy find_peaks(prominence=6), keep peaks
+    within threshold_db of the strongest, strongest first, at most max_peaks.  Returns (bins[idx], resp_db[idx], idx)."""
+    resp_db = np.asarray(resp_db, dtype=np.float64)
+    peaks = local_maxima_1d(resp_db)
+    if len(peaks):
+        prom = peak_prominences(resp_db, peaks)
+        peaks = peaks[prom >= prominence]
+    if len(peaks) == 0:
+        return np.array([]), np.array([]), np.array([], dtype=np.intp)
+    vals = resp_db[peaks]
+    keep = vals >= (np.max(vals) - threshold_db)
+    peaks, vals = peaks[keep], vals[keep]
+    top = peaks[np.argsort(vals)[::-1]][:max_peaks]
+    return np.asarray(bins)[top], resp_db[top], top
+
+
+def altimeter_step(state: dict, profile: np.ndarray, range_bins: np.ndarray, cube_v=None, range_max_m: float = 0.0,
+                   precise: bool = False) -> float:
+    """One Altimeter.process call (reference processors/altimeter.py:56-139).  state: min_altitude_m, zoom_search_region_m,
+    altitude_search_limit_m, range_bias, measured, corrected (updated in place).  Returns the corrected altitude."""
+    def ground_peak(peaks_m):
+        if peaks_m.size > 0:
+            ok = peaks_m[(peaks_m >= state["min_altitude_m"]) &
+                         (np.abs(peaks_m - state["measured"]) <= state["altitude_search_limit_m"])]
+            if ok.size > 0:
+                return float(np.min(ok))
+        return -1.0
+    with np.errstate(divide="ignore"):
+        db = 20 * np.log10(np.asarray(profile, dtype=np.float64))
+    peaks_m, _, _ = find_range_peaks(db, range_bins, max_peaks=3)
+    if peaks_m.size == 0:
+        return state["corrected"]
+    g = ground_peak(peaks_m)
+    if g < 0:
+        return state["corrected"]
+    if precise:
+        lo = max(1e-6, g - state["zoom_search_region_m"])
+        hi = min(np.max(range_bins) - 1e-6, g + state["zoom_search_region_m"])
+        zoom, zbins = zoom_range_profile(cube_v, lo, hi, range_max_m, 0)
+        zp, _, _ = find_range_peaks(20 * np.log10(zoom), zbins, max_peaks=2)
+        g = ground_peak(zp) if zp.size > 0 else -1.0
+        if g < 0:
+            return state["corrected"]
+    state["measured"] = g
+    state["corrected"] = g + state["range_bias"]
+    return state["corrected"]
