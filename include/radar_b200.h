@@ -45,6 +45,12 @@ extern "C" {
 #define RADAR_WIN_DOPPLER  2      /* Hann over chirp loops */
 #define RADAR_WIN_ANTENNA  4      /* Hann over antennas (range-angle / DBS) */
 
+#define RADAR_RD_RANGE_ONLY 8      /* radar_range_doppler: stop after the range transform (chirp axis stays in loop order,
+                                      no Doppler FFT, no fftshift) - the input of radar_chirp_zoom */
+
+#define RADAR_REDUCE_MAX  0
+#define RADAR_REDUCE_MEAN 1
+
 #define RADAR_CFAR_CA 0
 #define RADAR_CFAR_OS 1
 #define RADAR_CFAR_GO 2
@@ -215,6 +221,35 @@ int radar_dbs(radar_ctx* ctx, const void* adc, int in_kind, int n_frames,
 int radar_sar_image(radar_ctx* ctx, const void* aperture, int num_samples, int n_elems,
                     const double* positions, const double* dirs, int n_dirs, double lambda_m,
                     int g_begin, int g_end, void* out, void* stream);
+
+/* ---- Doppler-azimuth response -------------------------------------------------- *
+ * DopplerAzimuthProcessor.coarse_doppler_azimuth_fft + the tail of .process
+ * (processors/doppler_azimuth_resp.py:296-334, 483-491):
+ *   out[f][d][a] = mean over rows k in [k_begin, k_end) of | sum_v w[v] cube[f][v][k][d] exp(-2 pi i v a'/A) |,
+ *   a' = (a - A/2) mod A if shift_angle else a  (zero-padded angle FFT, fftshift on the angle axis).
+ *   cube      : float2 [frame][n_ant][rows][cols] - the windowed range-Doppler cube of radar_range_doppler
+ *               (rows = S, cols = L, Doppler axis already shifted) or the zoom cube of radar_chirp_zoom
+ *   ant_weight: device float[n_ant] (np.hanning(n_ant) for standard arrays with TDM-MIMO, :95-98) or NULL
+ *   out       : float [frame][cols][num_angle_bins]; the host layer keeps the valid-angle columns. */
+int radar_doppler_azimuth(radar_ctx* ctx, const void* cube, int n_frames, int n_ant, int rows, int cols,
+                          int k_begin, int k_end, const float* ant_weight, int num_angle_bins, int shift_angle,
+                          float* out, void* stream);
+
+/* Zoom Doppler transform of the "precise" Doppler-azimuth response: scipy.signal.ZoomFFT over the chirp axis
+ * (processors/doppler_azimuth_resp.py:130-162), X[j] = sum_l x[l] exp(-2 pi i l turns[j]).
+ *   range_cube: float2 [frame][n_ant][S][L] from radar_range_doppler(... | RADAR_RD_RANGE_ONLY)
+ *   turns     : device double[n_out], turns per chirp of every output bin (formed in fp64 by the host layer with
+ *               ZoomFFT's expressions: (f0 + j (f1 - f0)/m)/fs)
+ *   zoom_out  : float2 [frame][n_ant][k_end-k_begin][n_out] */
+int radar_chirp_zoom(radar_ctx* ctx, const void* range_cube, int n_frames, int n_ant, int k_begin, int k_end,
+                     const double* turns, int n_out, void* zoom_out, void* stream);
+
+/* Column-wise reduction over the selected rows of every map: MicroDopplerProcessor.process takes np.max of |RD|
+ * over the range rows inside target_ranges (processors/micro_doppler_resp.py:104-108).
+ *   maps float [n_maps][rows][cols]; row_select device uint8[rows] or NULL (all rows); op RADAR_REDUCE_*;
+ *   out float [n_maps][cols]. */
+int radar_row_reduce(radar_ctx* ctx, const float* maps, int n_maps, int rows, int cols, const uint8_t* row_select,
+                     int op, float* out, void* stream);
 
 #ifdef __cplusplus
 }

@@ -16,6 +16,8 @@ RADAR_IN_CUBE64 = 1
 RADAR_WIN_RANGE = 1
 RADAR_WIN_DOPPLER = 2
 RADAR_WIN_ANTENNA = 4
+RADAR_RD_RANGE_ONLY = 8
+RADAR_REDUCE_MAX, RADAR_REDUCE_MEAN = 0, 1
 RADAR_CFAR_CA, RADAR_CFAR_OS, RADAR_CFAR_GO, RADAR_CFAR_SO = 0, 1, 2, 3
 CFAR_KIND = {"ca": RADAR_CFAR_CA, "os": RADAR_CFAR_OS, "go": RADAR_CFAR_GO, "so": RADAR_CFAR_SO}
 ABI_VERSION = 1
@@ -54,6 +56,9 @@ SIGNATURES = {
     "radar_range_angle": (_I, [_P, _P, _I, _I, _I, _P, _I, _I, _I, _P, _P]),
     "radar_dbs": (_I, [_P, _P, _I, _I, _P, _I, _I, _P, _P, _I, _P, _P]),
     "radar_sar_image": (_I, [_P, _P, _I, _I, _P, _P, _I, C.c_double, _I, _I, _P, _P]),
+    "radar_doppler_azimuth": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _I, _I, _P, _P]),
+    "radar_chirp_zoom": (_I, [_P, _P, _I, _I, _I, _I, _P, _I, _P, _P]),
+    "radar_row_reduce": (_I, [_P, _P, _I, _I, _I, _P, _I, _P, _P]),
 }
 
 _lib = None

@@ -286,4 +286,27 @@ int radar_sar_image(radar_ctx* ctx, const void* aperture, int num_samples, int n
                             g_begin, g_end, reinterpret_cast<cf*>(out), (cudaStream_t)stream);
 }
 
+int radar_doppler_azimuth(radar_ctx* ctx, const void* cube, int n_frames, int n_ant, int rows, int cols, int k_begin, int k_end,
+                          const float* ant_weight, int num_angle_bins, int shift_angle, float* out, void* stream) {
+    RB_ENTER(ctx);
+    if (n_frames > 0 && (!cube || !out)) return set_error(ctx, RADAR_E_INVALID, "null pointer");
+    return launch_doppler_azimuth(ctx, reinterpret_cast<const cf*>(cube), n_frames, n_ant, rows, cols, k_begin, k_end, ant_weight,
+                                  num_angle_bins, shift_angle, out, (cudaStream_t)stream);
+}
+
+int radar_chirp_zoom(radar_ctx* ctx, const void* range_cube, int n_frames, int n_ant, int k_begin, int k_end, const double* turns,
+                     int n_out, void* zoom_out, void* stream) {
+    RB_ENTER(ctx);
+    if (n_frames > 0 && (!range_cube || !turns || !zoom_out)) return set_error(ctx, RADAR_E_INVALID, "null pointer");
+    return launch_chirp_zoom(ctx, reinterpret_cast<const cf*>(range_cube), n_frames, n_ant, k_begin, k_end, turns, n_out,
+                             reinterpret_cast<cf*>(zoom_out), (cudaStream_t)stream);
+}
+
+int radar_row_reduce(radar_ctx* ctx, const float* maps, int n_maps, int rows, int cols, const uint8_t* row_select, int op, float* out,
+                     void* stream) {
+    RB_ENTER(ctx);
+    if (n_maps > 0 && (!maps || !out)) return set_error(ctx, RADAR_E_INVALID, "null pointer");
+    return launch_row_reduce(ctx, maps, n_maps, rows, cols, row_select, op, out, (cudaStream_t)stream);
+}
+
 }  // extern "C"

@@ -52,6 +52,7 @@ struct RdArgs {
     cf* rd_out;
     float* mag_out;
     int mag_antenna;
+    int range_only;            // RADAR_RD_RANGE_ONLY: stop after the range transform, chirp axis left in loop order
     FftPlan planS, planL;
     FastDiv divS, divL;
 };
@@ -88,7 +89,7 @@ __device__ __forceinline__ void rd_load_tables(const RdSmem& sm, const RdArgs& a
     for (int d = threadIdx.x; d < L; d += blockDim.x) {
         int f = d - L / 2;
         if (f < 0) f += L;
-        sm.srcL[d] = a.posL[f];
+        sm.srcL[d] = a.range_only ? (uint16_t)d : a.posL[f];
     }
 }
 
@@ -116,7 +117,7 @@ __device__ __forceinline__ void rd_compute_tile(const RdSmem& sm, const RdArgs& 
     }
     __syncthreads();
     fft_axis(sm.tile, /*strideF=*/Lp, /*strideO=*/1, /*O=*/L, a.divL, a.planS, sm.twS);   // range
-    fft_axis(sm.tile, /*strideF=*/1, /*strideO=*/Lp, /*O=*/S, a.divS, a.planL, sm.twL);   // Doppler
+    if (!a.range_only) fft_axis(sm.tile, /*strideF=*/1, /*strideO=*/Lp, /*O=*/S, a.divS, a.planL, sm.twL);   // Doppler
 }
 
 __global__ void __launch_bounds__(kRdThreads) rd_fused_kernel(const __grid_constant__ RdArgs a) {
@@ -178,11 +179,13 @@ int launch_range_doppler(radar_ctx* ctx, const void* adc, int in_kind, int n_fra
     a.n_out_ant = ant_list ? n_ant : ctx->V;
     if (a.n_out_ant <= 0) return set_error(ctx, RADAR_E_INVALID, "empty antenna list");
     if (mag_out && mag_antenna >= a.n_out_ant) return set_error(ctx, RADAR_E_INVALID, "mag_antenna %d out of range", mag_antenna);
-    if (in_kind == RADAR_IN_IQ16 && !ant_weight && !ant_list && ctx->force_generic == 0) {
+    const bool range_only = (window_flags & RADAR_RD_RANGE_ONLY) != 0;
+    a.range_only = range_only ? 1 : 0;
+    if (!range_only && in_kind == RADAR_IN_IQ16 && !ant_weight && !ant_list && ctx->force_generic == 0) {
         const int rc = launch_range_doppler_stream(ctx, adc, n_frames, window_flags, rd_out, mag_out, mag_antenna, st);
         if (rc <= 0) return rc;            // launched (0) or failed (<0); 1 = no streaming instantiation for this shape
     }
-    if (in_kind == RADAR_IN_IQ16 && !ant_weight && ctx->force_generic != 1) {
+    if (!range_only && in_kind == RADAR_IN_IQ16 && !ant_weight && ctx->force_generic != 1) {
         const int rc = launch_range_doppler_spec(ctx, adc, n_frames, ant_list, n_ant, window_flags, rd_out, mag_out, mag_antenna, st);
         if (rc <= 0) return rc;            // launched (0) or failed (<0); 1 = no specialisation for this shape
     }
@@ -513,7 +516,7 @@ int launch_dbs(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, const
     a.rd.n_out_ant = N; a.rd.ant_list = ant_list; a.rd.ant_weight = hannN;
     a.rd.winS = ctx->fftS.hann; a.rd.winL = ctx->fftL.hann;
     a.rd.twS = ctx->fftS.tw; a.rd.twL = ctx->fftL.tw; a.rd.posS = ctx->fftS.pos; a.rd.posL = ctx->fftL.pos;
-    a.rd.rd_out = nullptr; a.rd.mag_out = nullptr; a.rd.mag_antenna = 0;
+    a.rd.rd_out = nullptr; a.rd.mag_out = nullptr; a.rd.mag_antenna = 0; a.rd.range_only = 0;
     a.rd.planS = ctx->fftS.plan; a.rd.planL = ctx->fftL.plan;
     a.rd.divS = make_fastdiv((uint32_t)a.rd.adc.S); a.rd.divL = make_fastdiv((uint32_t)a.rd.adc.L);
     a.A = num_angle_bins; a.n_out = n_out;

@@ -94,6 +94,13 @@ int launch_point_cloud(radar_ctx* ctx, const cf* rd, int n_frames, const int32_t
                        int32_t* az_bin_out, int32_t* el_bin_out, cudaStream_t st);
 int launch_det_offsets(radar_ctx* ctx, const int32_t* counts, int n_frames, int max_dets, int32_t* offsets_out,
                        cudaStream_t st);
+int launch_doppler_azimuth(radar_ctx* ctx, const cf* cube, int n_frames, int n_ant, int rows, int cols, int k_begin,
+                           int k_end, const float* weight, int num_angle_bins, int shift_angle, float* out,
+                           cudaStream_t st);
+int launch_chirp_zoom(radar_ctx* ctx, const cf* range_cube, int n_frames, int n_ant, int k_begin, int k_end,
+                      const double* turns, int n_out, cf* out, cudaStream_t st);
+int launch_row_reduce(radar_ctx* ctx, const float* maps, int n_maps, int rows, int cols, const uint8_t* row_select,
+                      int op, float* out, cudaStream_t st);
 int launch_sar_image(radar_ctx* ctx, const cf* aperture, int num_samples, int n_elems, const double* positions,
                      const double* dirs, int n_dirs, double lambda_m, int g_begin, int g_end, cf* out,
                      cudaStream_t st);

@@ -270,6 +270,61 @@ class RadarEngine:
                                      n_out, nat.ptr(out), _stream_ptr()), self.ctx)
         return out
 
+    def _floats(self, values):
+        """Small float32 device array cached by content (antenna windows)."""
+        if values is None:
+            return None
+        key = ("f32",) + tuple(float(v) for v in values)
+        t = self._int_cache.get(key)
+        if t is None:
+            t = torch.tensor(key[1:], dtype=torch.float32, device=self.device)
+            self._int_cache[key] = t
+        return t
+
+    def doppler_azimuth(self, cube: torch.Tensor, k_begin: int = 0, k_end: Optional[int] = None, ant_weight=None,
+                        num_angle_bins: int = 64, shift_angle: bool = True, out=None) -> torch.Tensor:
+        """cube complex64 [F, n_ant, rows, cols] (range-Doppler or zoom cube) -> float32 [F, cols, A]:
+        mean over rows [k_begin, k_end) of |zero-padded angle DFT| (DopplerAzimuthProcessor, coarse / precise tail)."""
+        if cube.dtype != torch.complex64 or cube.dim() != 4 or not cube.is_contiguous():
+            raise ValueError("cube must be a contiguous complex64 [F, n_ant, rows, cols] tensor")
+        f, n_ant, rows, cols = cube.shape
+        k_end = rows if k_end is None else k_end
+        if out is None:
+            out = torch.empty((f, cols, num_angle_bins), dtype=torch.float32, device=self.device)
+        nat.check(self.lib.radar_doppler_azimuth(self.ctx, nat.ptr(cube), f, n_ant, rows, cols, int(k_begin), int(k_end),
+                                                 nat.ptr(self._floats(ant_weight)), int(num_angle_bins),
+                                                 int(bool(shift_angle)), nat.ptr(out), _stream_ptr()), self.ctx)
+        return out
+
+    def chirp_zoom(self, range_cube: torch.Tensor, turns, k_begin: int = 0, k_end: Optional[int] = None) -> torch.Tensor:
+        """range_cube complex64 [F, n_ant, S, L] (range transform only) -> complex64 [F, n_ant, k_end-k_begin, J]:
+        X[j] = sum_l x[l] exp(-2 pi i l turns[j]) (scipy ZoomFFT over the chirp axis)."""
+        if range_cube.dtype != torch.complex64 or range_cube.dim() != 4 or tuple(range_cube.shape[2:]) != (self.S, self.L):
+            raise ValueError("range_cube must be complex64 [F, n_ant, S, L]")
+        f, n_ant = range_cube.shape[:2]
+        k_end = self.S if k_end is None else k_end
+        tt = torch.as_tensor(np.ascontiguousarray(turns, dtype=np.float64)).to(self.device)
+        out = torch.empty((f, n_ant, k_end - k_begin, tt.numel()), dtype=torch.complex64, device=self.device)
+        nat.check(self.lib.radar_chirp_zoom(self.ctx, nat.ptr(range_cube.contiguous()), f, n_ant, int(k_begin), int(k_end),
+                                            nat.ptr(tt), tt.numel(), nat.ptr(out), _stream_ptr()), self.ctx)
+        return out
+
+    def row_reduce(self, maps: torch.Tensor, row_select=None, op: str = "max") -> torch.Tensor:
+        """maps float32 [n, rows, cols] -> float32 [n, cols]: max / mean over the selected rows."""
+        if maps.dtype != torch.float32 or maps.dim() != 3 or not maps.is_contiguous():
+            raise ValueError("maps must be a contiguous float32 [n, rows, cols] tensor")
+        n, rows, cols = maps.shape
+        sel = None
+        if row_select is not None:
+            sel = torch.as_tensor(np.ascontiguousarray(row_select, dtype=np.uint8)).to(self.device)
+            if sel.numel() != rows:
+                raise ValueError("row_select must hold one flag per row")
+        out = torch.empty((n, cols), dtype=torch.float32, device=self.device)
+        nat.check(self.lib.radar_row_reduce(self.ctx, nat.ptr(maps), n, rows, cols, nat.ptr(sel),
+                                            nat.RADAR_REDUCE_MAX if op == "max" else nat.RADAR_REDUCE_MEAN,
+                                            nat.ptr(out), _stream_ptr()), self.ctx)
+        return out
+
     def sar_image(self, aperture: torch.Tensor, positions: torch.Tensor, dirs: torch.Tensor, lambda_m: float,
                   g_begin: int = 0, g_end: Optional[int] = None, out=None) -> torch.Tensor:
         """aperture complex64 [S,N], positions float64 [3,N], dirs float64 [3,G] -> complex64 [S, g_end-g_begin]."""

@@ -518,3 +518,144 @@ def altimeter_step(state: dict, profile: np.ndarray, range_bins: np.ndarray, cub
     state["measured"] = g
     state["corrected"] = g + state["range_bias"]
     return state["corrected"]
+
+
+# ------------------------------------------------------------------------------------------------
+# Doppler-azimuth (coarse + zoom), micro-Doppler, strip-map SAR
+# ------------------------------------------------------------------------------------------------
+def doppler_azimuth_windowed(cube_v: np.ndarray, rx_antennas=(), antenna_window: bool = False) -> np.ndarray:
+    """DopplerAzimuthProcessor.process head (reference processors/doppler_azimuth_resp.py:460-466) +
+    apply_hanning_windows (:84-100): the antenna subset is taken FIRST, then Hann over samples, Hann over chirps and -
+    for standard arrays with TDM-MIMO (``antenna_window``) - Hann over the subset's antennas."""
+    x = np.asarray(cube_v).astype(np.complex128)
+    ants = np.asarray(rx_antennas, dtype=int).ravel()
+    if ants.size > 0:
+        x = x[ants]
+    x = x * hann(x.shape[1])[None, :, None] * hann(x.shape[2])[None, None, :]
+    if antenna_window:
+        x = x * hann(x.shape[0])[:, None, None]
+    return x
+
+
+def doppler_azimuth_coarse(cube_v, range_bins, num_angle_bins=64, rx_antennas=(), range_window=(), shift_angle=True,
+                           antenna_window=False, range_max_m=None):
+    """Coarse Doppler-azimuth response BEFORE the valid-angle column selection (reference :102-128, :296-334, :491):
+    range FFT, rows inside ``range_window`` (default [0, range_max]), zero-padded fft2 over (chirp, antenna), fftshift
+    over Doppler (always) and angle (``shift_angle``), abs, mean over the kept range rows.  -> [L, A]."""
+    x = doppler_azimuth_windowed(cube_v, rx_antennas, antenna_window)
+    rf = np.fft.fft(x, axis=1)
+    rw = np.asarray(range_window, dtype=float).ravel()
+    if rw.size == 0:
+        rw = np.array([0.0, range_max_m])
+    keep = (range_bins >= rw[0]) & (range_bins <= rw[1])
+    rf = rf[:, keep, :]
+    n, k, l = rf.shape
+    data = np.zeros((k, l, num_angle_bins), dtype=complex)
+    data[:, :, :n] = np.transpose(rf, (1, 2, 0))
+    spec = np.fft.fft(np.fft.fft(data, axis=1), axis=2)
+    idx_d = shift_index(l)
+    spec = spec[:, idx_d, :]
+    if shift_angle:
+        spec = spec[:, :, shift_index(num_angle_bins)]
+    return np.mean(np.abs(spec), axis=0)
+
+
+def zoom_vel_bins(vel_range, num_vel_bins: int):
+    """DopplerAzimuthProcessor.set_zoomed_fft_vel_bins (reference :164-205)."""
+    neg = np.linspace(vel_range[0], min(-1e-4, vel_range[1]), num_vel_bins if vel_range[0] <= 0 else 0, endpoint=False)
+    pos = np.linspace(max(1e-4, vel_range[0]), vel_range[1], num_vel_bins if vel_range[1] > 0 else 0, endpoint=False)
+    if neg.size > 0 and pos.size > 0:
+        return np.concatenate((neg, pos))
+    if neg.size > 0:
+        return neg
+    if pos.size > 0:
+        return pos
+    return np.array([])
+
+
+def zoom_turns(vel_lo: float, vel_hi: float, m: int, vel_res: float, vel_max: float) -> np.ndarray:
+    """Turns per chirp of the m output bins of DopplerAzimuthProcessor.zoom_fft (reference :130-162):
+    fs = 1/vel_res, f = v*fs/vel_max, ZoomFFT(m, [f0, f1], fs=2*fs) -> nu_j = (f0 + j (f1-f0)/m)/(2 fs)."""
+    fs = 1 / vel_res
+    f0 = vel_lo * fs / vel_max
+    f1 = vel_hi * fs / vel_max
+    return (f0 + np.arange(m) * (f1 - f0) / m) / (fs * 2)
+
+
+def doppler_azimuth_precise_plan(vel_range, vel_bins, vel_res, vel_max, min_zoom_span=0.1):
+    """Host logic of DopplerAzimuthProcessor.precise_doppler_azimuth_fft (reference :207-294): clamp the velocity range,
+    enforce the minimum spread, build the zoomed velocity bins, and decide for the negative and the positive half
+    whether a zoom transform is computed (span > min_zoom_span) or the half is zero.
+    -> (zoomed_vel_bins, [(n_bins, turns or None), (n_bins, turns or None)])."""
+    vr = np.array(vel_range, dtype=float)
+    vr[0] = max(vr[0], -1 * vel_max)
+    vr[1] = min(vr[1], vel_max)
+    spread = 2 * min_zoom_span
+    if (vr[1] - vr[0]) < spread:
+        to_max = abs(vr[1] - vel_max)
+        to_min = abs(vr[0] - (-1 * vel_max))
+        if to_max > to_min:
+            vr[1] = vr[0] + spread
+        elif to_min > to_max:
+            vr[0] = vr[1] - spread
+    zb = zoom_vel_bins(vr, vel_bins.size)
+    halves = []
+    neg = zb[zb <= 0]
+    if len(neg) > 0 and np.abs(max(neg) - min(neg)) > min_zoom_span:
+        halves.append((len(neg), zoom_turns(np.min(neg) + 2 * vel_max, np.max(neg) + 2 * vel_max, len(neg), vel_res, vel_max)))
+    else:
+        halves.append((len(neg), None))
+    pos = zb[zb > 0]
+    if len(pos) > 0 and np.abs(max(pos) - min(pos)) > min_zoom_span:
+        halves.append((len(pos), zoom_turns(np.min(pos), np.max(pos), len(pos), vel_res, vel_max)))
+    else:
+        halves.append((len(pos), None))
+    return zb, halves
+
+
+def doppler_azimuth_precise(cube_v, range_bins, vel_bins, vel_res, vel_max, num_angle_bins=64, rx_antennas=(),
+                            range_window=(), shift_angle=True, antenna_window=False, range_max_m=None,
+                            vel_range=(-0.25, 0.25), min_zoom_span=0.1):
+    """Precise (zoom) Doppler-azimuth response before the valid-angle selection (reference :130-162, :207-294, :491).
+    Each computed half is a direct DFT over the first n_bins chirps at the zoom frequencies, then the zero-padded
+    angle FFT, abs; halves are concatenated along Doppler; only the angle axis is shifted.  -> (resp [J, A], zoomed bins)."""
+    x = doppler_azimuth_windowed(cube_v, rx_antennas, antenna_window)
+    rf = np.fft.fft(x, axis=1)
+    rw = np.asarray(range_window, dtype=float).ravel()
+    if rw.size == 0:
+        rw = np.array([0.0, range_max_m])
+    keep = (range_bins >= rw[0]) & (range_bins <= rw[1])
+    rf = rf[:, keep, :]
+    n, k, l = rf.shape
+    zb, halves = doppler_azimuth_precise_plan(vel_range, vel_bins, vel_res, vel_max, min_zoom_span)
+    parts = []
+    for m, turns in halves:
+        if turns is None:
+            parts.append(np.zeros((k, m, num_angle_bins)))
+            continue
+        y = rf[:, :, :m]                                                  # [n, k, m] first m chirps
+        kern = np.exp(-2j * np.pi * np.outer(np.arange(m), turns))        # [chirp, j]
+        z = np.einsum("nkl,lj->kjn", y, kern)
+        data = np.zeros((k, m, num_angle_bins), dtype=complex)
+        data[:, :, :n] = z
+        parts.append(np.abs(np.fft.fft(data, axis=2)))
+    resp = np.concatenate(parts, axis=1)
+    if shift_angle:
+        resp = resp[:, :, shift_index(num_angle_bins)]
+    return np.mean(resp, axis=0), zb
+
+
+def micro_doppler_column(cube_v, range_bins, target_ranges=(0.0, 1.0), rx_idx=0) -> np.ndarray:
+    """One new column of MicroDopplerProcessor.process (reference processors/micro_doppler_resp.py:91-114):
+    UN-windowed fft2 of one antenna, fftshift over Doppler, abs, max over the range rows inside target_ranges."""
+    x = np.asarray(cube_v)[rx_idx].astype(np.complex128)
+    resp = np.abs(np.fft.fft2(x, axes=(-2, -1))[:, shift_index(x.shape[1])])
+    keep = (range_bins >= target_ranges[0]) & (range_bins <= target_ranges[1])
+    return np.max(resp[keep, :], axis=0)
+
+
+def strip_map_response(cube_v, rx_index=0) -> np.ndarray:
+    """StripMapSARProcessor.process before the range / angle slices (reference processors/strip_map_SAR_processor.py:
+    176-188): un-windowed fft2 of one antenna, fftshift over the chirp axis, complex."""
+    x = np.asarray(cube_v)[rx_index].astype(np.complex128)
+    return np.fft.fft2(x, axes=(-2, -1))[:, shift_index(x.shape[1])]
