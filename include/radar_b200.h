@@ -251,6 +251,26 @@ int radar_chirp_zoom(radar_ctx* ctx, const void* range_cube, int n_frames, int n
 int radar_row_reduce(radar_ctx* ctx, const float* maps, int n_maps, int rows, int cols, const uint8_t* row_select,
                      int op, float* out, void* stream);
 
+/* ---- point cloud -> ego velocity ------------------------------------------------ *
+ * VelocityEstimator.lsq_fit_ego_vel_ransac_points_2D / _3D (point_cloud_processing/vel_estimator.py:76-170):
+ * y = -v, H = xyz[:dims]/|xyz[:dims]|, sklearn RANSACRegressor(LinearRegression(fit_intercept=False),
+ * residual_threshold, random_state=42, max_trials, min_samples) - one warp per frame, fp64.
+ *   points  : double [rows][4] packed point clouds (radar_point_cloud with offsets), offsets int32 [n_frames+1]
+ *   subsets : device int32 [n_blocks][max_trials][min_samples]; a block holds the point indices sklearn draws for a
+ *             cloud of n points (random_state=42 re-seeds every fit, so they depend only on n and the trial);
+ *             tabulated by the host layer with numpy's RandomState
+ *   subset_index : device int32 [table_max_n + 1], block number for n points, -1 = not tabulated
+ *   vel_out : double [n_frames][3] (vx, vy, vz; vz = 0 for dims == 2; zeros when there is no estimate)
+ *   r2_out  : double [n_frames] R^2 of the final model on its inliers (0 with <= 3 inliers) or NULL
+ *   inlier_frac_out : double [n_frames] inliers / points or NULL
+ *   status_out : int32 [n_frames] inlier count of the final model; 0 = no estimate (fewer than min_samples points,
+ *             non-finite input, no consensus set: the ValueErrors the reference swallows); -1 = no subset block for
+ *             this frame's point count; or NULL */
+int radar_ego_velocity(radar_ctx* ctx, const double* points, const int32_t* offsets, int n_frames, int dims,
+                       const int32_t* subsets, const int32_t* subset_index, int table_max_n, int max_trials,
+                       int min_samples, double residual_threshold, double stop_probability,
+                       double* vel_out, double* r2_out, double* inlier_frac_out, int32_t* status_out, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

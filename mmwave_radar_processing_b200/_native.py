@@ -59,6 +59,7 @@ SIGNATURES = {
     "radar_doppler_azimuth": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _I, _I, _P, _P]),
     "radar_chirp_zoom": (_I, [_P, _P, _I, _I, _I, _I, _P, _I, _P, _P]),
     "radar_row_reduce": (_I, [_P, _P, _I, _I, _I, _P, _I, _P, _P]),
+    "radar_ego_velocity": (_I, [_P, _P, _P, _I, _I, _P, _P, _I, _I, _I, C.c_double, C.c_double, _P, _P, _P, _P, _P]),
 }
 
 _lib = None

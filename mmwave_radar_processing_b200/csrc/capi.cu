@@ -309,4 +309,13 @@ int radar_row_reduce(radar_ctx* ctx, const float* maps, int n_maps, int rows, in
     return launch_row_reduce(ctx, maps, n_maps, rows, cols, row_select, op, out, (cudaStream_t)stream);
 }
 
+int radar_ego_velocity(radar_ctx* ctx, const double* points, const int32_t* offsets, int n_frames, int dims, const int32_t* subsets,
+                       const int32_t* subset_index, int table_max_n, int max_trials, int min_samples, double residual_threshold, double stop_probability,
+                       double* vel_out, double* r2_out, double* inlier_frac_out, int32_t* status_out, void* stream) {
+    RB_ENTER(ctx);
+    if (n_frames > 0 && (!points || !offsets || !subsets || !subset_index || !vel_out)) return set_error(ctx, RADAR_E_INVALID, "null pointer");
+    return launch_ego_velocity(ctx, points, offsets, n_frames, dims, subsets, subset_index, table_max_n, max_trials, min_samples, residual_threshold,
+                               stop_probability, vel_out, r2_out, inlier_frac_out, status_out, (cudaStream_t)stream);
+}
+
 }  // extern "C"

@@ -101,6 +101,10 @@ int launch_chirp_zoom(radar_ctx* ctx, const cf* range_cube, int n_frames, int n_
                       const double* turns, int n_out, cf* out, cudaStream_t st);
 int launch_row_reduce(radar_ctx* ctx, const float* maps, int n_maps, int rows, int cols, const uint8_t* row_select,
                       int op, float* out, cudaStream_t st);
+int launch_ego_velocity(radar_ctx* ctx, const double* points, const int32_t* offsets, int n_frames, int dims,
+                        const int32_t* subsets, const int32_t* subset_index, int table_max_n, int max_trials,
+                        int min_samples, double residual_threshold, double stop_probability, double* vel_out,
+                        double* r2_out, double* frac_out, int32_t* status_out, cudaStream_t st);
 int launch_sar_image(radar_ctx* ctx, const cf* aperture, int num_samples, int n_elems, const double* positions,
                      const double* dirs, int n_dirs, double lambda_m, int g_begin, int g_end, cf* out,
                      cudaStream_t st);

@@ -325,6 +325,28 @@ class RadarEngine:
                                             nat.ptr(out), _stream_ptr()), self.ctx)
         return out
 
+    def ego_velocity(self, points: torch.Tensor, offsets: torch.Tensor, dims: int, table, residual_threshold: float = 0.15,
+                     stop_probability: float = 0.99):
+        """Packed point clouds float64 [rows, 4] + offsets int32 [F+1] -> (vel float64 [F, 3], r2 [F], inlier
+        fraction [F], status int32 [F]); ``table`` is a point_cloud_processing.ransac_subsets.SubsetTable that already
+        holds a block for every point count of the batch (status -1 marks frames it does not cover)."""
+        if points.dtype != torch.float64 or points.dim() != 2 or points.shape[1] != 4 or not points.is_contiguous():
+            raise ValueError("points must be a contiguous float64 [rows, 4] tensor")
+        if offsets.dtype != torch.int32 or offsets.dim() != 1:
+            raise ValueError("offsets must be int32 [F+1]")
+        f = offsets.shape[0] - 1
+        blocks, index, max_n = table.device_arrays(self.device)
+        vel = torch.empty((f, 3), dtype=torch.float64, device=self.device)
+        r2 = torch.empty((f,), dtype=torch.float64, device=self.device)
+        frac = torch.empty((f,), dtype=torch.float64, device=self.device)
+        status = torch.empty((f,), dtype=torch.int32, device=self.device)
+        nat.check(self.lib.radar_ego_velocity(self.ctx, nat.ptr(points), nat.ptr(offsets.contiguous()), f, int(dims),
+                                              nat.ptr(blocks), nat.ptr(index), int(max_n), int(table.max_trials),
+                                              int(table.min_samples), float(residual_threshold), float(stop_probability),
+                                              nat.ptr(vel), nat.ptr(r2), nat.ptr(frac), nat.ptr(status), _stream_ptr()),
+                  self.ctx)
+        return vel, r2, frac, status
+
     def sar_image(self, aperture: torch.Tensor, positions: torch.Tensor, dirs: torch.Tensor, lambda_m: float,
                   g_begin: int = 0, g_end: Optional[int] = None, out=None) -> torch.Tensor:
         """aperture complex64 [S,N], positions float64 [3,N], dirs float64 [3,G] -> complex64 [S, g_end-g_begin]."""

@@ -659,3 +659,109 @@ def strip_map_response(cube_v, rx_index=0) -> np.ndarray:
     176-188): un-windowed fft2 of one antenna, fftshift over the chirp axis, complex."""
     x = np.asarray(cube_v)[rx_index].astype(np.complex128)
     return np.fft.fft2(x, axes=(-2, -1))[:, shift_index(x.shape[1])]
+
+
+# ------------------------------------------------------------------------------------------------
+# SURVEY 8f next-2: point cloud -> ego velocity (least squares inside RANSAC)
+# ------------------------------------------------------------------------------------------------
+_RANSAC_EPS = np.spacing(1)
+
+
+def ransac_subsets(n_points: int, min_samples: int = 10, max_trials: int = 20, seed: int = 42,
+                   policy: str = "permutation") -> np.ndarray:
+    """Random subsets sklearn's RANSACRegressor.fit draws with random_state=seed: ``check_random_state(seed)`` builds a
+    fresh ``np.random.RandomState(seed)`` on every fit, and every trial calls
+    ``sample_without_replacement(n, min_samples, random_state=rng)`` exactly once, so the subsets depend only on
+    (n_points, trial).  sklearn 1.9.0 (the build the goldens ran on; utils/_random.pyx) takes
+    ``rng.permutation(n)[:k]`` for 0.01 < k/n < 0.99 ("permutation"); outside that band, and in the older releases the
+    reference pins (1.5.2: "reservoir" for every ratio below 0.99 - not verifiable here), it is reservoir sampling
+    (ratio >= 0.2) or tracking selection.  -> int [max_trials, min_samples]."""
+    rng = np.random.RandomState(seed)
+    out = np.empty((max_trials, min_samples), dtype=np.int64)
+    ratio = min_samples / n_points
+    for t in range(max_trials):
+        if policy == "permutation" and 0.01 < ratio < 0.99:
+            out[t] = rng.permutation(n_points)[:min_samples]
+        elif ratio < 0.2 and not (policy == "reservoir" and ratio >= 0.01):
+            sel, chosen = [], set()
+            for _ in range(min_samples):
+                j = rng.randint(n_points)
+                while j in chosen:
+                    j = rng.randint(n_points)
+                chosen.add(j)
+                sel.append(j)
+            out[t] = sel
+        else:
+            res = np.arange(min_samples)
+            for i in range(min_samples, n_points):
+                j = rng.randint(0, i + 1)
+                if j < min_samples:
+                    res[j] = i
+            out[t] = res
+    return out
+
+
+def _r2(y, pred):
+    """sklearn.metrics.r2_score with force_finite=True on 1-D targets; nan below two samples."""
+    if y.shape[0] < 2:
+        return float("nan")
+    num = float(np.sum((y - pred) ** 2))
+    den = float(np.sum((y - np.mean(y)) ** 2))
+    if den == 0.0:
+        return 1.0 if num == 0.0 else 0.0
+    return 1.0 - num / den
+
+
+def _dynamic_max_trials(n_inliers, n_samples, min_samples, probability):
+    ratio = n_inliers / float(n_samples)
+    nom = max(_RANSAC_EPS, 1 - probability)
+    denom = max(_RANSAC_EPS, 1 - ratio ** min_samples)
+    if nom == 1:
+        return 0
+    if denom == 1:
+        return float("inf")
+    return abs(float(np.ceil(np.log(nom) / np.log(denom))))
+
+
+def ego_velocity_ransac(points: np.ndarray, dims: int = 2, residual_threshold: float = 0.15, min_samples: int = 10,
+                        max_trials: int = 20, seed: int = 42, policy: str = "permutation"):
+    """VelocityEstimator.lsq_fit_ego_vel_ransac_points_2D / _3D (reference point_cloud_processing/vel_estimator.py:
+    76-170): y = -v, H = xyz[:dims]/|xyz[:dims]|, RANSACRegressor(LinearRegression(fit_intercept=False),
+    residual_threshold=0.15, random_state=42, max_trials=20, min_samples=10) restated from sklearn's fit loop
+    (linear_model/_ransac.py): per trial a least-squares fit on the subset, inliers = |y - H c| <= threshold, keep the
+    trial with more inliers (ties: the better R^2 on its inliers), shrink max_trials with the inlier ratio
+    (stop_probability 0.99), final fit on the best inlier set.  Any ValueError inside sklearn (fewer points than
+    min_samples, non-finite input, no consensus set) is swallowed by the reference -> zeros.
+    -> (coef [dims] or zeros(2) on failure, r2 of the final model on its inliers (0 if <= 3 inliers), inlier fraction,
+        inlier mask or None)."""
+    pts = np.asarray(points, dtype=np.float64)
+    fail = (np.array([0.0, 0.0]), 0.0, 0.0, None)
+    n = pts.shape[0]
+    if n < min_samples:
+        return fail
+    y = -1 * pts[:, 3]
+    with np.errstate(invalid="ignore", divide="ignore"):
+        h = pts[:, 0:dims] / np.linalg.norm(pts[:, 0:dims], axis=1, keepdims=True)
+    if not (np.all(np.isfinite(h)) and np.all(np.isfinite(y))):
+        return fail
+    subsets = ransac_subsets(n, min_samples, max_trials, seed, policy)
+    n_best, score_best, mask_best = 1, -np.inf, None
+    trials, limit = 0, max_trials
+    while trials < limit:
+        idx = subsets[trials]
+        trials += 1
+        coef = np.linalg.lstsq(h[idx], y[idx], rcond=None)[0]
+        mask = np.abs(y - h @ coef) <= residual_threshold
+        n_in = int(mask.sum())
+        if n_in < n_best:
+            continue
+        score = _r2(y[mask], h[mask] @ coef)
+        if n_in == n_best and score < score_best:
+            continue
+        n_best, score_best, mask_best = n_in, score, mask
+        limit = min(limit, _dynamic_max_trials(n_best, n, min_samples, 0.99))
+    if mask_best is None:
+        return fail
+    coef = np.linalg.lstsq(h[mask_best], y[mask_best], rcond=None)[0]
+    r2 = _r2(y[mask_best], h[mask_best] @ coef) if mask_best.sum() > 3 else 0.0
+    return coef, r2, mask_best.sum() / n, mask_best

@@ -77,6 +77,10 @@ def test_native_stream_kernel_phases_on_cpu():
     assert worst < 2e-6
 
 
+def test_native_ego_velocity_solvers_on_cpu():
+    assert "ok" in _native_check("host_vel_solve_check")
+
+
 def test_no_cpu_fallback_when_library_missing(monkeypatch):
     from mmwave_radar_processing_b200 import _native
     monkeypatch.setattr(_native, "_lib", None)
