@@ -115,6 +115,10 @@ int launch_sar_image(radar_ctx* ctx, const cf* aperture, int num_samples, int n_
     if (n_elems <= 0 || n_dirs <= 0 || !(lambda_m > 0)) return set_error(ctx, RADAR_E_INVALID, "empty aperture / grid or bad wavelength");
     if (g_begin < 0 || g_end > n_dirs || g_begin > g_end) return set_error(ctx, RADAR_E_INVALID, "voxel slice [%d,%d) outside [0,%d)", g_begin, g_end, n_dirs);
     if (g_begin == g_end) return RADAR_OK;
+    if (ctx->sar_mode != 1) {              // tensor-core path (kernels_sar_tc.cu); 1 = shape not handled there
+        const int rc = launch_sar_image_tc(ctx, aperture, num_samples, n_elems, positions, dirs, n_dirs, lambda_m, g_begin, g_end, out, st);
+        if (rc <= 0) return rc;
+    }
     SarArgs a;
     a.aperture = aperture; a.S = num_samples; a.N = n_elems; a.pos = positions; a.dirs = dirs; a.G = n_dirs;
     a.inv_lambda = 1.0 / lambda_m;

@@ -1,0 +1,347 @@
+// K5a on the 5th-generation tensor cores: the synthetic-array beamformer as a split-precision TF32 GEMM (tcgen05 + TMEM).
+//
+// Reference arithmetic (processors/simple_synthetic_array_beamformer_processor_multiFrame.py:499-585):
+//   out[:, g] = FFT_S( hanning(S) * sum_n hamming(N)[n] * x[s, n] * exp(+2 pi i (d_g . p_n) / lambda) )
+//
+// The complex product  beams[g][s] = sum_n W[n][g] X[s][n]  is written as ONE real GEMM  D[M x Nb] = A[M x K] B[K x Nb]:
+//   M  = directions (128 per accumulator tile),          K = 2 N  (k = 2n: Re W, k = 2n+1: Im W),
+//   Nb = 2 SP columns (SP = S rounded up to 8): column s holds Re beams, column SP + s holds Im beams,
+//   B[2n][s] = Xr, B[2n+1][s] = -Xi, B[2n][SP+s] = Xi, B[2n+1][SP+s] = Xr   (X pre-multiplied by hamming(N)[n]).
+// * A is never stored in HBM: every thread owns one direction and generates its row of the current K chunk - the phase
+//   (d.p)/lambda reaches 1e2..1e4 turns, so it is reduced modulo 1 in fp64 before the fp32 sincospi - and writes it
+//   straight into shared memory in the UMMA canonical K-major layout (no swizzle: 8-row x 16-byte core matrices).
+// * B is prepared once per call (sar_tc_prep_kernel) in global memory in exactly that layout, chunk by chunk, so a CTA
+//   moves a chunk with flat 16-byte copies.
+// * TF32 keeps 11 significant bits, far from the 1e-4 bar, so both operands are split  v = hi + lo  (hi = v rounded to
+//   TF32, lo = v - hi exactly) and three MMAs accumulate  hi.hi + hi.lo + lo.hi  in the fp32 TMEM accumulator: relative
+//   error ~2^-21 per product.  The dropped lo.lo term is ~2^-22.
+// * One thread issues tcgen05.mma; tcgen05.commit arrives on an mbarrier per shared-memory stage, so generating chunk
+//   c+1 overlaps the MMAs of chunk c (two stages).  The accumulators (128 lanes x Nb columns per tile, MT tiles per CTA so
+//   a B chunk is reused for 128 MT directions) stay in TMEM for the whole K loop and are read once with tcgen05.ld.
+// * The tensor core adds into the accumulator with truncation; the K loop is cut into segments that are drained from
+//   TMEM and summed in ordinary fp32 (see the drain in sar_tc_kernel).
+// * The beams go to a scratch array [S][width] (coalesced: lanes = directions); sar_range_fft_kernel applies Hann and the
+//   range FFT per direction with the shared-memory FFT of the range-Doppler family.
+#include "radar_internal.h"
+#include "rd_core.cuh"
+
+namespace rb {
+
+constexpr int kTcKC = 32;                 // real k-values per chunk (= 16 aperture elements); 4 MMA k-steps of 8
+constexpr int kTcElems = kTcKC / 2;
+constexpr int kTcATile = 128 * kTcKC;     // floats of one A tile (128 rows)
+constexpr int kTcFftDirs = 32;
+
+__host__ __device__ inline int tc_canon(int row, int k) {   // float index inside a K-major no-swizzle tile, kTcKC wide
+    return ((row >> 3) * (kTcKC / 4) + (k >> 2)) * 32 + (row & 7) * 4 + (k & 3);
+}
+
+// ---- operand preparation -----------------------------------------------------------------------------------------
+struct SarPrepArgs {
+    const cf* aperture;   // [S][N]
+    int S, N, SP, NB, n_chunks;
+    const double* pos;    // [3][N]
+    double inv_lambda;
+    float* bblk;          // [n_chunks][2][NB * kTcKC]
+    double* posl;         // [3][n_chunks * kTcElems]  positions / lambda, zero padded
+};
+
+__device__ __forceinline__ float tf32_round(float v) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+    return __uint_as_float(r);
+}
+
+__global__ void __launch_bounds__(256) sar_tc_prep_kernel(const __grid_constant__ SarPrepArgs a) {
+    const int c = blockIdx.x;
+    const int npad = a.n_chunks * kTcElems;
+    for (int i = threadIdx.x; i < 3 * kTcElems; i += blockDim.x) {
+        const int axis = i / kTcElems, n = c * kTcElems + (i - axis * kTcElems);
+        a.posl[(size_t)axis * npad + n] = n < a.N ? a.pos[(size_t)axis * a.N + n] * a.inv_lambda : 0.0;
+    }
+    float* hi = a.bblk + (size_t)c * 2 * a.NB * kTcKC;
+    float* lo = hi + a.NB * kTcKC;
+    for (int i = threadIdx.x; i < a.NB * kTcElems; i += blockDim.x) {
+        const int col = i / kTcElems, nl = i - col * kTcElems;      // consecutive threads: consecutive n (coalesced reads)
+        const int n = c * kTcElems + nl;
+        const int s = col >= a.SP ? col - a.SP : col;
+        cf x = cmake(0.f, 0.f);
+        if (s < a.S && n < a.N) {
+            const double ham = a.N > 1 ? 0.54 - 0.46 * cospi(2.0 * (double)n / (double)(a.N - 1)) : 1.0;
+            x = cscale(__ldg(a.aperture + (size_t)s * a.N + n), (float)ham);
+        }
+        const float v0 = col >= a.SP ? x.y : x.x;       // multiplies Re W
+        const float v1 = col >= a.SP ? x.x : -x.y;      // multiplies Im W
+        const float h0 = tf32_round(v0), h1 = tf32_round(v1);
+        const int idx = tc_canon(col, 2 * nl);
+        hi[idx] = h0; hi[idx + 1] = h1;
+        lo[idx] = v0 - h0; lo[idx + 1] = v1 - h1;
+    }
+}
+
+// ---- tcgen05 / mbarrier helpers ------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = smem_u32(bar);
+    uint32_t ok = 0, spins = 0;
+    do {
+        asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                     : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
+        if (!ok && ++spins > (1u << 27)) __trap();       // a lost arrive must not hang the device
+    } while (!ok);
+}
+// K-major, no swizzle: core matrices of 8 rows x 16 bytes; LBO = 128 B between the two 16-byte K chunks of one MMA,
+// SBO = kTcKC/4 * 128 B between 8-row groups; descriptor version 1 (sm_100).
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
+    return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)(128 >> 4) << 16) | ((uint64_t)((kTcKC / 4) * 128 >> 4) << 32) |
+           (1ull << 46);
+}
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+                   "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                 : "r"(taddr));
+}
+
+// ---- the GEMM ---------------------------------------------------------------------------------------------------
+struct SarTcArgs {
+    const float* bblk;    // prepared B chunks
+    const double* posl;   // [3][npad] positions / lambda
+    const double* dirs;   // [3][G]
+    int npad, n_chunks, seg_chunks, G, S, SP, NB;
+    int g_begin, g_end;
+    cf* beams;            // [S][g_end - g_begin]
+};
+
+template <int MT>
+__global__ void __launch_bounds__(128 * MT, 1) sar_tc_kernel(const __grid_constant__ SarTcArgs a) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int mt = tid >> 7, row = tid & 127;
+    const int b_floats = a.NB * kTcKC;                         // one of B_hi / B_lo
+    const int stage_floats = MT * 2 * kTcATile + 2 * b_floats;
+    float* stage0 = reinterpret_cast<float*>(smem_raw);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(stage0 + 2 * stage_floats);     // empty[0], empty[1], done
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
+
+    if (tid == 0) {
+        mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(&bars[2], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {                                           // one warp allocates (and later frees) the accumulators
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)), "r"(256 * MT) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;
+
+    // this thread's direction (clamped: surplus rows of the last tile compute a valid direction and are not written)
+    const int width = a.g_end - a.g_begin;
+    const int g_out = blockIdx.x * (128 * MT) + mt * 128 + row;            // column of `beams`
+    const int g = a.g_begin + min(g_out, width - 1);
+    const double dx = a.dirs[g], dy = a.dirs[(size_t)a.G + g], dz = a.dirs[2 * (size_t)a.G + g];
+    // M = 128, N = NB, fp32 accumulate, TF32 x TF32, both operands K-major
+    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(a.NB >> 3) << 17) | ((128u >> 4) << 24);
+
+    int n_drained = 0;
+    for (int c = 0; c < a.n_chunks; ++c) {
+        const int s = c & 1;
+        const int c_seg = c % a.seg_chunks;
+        const bool seg_end = (c_seg == a.seg_chunks - 1) || (c == a.n_chunks - 1);
+        float* st = stage0 + s * stage_floats;
+        float* a_hi = st + mt * kTcATile;
+        float* a_lo = st + MT * kTcATile + mt * kTcATile;
+        float* b_dst = st + MT * 2 * kTcATile;
+        if (c >= 2) {                                          // the MMAs of chunk c-2 have finished reading this stage
+            mbar_wait(&bars[s], ((c >> 1) - 1) & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        }
+        // B chunk: flat copy (already in the canonical layout)
+        {
+            const float4* src = reinterpret_cast<const float4*>(a.bblk + (size_t)c * 2 * b_floats);
+            float4* dst = reinterpret_cast<float4*>(b_dst);
+            for (int i = tid; i < 2 * b_floats / 4; i += 128 * MT) dst[i] = __ldg(src + i);
+        }
+        // A chunk: this thread's row, kTcElems steering coefficients
+        const double* px = a.posl + (size_t)c * kTcElems;
+#pragma unroll 2
+        for (int nl = 0; nl < kTcElems; nl += 2) {
+            float w[4];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const double turns = fma(dx, __ldg(px + nl + e), fma(dy, __ldg(px + a.npad + nl + e), dz * __ldg(px + 2 * (size_t)a.npad + nl + e)));
+                const float frac = (float)(turns - rint(turns));
+                sincospif(2.0f * frac, &w[2 * e + 1], &w[2 * e]);
+            }
+            float4 h, l;
+            h.x = tf32_round(w[0]); h.y = tf32_round(w[1]); h.z = tf32_round(w[2]); h.w = tf32_round(w[3]);
+            l.x = w[0] - h.x; l.y = w[1] - h.y; l.z = w[2] - h.z; l.w = w[3] - h.w;
+            const int idx = ((row >> 3) * (kTcKC / 4) + (nl >> 1)) * 32 + (row & 7) * 4;
+            *reinterpret_cast<float4*>(a_hi + idx) = h;
+            *reinterpret_cast<float4*>(a_lo + idx) = l;
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy writes -> visible to the tensor core
+        __syncthreads();
+        if (tid == 0) {
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t b_hi = smem_u32(b_dst), b_lo = b_hi + b_floats * 4;
+#pragma unroll
+            for (int m = 0; m < MT; ++m) {
+                const uint32_t ah = smem_u32(st + m * kTcATile), al = smem_u32(st + MT * kTcATile + m * kTcATile);
+                const uint32_t d = tmem_base + m * 256;
+#pragma unroll
+                for (int j = 0; j < kTcKC / 8; ++j) {                      // 8 k-values = two 16-byte chunks = 256 B further on
+                    const uint32_t off = j * 256;
+                    umma_tf32(d, umma_desc(al + off), umma_desc(b_hi + off), idesc, (c_seg | j) != 0);
+                    umma_tf32(d, umma_desc(ah + off), umma_desc(b_lo + off), idesc, 1);
+                    umma_tf32(d, umma_desc(ah + off), umma_desc(b_hi + off), idesc, 1);
+                }
+            }
+            umma_commit(&bars[s]);
+            if (seg_end) umma_commit(&bars[2]);
+        }
+        if (seg_end) {
+            // The tensor core adds into the fp32 accumulator with truncation, a bias that grows with the length of the
+            // accumulation chain (measured 1.3e-8 N relative).  The chain is therefore cut into segments: each one is
+            // drained from TMEM and summed into `beams` with ordinary round-to-nearest fp32 adds.
+            mbar_wait(&bars[2], n_drained & 1);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            // TMEM lane = direction row, column s = Re, column SP + s = Im
+            const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + mt * 256;
+            for (int s0 = 0; s0 < a.SP; s0 += 16) {
+                uint32_t re[16], im[16];
+                tmem_ld16(taddr + s0, re);
+                tmem_ld16(taddr + a.SP + s0, im);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (g_out < width) {
+                    cf* dst = a.beams + (size_t)s0 * width + g_out;
+                    cf old[16];
+                    if (n_drained > 0) {                                   // all loads in flight before the first store
+#pragma unroll
+                        for (int i = 0; i < 16; ++i)
+                            old[i] = (s0 + i < a.S) ? __ldcg(dst + (size_t)i * width) : cmake(0.f, 0.f);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; ++i) old[i] = cmake(0.f, 0.f);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 16; ++i)
+                        if (s0 + i < a.S)
+                            __stcg(dst + (size_t)i * width, cmake(__uint_as_float(re[i]) + old[i].x, __uint_as_float(im[i]) + old[i].y));
+                }
+            }
+            ++n_drained;
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");      // ordered before the next segment's first MMA
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256 * MT) : "memory");
+}
+
+// ---- Hann + range FFT of every beam -----------------------------------------------------------------------------
+struct SarFftArgs {
+    const cf* beams;      // [S][width]
+    int S, width;
+    const float* winS; const cf* twS; const uint16_t* posS;
+    cf* out;              // [S][width]
+    FftPlan planS;
+    FastDiv divDirs;
+};
+
+__global__ void __launch_bounds__(256) sar_range_fft_kernel(const __grid_constant__ SarFftArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int S = a.S, Gp = kTcFftDirs | 1;
+    SmemArena ar(smem_raw);
+    cf* tile = ar.take<cf>(S * Gp);
+    cf* tw = ar.take<cf>(S);
+    float* win = ar.take<float>(S);
+    uint16_t* pos = ar.take<uint16_t>(S);
+    load_table(tw, a.twS, S);
+    load_table(win, a.winS, S);
+    load_table(pos, a.posS, S);
+    __syncthreads();
+    const int g0 = blockIdx.x * kTcFftDirs;
+    const int cells = S * kTcFftDirs;
+    for (int i = threadIdx.x; i < cells; i += blockDim.x) {
+        const int s = i / kTcFftDirs, gl = i - s * kTcFftDirs;
+        const cf v = (g0 + gl < a.width) ? a.beams[(size_t)s * a.width + g0 + gl] : cmake(0.f, 0.f);
+        tile[s * Gp + gl] = cscale(v, win[s]);
+    }
+    __syncthreads();
+    fft_axis(tile, Gp, 1, kTcFftDirs, a.divDirs, a.planS, tw);
+    for (int i = threadIdx.x; i < cells; i += blockDim.x) {
+        const int k = i / kTcFftDirs, gl = i - k * kTcFftDirs;
+        if (g0 + gl < a.width) a.out[(size_t)k * a.width + g0 + gl] = tile[pos[k] * Gp + gl];
+    }
+}
+
+// 1 = shape not handled here (caller falls back to the FP32-pipe kernel), 0 = launched, < 0 = error
+int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const double* positions, const double* dirs,
+                        int G, double lambda_m, int g_begin, int g_end, cf* out, cudaStream_t st) {
+    const int SP = (S + 7) & ~7, NB = 2 * SP;
+    if (NB > 256 || (NB & 15) != 0) return 1;                   // tcgen05.mma with M = 128 takes N in 16..256, multiples of 16
+    const int width = g_end - g_begin;
+    const int n_chunks = (N + kTcElems - 1) / kTcElems, npad = n_chunks * kTcElems;
+    const size_t bblk_bytes = (size_t)n_chunks * 2 * NB * kTcKC * sizeof(float);
+    const size_t posl_bytes = (size_t)3 * npad * sizeof(double);
+    const size_t beams_bytes = (size_t)S * width * sizeof(cf);
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    if (int rc = ensure_scratch(ctx, up(bblk_bytes) + up(posl_bytes) + up(beams_bytes))) return rc;
+    unsigned char* base = reinterpret_cast<unsigned char*>(ctx->scratch);
+    float* bblk = reinterpret_cast<float*>(base);
+    double* posl = reinterpret_cast<double*>(base + up(bblk_bytes));
+    cf* beams = reinterpret_cast<cf*>(base + up(bblk_bytes) + up(posl_bytes));
+
+    SarPrepArgs p{aperture, S, N, SP, NB, n_chunks, positions, 1.0 / lambda_m, bblk, posl};
+    sar_tc_prep_kernel<<<n_chunks, 256, 0, st>>>(p);
+    RB_CUDA_OK(ctx, cudaGetLastError());
+
+    // segment length: measured bias 1.3e-8 * sqrt(N * len) relative; keep it near 1e-5
+    int seg_chunks = (int)(6.0e5 / (double)N) / kTcElems;
+    seg_chunks = seg_chunks < 4 ? 4 : (seg_chunks > n_chunks ? n_chunks : seg_chunks);
+    if (ctx->sar_seg_chunks > 0) seg_chunks = ctx->sar_seg_chunks;
+    SarTcArgs a{bblk, posl, dirs, npad, n_chunks, seg_chunks, G, S, SP, NB, g_begin, g_end, beams};
+    auto smem_for = [&](int tiles) {
+        const size_t stage_floats = (size_t)tiles * 2 * kTcATile + 2 * (size_t)NB * kTcKC;
+        return 2 * stage_floats * sizeof(float) + 3 * sizeof(uint64_t) + 16;
+    };
+    // two accumulator tiles per CTA (a B chunk serves 256 directions) once every SM has work anyway and the stages fit
+    int mt = (width > 128 * ctx->sm_count && smem_for(2) <= (size_t)ctx->max_smem_optin) ? 2 : 1;
+    if (ctx->sar_mode == 2) mt = 1;
+    if (ctx->sar_mode == 3 && smem_for(2) <= (size_t)ctx->max_smem_optin) mt = 2;
+    const size_t smem = smem_for(mt);
+    if (smem > (size_t)ctx->max_smem_optin) return 1;
+    const int per_cta = 128 * mt;
+    const unsigned grid = (unsigned)((width + per_cta - 1) / per_cta);
+    if (mt == 2) {
+        RB_CUDA_OK(ctx, cudaFuncSetAttribute(sar_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        sar_tc_kernel<2><<<grid, 256, smem, st>>>(a);
+    } else {
+        RB_CUDA_OK(ctx, cudaFuncSetAttribute(sar_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        sar_tc_kernel<1><<<grid, 128, smem, st>>>(a);
+    }
+    RB_CUDA_OK(ctx, cudaGetLastError());
+
+    SarFftArgs f{beams, S, width, ctx->fftS.hann, ctx->fftS.tw, ctx->fftS.pos, out, ctx->fftS.plan, make_fastdiv(kTcFftDirs)};
+    const size_t fsmem = arena_bytes((size_t)S * (kTcFftDirs | 1), sizeof(cf)) + arena_bytes(S, sizeof(cf)) + arena_bytes(S, 4) + arena_bytes(S, 2);
+    RB_CUDA_OK(ctx, cudaFuncSetAttribute(sar_range_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
+    sar_range_fft_kernel<<<(unsigned)((width + kTcFftDirs - 1) / kTcFftDirs), 256, fsmem, st>>>(f);
+    RB_CUDA_OK(ctx, cudaGetLastError());
+    return RADAR_OK;
+}
+
+}  // namespace rb

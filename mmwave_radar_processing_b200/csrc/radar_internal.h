@@ -42,6 +42,8 @@ struct radar_ctx {
     double* angle_cos = nullptr; double* angle_sin = nullptr;   // cos / sin of angle_bins (host fp64)
     void* scratch = nullptr; size_t scratch_bytes = 0;
     int force_generic = 0;                        // RADAR_B200_GENERIC=1: generic range-Doppler kernel only, =2: skip the streaming kernel (tests)
+    int sar_mode = 0;                             // RADAR_B200_SAR: 0 auto (tcgen05 when the shape fits), 1 FP32-pipe kernel, 2/3 tcgen05 with 1/2 tiles per CTA
+    int sar_seg_chunks = 0;                       // RADAR_B200_SAR_SEG: chunks (16 elements) per accumulation segment, 0 = automatic
     int stream_variant = 0;                       // RADAR_B200_STREAM_VARIANT: tuning candidate of the streaming kernel
     char err[512] = {0};
 };
@@ -105,6 +107,8 @@ int launch_ego_velocity(radar_ctx* ctx, const double* points, const int32_t* off
                         const int32_t* subsets, const int32_t* subset_index, int table_max_n, int max_trials,
                         int min_samples, double residual_threshold, double stop_probability, double* vel_out,
                         double* r2_out, double* frac_out, int32_t* status_out, cudaStream_t st);
+int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const double* positions, const double* dirs,
+                        int G, double lambda_m, int g_begin, int g_end, cf* out, cudaStream_t st);
 int launch_sar_image(radar_ctx* ctx, const cf* aperture, int num_samples, int n_elems, const double* positions,
                      const double* dirs, int n_dirs, double lambda_m, int g_begin, int g_end, cf* out,
                      cudaStream_t st);

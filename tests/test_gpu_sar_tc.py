@@ -1,0 +1,90 @@
+"""GPU parity of the tensor-core SAR beamformer (csrc/kernels_sar_tc.cu: tcgen05 TF32 GEMM with hi/lo operand splitting)
+against a direct fp64 evaluation of the reference formula (compute_synthetic_response,
+processors/simple_synthetic_array_beamformer_processor_multiFrame.py:543-585) and against the FP32-pipe kernel, over the
+shapes that take the tensor-core path, the fallback shapes, both tile configurations and voxel slices."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import rel_l2
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4          # relative L2 (BASELINE.json); measured ~3e-7 for the split-TF32 path
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    return torch
+
+
+def sar_case(s, n, g, seed):
+    rng = np.random.default_rng(seed)
+    lam = 0.0039
+    x = (rng.integers(-2000, 2000, (s, n)) + 1j * rng.integers(-2000, 2000, (s, n))).astype(np.complex64)
+    t = np.arange(n) * 1e-4
+    pos = np.stack([0.01 * t + 1e-5 * rng.standard_normal(n), 0.5 * t, 1e-5 * rng.standard_normal(n)])     # metres: 1e2..1e4 turns
+    az = rng.uniform(-1.0, 1.0, g)
+    el = rng.uniform(-0.3, 0.3, g)
+    dirs = np.stack([np.cos(az) * np.cos(el), np.sin(az) * np.cos(el), np.sin(el)])
+    return x, pos, dirs, lam
+
+
+def sar_direct(x, pos, dirs, lam, cols):
+    """fp64: out[:, g] = FFT_S(hanning(S) * sum_n hamming(N)[n] x[s, n] exp(+2 pi i d_g.p_n / lambda)) for the columns asked."""
+    s, n = x.shape
+    w = np.hamming(n)[:, None] * np.exp(2j * np.pi * (pos.T @ dirs[:, cols]) / lam)
+    return np.fft.fft((x.astype(np.complex128) @ w) * np.hanning(s)[:, None], axis=0)
+
+
+def engine_with_mode(mode, s):
+    from mmwave_radar_processing_b200.engine import RadarEngine
+    old = os.environ.get("RADAR_B200_SAR")
+    os.environ["RADAR_B200_SAR"] = str(mode)
+    try:
+        return RadarEngine(1, s, 1, 1)
+    finally:
+        if old is None:
+            del os.environ["RADAR_B200_SAR"]
+        else:
+            os.environ["RADAR_B200_SAR"] = old
+
+
+@pytest.mark.parametrize("s,n,g", [(90, 500, 300), (63, 210, 129), (64, 37, 128), (100, 333, 200), (128, 100, 64), (120, 65, 257)])
+def test_tensor_core_path_matches_fp64_and_fp32_kernel(torch_cuda, s, n, g):
+    torch = torch_cuda
+    x, pos, dirs, lam = sar_case(s, n, g, seed=s + n)
+    want = sar_direct(x, pos, dirs, lam, np.arange(g))
+    xs, ps, ds = torch.from_numpy(x).cuda(), torch.from_numpy(pos).cuda(), torch.from_numpy(dirs).cuda()
+    outs = {}
+    for mode in (1, 2, 3):              # FP32-pipe kernel, tcgen05 one tile per CTA, tcgen05 two tiles per CTA
+        eng = engine_with_mode(mode, s)
+        outs[mode] = eng.sar_image(xs, ps, ds, lam).cpu().numpy()
+        err = rel_l2(outs[mode], want)
+        assert err < TOL, (mode, err)
+    assert rel_l2(outs[2], outs[1]) < 1e-5
+    np.testing.assert_array_equal(outs[2], outs[3])                 # tiling must not change a single bit
+    eng = engine_with_mode(2, s)
+    lo, hi = g // 3, g - 5
+    part = eng.sar_image(xs, ps, ds, lam, lo, hi).cpu().numpy()     # voxel slice (multi-GPU sharding unit)
+    np.testing.assert_array_equal(part, outs[2][:, lo:hi])
+
+
+def test_fallback_shape_and_throughput_grid(torch_cuda):
+    """S = 200 does not fit one MMA (N = 2 S > 256): the FP32-pipe kernel serves it.  The throughput grid of SURVEY.md
+    section 8d (S = 90, N = 2000, G = 32768) is checked on a sample of directions."""
+    torch = torch_cuda
+    x, pos, dirs, lam = sar_case(200, 64, 40, seed=5)
+    eng = engine_with_mode(0, 200)
+    out = eng.sar_image(torch.from_numpy(x).cuda(), torch.from_numpy(pos).cuda(), torch.from_numpy(dirs).cuda(), lam)
+    assert rel_l2(out.cpu().numpy(), sar_direct(x, pos, dirs, lam, np.arange(40))) < TOL
+    x, pos, dirs, lam = sar_case(90, 2000, 32768, seed=6)
+    eng = engine_with_mode(0, 90)
+    out = eng.sar_image(torch.from_numpy(x).cuda(), torch.from_numpy(pos).cuda(), torch.from_numpy(dirs).cuda(), lam)
+    cols = np.random.default_rng(0).choice(32768, 96, replace=False)
+    cols[:4] = [0, 127, 128, 32767]
+    assert rel_l2(out[:, torch.from_numpy(cols).cuda()].cpu().numpy(), sar_direct(x, pos, dirs, lam, cols)) < TOL
+    assert torch.isfinite(torch.view_as_real(out)).all()

@@ -1,0 +1,64 @@
+#!/usr/bin/env python
+"""Timing of radar_sar_image on the throughput grid of SURVEY.md section 8d (S = 90, N = 2000, G = 32768) for the
+FP32-pipe kernel and the tcgen05 split-TF32 path.  One JSON line per mode: ms per image, useful complex-GEMM TFLOP/s
+(8 S N G flop) and, for the tensor-core path, executed TF32 TFLOP/s (3 MMAs per product, padded tile) against the dense
+bf16 peak of MEASURED_PEAKS.json (TF32 peaks at half of it).  CUDA events on the launching stream, warm-up first."""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, REPO)
+from mmwave_radar_processing_b200.engine import RadarEngine  # noqa: E402
+
+
+def main():
+    s, n, g = 90, 2000, 32768
+    rng = np.random.default_rng(0)
+    x = (rng.integers(-2000, 2000, (s, n)) + 1j * rng.integers(-2000, 2000, (s, n))).astype(np.complex64)
+    t = np.arange(n) * 1e-4
+    pos = np.stack([0.01 * t, 0.5 * t, np.zeros(n)])
+    az, el = rng.uniform(-1, 1, g), rng.uniform(-0.3, 0.3, g)
+    dirs = np.stack([np.cos(az) * np.cos(el), np.sin(az) * np.cos(el), np.sin(el)])
+    xs, ps, ds = torch.from_numpy(x).cuda(), torch.from_numpy(pos).cuda(), torch.from_numpy(dirs).cuda()
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(REPO, "MEASURED_PEAKS.json")))
+    except Exception:  # noqa: BLE001
+        pass
+    bf16_peak = float(peaks.get("bf16_tflops", peaks.get("tensor_bf16_tflops", 0.0)) or 0.0)
+    ref = None
+    for mode, label in ((1, "fp32_pipe"), (2, "tcgen05_tf32x3_1tile"), (3, "tcgen05_tf32x3_2tiles"), (0, "auto")):
+        os.environ["RADAR_B200_SAR"] = str(mode)
+        eng = RadarEngine(1, s, 1, 1)
+        out = torch.empty((s, g), dtype=torch.complex64, device="cuda")
+        for _ in range(3):
+            eng.sar_image(xs, ps, ds, 0.0039, out=out)
+        torch.cuda.synchronize()
+        reps = 5 if mode == 1 else 20
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            eng.sar_image(xs, ps, ds, 0.0039, out=out)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        if ref is None:
+            ref = out.clone()
+        line = {"kernel": label, "S": s, "N": n, "G": g, "ms_per_image": ms,
+                "useful_tflops": 8.0 * s * n * g / (ms * 1e-3) / 1e12,
+                "rel_l2_vs_fp32_pipe": float((torch.linalg.norm(out - ref) / torch.linalg.norm(ref)).item())}
+        if mode != 1:
+            executed = 3 * 2.0 * 192 * (2 * 2000) * g        # three MMAs, N padded to 192 columns, K = 2 N real
+            line["executed_tf32_tflops"] = executed / (ms * 1e-3) / 1e12
+            if bf16_peak:
+                line["frac_of_measured_bf16_peak"] = line["executed_tf32_tflops"] / bf16_peak
+                line["measured_bf16_peak_tflops"] = bf16_peak
+        print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()
