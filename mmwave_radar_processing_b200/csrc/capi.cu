@@ -147,6 +147,8 @@ int radar_ctx_create(const radar_shape* shape, int device, radar_ctx** out_ctx) 
     ctx->shape = *shape;
     ctx->V = shape->num_rx * shape->chirps_per_loop;
     ctx->C = shape->chirps_per_loop * shape->num_loops;
+    { const char* db = std::getenv("RADAR_B200_SAR_DBG"); ctx->sar_dbg = db ? std::atoi(db) : 0; }
+    { const char* tp = std::getenv("RADAR_B200_SAR_TPR"); ctx->sar_tpr = tp ? std::atoi(tp) : 0; }
     { const char* sg = std::getenv("RADAR_B200_SAR_SEG"); ctx->sar_seg_chunks = sg ? std::atoi(sg) : 0; }
     { const char* sm = std::getenv("RADAR_B200_SAR"); ctx->sar_mode = sm ? std::atoi(sm) : 0; }
     { const char* sv = std::getenv("RADAR_B200_STREAM_VARIANT"); ctx->stream_variant = sv ? std::atoi(sv) : 0; }

@@ -11,7 +11,8 @@
 //   (d.p)/lambda reaches 1e2..1e4 turns, so it is reduced modulo 1 in fp64 before the fp32 sincospi - and writes it
 //   straight into shared memory in the UMMA canonical K-major layout (no swizzle: 8-row x 16-byte core matrices).
 // * B is prepared once per call (sar_tc_prep_kernel) in global memory in exactly that layout, chunk by chunk, so a CTA
-//   moves a chunk with flat 16-byte copies.
+//   moves a chunk (hi and lo, 48 KB for S = 90) with ONE bulk copy of the TMA engine (cp.async.bulk, completion counted
+//   on an mbarrier) - no thread touches it.
 // * TF32 keeps 11 significant bits, far from the 1e-4 bar, so both operands are split  v = hi + lo  (hi = v rounded to
 //   TF32, lo = v - hi exactly) and three MMAs accumulate  hi.hi + hi.lo + lo.hi  in the fp32 TMEM accumulator: relative
 //   error ~2^-21 per product.  The dropped lo.lo term is ~2^-22.
@@ -44,6 +45,7 @@ struct SarPrepArgs {
     double inv_lambda;
     float* bblk;          // [n_chunks][2][NB * kTcKC]
     double* posl;         // [3][n_chunks * kTcElems]  positions / lambda, zero padded
+    float* posf;          // [6][n_chunks * kTcElems]  the same as float pairs: rows 2a = hi, 2a+1 = lo of axis a
 };
 
 __device__ __forceinline__ float tf32_round(float v) {
@@ -57,7 +59,11 @@ __global__ void __launch_bounds__(256) sar_tc_prep_kernel(const __grid_constant_
     const int npad = a.n_chunks * kTcElems;
     for (int i = threadIdx.x; i < 3 * kTcElems; i += blockDim.x) {
         const int axis = i / kTcElems, n = c * kTcElems + (i - axis * kTcElems);
-        a.posl[(size_t)axis * npad + n] = n < a.N ? a.pos[(size_t)axis * a.N + n] * a.inv_lambda : 0.0;
+        const double v = n < a.N ? a.pos[(size_t)axis * a.N + n] * a.inv_lambda : 0.0;
+        a.posl[(size_t)axis * npad + n] = v;
+        const float vh = (float)v;
+        a.posf[(size_t)(2 * axis) * npad + n] = vh;
+        a.posf[(size_t)(2 * axis + 1) * npad + n] = (float)(v - (double)vh);
     }
     float* hi = a.bblk + (size_t)c * 2 * a.NB * kTcKC;
     float* lo = hi + a.NB * kTcKC;
@@ -114,29 +120,69 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
                  : "r"(taddr));
 }
 
+// exp(2 pi i t) for t in [-1/2, 1/2] turns: quadrant by the magic-number round (no conversion-unit instructions), Taylor
+// polynomials on |2 pi r| <= pi/4 (sin to x^9, cos to x^8: truncation error < 3e-8), quadrant rotation by sign-bit XORs.
+__device__ __forceinline__ void sincos_turns(float t, float* sn, float* cs) {
+    const float m = fmaf(4.0f, t, 12582912.0f);                 // 1.5 * 2^23: the low mantissa bits hold rint(4 t)
+    const int q = __float_as_int(m);
+    const float r = fmaf(-0.25f, m - 12582912.0f, t);           // |r| <= 1/8 turn
+    const float r2 = r * r;
+    float s = fmaf(r2, 42.0586939448976f, -76.7058597530614f);          // (2pi)^9/9! = 42.0586939, -(2pi)^7/7!
+    s = fmaf(r2, s, 81.6052492760750f);                                                // (2pi)^5/5!
+    s = fmaf(r2, s, -41.3417022403998f);                                               // -(2pi)^3/3!
+    s = fmaf(r2, s, 6.28318530717959f);
+    s *= r;
+    float c = fmaf(r2, 60.2446413718763f, -85.4568172066937f);                         // (2pi)^8/8!, -(2pi)^6/6!
+    c = fmaf(r2, c, 64.9393940226683f);                                                // (2pi)^4/4!
+    c = fmaf(r2, c, -19.7392088021787f);                                               // -(2pi)^2/2!
+    c = fmaf(r2, c, 1.0f);
+    const bool swap = q & 1;
+    const float c0 = swap ? s : c, s0 = swap ? c : s;
+    *cs = __int_as_float(__float_as_int(c0) ^ (((q + 1) & 2) << 30));
+    *sn = __int_as_float(__float_as_int(s0) ^ ((q & 2) << 30));
+}
+
 // ---- the GEMM ---------------------------------------------------------------------------------------------------
 struct SarTcArgs {
     const float* bblk;    // prepared B chunks
     const double* posl;   // [3][npad] positions / lambda
+    const float* posf;    // [6][npad] hi / lo float pairs of the same
     const double* dirs;   // [3][G]
     int npad, n_chunks, seg_chunks, G, S, SP, NB;
     int g_begin, g_end;
     cf* beams;            // [S][g_end - g_begin]
 };
 
-template <int MT>
-__global__ void __launch_bounds__(128 * MT, 1) sar_tc_kernel(const __grid_constant__ SarTcArgs a) {
+// MT accumulator tiles (128 directions each) per CTA, TPR threads per direction row (they split the elements of a chunk and
+// the columns of a drain).  Warp roles: GW = 4 MT TPR generator warps (steering rows -> shared memory, drains), one MMA
+// warp (a single lane issues tcgen05.mma / commit) and one TMA warp (a single lane issues the bulk copies of B).  The roles
+// meet only through mbarriers - no CTA-wide barrier inside the K loop:
+//   empty[s]   tcgen05.commit: the MMAs that read stage s are complete            -> generators, TMA warp
+//   full[s]    one arrive per generator warp: the A rows of stage s are written    -> MMA warp
+//   bfull[s]   TMA transaction bytes: the B chunk of stage s has landed            -> MMA warp
+//   done       tcgen05.commit at the end of an accumulation segment               -> generators (drain)
+//   drained    one arrive per generator warp: the accumulators have been read      -> MMA warp (next segment may overwrite)
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+template <int MT, int TPR, int UNR, bool CS>
+__global__ void __launch_bounds__(128 * MT * TPR + 64, 1) sar_tc_kernel(const __grid_constant__ SarTcArgs a) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr int kGenThreads = 128 * MT * TPR, kGenWarps = kGenThreads / 32;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int mt = tid >> 7, row = tid & 127;
     const int b_floats = a.NB * kTcKC;                         // one of B_hi / B_lo
     const int stage_floats = MT * 2 * kTcATile + 2 * b_floats;
     float* stage0 = reinterpret_cast<float*>(smem_raw);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(stage0 + 2 * stage_floats);     // empty[0], empty[1], done
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 3);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(stage0 + 2 * stage_floats);
+    uint64_t *empty = bars, *full = bars + 2, *bfull = bars + 4, *done = bars + 6, *drained = bars + 7;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
 
     if (tid == 0) {
-        mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_init(&bars[2], 1);
+        mbar_init(&empty[0], 1); mbar_init(&empty[1], 1);
+        mbar_init(&full[0], kGenWarps); mbar_init(&full[1], kGenWarps);
+        mbar_init(&bfull[0], 1); mbar_init(&bfull[1], 1);
+        mbar_init(done, 1); mbar_init(drained, kGenWarps);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {                                           // one warp allocates (and later frees) the accumulators
@@ -147,104 +193,150 @@ __global__ void __launch_bounds__(128 * MT, 1) sar_tc_kernel(const __grid_consta
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_slot;
-
-    // this thread's direction (clamped: surplus rows of the last tile compute a valid direction and are not written)
     const int width = a.g_end - a.g_begin;
-    const int g_out = blockIdx.x * (128 * MT) + mt * 128 + row;            // column of `beams`
-    const int g = a.g_begin + min(g_out, width - 1);
-    const double dx = a.dirs[g], dy = a.dirs[(size_t)a.G + g], dz = a.dirs[2 * (size_t)a.G + g];
-    // M = 128, N = NB, fp32 accumulate, TF32 x TF32, both operands K-major
-    const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(a.NB >> 3) << 17) | ((128u >> 4) << 24);
 
-    int n_drained = 0;
-    for (int c = 0; c < a.n_chunks; ++c) {
-        const int s = c & 1;
-        const int c_seg = c % a.seg_chunks;
-        const bool seg_end = (c_seg == a.seg_chunks - 1) || (c == a.n_chunks - 1);
-        float* st = stage0 + s * stage_floats;
-        float* a_hi = st + mt * kTcATile;
-        float* a_lo = st + MT * kTcATile + mt * kTcATile;
-        float* b_dst = st + MT * 2 * kTcATile;
-        if (c >= 2) {                                          // the MMAs of chunk c-2 have finished reading this stage
-            mbar_wait(&bars[s], ((c >> 1) - 1) & 1);
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        }
-        // B chunk: flat copy (already in the canonical layout)
-        {
-            const float4* src = reinterpret_cast<const float4*>(a.bblk + (size_t)c * 2 * b_floats);
-            float4* dst = reinterpret_cast<float4*>(b_dst);
-            for (int i = tid; i < 2 * b_floats / 4; i += 128 * MT) dst[i] = __ldg(src + i);
-        }
-        // A chunk: this thread's row, kTcElems steering coefficients
-        const double* px = a.posl + (size_t)c * kTcElems;
-#pragma unroll 2
-        for (int nl = 0; nl < kTcElems; nl += 2) {
-            float w[4];
+    if (warp == kGenWarps) {
+        // ===== MMA issuer =====
+        if (lane == 0) {
+            // M = 128, N = NB, fp32 accumulate, TF32 x TF32, both operands K-major
+            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(a.NB >> 3) << 17) | ((128u >> 4) << 24);
+            int n_seg = 0;
+            for (int c = 0; c < a.n_chunks; ++c) {
+                const int s = c & 1, c_seg = c % a.seg_chunks;
+                const bool seg_end = (c_seg == a.seg_chunks - 1) || (c == a.n_chunks - 1);
+                float* st = stage0 + s * stage_floats;
+                mbar_wait(&full[s], (c >> 1) & 1);
+                mbar_wait(&bfull[s], (c >> 1) & 1);
+                if (c_seg == 0 && c > 0) mbar_wait(drained, (n_seg - 1) & 1);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t b_hi = smem_u32(st + MT * 2 * kTcATile), b_lo = b_hi + b_floats * 4;
 #pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                const double turns = fma(dx, __ldg(px + nl + e), fma(dy, __ldg(px + a.npad + nl + e), dz * __ldg(px + 2 * (size_t)a.npad + nl + e)));
-                const float frac = (float)(turns - rint(turns));
-                sincospif(2.0f * frac, &w[2 * e + 1], &w[2 * e]);
-            }
-            float4 h, l;
-            h.x = tf32_round(w[0]); h.y = tf32_round(w[1]); h.z = tf32_round(w[2]); h.w = tf32_round(w[3]);
-            l.x = w[0] - h.x; l.y = w[1] - h.y; l.z = w[2] - h.z; l.w = w[3] - h.w;
-            const int idx = ((row >> 3) * (kTcKC / 4) + (nl >> 1)) * 32 + (row & 7) * 4;
-            *reinterpret_cast<float4*>(a_hi + idx) = h;
-            *reinterpret_cast<float4*>(a_lo + idx) = l;
-        }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // generic-proxy writes -> visible to the tensor core
-        __syncthreads();
-        if (tid == 0) {
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint32_t b_hi = smem_u32(b_dst), b_lo = b_hi + b_floats * 4;
+                for (int m = 0; m < MT; ++m) {
+                    const uint32_t ah = smem_u32(st + m * kTcATile), al = smem_u32(st + MT * kTcATile + m * kTcATile);
+                    const uint32_t d = tmem_base + m * 256;
 #pragma unroll
-            for (int m = 0; m < MT; ++m) {
-                const uint32_t ah = smem_u32(st + m * kTcATile), al = smem_u32(st + MT * kTcATile + m * kTcATile);
-                const uint32_t d = tmem_base + m * 256;
-#pragma unroll
-                for (int j = 0; j < kTcKC / 8; ++j) {                      // 8 k-values = two 16-byte chunks = 256 B further on
-                    const uint32_t off = j * 256;
-                    umma_tf32(d, umma_desc(al + off), umma_desc(b_hi + off), idesc, (c_seg | j) != 0);
-                    umma_tf32(d, umma_desc(ah + off), umma_desc(b_lo + off), idesc, 1);
-                    umma_tf32(d, umma_desc(ah + off), umma_desc(b_hi + off), idesc, 1);
+                    for (int j = 0; j < kTcKC / 8; ++j) {                  // 8 k-values = two 16-byte chunks = 256 B further on
+                        const uint32_t off = j * 256;
+                        umma_tf32(d, umma_desc(al + off), umma_desc(b_hi + off), idesc, (c_seg | j) != 0);
+                        umma_tf32(d, umma_desc(ah + off), umma_desc(b_lo + off), idesc, 1);
+                        umma_tf32(d, umma_desc(ah + off), umma_desc(b_hi + off), idesc, 1);
+                    }
                 }
+                umma_commit(&empty[s]);
+                if (seg_end) { umma_commit(done); ++n_seg; }
             }
-            umma_commit(&bars[s]);
-            if (seg_end) umma_commit(&bars[2]);
         }
-        if (seg_end) {
-            // The tensor core adds into the fp32 accumulator with truncation, a bias that grows with the length of the
-            // accumulation chain (measured 1.3e-8 N relative).  The chain is therefore cut into segments: each one is
-            // drained from TMEM and summed into `beams` with ordinary round-to-nearest fp32 adds.
-            mbar_wait(&bars[2], n_drained & 1);
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            // TMEM lane = direction row, column s = Re, column SP + s = Im
-            const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + mt * 256;
-            for (int s0 = 0; s0 < a.SP; s0 += 16) {
-                uint32_t re[16], im[16];
-                tmem_ld16(taddr + s0, re);
-                tmem_ld16(taddr + a.SP + s0, im);
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                if (g_out < width) {
-                    cf* dst = a.beams + (size_t)s0 * width + g_out;
-                    cf old[16];
-                    if (n_drained > 0) {                                   // all loads in flight before the first store
+    } else if (warp == kGenWarps + 1) {
+        // ===== B loader: one bulk copy (hi and lo, canonical layout) per chunk =====
+        if (lane == 0) {
+            const uint32_t bytes = 2u * (uint32_t)b_floats * 4u;
+            for (int c = 0; c < a.n_chunks; ++c) {
+                const int s = c & 1;
+                if (c >= 2) mbar_wait(&empty[s], ((c >> 1) - 1) & 1);
+                const uint32_t bar = smem_u32(&bfull[s]);
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                             ::"r"(smem_u32(stage0 + s * stage_floats + MT * 2 * kTcATile)), "l"(a.bblk + (size_t)c * 2 * b_floats),
+                               "r"(bytes), "r"(bar) : "memory");
+            }
+        }
+    } else {
+        // ===== generators =====
+        const int part = tid / (128 * MT), rt = tid - part * (128 * MT);
+        const int mt = rt >> 7, row = rt & 127;
+        // this thread's direction (clamped: surplus rows of the last tile compute a valid direction and are not written)
+        const int g_out = blockIdx.x * (128 * MT) + mt * 128 + row;            // column of `beams`
+        const int g = a.g_begin + min(g_out, width - 1);
+        const double dx = a.dirs[g], dy = a.dirs[(size_t)a.G + g], dz = a.dirs[2 * (size_t)a.G + g];
+        // float pairs of the direction for the fp32 phase (CS): d = dh + dl to 2^-48
+        const float dh[3] = {(float)dx, (float)dy, (float)dz};
+        const float dl[3] = {(float)(dx - (double)dh[0]), (float)(dy - (double)dh[1]), (float)(dz - (double)dh[2])};
+        int n_drained = 0;
+        for (int c = 0; c < a.n_chunks; ++c) {
+            const int s = c & 1, c_seg = c % a.seg_chunks;
+            const bool seg_end = (c_seg == a.seg_chunks - 1) || (c == a.n_chunks - 1);
+            float* st = stage0 + s * stage_floats;
+            float* a_hi = st + mt * kTcATile;
+            float* a_lo = st + MT * kTcATile + mt * kTcATile;
+            if (c >= 2) mbar_wait(&empty[s], ((c >> 1) - 1) & 1);            // the MMAs of chunk c-2 have finished reading this stage
+            const double* px = a.posl + (size_t)c * kTcElems;
+            const float* pf = a.posf + (size_t)c * kTcElems;
+#pragma unroll UNR
+            for (int nq = 0; nq < kTcElems / TPR; nq += 2) {
+                const int nl = part * (kTcElems / TPR) + nq;
+                float w[4];
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    if (CS) {
+                        // Phase (d.p)/lambda modulo 1 WITHOUT the fp64 pipe (ncu: a third of all stall samples were
+                        // math-pipe throttle on DFMA / DMUL).  d = dh + dl, p = ph + pl as float pairs; dh*ph is split
+                        // exactly into a rounded product and its FMA remainder; the rounded product (up to 1e4 turns) loses
+                        // its integer part exactly (x - rint(x) is exact below 2^22, rint by the magic-number add);
+                        // what is left are terms below one turn, summed in fp32: ~1e-7 turns of error.
+                        float acc = 0.0f, small = 0.0f;
+#pragma unroll
+                        for (int ax = 0; ax < 3; ++ax) {
+                            const float ph = __ldg(pf + (size_t)(2 * ax) * a.npad + nl + e), pl = __ldg(pf + (size_t)(2 * ax + 1) * a.npad + nl + e);
+                            const float hi = dh[ax] * ph;
+                            const float lo = fmaf(dh[ax], ph, -hi);
+                            const float ri = (hi + 12582912.0f) - 12582912.0f;
+                            acc += hi - ri;
+                            small += fmaf(dh[ax], pl, fmaf(dl[ax], ph, lo));
+                        }
+                        float t = acc + small;
+                        t -= (t + 12582912.0f) - 12582912.0f;
+                        sincos_turns(t, &w[2 * e + 1], &w[2 * e]);
+                    } else {
+                        const double turns = fma(dx, __ldg(px + nl + e), fma(dy, __ldg(px + a.npad + nl + e), dz * __ldg(px + 2 * (size_t)a.npad + nl + e)));
+                        const float frac = (float)(turns - rint(turns));
+                        sincospif(2.0f * frac, &w[2 * e + 1], &w[2 * e]);
+                    }
+                }
+                float4 h, l;
+                h.x = tf32_round(w[0]); h.y = tf32_round(w[1]); h.z = tf32_round(w[2]); h.w = tf32_round(w[3]);
+                l.x = w[0] - h.x; l.y = w[1] - h.y; l.z = w[2] - h.z; l.w = w[3] - h.w;
+                const int idx = ((row >> 3) * (kTcKC / 4) + (nl >> 1)) * 32 + (row & 7) * 4;
+                *reinterpret_cast<float4*>(a_hi + idx) = h;
+                *reinterpret_cast<float4*>(a_lo + idx) = l;
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the tensor core
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&full[s]);
+            if (seg_end) {
+                // The tensor core adds into the fp32 accumulator with truncation, a bias that grows with the length of the
+                // accumulation chain (measured 1.3e-8 N relative).  The chain is therefore cut into segments: each one is
+                // drained from TMEM and summed into `beams` with ordinary round-to-nearest fp32 adds.
+                mbar_wait(done, n_drained & 1);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                // TMEM lane = direction row, column s = Re, column SP + s = Im
+                const uint32_t taddr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + mt * 256;
+                for (int s0 = part * 16; s0 < a.SP; s0 += 16 * TPR) {
+                    uint32_t re[16], im[16];
+                    tmem_ld16(taddr + s0, re);
+                    tmem_ld16(taddr + a.SP + s0, im);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    if (g_out < width) {
+                        cf* dst = a.beams + (size_t)s0 * width + g_out;
+                        cf old[16];
+                        if (n_drained > 0) {                               // all loads in flight before the first store
+#pragma unroll
+                            for (int i = 0; i < 16; ++i)
+                                old[i] = (s0 + i < a.S) ? __ldcg(dst + (size_t)i * width) : cmake(0.f, 0.f);
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 16; ++i) old[i] = cmake(0.f, 0.f);
+                        }
 #pragma unroll
                         for (int i = 0; i < 16; ++i)
-                            old[i] = (s0 + i < a.S) ? __ldcg(dst + (size_t)i * width) : cmake(0.f, 0.f);
-                    } else {
-#pragma unroll
-                        for (int i = 0; i < 16; ++i) old[i] = cmake(0.f, 0.f);
+                            if (s0 + i < a.S)
+                                __stcg(dst + (size_t)i * width, cmake(__uint_as_float(re[i]) + old[i].x, __uint_as_float(im[i]) + old[i].y));
                     }
-#pragma unroll
-                    for (int i = 0; i < 16; ++i)
-                        if (s0 + i < a.S)
-                            __stcg(dst + (size_t)i * width, cmake(__uint_as_float(re[i]) + old[i].x, __uint_as_float(im[i]) + old[i].y));
                 }
+                ++n_drained;
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                __syncwarp();
+                if (lane == 0) mbar_arrive(drained);
             }
-            ++n_drained;
-            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");      // ordered before the next segment's first MMA
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -298,15 +390,17 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
     const int n_chunks = (N + kTcElems - 1) / kTcElems, npad = n_chunks * kTcElems;
     const size_t bblk_bytes = (size_t)n_chunks * 2 * NB * kTcKC * sizeof(float);
     const size_t posl_bytes = (size_t)3 * npad * sizeof(double);
+    const size_t posf_bytes = (size_t)6 * npad * sizeof(float);
     const size_t beams_bytes = (size_t)S * width * sizeof(cf);
     auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
-    if (int rc = ensure_scratch(ctx, up(bblk_bytes) + up(posl_bytes) + up(beams_bytes))) return rc;
+    if (int rc = ensure_scratch(ctx, up(bblk_bytes) + up(posl_bytes) + up(posf_bytes) + up(beams_bytes))) return rc;
     unsigned char* base = reinterpret_cast<unsigned char*>(ctx->scratch);
     float* bblk = reinterpret_cast<float*>(base);
     double* posl = reinterpret_cast<double*>(base + up(bblk_bytes));
-    cf* beams = reinterpret_cast<cf*>(base + up(bblk_bytes) + up(posl_bytes));
+    float* posf = reinterpret_cast<float*>(base + up(bblk_bytes) + up(posl_bytes));
+    cf* beams = reinterpret_cast<cf*>(base + up(bblk_bytes) + up(posl_bytes) + up(posf_bytes));
 
-    SarPrepArgs p{aperture, S, N, SP, NB, n_chunks, positions, 1.0 / lambda_m, bblk, posl};
+    SarPrepArgs p{aperture, S, N, SP, NB, n_chunks, positions, 1.0 / lambda_m, bblk, posl, posf};
     sar_tc_prep_kernel<<<n_chunks, 256, 0, st>>>(p);
     RB_CUDA_OK(ctx, cudaGetLastError());
 
@@ -314,10 +408,10 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
     int seg_chunks = (int)(6.0e5 / (double)N) / kTcElems;
     seg_chunks = seg_chunks < 4 ? 4 : (seg_chunks > n_chunks ? n_chunks : seg_chunks);
     if (ctx->sar_seg_chunks > 0) seg_chunks = ctx->sar_seg_chunks;
-    SarTcArgs a{bblk, posl, dirs, npad, n_chunks, seg_chunks, G, S, SP, NB, g_begin, g_end, beams};
+    SarTcArgs a{bblk, posl, posf, dirs, npad, n_chunks, seg_chunks, G, S, SP, NB, g_begin, g_end, beams};
     auto smem_for = [&](int tiles) {
         const size_t stage_floats = (size_t)tiles * 2 * kTcATile + 2 * (size_t)NB * kTcKC;
-        return 2 * stage_floats * sizeof(float) + 3 * sizeof(uint64_t) + 16;
+        return 2 * stage_floats * sizeof(float) + 8 * sizeof(uint64_t) + 16;
     };
     // two accumulator tiles per CTA (a B chunk serves 256 directions) once every SM has work anyway and the stages fit
     int mt = (width > 128 * ctx->sm_count && smem_for(2) <= (size_t)ctx->max_smem_optin) ? 2 : 1;
@@ -327,13 +421,24 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
     if (smem > (size_t)ctx->max_smem_optin) return 1;
     const int per_cta = 128 * mt;
     const unsigned grid = (unsigned)((width + per_cta - 1) / per_cta);
-    if (mt == 2) {
-        RB_CUDA_OK(ctx, cudaFuncSetAttribute(sar_tc_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        sar_tc_kernel<2><<<grid, 256, smem, st>>>(a);
-    } else {
-        RB_CUDA_OK(ctx, cudaFuncSetAttribute(sar_tc_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        sar_tc_kernel<1><<<grid, 128, smem, st>>>(a);
-    }
+    const int tpr = ctx->sar_tpr > 0 ? ctx->sar_tpr : (mt == 2 ? 1 : 2);      // measured: 0.443 / 0.450 ms (2 tiles), 0.550 / 0.503 ms (1 tile)
+    const int unr = ctx->sar_dbg & 15, cs = !(ctx->sar_dbg & 16);      // RADAR_B200_SAR_DBG: unroll of the element loop (0 = default), +16 = sincospif
+#define RB_SAR_TC_LAUNCH(MT_, TPR_, UNR_, CS_)                                                                               \
+    do {                                                                                                                     \
+        RB_CUDA_OK(ctx, cudaFuncSetAttribute(sar_tc_kernel<MT_, TPR_, UNR_, CS_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        sar_tc_kernel<MT_, TPR_, UNR_, CS_><<<grid, 128 * MT_ * TPR_ + 64, smem, st>>>(a);                                   \
+    } while (0)
+#define RB_SAR_TC_VARIANTS(MT_, TPR_)                                                                                        \
+    do {                                                                                                                     \
+        if (cs) { if (unr == 1) RB_SAR_TC_LAUNCH(MT_, TPR_, 1, true); else if (unr == 2) RB_SAR_TC_LAUNCH(MT_, TPR_, 2, true); else RB_SAR_TC_LAUNCH(MT_, TPR_, 8, true); } \
+        else { if (unr == 1) RB_SAR_TC_LAUNCH(MT_, TPR_, 1, false); else if (unr == 2) RB_SAR_TC_LAUNCH(MT_, TPR_, 2, false); else RB_SAR_TC_LAUNCH(MT_, TPR_, 8, false); } \
+    } while (0)
+    if (mt == 2 && tpr == 2) RB_SAR_TC_VARIANTS(2, 2);
+    else if (mt == 2) RB_SAR_TC_VARIANTS(2, 1);
+    else if (tpr == 2) RB_SAR_TC_VARIANTS(1, 2);
+    else RB_SAR_TC_VARIANTS(1, 1);
+#undef RB_SAR_TC_VARIANTS
+#undef RB_SAR_TC_LAUNCH
     RB_CUDA_OK(ctx, cudaGetLastError());
 
     SarFftArgs f{beams, S, width, ctx->fftS.hann, ctx->fftS.tw, ctx->fftS.pos, out, ctx->fftS.plan, make_fastdiv(kTcFftDirs)};

@@ -43,6 +43,8 @@ struct radar_ctx {
     void* scratch = nullptr; size_t scratch_bytes = 0;
     int force_generic = 0;                        // RADAR_B200_GENERIC=1: generic range-Doppler kernel only, =2: skip the streaming kernel (tests)
     int sar_mode = 0;                             // RADAR_B200_SAR: 0 auto (tcgen05 when the shape fits), 1 FP32-pipe kernel, 2/3 tcgen05 with 1/2 tiles per CTA
+    int sar_dbg = 0;                              // RADAR_B200_SAR_DBG: timing experiments of the tensor-core SAR kernel (results invalid)
+    int sar_tpr = 0;                              // RADAR_B200_SAR_TPR: threads per direction row of the tensor-core SAR kernel (0 = default)
     int sar_seg_chunks = 0;                       // RADAR_B200_SAR_SEG: chunks (16 elements) per accumulation segment, 0 = automatic
     int stream_variant = 0;                       // RADAR_B200_STREAM_VARIANT: tuning candidate of the streaming kernel
     char err[512] = {0};
