@@ -130,8 +130,15 @@ __device__ __forceinline__ int count_below_fixed(const float* __restrict__ row, 
 }
 
 // TD, GD > 0: Doppler-axis window compiled in (the common detector settings); TD == 0: run-time widths.
+//
+// Two phases against warp divergence (ncu: a warp ran ~19 window rows because one hard cell keeps 31 decided lanes
+// waiting, while the average cell is decided after ~6): phase 1 counts the first ph1 full rows for EVERY cell with no
+// exit test in between (uniform, all loads independent) and decides the easy cells (noise: too few cells below the bound
+// are still possible); the undecided ones are appended to a shared-memory work list (warp-aggregated) with their count
+// and bound, and phase 2 walks that list with dense warps, row by row with the early exit.
 template <int TD, int GD>
-__device__ __forceinline__ void os_count_cells(const CfarArgs& a, const float* map, uint8_t* mask) {
+__device__ __forceinline__ void os_count_cells(const CfarArgs& a, const float* map, uint8_t* mask, int* work_cell,
+                                               float* work_t, int* work_n) {
     const int td = TD > 0 ? TD : a.td, gd = TD > 0 ? GD : a.gd;
     const int cr = a.tr + a.gr, cd = td + gd;
     const int wr = 2 * cr + 1, wd = 2 * cd + 1;
@@ -139,16 +146,57 @@ __device__ __forceinline__ void os_count_cells(const CfarArgs& a, const float* m
     const int n_cut = nvr * nvd;
     const int g_lo = a.tr, g_hi = a.tr + 2 * a.gr;                 // window rows crossing the guard band
     const int seg2 = td + 2 * gd + 1;
-    for (int c = threadIdx.x; c < n_cut; c += blockDim.x) {
+    // rows of phase 1: enough that "all of them above the bound" already rules a detection out, plus two, all full rows
+    int ph1 = (a.n_train - a.k_rank + wd) / wd + 2;
+    ph1 = ph1 < g_lo ? ph1 : g_lo;
+    const int lane = threadIdx.x & 31;
+    for (int c0 = 0; c0 < n_cut; c0 += blockDim.x) {
+        const int c = c0 + threadIdx.x;
+        bool undecided = false;
+        int cnt = 0, cell = 0;
+        float t = 0.0f;
+        if (c < n_cut) {
+            const int vr = (int)a.div_vd.div((uint32_t)c);
+            const int vd = c - vr * nvd;
+            const int r = vr + cr;
+            if (!(a.row_select && !a.row_select[r])) {
+                cell = r * a.cols + vd + cd;
+                const float* row = map + vr * a.pitch + vd;           // top-left corner of the window
+                t = os_compare_bound(row[cr * a.pitch + cd], a.alpha);
+                for (int y = 0; y < ph1; ++y, row += a.pitch) {
+                    if (TD > 0) cnt += count_below_fixed<0, 2 * (TD + GD) + 1>(row, t);
+                    else cnt += count_below(row, 0, wd, t);
+                }
+                const int unseen = a.n_train - ph1 * wd;
+                if (cnt >= a.k_rank) mask[cell] = 1;
+                else if (cnt + unseen >= a.k_rank) undecided = true;  // else: no detection, mask stays 0
+            }
+        }
+        const unsigned vote = __ballot_sync(0xffffffffu, undecided);
+        if (vote) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(work_n, __popc(vote));
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (undecided) {
+                const int slot = base + __popc(vote & ((1u << lane) - 1u));
+                work_cell[slot] = c | (cnt << 16);
+                work_t[slot] = t;
+            }
+        }
+    }
+    __syncthreads();
+    const int n_work = *work_n;
+    for (int i = threadIdx.x; i < n_work; i += blockDim.x) {
+        const int packed = work_cell[i];
+        const int c = packed & 0xffff;
+        int cnt = packed >> 16;
+        const float t = work_t[i];
         const int vr = (int)a.div_vd.div((uint32_t)c);
         const int vd = c - vr * nvd;
-        const int r = vr + cr;
-        if (a.row_select && !a.row_select[r]) continue;
-        const int cell = r * a.cols + vd + cd;
-        const float* row = map + vr * a.pitch + vd;               // top-left corner of the window
-        const float t = os_compare_bound(row[cr * a.pitch + cd], a.alpha);
-        int cnt = 0, unseen = a.n_train;
-        for (int y = 0; y < wr; ++y, row += a.pitch) {
+        const int cell = (vr + cr) * a.cols + vd + cd;
+        const float* row = map + (vr + ph1) * a.pitch + vd;
+        int unseen = a.n_train - ph1 * wd;
+        for (int y = ph1; y < wr; ++y, row += a.pitch) {
             if (y < g_lo || y > g_hi) {
                 if (TD > 0) cnt += count_below_fixed<0, 2 * (TD + GD) + 1>(row, t);
                 else cnt += count_below(row, 0, wd, t);
@@ -164,14 +212,14 @@ __device__ __forceinline__ void os_count_cells(const CfarArgs& a, const float* m
     }
 }
 
-__device__ __forceinline__ void os_count_dispatch(const CfarArgs& a, const float* map, uint8_t* mask) {
+__device__ __forceinline__ void os_count_dispatch(const CfarArgs& a, const float* map, uint8_t* mask, int* wc, float* wt, int* wn) {
     // Doppler-axis (train, guard) of the reference's detector settings (tests/verify_processors.py:121-143,
     // gui_configs/processor_params.yaml:41-88)
-    if (a.td == 4 && a.gd == 1) os_count_cells<4, 1>(a, map, mask);
-    else if (a.td == 5 && a.gd == 2) os_count_cells<5, 2>(a, map, mask);
-    else if (a.td == 5 && a.gd == 3) os_count_cells<5, 3>(a, map, mask);
-    else if (a.td == 12 && a.gd == 4) os_count_cells<12, 4>(a, map, mask);
-    else os_count_cells<0, 0>(a, map, mask);
+    if (a.td == 4 && a.gd == 1) os_count_cells<4, 1>(a, map, mask, wc, wt, wn);
+    else if (a.td == 5 && a.gd == 2) os_count_cells<5, 2>(a, map, mask, wc, wt, wn);
+    else if (a.td == 5 && a.gd == 3) os_count_cells<5, 3>(a, map, mask, wc, wt, wn);
+    else if (a.td == 12 && a.gd == 4) os_count_cells<12, 4>(a, map, mask, wc, wt, wn);
+    else os_count_cells<0, 0>(a, map, mask, wc, wt, wn);
 }
 
 __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_constant__ CfarArgs a) {
@@ -181,6 +229,10 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
     SmemArena ar(smem_raw);
     float* map = ar.take<float>(a.rows * a.pitch);
     uint8_t* mask = ar.take<uint8_t>(n_cells);
+    int* work_cell = ar.take<int>(n_cells);              // OS counting path: undecided cells after phase 1
+    float* work_t = ar.take<float>(n_cells);
+    __shared__ int work_n;
+    if (threadIdx.x == 0) work_n = 0;
     const long long m = blockIdx.x;
     const float* src = a.maps + m * n_cells;
     double* noise_dst = a.noise_out ? a.noise_out + m * n_cells : nullptr;
@@ -198,7 +250,7 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
     const int nvr = a.rows - 2 * cr, nvd = a.cols - 2 * cd;
     if (nvr > 0 && nvd > 0) {      // window larger than the map: no valid cell (reference swallows the ValueError)
         if (a.kind == RADAR_CFAR_OS && !noise_dst && a.alpha > 0.0) {
-            os_count_dispatch(la, map, mask);
+            os_count_dispatch(la, map, mask, work_cell, work_t, &work_n);
         } else if (a.kind == RADAR_CFAR_OS) {
             const int wcells = (2 * cr + 1) * (2 * cd + 1);
             if (wcells <= 32 * 8) os_cells<8>(la, map, mask, noise_dst);
@@ -335,7 +387,7 @@ static int launch_cfar(radar_ctx* ctx, const float* maps, int n_maps, int rows, 
     const size_t n_cells = (size_t)rows * cols;
     a.pitch = cols;
     if (nvd > 0) while ((a.pitch - nvd) % 32 != 0) ++a.pitch;
-    const size_t smem = arena_bytes((size_t)rows * a.pitch, 4) + arena_bytes(n_cells, 1);
+    const size_t smem = arena_bytes((size_t)rows * a.pitch, 4) + arena_bytes(n_cells, 1) + 2 * arena_bytes(n_cells, 4);
     if (smem > (size_t)ctx->max_smem_optin)
         return set_error(ctx, RADAR_E_UNSUPPORTED, "CFAR map of %d x %d cells exceeds shared memory", rows, cols);
     RB_CUDA_OK(ctx, cudaFuncSetAttribute(cfar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
