@@ -256,6 +256,9 @@ int radar_row_reduce(radar_ctx* ctx, const float* maps, int n_maps, int rows, in
  * y = -v, H = xyz[:dims]/|xyz[:dims]|, sklearn RANSACRegressor(LinearRegression(fit_intercept=False),
  * residual_threshold, random_state=42, max_trials, min_samples) - one warp per frame, fp64.
  *   points  : double [rows][4] packed point clouds (radar_point_cloud with offsets), offsets int32 [n_frames+1]
+ *   dims    : 2 / 3 = fit (vx, vy) / (vx, vy, vz) to point rows (x, y, z, v);  -1 / -2 / -3 = the rows already hold the
+ *             design matrix and target (h0, h1, h2, y) with that many columns in use (unused columns zero): the 1-D
+ *             regressions of the ADC-domain estimator (processors/velocity_estimator.py:409-506)
  *   subsets : device int32 [n_blocks][max_trials][min_samples]; a block holds the point indices sklearn draws for a
  *             cloud of n points (random_state=42 re-seeds every fit, so they depend only on n and the trial);
  *             tabulated by the host layer with numpy's RandomState

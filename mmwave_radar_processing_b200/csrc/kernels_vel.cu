@@ -45,9 +45,15 @@ __device__ __forceinline__ int warp_sum(int v) { return __reduce_add_sync(0xffff
 struct Row { double h[3]; double y; };
 
 // H row and target of one point, operation for operation what numpy does (np.linalg.norm: sqrt(sum(x*x)), then divide).
-template <int D>
+// RAW: the row already holds (h0, h1, h2, y) - the 1-D regressions of the ADC-domain estimator
+// (processors/velocity_estimator.py:409-506) hand their own design matrix.
+template <int D, bool RAW = false>
 __device__ __forceinline__ Row load_row(const double* __restrict__ p) {
     Row r;
+    if (RAW) {
+        r.h[0] = p[0]; r.h[1] = D >= 2 ? p[1] : 0.0; r.h[2] = D == 3 ? p[2] : 0.0; r.y = p[3];
+        return r;
+    }
     double s = __dmul_rn(p[0], p[0]);
     s = __dadd_rn(s, __dmul_rn(p[1], p[1]));
     if (D == 3) s = __dadd_rn(s, __dmul_rn(p[2], p[2]));
@@ -78,13 +84,13 @@ __device__ __forceinline__ double residual(const Row& r, const double (&c)[3]) {
 
 // Inlier count, R^2 of model c on its inliers (sklearn r2_score, force_finite): two passes like the reference
 // (mean first, then the sums of squares).  All lanes return the same values.
-template <int D>
+template <int D, bool RAW>
 __device__ __forceinline__ void score_model(const double* __restrict__ pts, int n, int lane, const double (&c)[3], double thr,
                                             int* n_in_out, double* r2_out) {
     int cnt = 0;
     double sy = 0.0;
     for (int i = lane; i < n; i += 32) {
-        const Row r = load_row<D>(pts + 4 * (size_t)i);
+        const Row r = load_row<D, RAW>(pts + 4 * (size_t)i);
         if (residual<D>(r, c) <= thr) { ++cnt; sy += r.y; }
     }
     cnt = warp_sum(cnt);
@@ -94,7 +100,7 @@ __device__ __forceinline__ void score_model(const double* __restrict__ pts, int 
     const double mean = sy / (double)cnt;
     double ss_res = 0.0, ss_tot = 0.0;
     for (int i = lane; i < n; i += 32) {
-        const Row r = load_row<D>(pts + 4 * (size_t)i);
+        const Row r = load_row<D, RAW>(pts + 4 * (size_t)i);
         const double e = residual<D>(r, c);
         if (e <= thr) { ss_res += e * e; ss_tot += (r.y - mean) * (r.y - mean); }
     }
@@ -113,7 +119,7 @@ __device__ __forceinline__ double dynamic_max_trials(int n_inliers, int n_sample
     return fabs(ceil(log(nom) / log(denom)));
 }
 
-template <int D>
+template <int D, bool RAW>
 __global__ void __launch_bounds__(kVelWarps * 32) ego_velocity_kernel(const __grid_constant__ EgoArgs a) {
     const int lane = threadIdx.x & 31;
     const int frame = blockIdx.x * kVelWarps + (threadIdx.x >> 5);
@@ -128,7 +134,7 @@ __global__ void __launch_bounds__(kVelWarps * 32) ego_velocity_kernel(const __gr
     if (ok) {                                  // sklearn's input validation: any nan / inf -> ValueError -> zeros
         bool finite = true;
         for (int i = lane; i < n; i += 32) {
-            const Row r = load_row<D>(pts + 4 * (size_t)i);
+            const Row r = load_row<D, RAW>(pts + 4 * (size_t)i);
             finite = finite && isfinite(r.h[0]) && isfinite(r.h[1]) && isfinite(r.h[2]) && isfinite(r.y);
         }
         ok = __all_sync(0xffffffffu, finite);
@@ -143,11 +149,11 @@ __global__ void __launch_bounds__(kVelWarps * 32) ego_velocity_kernel(const __gr
         for (int t = 0; (double)t < limit; ++t) {
             double g[6] = {0, 0, 0, 0, 0, 0}, b[3] = {0, 0, 0}, c[3];
             for (int j = 0; j < a.min_samples; ++j)           // every lane forms the same small system (broadcast loads)
-                accumulate<D>(load_row<D>(pts + 4 * (size_t)table[t * a.min_samples + j]), g, b);
+                accumulate<D>(load_row<D, RAW>(pts + 4 * (size_t)table[t * a.min_samples + j]), g, b);
             solve_normal<D>(g, b, c);
             int n_in;
             double score;
-            score_model<D>(pts, n, lane, c, a.thr, &n_in, &score);
+            score_model<D, RAW>(pts, n, lane, c, a.thr, &n_in, &score);
             if (n_in < n_best) continue;
             if (n_in == n_best && score < score_best) continue;
             n_best = n_in; score_best = score; have = true;
@@ -157,7 +163,7 @@ __global__ void __launch_bounds__(kVelWarps * 32) ego_velocity_kernel(const __gr
         if (have) {                            // final model: least squares over the inliers of the best trial
             double g[6] = {0, 0, 0, 0, 0, 0}, b[3] = {0, 0, 0}, c[3];
             for (int i = lane; i < n; i += 32) {
-                const Row r = load_row<D>(pts + 4 * (size_t)i);
+                const Row r = load_row<D, RAW>(pts + 4 * (size_t)i);
                 if (residual<D>(r, best) <= a.thr) accumulate<D>(r, g, b);
             }
 #pragma unroll
@@ -169,7 +175,7 @@ __global__ void __launch_bounds__(kVelWarps * 32) ego_velocity_kernel(const __gr
             int cnt = 0;
             double sy = 0.0;
             for (int i = lane; i < n; i += 32) {
-                const Row r = load_row<D>(pts + 4 * (size_t)i);
+                const Row r = load_row<D, RAW>(pts + 4 * (size_t)i);
                 if (residual<D>(r, best) <= a.thr) { ++cnt; sy += r.y; }
             }
             cnt = warp_sum(cnt);
@@ -177,7 +183,7 @@ __global__ void __launch_bounds__(kVelWarps * 32) ego_velocity_kernel(const __gr
             const double mean = sy / (double)cnt;
             double ss_res = 0.0, ss_tot = 0.0;
             for (int i = lane; i < n; i += 32) {
-                const Row r = load_row<D>(pts + 4 * (size_t)i);
+                const Row r = load_row<D, RAW>(pts + 4 * (size_t)i);
                 if (residual<D>(r, best) <= a.thr) {
                     const double e = residual<D>(r, c);
                     ss_res += e * e; ss_tot += (r.y - mean) * (r.y - mean);
@@ -205,15 +211,18 @@ int launch_ego_velocity(radar_ctx* ctx, const double* points, const int32_t* off
                         const int32_t* subsets, const int32_t* subset_index, int table_max_n, int max_trials,
                         int min_samples, double residual_threshold, double stop_probability, double* vel_out,
                         double* r2_out, double* frac_out, int32_t* status_out, cudaStream_t st) {
-    if (dims != 2 && dims != 3) return set_error(ctx, RADAR_E_INVALID, "dims must be 2 or 3, got %d", dims);
+    if (dims != 2 && dims != 3 && dims != -1 && dims != -2 && dims != -3)
+        return set_error(ctx, RADAR_E_INVALID, "dims must be 2 or 3 (point rows) or -1..-3 (raw design rows), got %d", dims);
     if (max_trials <= 0 || min_samples <= 0 || table_max_n < min_samples)
         return set_error(ctx, RADAR_E_INVALID, "bad RANSAC table (max_trials %d, min_samples %d, table_max_n %d)", max_trials, min_samples, table_max_n);
     if (n_frames <= 0) return RADAR_OK;
     EgoArgs a{points, offsets, n_frames, dims, subsets, subset_index, table_max_n, max_trials, min_samples, residual_threshold,
               stop_probability, vel_out, r2_out, frac_out, status_out};
     const unsigned grid = (unsigned)((n_frames + kVelWarps - 1) / kVelWarps);
-    if (dims == 2) ego_velocity_kernel<2><<<grid, kVelWarps * 32, 0, st>>>(a);
-    else ego_velocity_kernel<3><<<grid, kVelWarps * 32, 0, st>>>(a);
+    if (dims == 2) ego_velocity_kernel<2, false><<<grid, kVelWarps * 32, 0, st>>>(a);
+    else if (dims == 3) ego_velocity_kernel<3, false><<<grid, kVelWarps * 32, 0, st>>>(a);
+    else if (dims == -3) ego_velocity_kernel<3, true><<<grid, kVelWarps * 32, 0, st>>>(a);
+    else ego_velocity_kernel<2, true><<<grid, kVelWarps * 32, 0, st>>>(a);      // one or two raw columns (a zero column is dropped by the minimum-norm solve)
     RB_CUDA_OK(ctx, cudaGetLastError());
     return RADAR_OK;
 }

@@ -61,3 +61,48 @@ def iq_to_complex_cube(iq: np.ndarray) -> np.ndarray:
     reference's dataset loader hands to processors (exact cast)."""
     z = iq[..., 0].astype(np.float64) + 1j * iq[..., 1].astype(np.float64)
     return np.ascontiguousarray(np.moveaxis(z, -3, -1))         # (..., R, S, C)
+
+
+# (row, column) of each virtual antenna, in half wavelengths.  "ods": the 4x4-minus-corners ODS array, consistent with
+# the antenna sets the reference's ADC-domain velocity estimator uses (azimuth rows [0,3,4,7] / [1,2,5,6], elevation
+# columns [10,11,6,7] / [9,8,5,4]); "standard": a uniform line.
+ODS_ROW_COL = {0: (3, 0), 3: (3, 1), 4: (3, 2), 7: (3, 3), 1: (2, 0), 2: (2, 1), 5: (2, 2), 6: (2, 3),
+               10: (0, 3), 11: (1, 3), 9: (0, 2), 8: (1, 2)}
+
+
+def synth_ego_motion_iq(num_rx: int, num_samples: int, cpl: int, loops: int, seed: int, ego, vel_res: float,
+                        geometry: str = "standard", range_bins=(8.0, 20.0), num_scatterers: int = 60,
+                        mover_frac: float = 0.15, noise_sigma: float = 20.0) -> np.ndarray:
+    """One frame of a static scene seen from a platform moving at ``ego`` = (boresight, azimuth-lateral,
+    elevation-lateral) m/s: every scatterer at (theta, phi) shows the Doppler -(e0 cos(theta) cos(phi) + e1 sin(theta) +
+    e2 sin(phi)); a fraction are movers with unrelated Doppler.  int16 ``[chirp][rx][sample][2]``."""
+    rng = np.random.default_rng(seed)
+    r, s, l = num_rx, num_samples, loops
+    c = cpl * l
+    k = num_scatterers
+    theta = np.deg2rad(rng.uniform(-55.0, 55.0, k))
+    phi = np.deg2rad(rng.uniform(-55.0, 55.0, k)) if geometry == "ods" else np.zeros(k)
+    amp = rng.uniform(200.0, 600.0, k)
+    rho = rng.uniform(range_bins[0], range_bins[1], k)
+    dop = -(ego[0] * np.cos(theta) * np.cos(phi) + ego[1] * np.sin(theta) + ego[2] * np.sin(phi))
+    movers = rng.random(k) < mover_frac
+    dop[movers] = rng.uniform(-0.4, 0.4, int(movers.sum())) * vel_res * l
+    chirp = np.arange(c)
+    v = (chirp % cpl)[:, None] * r + np.arange(r)[None, :]       # (C, R) virtual index
+    if geometry == "ods":
+        row = np.vectorize(lambda i: ODS_ROW_COL.get(int(i), (0, 0))[0])(v)
+        col = np.vectorize(lambda i: ODS_ROW_COL.get(int(i), (0, 0))[1])(v)
+    else:
+        row, col = np.zeros_like(v), v
+    loop = (chirp // cpl)[:, None, None]
+    n = np.arange(s)[None, None, :]
+    x = np.zeros((c, r, s), dtype=np.complex128)
+    for t in range(k):
+        ph = rho[t] * n / s + dop[t] / (vel_res * l) * loop + \
+            0.5 * (np.sin(theta[t]) * col + np.sin(phi[t]) * row)[:, :, None]
+        x += amp[t] * np.exp(2j * np.pi * ph)
+    x += noise_sigma * (rng.standard_normal(x.shape) + 1j * rng.standard_normal(x.shape))
+    iq = np.empty((c, r, s, 2), dtype=np.int16)
+    iq[..., 0] = np.clip(np.rint(x.real), -32768, 32767).astype(np.int16)
+    iq[..., 1] = np.clip(np.rint(x.imag), -32768, 32767).astype(np.int16)
+    return iq

@@ -736,14 +736,26 @@ def ego_velocity_ransac(points: np.ndarray, dims: int = 2, residual_threshold: f
         inlier mask or None)."""
     pts = np.asarray(points, dtype=np.float64)
     fail = (np.array([0.0, 0.0]), 0.0, 0.0, None)
-    n = pts.shape[0]
-    if n < min_samples:
+    if pts.shape[0] < min_samples:
         return fail
     y = -1 * pts[:, 3]
     with np.errstate(invalid="ignore", divide="ignore"):
         h = pts[:, 0:dims] / np.linalg.norm(pts[:, 0:dims], axis=1, keepdims=True)
-    if not (np.all(np.isfinite(h)) and np.all(np.isfinite(y))):
-        return fail
+    fit = ransac_fit(h, y, residual_threshold, min_samples, max_trials, seed, policy)
+    return fail if fit is None else fit
+
+
+def ransac_fit(h, y, residual_threshold, min_samples: int = 10, max_trials: int = 20, seed: int = 42,
+               policy: str = "permutation"):
+    """RANSACRegressor(LinearRegression(fit_intercept=False), random_state=seed).fit(h, y) restated from sklearn's
+    linear_model/_ransac.py (see ego_velocity_ransac).  h [N, D], y [N].
+    -> (coef [D], r2 of the final model on its inliers (0 if <= 3 inliers), inlier fraction, inlier mask), or None where
+    sklearn raises ValueError."""
+    h = np.asarray(h, dtype=np.float64).reshape(len(y), -1)
+    y = np.asarray(y, dtype=np.float64)
+    n = y.shape[0]
+    if n < min_samples or not (np.all(np.isfinite(h)) and np.all(np.isfinite(y))):
+        return None
     subsets = ransac_subsets(n, min_samples, max_trials, seed, policy)
     n_best, score_best, mask_best = 1, -np.inf, None
     trials, limit = 0, max_trials
@@ -761,7 +773,136 @@ def ego_velocity_ransac(points: np.ndarray, dims: int = 2, residual_threshold: f
         n_best, score_best, mask_best = n_in, score, mask
         limit = min(limit, _dynamic_max_trials(n_best, n, min_samples, 0.99))
     if mask_best is None:
-        return fail
+        return None
     coef = np.linalg.lstsq(h[mask_best], y[mask_best], rcond=None)[0]
     r2 = _r2(y[mask_best], h[mask_best] @ coef) if mask_best.sum() > 3 else 0.0
     return coef, r2, mask_best.sum() / n, mask_best
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# ADC-domain ego velocity (reference processors/velocity_estimator.py) - test infrastructure like the rest of this file
+# ---------------------------------------------------------------------------------------------------------------------
+def da_valid_angles(num_angle_bins: int, valid_angle_range):
+    """DopplerAzimuthProcessor.configure (reference processors/doppler_azimuth_resp.py:66-76) -> (mask, valid bins)."""
+    a = num_angle_bins
+    ph = np.arange(start=np.pi, stop=-np.pi - 2 * np.pi / (a - 1), step=-2 * np.pi / (a - 1))
+    ph[-1] = -np.pi
+    with np.errstate(invalid="ignore"):
+        ang = np.arcsin(ph / np.pi)
+    mask = (ang >= valid_angle_range[0]) & (ang <= valid_angle_range[1])
+    return mask, ang[mask]
+
+
+def _da_floor_db(resp, thr_db):
+    db = 20 * np.log10(np.abs(resp) + 1e-12)
+    floor = np.max(db) - thr_db
+    db[db <= floor] = floor
+    return db
+
+
+def da_peaks_rows(resp, vel_bins, valid_angle_bins, thr_db=30.0):
+    """detect_peaks_rows (reference doppler_azimuth_resp.py:336-377): per Doppler row, scipy find_peaks(prominence=4) on the
+    floored dB row, strongest survivor -> rows of (angle, velocity)."""
+    db = _da_floor_db(resp, thr_db)
+    out = []
+    for r, row in enumerate(db):
+        pk = local_maxima_1d(row)
+        if len(pk):
+            pk = pk[peak_prominences(row, pk) >= 4.0]
+        if len(pk):
+            out.append((valid_angle_bins[pk[np.argmax(row[pk])]], vel_bins[r]))
+    return np.array(out, dtype=np.float64).reshape(-1, 2)
+
+
+def da_peak_zero_az(resp, vel_bins, valid_angle_bins, thr_db=30.0):
+    """detect_peak_zero_az (reference doppler_azimuth_resp.py:379-417): strongest local maximum down the zero-azimuth column."""
+    col = _da_floor_db(resp, thr_db)[:, np.argmin(np.abs(valid_angle_bins))]
+    pk = local_maxima_1d(col)
+    if len(pk):
+        return np.array([0.0, vel_bins[pk[np.argmax(col[pk])]]])
+    return np.empty((0, 2))
+
+
+def adc_velocity_sets(geometry: str, virtual: bool):
+    """Antenna sets of compute_azimuth_response / compute_elevation_response (reference velocity_estimator.py:129-264)
+    -> (azimuth sets, elevation sets)."""
+    if geometry == "standard":
+        return [list(range(8 if virtual else 4))], []
+    if virtual:
+        return [[0, 3, 4, 7], [1, 2, 5, 6]], [[10, 11, 6, 7], [9, 8, 5, 4]]
+    return [[0, 3], [1, 2]], [[1, 0], [3, 4]]
+
+
+def adc_fit_vy(peaks, vx):
+    """lsq_fit_ego_vy_ransac (reference velocity_estimator.py:344-507) -> (vy, r2, inlier share); the standard model for
+    vx >= 0.1, the small-vx model (threshold 0.20, vy = -1/a) below."""
+    if vx >= 0.1:
+        fit = ransac_fit(np.sin(peaks[:, 0]), -1 * peaks[:, 1] - vx * np.cos(peaks[:, 0]), 0.15)
+        return (0.0, 0.0, 0.0) if fit is None else (fit[0][0], fit[1], fit[2])
+    fit = ransac_fit(peaks[:, 1] - vx, peaks[:, 0], 0.20)
+    if fit is None:
+        return 0.0, 0.0, 0.0
+    a = fit[0][0]
+    return (-1 / a if a != 0 else 0.0), fit[1], fit[2]
+
+
+def adc_velocity_estimate(cube_v, geometry, virtual, range_bins, vel_bins, vel_res, vel_max, range_max_m, range_window,
+                          valid_angle_range, current, precise=False, precise_vel_bound=0.25, thr_db=30.0,
+                          min_r2=0.6, min_inlier=0.75, x_only=False):
+    """VelocityEstimator.process with an ADC cube (reference velocity_estimator.py:783-865).  ``current`` is the running
+    [vx, vy, vz] estimate (updated copy returned).  -> dict(current, proposed, vx, az/el (vy, r2, inlier), peaks)."""
+    mask, vbins = da_valid_angles(64, valid_angle_range)
+    az_sets, el_sets = adc_velocity_sets(geometry, virtual)
+    ant_win = geometry == "standard" and virtual
+    state = dict(az=(0.0, 0.0, 0.0), el=(0.0, 0.0, 0.0))
+
+    def responses(use_precise, center):
+        out, bins = [], vel_bins
+        for sets, shift in ((az_sets, True), (el_sets, False)):
+            acc = []
+            for s in sets:
+                if use_precise:
+                    r, bins = doppler_azimuth_precise(cube_v, range_bins, vel_bins, vel_res, vel_max, 64, s, range_window,
+                                                      shift, ant_win, range_max_m,
+                                                      vel_range=[center - precise_vel_bound, center + precise_vel_bound])
+                else:
+                    r = doppler_azimuth_coarse(cube_v, range_bins, 64, s, range_window, shift, ant_win, range_max_m)
+                acc.append(r[:, mask])
+            out.append(sum(acc) / len(acc) if acc else None)
+        return out, bins
+
+    def vx_from(resps, bins):
+        z = [da_peak_zero_az(r, bins, vbins, thr_db) for r in resps if r is not None]
+        z = [p[1] for p in z if p.shape[0] > 0]
+        return -1 * sum(z) / len(z) if z else 0.0
+
+    resps, bins = responses(False, 0.0)
+    vx = vx_from(resps, bins)
+    if precise:
+        resps, bins = responses(True, -1 * vx)
+        vx = vx_from(resps, bins)
+    peaks = [None, None]
+    if not x_only:
+        for i, key in enumerate(("az", "el")):
+            if resps[i] is not None:
+                peaks[i] = da_peaks_rows(resps[i], bins, vbins, thr_db)
+                if peaks[i].shape[0] > 0:
+                    state[key] = adc_fit_vy(peaks[i], vx)
+    cur = np.array(current, dtype=np.float64)
+    if x_only:
+        proposed = np.array([vx])
+        cur[0] = vx
+    elif geometry == "ods":
+        proposed = np.array([state["az"][0], state["el"][0], vx])
+        for i, key in enumerate(("az", "el")):
+            ok = state[key][1] >= min_r2 and state[key][2] >= min_inlier
+            cur[i] = proposed[i] if ok else 0.0
+        cur[2] = proposed[2]
+    else:
+        proposed = np.array([vx, state["az"][0], 0.0])
+        if vx < 0.0:
+            cur = proposed.copy() if state["az"][1] >= min_r2 else np.zeros(3)
+        else:
+            cur = np.array([proposed[0], proposed[1] if state["az"][1] >= min_r2 else 0.0, 0.0])
+    return dict(current=cur, proposed=proposed, vx=vx, az=state["az"], el=state["el"], az_peaks=peaks[0],
+                el_peaks=peaks[1])
