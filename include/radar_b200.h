@@ -222,6 +222,26 @@ int radar_sar_image(radar_ctx* ctx, const void* aperture, int num_samples, int n
                     const double* positions, const double* dirs, int n_dirs, double lambda_m,
                     int g_begin, int g_end, void* out, void* stream);
 
+/* ---- SAR self-calibration of the synthetic-array geometry ---------------------- *
+ * SyntheticArrayBeamformerProcessor.perform_array_calibration
+ * (processors/simple_synthetic_array_beamformer_processor_multiFrame.py:673-816): range FFT of the windowed
+ * aperture, three calibration targets (scipy find_peaks(height=0) on the mean range profile in dB, top three; per
+ * target the strongest azimuth peak of |10 log10 |image[rng, :, 0]||), steered phase steps between neighbouring
+ * elements (diff of np.unwrap), per-step least squares on (2 pi / lambda) dirs[0:2] and the running sum
+ * subtracted from positions[0:2, 1:].  fp64 throughout.
+ *   aperture     : float2 [S][N]   as for radar_sar_image
+ *   window       : double [N]      element weights (np.hamming(N) in the reference), device
+ *   positions    : double [3][N]
+ *   image        : float2 [S][n_dirs]  the beamformed response of radar_sar_image over ALL directions
+ *   dirs         : double [3][n_dirs], g = az*n_elev + el; only el = 0 is used
+ *   positions_out: double [3][N]   calibrated geometry (a copy of positions when status != 3)
+ *   targets_out  : int32 [7]       (range bin, azimuth bin) x 3, then status: 3 = calibrated, 0..2 = too few targets
+ *                  with an azimuth peak (the reference then keeps the geometry), -1 = fewer than three range peaks
+ *                  (the reference raises IndexError there) */
+int radar_sar_calibrate(radar_ctx* ctx, const void* aperture, int num_samples, int n_elems, const double* window,
+                        const double* positions, const void* image, int n_dirs, int n_elev, const double* dirs,
+                        double lambda_m, double* positions_out, int32_t* targets_out, void* stream);
+
 /* ---- Doppler-azimuth response -------------------------------------------------- *
  * DopplerAzimuthProcessor.coarse_doppler_azimuth_fft + the tail of .process
  * (processors/doppler_azimuth_resp.py:296-334, 483-491):

@@ -290,6 +290,17 @@ int radar_sar_image(radar_ctx* ctx, const void* aperture, int num_samples, int n
                             g_begin, g_end, reinterpret_cast<cf*>(out), (cudaStream_t)stream);
 }
 
+int radar_sar_calibrate(radar_ctx* ctx, const void* aperture, int num_samples, int n_elems, const double* window,
+                        const double* positions, const void* image, int n_dirs, int n_elev, const double* dirs, double lambda_m,
+                        double* positions_out, int32_t* targets_out, void* stream) {
+    RB_ENTER(ctx);
+    if (!aperture || !window || !positions || !image || !dirs || !positions_out || !targets_out)
+        return set_error(ctx, RADAR_E_INVALID, "null pointer");
+    return launch_sar_calibrate(ctx, reinterpret_cast<const cf*>(aperture), num_samples, n_elems, window, positions,
+                                reinterpret_cast<const cf*>(image), n_dirs, n_elev, dirs, lambda_m, positions_out, targets_out,
+                                (cudaStream_t)stream);
+}
+
 int radar_doppler_azimuth(radar_ctx* ctx, const void* cube, int n_frames, int n_ant, int rows, int cols, int k_begin, int k_end,
                           const float* ant_weight, int num_angle_bins, int shift_angle, float* out, void* stream) {
     RB_ENTER(ctx);

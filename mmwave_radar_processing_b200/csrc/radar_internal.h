@@ -111,6 +111,9 @@ int launch_ego_velocity(radar_ctx* ctx, const double* points, const int32_t* off
                         double* r2_out, double* frac_out, int32_t* status_out, cudaStream_t st);
 int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const double* positions, const double* dirs,
                         int G, double lambda_m, int g_begin, int g_end, cf* out, cudaStream_t st);
+int launch_sar_calibrate(radar_ctx* ctx, const cf* aperture, int S, int N, const double* window, const double* positions,
+                         const cf* image, int n_dirs, int n_elev, const double* dirs, double lambda_m, double* positions_out,
+                         int32_t* targets_out, cudaStream_t st);
 int launch_sar_image(radar_ctx* ctx, const cf* aperture, int num_samples, int n_elems, const double* positions,
                      const double* dirs, int n_dirs, double lambda_m, int g_begin, int g_end, cf* out,
                      cudaStream_t st);

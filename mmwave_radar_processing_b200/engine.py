@@ -365,6 +365,27 @@ class RadarEngine:
         return out
 
 
+    def sar_calibrate(self, aperture: torch.Tensor, window: torch.Tensor, positions: torch.Tensor, image: torch.Tensor,
+                      dirs: torch.Tensor, n_elev: int, lambda_m: float):
+        """aperture complex64 [S,N], window float64 [N], positions float64 [3,N], image complex64 [S,G] (all directions),
+        dirs float64 [3,G] -> (calibrated positions float64 [3,N], targets int32 [7]: (range, azimuth) x 3 + status)."""
+        s, n = aperture.shape
+        g = dirs.shape[1]
+        if aperture.dtype != torch.complex64 or image.dtype != torch.complex64:
+            raise ValueError("aperture / image must be complex64")
+        if any(t.dtype != torch.float64 for t in (window, positions, dirs)):
+            raise ValueError("window / positions / dirs must be float64")
+        if tuple(positions.shape) != (3, n) or tuple(image.shape) != (s, g) or window.numel() != n or dirs.shape[0] != 3:
+            raise ValueError("shapes: positions [3,N], window [N], image [S,G], dirs [3,G]")
+        out = torch.empty((3, n), dtype=torch.float64, device=self.device)
+        targets = torch.empty((7,), dtype=torch.int32, device=self.device)
+        nat.check(self.lib.radar_sar_calibrate(self.ctx, nat.ptr(aperture.contiguous()), s, n, nat.ptr(window.contiguous()),
+                                               nat.ptr(positions.contiguous()), nat.ptr(image.contiguous()), g, int(n_elev),
+                                               nat.ptr(dirs.contiguous()), float(lambda_m), nat.ptr(out), nat.ptr(targets),
+                                               _stream_ptr()), self.ctx)
+        return out, targets
+
+
 _ENGINES = {}
 
 

@@ -6,9 +6,9 @@ element positions chained backwards over frames, pointing vectors, mesh grids.  
 (``radar_sar_image``): Hamming-weighted steering + beam sum + Hann + range FFT for every (azimuth,
 elevation) voxel; the ring buffer of valid chirps lives in device memory as complex64.
 
-``enable_calibration`` (ref :673-816) and the polar->cartesian ``griddata`` resampling (ref :587-613) are
-SURVEY section 8f next-4: the resampling is done with scipy on the host after the device image is
-downloaded; calibration raises NotImplementedError.
+``enable_calibration`` (ref :673-816) runs in ``radar_sar_calibrate`` (fp64 on the device, from the history ring
+and the image already there).  The polar->cartesian ``griddata`` resampling (ref :587-613, SURVEY section 8f
+next-4) is done with scipy on the host after the device image is downloaded.
 """
 import numpy as np
 
@@ -61,6 +61,8 @@ class SyntheticArrayBeamformerProcessor(_Processor):
         self.max_vel = _arr(max_vel)
         self.max_vel_stdev = _arr(max_vel_stdev)
         self.enable_calibration = enable_calibration
+        self._resp_dev = None
+        self.calibration_targets = []
         self.num_calibration_iters = num_calibration_iters
         self.array_geometry_valid = False
         self._hist_dev = None            # complex64 [F, S, Lv] on the device, oldest -> newest
@@ -207,6 +209,34 @@ class SyntheticArrayBeamformerProcessor(_Processor):
         self.interpolated_beamformed_resp = np.reshape(resp, self.interp_x_s.shape)
         return self.interpolated_beamformed_resp
 
+    def perform_array_calibration(self):
+        """Self-calibration of the synthetic-array geometry against three strong scatterers (ref :673-816) in
+        ``radar_sar_calibrate``, from the device history and the image of the last ``compute_synthetic_response``.
+        -> corrected geometry (3, N) (also stored per frame in ``array_geometry_calibrated``), or an empty array when
+        fewer than three targets qualify."""
+        import torch
+        eng = self._engine()
+        s = self.num_range_bins
+        aperture = self._hist_dev.permute(1, 0, 2).reshape(s, -1).contiguous()
+        n = aperture.shape[1]
+        pos = np.ascontiguousarray(np.asarray(self.array_geometry).transpose((1, 0, 2)).reshape(3, -1), dtype=np.float64)
+        dirs = np.ascontiguousarray(self.d.reshape(3, -1), dtype=np.float64)
+        if self._resp_dev is None or self._resp_dev.shape[1] != dirs.shape[1]:
+            raise ValueError("calibration needs the full beamformed response (compute_synthetic_response over all voxels)")
+        up = lambda a: torch.from_numpy(a).to(eng.device)
+        new, targets = eng.sar_calibrate(aperture, up(np.hamming(n)), up(pos), self._resp_dev, up(dirs),
+                                         self.el_angle_bins_rad.shape[0], self.lambda_m)
+        targets = targets.cpu().numpy()
+        self.calibration_targets = [(int(targets[2 * t]), int(targets[2 * t + 1])) for t in range(3) if targets[2 * t] >= 0]
+        if targets[6] < 0:
+            raise IndexError("fewer than three range peaks for calibration")      # the reference indexes past its peak list
+        if targets[6] < 3:
+            print("No suitable calibration targets found.")
+            return np.empty(shape=0)
+        new = new.cpu().numpy()
+        self.array_geometry_calibrated = new.reshape(3, self.num_frames, -1).transpose(1, 0, 2)
+        return new
+
     def process(self, adc_cube: np.ndarray, current_vel) -> np.ndarray:
         if isinstance(current_vel, list):
             current_vel = np.array(current_vel)
@@ -214,9 +244,14 @@ class SyntheticArrayBeamformerProcessor(_Processor):
         self._update_array_geometries(current_vel=current_vel)
         if not self.array_geometry_valid:
             return np.empty(shape=0)
-        if self.enable_calibration:
-            raise NotImplementedError("SAR self-calibration is SURVEY 8f next-4 (not on the accelerated path yet)")
         resp = self.compute_synthetic_response(self.array_geometry)
+        if self.enable_calibration:
+            for _ in range(self.num_calibration_iters):
+                if self.perform_array_calibration().shape[0] != 0:
+                    resp = self.compute_synthetic_response(self.array_geometry_calibrated)
+                else:
+                    self.array_geometry_calibrated = self.array_geometry
+                    break
         self.get_interpolated_response_cart()
         return resp
 

@@ -906,3 +906,55 @@ def adc_velocity_estimate(cube_v, geometry, virtual, range_bins, vel_bins, vel_r
             cur = np.array([proposed[0], proposed[1] if state["az"][1] >= min_r2 else 0.0, 0.0])
     return dict(current=cur, proposed=proposed, vx=vx, az=state["az"], el=state["el"], az_peaks=peaks[0],
                 el_peaks=peaks[1])
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# SAR self-calibration (reference processors/simple_synthetic_array_beamformer_processor_multiFrame.py:673-816)
+# ---------------------------------------------------------------------------------------------------------------------
+def _peaks_height0(x):
+    """scipy.signal.find_peaks(x, height=0): local maxima (plateau midpoints) whose value is >= 0."""
+    pk = local_maxima_1d(x)
+    return pk[np.asarray(x)[pk] >= 0] if len(pk) else pk
+
+
+def sar_calibration_targets(freq_resps, image_el0, num_targets=3):
+    """_find_calibration_targets (ref :698-729): the num_targets strongest peaks of the mean range profile in dB, then per
+    range the strongest peak over azimuth of |10 log10 |image||.  Raises IndexError like the reference when the profile has
+    fewer peaks than targets.  -> list of (range idx, azimuth idx)."""
+    with np.errstate(divide="ignore"):
+        avg = np.mean(20 * np.log10(np.abs(freq_resps)), axis=1)
+    pk = _peaks_height0(avg)
+    order = pk[np.argsort(avg[pk], kind="stable")[-num_targets:][::-1]]
+    targets = []
+    for i in range(num_targets):
+        rng = order[i]
+        with np.errstate(divide="ignore"):
+            row = np.abs(10 * np.log10(np.abs(image_el0[rng])))
+        p = _peaks_height0(row)
+        if len(p) == 0:
+            continue
+        targets.append((int(rng), int(p[np.argmax(row[p])])))
+    return targets
+
+
+def sar_calibrate(aperture, geometry, image_el0, d_el0, lambda_m):
+    """perform_array_calibration (ref :673-816).  aperture [S, N] (history reshaped), geometry (3, N), image_el0 [S, A]
+    (beamformed response at elevation index 0), d_el0 (3, A) steering vectors.  -> (new geometry (3, N) or None when fewer
+    than three targets qualify, targets)."""
+    n = aperture.shape[1]
+    freq = np.fft.fft(np.hamming(n).reshape(1, -1) * aperture, axis=0)
+    targets = sar_calibration_targets(freq, image_el0)
+    if len(targets) < 3:
+        return None, targets
+    diffs, vecs = [], []
+    for rng, az in targets:
+        sv = d_el0[:, az]
+        shifted = freq[rng, :] * np.exp(1j * 2 * np.pi * (sv @ geometry) / lambda_m)
+        diffs.append(np.diff(np.unwrap(np.angle(shifted))))
+        vecs.append(sv)
+    diffs, vecs = np.array(diffs), np.array(vecs)
+    dj = 2 * np.pi / lambda_m * vecs[:, 0:2]
+    corr = np.stack([np.linalg.lstsq(dj, diffs[:, i], rcond=None)[0] for i in range(diffs.shape[1])], axis=1)
+    out = np.array(geometry, dtype=np.float64)
+    out[0:2, 1:] -= np.cumsum(corr, axis=1)
+    return out, targets
