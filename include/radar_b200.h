@@ -242,6 +242,21 @@ int radar_sar_calibrate(radar_ctx* ctx, const void* aperture, int num_samples, i
                         const double* positions, const void* image, int n_dirs, int n_elev, const double* dirs,
                         double lambda_m, double* positions_out, int32_t* targets_out, void* stream);
 
+/* ---- polar -> cartesian resampling of the SAR image -------------------------------- *
+ * SyntheticArrayBeamformerProcessor.get_interpolated_response_cart
+ * (processors/simple_synthetic_array_beamformer_processor_multiFrame.py:587-613): scipy griddata(method="linear",
+ * fill_value=0) of image[:, :, el 0] given at (r cos az, r sin az), evaluated on the grid x0 + ix*dx, y0 + iy*dy.
+ * Every polar cell is a cyclic trapezoid, so both of its diagonals are Delaunay and Qhull's pick is arbitrary per cell;
+ * `diagonal` (0: (i,j)-(i+1,j+1), 1: (i,j+1)-(i+1,j)) fixes the split.  Pixels outside the convex hull are 0.
+ *   image     : float2 [S][n_dirs], n_dirs = n_az*n_elev, g = az*n_elev + el (el 0 is read)
+ *   range_bins: double [S] ascending; az_bins: double [n_az] ascending (radians, inside (-pi, pi))
+ *   az_order  : int32 [n_az] image column of each entry of az_bins (NULL = identity), for descending user axes
+ *   out       : float2 [nx][ny]; inside_out: uint8 [nx][ny] or NULL (1 = inside the hull) */
+int radar_polar_to_cart(radar_ctx* ctx, const void* image, int num_samples, int n_dirs, int n_elev,
+                        const double* range_bins, const double* az_bins, const int32_t* az_order, int n_az,
+                        double x0, double dx, int nx, double y0, double dy, int ny, int diagonal,
+                        void* out, uint8_t* inside_out, void* stream);
+
 /* ---- Doppler-azimuth response -------------------------------------------------- *
  * DopplerAzimuthProcessor.coarse_doppler_azimuth_fft + the tail of .process
  * (processors/doppler_azimuth_resp.py:296-334, 483-491):

@@ -301,6 +301,15 @@ int radar_sar_calibrate(radar_ctx* ctx, const void* aperture, int num_samples, i
                                 (cudaStream_t)stream);
 }
 
+int radar_polar_to_cart(radar_ctx* ctx, const void* image, int num_samples, int n_dirs, int n_elev, const double* range_bins,
+                        const double* az_bins, const int32_t* az_order, int n_az, double x0, double dx, int nx, double y0, double dy,
+                        int ny, int diagonal, void* out, uint8_t* inside_out, void* stream) {
+    RB_ENTER(ctx);
+    if (!image || !range_bins || !az_bins || (!out && nx > 0 && ny > 0)) return set_error(ctx, RADAR_E_INVALID, "null pointer");
+    return launch_polar_to_cart(ctx, reinterpret_cast<const cf*>(image), num_samples, n_dirs, n_elev, range_bins, az_bins, az_order,
+                                n_az, x0, dx, nx, y0, dy, ny, diagonal, reinterpret_cast<cf*>(out), inside_out, (cudaStream_t)stream);
+}
+
 int radar_doppler_azimuth(radar_ctx* ctx, const void* cube, int n_frames, int n_ant, int rows, int cols, int k_begin, int k_end,
                           const float* ant_weight, int num_angle_bins, int shift_angle, float* out, void* stream) {
     RB_ENTER(ctx);

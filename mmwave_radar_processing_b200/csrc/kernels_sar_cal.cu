@@ -248,3 +248,91 @@ int launch_sar_calibrate(radar_ctx* ctx, const cf* aperture, int S, int N, const
 }
 
 }  // namespace rb
+
+// ------------------------------------------------------------------------------------------------------------------
+// Polar -> cartesian resampling of the SAR image at elevation index 0 (reference ...multiFrame.py:587-613:
+// scipy.interpolate.griddata(method="linear", fill_value=0) = Delaunay triangulation + barycentric weights).  On a polar
+// grid every cell is a cyclic trapezoid, so both diagonals are Delaunay and Qhull's pick is arbitrary per cell; the
+// kernel splits every cell along `diagonal` (0: (i,j)-(i+1,j+1), 1: (i,j+1)-(i+1,j)).  One pixel per thread: sector by
+// binary search on the angle, ring by binary search on the bisector coordinate (rings are bounded by CHORDS in the
+// plane, not arcs), barycentric weights in fp64, values complex64.  Writes 2 floats per pixel: HBM-trivial.
+// ------------------------------------------------------------------------------------------------------------------
+namespace rb {
+namespace {
+
+struct P2cArgs {
+    const cf* image; int S, G, E, A;
+    const double* r; const double* az; const int32_t* az_order;
+    double x0, dx, y0, dy; int nx, ny, diagonal;
+    cf* out; uint8_t* inside;
+};
+
+__device__ __forceinline__ int upper_cell(const double* v, int n, double q) {      // searchsorted(v, q, "right") - 1, clipped
+    int lo = 0, hi = n;
+    while (lo < hi) { const int m = (lo + hi) >> 1; if (v[m] <= q) lo = m + 1; else hi = m; }
+    return min(max(lo - 1, 0), n - 2);
+}
+
+__global__ void __launch_bounds__(256) polar_to_cart_kernel(const __grid_constant__ P2cArgs a) {
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (long long)a.nx * a.ny) return;
+    const int ix = (int)(idx / a.ny), iy = (int)(idx - (long long)ix * a.ny);
+    const double x = a.x0 + ix * a.dx, y = a.y0 + iy * a.dy;
+    const double th = atan2(y, x);
+    const int j = upper_cell(a.az, a.A, th);
+    const double az0 = a.az[j], az1 = a.az[j + 1];
+    double s0, c0, s1, c1, sm, cm;
+    sincos(az0, &s0, &c0);
+    sincos(az1, &s1, &c1);
+    sincos(0.5 * (az0 + az1), &sm, &cm);
+    const double u = (x * cm + y * sm) / cos(0.5 * (az1 - az0));
+    const int i = upper_cell(a.r, a.S, u);
+    cf val = cmake(0.f, 0.f);
+    bool hit = false;
+    if (th >= a.az[0] && th <= a.az[a.A - 1] && u >= a.r[0] && u <= a.r[a.S - 1]) {
+        const double r0 = a.r[i], r1 = a.r[i + 1];
+        const int g0 = (a.az_order ? a.az_order[j] : j) * a.E, g1 = (a.az_order ? a.az_order[j + 1] : j + 1) * a.E;
+        // corners: 0 = (i,j), 1 = (i,j+1), 2 = (i+1,j), 3 = (i+1,j+1)
+        const double px[4] = {r0 * c0, r0 * c1, r1 * c0, r1 * c1}, py[4] = {r0 * s0, r0 * s1, r1 * s0, r1 * s1};
+        // at r == 0 every azimuth sample sits on the origin; Qhull keeps the first duplicate (image column 0)
+        const size_t at[4] = {(size_t)i * a.G + (r0 == 0.0 ? 0 : g0), (size_t)i * a.G + (r0 == 0.0 ? 0 : g1),
+                              (size_t)(i + 1) * a.G + g0, (size_t)(i + 1) * a.G + g1};
+        const int tri[2][2][3] = {{{0, 3, 2}, {0, 1, 3}}, {{0, 1, 2}, {1, 3, 2}}};
+#pragma unroll
+        for (int t = 0; t < 2; ++t) {
+            const int ia = tri[a.diagonal][t][0], ib = tri[a.diagonal][t][1], ic = tri[a.diagonal][t][2];
+            const double det = (py[ib] - py[ic]) * (px[ia] - px[ic]) + (px[ic] - px[ib]) * (py[ia] - py[ic]);
+            if (hit || det == 0.0) continue;
+            const double l0 = ((py[ib] - py[ic]) * (x - px[ic]) + (px[ic] - px[ib]) * (y - py[ic])) / det;
+            const double l1 = ((py[ic] - py[ia]) * (x - px[ic]) + (px[ia] - px[ic]) * (y - py[ic])) / det;
+            const double l2 = 1.0 - l0 - l1;
+            if (l0 >= -1e-12 && l1 >= -1e-12 && l2 >= -1e-12) {
+                const cf va = a.image[at[ia]], vb = a.image[at[ib]], vc = a.image[at[ic]];
+                val = cmake((float)(l0 * va.x + l1 * vb.x + l2 * vc.x), (float)(l0 * va.y + l1 * vb.y + l2 * vc.y));
+                hit = true;
+            }
+        }
+    }
+    a.out[idx] = val;
+    if (a.inside) a.inside[idx] = hit ? 1 : 0;
+}
+
+}  // namespace
+
+int launch_polar_to_cart(radar_ctx* ctx, const cf* image, int S, int n_dirs, int n_elev, const double* range_bins,
+                         const double* az_bins, const int32_t* az_order, int n_az, double x0, double dx, int nx, double y0,
+                         double dy, int ny, int diagonal, cf* out, uint8_t* inside_out, cudaStream_t st) {
+    if (S < 2 || n_az < 2) return set_error(ctx, RADAR_E_INVALID, "resampling needs at least 2 range and 2 azimuth bins");
+    if (n_elev <= 0 || n_dirs != n_az * n_elev)
+        return set_error(ctx, RADAR_E_INVALID, "n_dirs %d != n_az %d * n_elev %d", n_dirs, n_az, n_elev);
+    if (diagonal != 0 && diagonal != 1) return set_error(ctx, RADAR_E_INVALID, "diagonal must be 0 or 1");
+    if (nx < 0 || ny < 0) return set_error(ctx, RADAR_E_INVALID, "negative grid size");
+    const long long total = (long long)nx * ny;
+    if (total == 0) return RADAR_OK;
+    P2cArgs a{image, S, n_dirs, n_elev, n_az, range_bins, az_bins, az_order, x0, dx, y0, dy, nx, ny, diagonal, out, inside_out};
+    polar_to_cart_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(a);
+    RB_CUDA_OK(ctx, cudaGetLastError());
+    return RADAR_OK;
+}
+
+}  // namespace rb

@@ -114,6 +114,9 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
 int launch_sar_calibrate(radar_ctx* ctx, const cf* aperture, int S, int N, const double* window, const double* positions,
                          const cf* image, int n_dirs, int n_elev, const double* dirs, double lambda_m, double* positions_out,
                          int32_t* targets_out, cudaStream_t st);
+int launch_polar_to_cart(radar_ctx* ctx, const cf* image, int S, int n_dirs, int n_elev, const double* range_bins,
+                         const double* az_bins, const int32_t* az_order, int n_az, double x0, double dx, int nx, double y0,
+                         double dy, int ny, int diagonal, cf* out, uint8_t* inside_out, cudaStream_t st);
 int launch_sar_image(radar_ctx* ctx, const cf* aperture, int num_samples, int n_elems, const double* positions,
                      const double* dirs, int n_dirs, double lambda_m, int g_begin, int g_end, cf* out,
                      cudaStream_t st);

@@ -386,6 +386,27 @@ class RadarEngine:
         return out, targets
 
 
+    def polar_to_cart(self, image: torch.Tensor, n_elev: int, range_bins: torch.Tensor, az_bins: torch.Tensor, x0: float,
+                      dx: float, nx: int, y0: float, dy: float, ny: int, diagonal: int = 0, az_order=None,
+                      want_inside: bool = False):
+        """image complex64 [S,G] -> complex64 [nx,ny] piecewise-linear resampling of image[:, az, el 0] onto the grid
+        (x0 + ix dx, y0 + iy dy) (+ uint8 inside mask).  range_bins / az_bins float64, ascending."""
+        s, g = image.shape
+        if image.dtype != torch.complex64 or range_bins.dtype != torch.float64 or az_bins.dtype != torch.float64:
+            raise ValueError("image complex64, range_bins / az_bins float64 expected")
+        if range_bins.numel() != s:
+            raise ValueError("range_bins must have one entry per image row")
+        out = torch.empty((nx, ny), dtype=torch.complex64, device=self.device)
+        inside = torch.empty((nx, ny), dtype=torch.uint8, device=self.device) if want_inside else None
+        order = None if az_order is None else az_order.to(torch.int32).contiguous()
+        nat.check(self.lib.radar_polar_to_cart(self.ctx, nat.ptr(image.contiguous()), s, g, int(n_elev),
+                                               nat.ptr(range_bins.contiguous()), nat.ptr(az_bins.contiguous()),
+                                               nat.ptr(order) if order is not None else None, az_bins.numel(), float(x0),
+                                               float(dx), int(nx), float(y0), float(dy), int(ny), int(diagonal), nat.ptr(out),
+                                               nat.ptr(inside) if inside is not None else None, _stream_ptr()), self.ctx)
+        return (out, inside) if want_inside else out
+
+
 _ENGINES = {}
 
 

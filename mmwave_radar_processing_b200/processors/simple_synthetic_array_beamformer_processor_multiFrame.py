@@ -7,8 +7,8 @@ element positions chained backwards over frames, pointing vectors, mesh grids.  
 elevation) voxel; the ring buffer of valid chirps lives in device memory as complex64.
 
 ``enable_calibration`` (ref :673-816) runs in ``radar_sar_calibrate`` (fp64 on the device, from the history ring
-and the image already there).  The polar->cartesian ``griddata`` resampling (ref :587-613, SURVEY section 8f
-next-4) is done with scipy on the host after the device image is downloaded.
+and the image already there), the polar->cartesian ``griddata`` resampling (ref :587-613) in
+``radar_polar_to_cart``.  scipy is not imported.
 """
 import numpy as np
 
@@ -201,12 +201,30 @@ class SyntheticArrayBeamformerProcessor(_Processor):
         flat[:, g_begin:g_end] = out.cpu().numpy().astype(np.complex128)
         return self.beamformed_resp
 
-    def get_interpolated_response_cart(self) -> np.ndarray:
-        """Polar -> cartesian resampling at el index 0 (ref :587-613).  SURVEY 8f next-4: host scipy for now."""
-        from scipy.interpolate import griddata
-        resp = griddata(points=self.orig_grid_points, values=self.beamformed_resp[:, :, 0].flatten(),
-                        xi=self.interp_grid_points, method="linear", fill_value=0.0)
-        self.interpolated_beamformed_resp = np.reshape(resp, self.interp_x_s.shape)
+    def get_interpolated_response_cart(self, diagonal: int = 0) -> np.ndarray:
+        """Polar -> cartesian resampling at el index 0 (ref :587-613: scipy griddata, method="linear", fill 0) in
+        ``radar_polar_to_cart``.  Every polar cell is a cyclic trapezoid, so the Delaunay split scipy/Qhull picks per cell
+        is arbitrary; ``diagonal`` fixes ours (each reference pixel equals one of the two splits, tests/test_gpu_sarcal.py)."""
+        import torch
+        if self.el_angle_bins_rad.shape[0] != 1:
+            # the reference hands griddata S*A*E points but S*A values here
+            raise ValueError("different number of values and points")
+        eng = self._engine()
+        if self._resp_dev is None or self._resp_dev.shape[1] != self.az_angle_bins_rad.shape[0]:
+            image = torch.from_numpy(np.ascontiguousarray(self.beamformed_resp[:, :, 0], dtype=np.complex64)).to(eng.device)
+        else:
+            image = self._resp_dev
+        az = np.asarray(self.az_angle_bins_rad, dtype=np.float64)
+        order = np.argsort(az, kind="stable")
+        if np.any(np.diff(az[order]) <= 0) or np.any(np.diff(self.range_bins) <= 0):
+            raise ValueError("range and azimuth bins must be distinct")
+        nx, ny = self.interp_x_s.shape
+        x0, y0 = (self.interp_x_s[0, 0], self.interp_y_s[0, 0]) if nx and ny else (0.0, 0.0)
+        res = self.interpolated_grid_resolution_m
+        up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(eng.device)
+        out = eng.polar_to_cart(image, 1, up(np.asarray(self.range_bins, dtype=np.float64)), up(az[order]), x0, res, nx, y0,
+                                res, ny, diagonal=diagonal, az_order=up(order.astype(np.int32)))
+        self.interpolated_beamformed_resp = out.cpu().numpy().astype(np.complex128)
         return self.interpolated_beamformed_resp
 
     def perform_array_calibration(self):

@@ -958,3 +958,47 @@ def sar_calibrate(aperture, geometry, image_el0, d_el0, lambda_m):
     out = np.array(geometry, dtype=np.float64)
     out[0:2, 1:] -= np.cumsum(corr, axis=1)
     return out, targets
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Polar -> cartesian resampling of the SAR image (reference ...multiFrame.py:587-613: scipy griddata(method="linear"))
+# ---------------------------------------------------------------------------------------------------------------------
+def polar_to_cart(values, range_bins, az_bins, xq, yq, diagonal=0):
+    """Piecewise-linear interpolation of ``values`` [S, A], given at (r cos az, r sin az), at the points (xq, yq) over the
+    triangulation that splits every polar cell (a cyclic trapezoid: BOTH of its diagonals give a Delaunay triangulation,
+    so Qhull's pick inside scipy.griddata is arbitrary per cell) along diagonal 0 = (i, j)-(i+1, j+1) or 1 =
+    (i, j+1)-(i+1, j); 0 outside the convex hull.  range_bins ascending from 0, az_bins ascending (column 0 of ``values``
+    is the first sample of the flattened grid: the duplicate Qhull keeps at the origin).
+    -> (interpolated values, inside mask)."""
+    values = np.asarray(values)
+    r = np.asarray(range_bins, dtype=np.float64)
+    az = np.asarray(az_bins, dtype=np.float64)
+    xq = np.asarray(xq, dtype=np.float64).ravel()
+    yq = np.asarray(yq, dtype=np.float64).ravel()
+    out = np.zeros(xq.shape, dtype=values.dtype)
+    inside = np.zeros(xq.shape, dtype=bool)
+    th = np.arctan2(yq, xq)
+    j = np.clip(np.searchsorted(az, th, side="right") - 1, 0, len(az) - 2)
+    half = 0.5 * (az[j + 1] - az[j])
+    mid = 0.5 * (az[j + 1] + az[j])
+    u = (xq * np.cos(mid) + yq * np.sin(mid)) / np.cos(half)          # chord index coordinate along the sector's bisector
+    i = np.clip(np.searchsorted(r, u, side="right") - 1, 0, len(r) - 2)
+    ok = (th >= az[0]) & (th <= az[-1]) & (u >= r[0]) & (u <= r[-1])
+
+    def corner(ii, jj):
+        # at r == 0 all azimuth samples coincide; Qhull keeps the first duplicate (flat index 0 = column 0)
+        return r[ii] * np.cos(az[jj]), r[ii] * np.sin(az[jj]), np.where(r[ii] == 0.0, values[ii, 0], values[ii, jj])
+
+    p00, p01, p10, p11 = corner(i, j), corner(i, j + 1), corner(i + 1, j), corner(i + 1, j + 1)
+    tris = ((p00, p11, p10), (p00, p01, p11)) if diagonal == 0 else ((p00, p01, p10), (p01, p11, p10))
+    for a, b, c in tris:
+        det = (b[1] - c[1]) * (a[0] - c[0]) + (c[0] - b[0]) * (a[1] - c[1])
+        with np.errstate(divide="ignore", invalid="ignore"):
+            l0 = ((b[1] - c[1]) * (xq - c[0]) + (c[0] - b[0]) * (yq - c[1])) / det
+            l1 = ((c[1] - a[1]) * (xq - c[0]) + (a[0] - c[0]) * (yq - c[1])) / det
+            l2 = 1.0 - l0 - l1
+            eps = -1e-12
+            hit = ok & ~inside & (det != 0) & (l0 >= eps) & (l1 >= eps) & (l2 >= eps)
+            out[hit] = (l0[hit] * a[2][hit] + l1[hit] * b[2][hit] + l2[hit] * c[2][hit])
+        inside |= hit
+    return out, inside

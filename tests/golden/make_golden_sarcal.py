@@ -56,6 +56,7 @@ def main():
                 resp = p.process(raw, current_vel=vel)
         assert p.array_geometry_valid and resp.shape[0] > 0
         out[f"{tag}_resp"] = np.array(resp)
+        out[f"{tag}_interp"] = np.array(p.interpolated_beamformed_resp)          # scipy griddata of the calibrated image
         out[f"{tag}_geometry"] = np.array(p.array_geometry)
         out[f"{tag}_calibrated"] = np.array(p.array_geometry_calibrated)
         # the targets of one more calibration pass on the final state (what an extra iteration would pick)
@@ -66,6 +67,8 @@ def main():
         out[f"{tag}_first_targets"] = np.array(p._find_calibration_targets(freq, num_targets=3))
         out[f"{tag}_first_calibrated"] = np.array(p.perform_array_calibration())
         out[f"{tag}_first_resp"] = np.array(p.compute_synthetic_response(p.array_geometry))
+        out[f"{tag}_first_interp"] = np.array(p.get_interpolated_response_cart())
+        out[f"{tag}_interp_x0y0"] = np.array([p.interp_x_s[0, 0], p.interp_y_s[0, 0], p.interpolated_grid_resolution_m])
         shift = out[f"{tag}_calibrated"] - out[f"{tag}_geometry"]
         print(tag, "targets", out[f"{tag}_first_targets"].tolist(), "max |shift| m", np.abs(shift).max(),
               "resp max", np.abs(resp).max())

@@ -91,3 +91,61 @@ def test_sar_calibrate_degenerate_inputs(torch_cuda):
     np.testing.assert_array_equal(new.cpu().numpy(), pos)
     with pytest.raises(nat.RadarError):
         eng.sar_calibrate(up(x), up(np.ones(n)), up(pos), up(flat), up(dirs), 2, 0.004)      # 9 dirs, 2 elevations
+
+
+@pytest.mark.parametrize("tag", sorted(SARCAL_CASES))
+def test_polar_to_cart_matches_reference_griddata(torch_cuda, tag):
+    """radar_polar_to_cart with either diagonal against the oracle; every pixel of the reference's scipy.griddata image
+    equals one of the two device images (Qhull's per-cell pick is arbitrary), and the hull is the same."""
+    torch = torch_cuda
+    from oracle import radar_oracle as orc
+    from mmwave_radar_processing_b200.processors._device import engine_for_cube_shape
+    cm = load_cfg(SARCAL_CFG)
+    g = np.load(os.path.join(GOLDEN_DIR, f"sarcal_{SARCAL_CFG}.npz"))
+    az = SARCAL_CASES[tag][0]
+    image = g[f"{tag}_first_resp"][:, :, 0]
+    want = g[f"{tag}_first_interp"]
+    x0, y0, res = g[f"{tag}_interp_x0y0"]
+    nx, ny = want.shape
+    r = np.linspace(0, cm.range_max_m, image.shape[0])
+    eng = engine_for_cube_shape(1, image.shape[0], 1)
+    up = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()
+    dev = up(image.astype(np.complex64))
+    xq, yq = np.meshgrid(x0 + res * np.arange(nx), y0 + res * np.arange(ny), indexing="ij")
+    scale = np.abs(image).max()
+    got = []
+    for diag in (0, 1):
+        out, inside = eng.polar_to_cart(dev, 1, up(r), up(az), x0, res, nx, y0, res, ny, diagonal=diag, want_inside=True)
+        ref, ref_in = orc.polar_to_cart(image, r, az, xq, yq, diag)
+        np.testing.assert_array_equal(inside.cpu().numpy().ravel().astype(bool), ref_in)
+        assert np.abs(out.cpu().numpy().ravel() - ref).max() < 1e-6 * scale
+        got.append(out.cpu().numpy())
+    close = (np.abs(want - got[0]) < 1e-6 * scale) | (np.abs(want - got[1]) < 1e-6 * scale)
+    assert close.all(), int((~close).sum())
+    # descending user axis through az_order: same image
+    order = np.arange(len(az))[::-1].copy()
+    flipped = eng.polar_to_cart(up(image[:, ::-1].astype(np.complex64)), 1, up(r), up(az), x0, res, nx, y0, res, ny,
+                                az_order=up(order.astype(np.int32)))
+    inner = np.hypot(xq, yq) > r[1]                      # the origin sample is column 0 of the image as given
+    np.testing.assert_array_equal(flipped.cpu().numpy()[inner], got[0][inner])
+
+
+def test_sar_processor_interpolated_image(torch_cuda):
+    """process() leaves interpolated_beamformed_resp = the device resampling of the final image (calibrated case 'a')."""
+    from mmwave_radar_processing_b200.processors.simple_synthetic_array_beamformer_processor_multiFrame import \
+        SyntheticArrayBeamformerProcessor
+    cm = load_cfg(SARCAL_CFG)
+    g = np.load(os.path.join(GOLDEN_DIR, f"sarcal_{SARCAL_CFG}.npz"))
+    az, nf, stride, iters, _ = SARCAL_CASES["a"]
+    p = SyntheticArrayBeamformerProcessor(cm, num_frames=nf, stride=stride, az_angle_bins_rad=az, enable_calibration=True,
+                                          num_calibration_iters=iters, **SARCAL_KW)
+    for raw, vel in sarcal_frames(cm, "a"):
+        p.process(raw, current_vel=vel)
+    want = g["a_interp"]
+    d0 = p.interpolated_beamformed_resp.copy()
+    d1 = p.get_interpolated_response_cart(diagonal=1)
+    assert d0.shape == want.shape and d0.dtype == np.complex128
+    scale = np.abs(g["a_resp"]).max()
+    close = (np.abs(want - d0) < 2e-4 * scale) | (np.abs(want - d1) < 2e-4 * scale)      # fp32 image under the resampling
+    assert close.mean() > 0.999, close.mean()
+    np.testing.assert_array_equal(d0 != 0, want != 0)

@@ -63,3 +63,28 @@ def test_sar_calibration_target_rules():
     assert orc.sar_calibration_targets(freq, image) == [(5, 3), (9, 6)]
     new, targets = orc.sar_calibrate(freq * rng.standard_normal((16, 8)), np.zeros((3, 8)), image, np.zeros((3, 9)), 0.004)
     assert new is None and len(targets) < 3
+
+
+@pytest.mark.parametrize("tag", sorted(SARCAL_CASES))
+def test_polar_to_cart_brackets_reference_griddata(tag):
+    """Every pixel of the reference's scipy.griddata output equals one of the two Delaunay splits of its polar cell, and the
+    hull (non-zero support) is the same."""
+    cm = load_cfg(SARCAL_CFG)
+    g = np.load(os.path.join(GOLDEN_DIR, f"sarcal_{SARCAL_CFG}.npz"))
+    az = SARCAL_CASES[tag][0]
+    image = g[f"{tag}_first_resp"][:, :, 0]
+    want = g[f"{tag}_first_interp"]
+    x0, y0, res = g[f"{tag}_interp_x0y0"]
+    xs = x0 + res * np.arange(want.shape[0])
+    ys = y0 + res * np.arange(want.shape[1])
+    xq, yq = np.meshgrid(xs, ys, indexing="ij")
+    r = np.linspace(0, cm.range_max_m, image.shape[0])
+    a, ia = orc.polar_to_cart(image, r, az, xq, yq, 0)
+    b, ib = orc.polar_to_cart(image, r, az, xq, yq, 1)
+    scale = np.abs(image).max()
+    ma = np.abs(want.ravel() - a) < 1e-9 * scale
+    mb = np.abs(want.ravel() - b) < 1e-9 * scale
+    assert (ma | mb).all(), (~(ma | mb)).sum()
+    assert ma.mean() < 1.0 and mb.mean() < 1.0          # the reference really mixes both splits
+    np.testing.assert_array_equal(ia, ib)
+    np.testing.assert_array_equal(ia, (want.ravel() != 0))
