@@ -419,18 +419,37 @@ int launch_range_angle(radar_ctx* ctx, const void* adc, int in_kind, int n_frame
     a.out = out;
     a.planS = ctx->fftS.plan;
     const int S = a.adc.S;
-    // frames per pass: up to a warp's worth of FFT columns, tile under 64 KB, and about 3 passes per SM
-    int fc = 32 / N; if (fc < 1) fc = 1; if (fc > 8) fc = 8;
-    while (fc > 1 && (long long)n_frames / fc < (long long)ctx->sm_count * 3) fc >>= 1;     // enough passes to fill the GPU
-    while (fc > 1 && (size_t)S * ((fc * N) | 1) * sizeof(cf) > 64 * 1024) --fc;
-    if (fc > n_frames) fc = n_frames;
+    // frames per pass: up to a warp's worth of FFT columns and a tile under 64 KB; among the halvings of that, the one whose
+    // pass count quantises best over the resident CTA slots (a pass of fc frames costs about fc + 1/2 frame times: the angle
+    // stage is per frame, the range FFT loses lane occupancy as the columns shrink).  The grid is then balanced: every CTA
+    // gets the same number of passes, to within one.
+    int fc_max = 32 / N; if (fc_max < 1) fc_max = 1; if (fc_max > 8) fc_max = 8;
+    while (fc_max > 1 && (size_t)S * ((fc_max * N) | 1) * sizeof(cf) > 64 * 1024) --fc_max;
+    if (fc_max > n_frames) fc_max = n_frames;
+    auto smem_for = [&](int fc) {
+        return arena_bytes((size_t)S * ((fc * N) | 1), sizeof(cf)) + arena_bytes(S, sizeof(cf)) +
+               arena_bytes(num_angle_bins, sizeof(cf)) + arena_bytes(S, 4) + arena_bytes(S, 2);
+    };
+    if (int rc = opt_in_smem(ctx, range_angle_kernel, smem_for(fc_max), "range-angle tile")) return rc;
+    int fc = fc_max;
+    long long slots = ctx->sm_count;
+    double best_cost = 0.0;
+    for (int cand = fc_max; cand >= 1; cand = cand > 1 ? (cand + 1) / 2 : 0) {
+        if (ctx->ra_fc > 0 && cand != ctx->ra_fc && !(cand == fc_max && ctx->ra_fc > fc_max)) continue;
+        int resident = 0;
+        RB_CUDA_OK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, range_angle_kernel, kRdThreads, smem_for(cand)));
+        if (resident < 1) resident = 1;
+        const long long sl = (long long)resident * ctx->sm_count;
+        const long long passes = ((long long)n_frames + cand - 1) / cand;
+        const double cost = (double)((passes + sl - 1) / sl) * ((double)cand + 0.5);
+        if (best_cost == 0.0 || cost < best_cost) { best_cost = cost; fc = cand; slots = sl; }
+    }
     a.n_frames = n_frames; a.frames_per_pass = fc;
     a.divS = make_fastdiv((uint32_t)S); a.divN = make_fastdiv((uint32_t)N); a.divW = make_fastdiv((uint32_t)(fc * N));
-    const size_t smem = arena_bytes((size_t)S * ((fc * N) | 1), sizeof(cf)) + arena_bytes(S, sizeof(cf)) +
-                        arena_bytes(num_angle_bins, sizeof(cf)) + arena_bytes(S, 4) + arena_bytes(S, 2);
-    if (int rc = opt_in_smem(ctx, range_angle_kernel, smem, "range-angle tile")) return rc;
+    const size_t smem = smem_for(fc);
     const long long passes = ((long long)n_frames + fc - 1) / fc;
-    const long long grid = passes < (long long)ctx->sm_count * 4 ? passes : (long long)ctx->sm_count * 4;
+    const long long per_cta = (passes + slots - 1) / slots;
+    const long long grid = (passes + per_cta - 1) / per_cta;
     range_angle_kernel<<<(unsigned)grid, kRdThreads, smem, st>>>(a);
     RB_CUDA_OK(ctx, cudaGetLastError());
     return RADAR_OK;
