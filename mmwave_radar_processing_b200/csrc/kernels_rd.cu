@@ -283,6 +283,14 @@ struct RaArgs {
     FftPlan planS; FastDiv divS, divN, divW;
 };
 
+// sqrt to 1 ulp in one MUFU (the IEEE sqrtf costs a Newton step and a guarded slow path per output cell; the heat map is
+// compared at 1e-4 relative L2)
+__device__ __forceinline__ float sqrt_fast(float x) {
+    float y;
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
 // Zero-padded angle DFT of one range row + fftshift + magnitude: out[k][ao] = | sum_j row[j] w^j |, w = W_A^((ao - A/2) mod A),
 // evaluated by Horner's rule.  One warp per range bin: the row is read once (broadcast) and kept in registers, lanes run
 // along the angle bin so the stores are coalesced.  NC > 0: antenna count compiled in.  NB > 0: A == 32*NB, every lane keeps
@@ -323,7 +331,7 @@ __device__ __forceinline__ void ra_angle_stage(const cf* tile, int Np, const uin
                     acc = cmake(fmaf(acc.x, w.x, fmaf(-acc.y, w.y, x.x)), fmaf(acc.x, w.y, fmaf(acc.y, w.x, x.y)));
                 }
             }
-            return sqrtf(acc.x * acc.x + acc.y * acc.y);
+            return sqrt_fast(acc.x * acc.x + acc.y * acc.y);
         };
         if (NB > 0) {
             float m[NB > 0 ? NB : 1];
@@ -340,9 +348,43 @@ __device__ __forceinline__ void ra_angle_stage(const cf* tile, int Np, const uin
         }
     }
 }
+// Same output as ra_angle_stage for NC in {2, 4, 8} antennas and A a power of two: the zero-padded A-point transform of NC
+// inputs splits as bin a' = r + (A/NC) q:  X[a'] = sum_j (x_j W_A^(j r)) W_NC^(j q), i.e. NC-1 twiddles and ONE NC-point
+// register butterfly give the NC bins of a residue r - about 3x fewer operations than NC-term Horner sums per bin.
+// One lane per (range bin, residue); a warp covers 32 consecutive residues (whole rows when A/NC <= 32), and for a fixed q
+// neighbouring lanes store neighbouring bins.
+template <int NC>
+__device__ __forceinline__ void ra_angle_stage_fft(const cf* tile, int Np, const uint16_t* pos, const cf* twA, int S, int A,
+                                                   float* dst) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    const int M = A / NC, total = S * M;
+    const int m_shift = 31 - __clz(M);
+    const bool fixed_r = M <= 32;                       // then r = lane mod M for every task of this lane
+    cf wj[NC];
+#pragma unroll
+    for (int j = 1; j < NC; ++j) wj[j] = twA[(j * (lane & (M - 1))) & (A - 1)];
+    for (int t0 = warp * 32; t0 < total; t0 += nw * 32) {
+        const int t = t0 + lane;
+        if (t >= total) break;
+        const int k = t >> m_shift, r = t & (M - 1);
+        const cf* row = tile + pos[k] * Np;
+        cf v[NC];
+        v[0] = row[0];
+#pragma unroll
+        for (int j = 1; j < NC; ++j) v[j] = cmul(row[j], fixed_r ? wj[j] : twA[(j * r) & (A - 1)]);
+        Dft<NC>::run(v);
+        float* out = dst + k * A;
+#pragma unroll
+        for (int q = 0; q < NC; ++q) out[(r + M * q + A / 2) & (A - 1)] = sqrt_fast(v[q].x * v[q].x + v[q].y * v[q].y);
+    }
+}
+
 template <int NC>
 __device__ __forceinline__ void ra_angle_stage_any(const cf* tile, int Np, const uint16_t* pos, const cf* twA, int S, int A,
                                                    float* dst, int n_rt = 0) {
+    if constexpr (NC == 2 || NC == 4 || NC == 8) {
+        if (A >= 32 && (A & (A - 1)) == 0) { ra_angle_stage_fft<NC>(tile, Np, pos, twA, S, A, dst); return; }
+    }
     if (A == 64) ra_angle_stage<NC, 2>(tile, Np, pos, twA, S, A, dst, n_rt);
     else if (A == 128) ra_angle_stage<NC, 4>(tile, Np, pos, twA, S, A, dst, n_rt);
     else if (A == 32) ra_angle_stage<NC, 1>(tile, Np, pos, twA, S, A, dst, n_rt);
