@@ -144,6 +144,120 @@ __global__ void __launch_bounds__(kPcThreads) point_cloud_kernel(const __grid_co
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Thread-per-detection variant (antenna sets of at most 8, power-of-two bin count): the warp-per-detection kernel above
+// spends ~230 warp instructions per detection, most of them on the warp reductions, the lane-0 tail and index arithmetic
+// (profiles/r1f_ncu_point_cloud_kernel_1843_RadVel.txt).  Here one thread owns a detection end to end.  The zero-padded
+// A-point transform of NP inputs (set padded with zeros to a power of two) splits by residue: bin a' = r + (A/NP) q is
+// sum_j (z_j W_A^(j r)) W_NP^(j q), so each residue costs NP-1 twiddles and one NP-point butterfly, all in fp64 registers;
+// the running first-maximum replaces the reductions, and every lane converts and stores its own point.
+// ------------------------------------------------------------------------------------------------
+struct D2 { double x, y; };
+__device__ __forceinline__ D2 dadd(D2 a, D2 b) { return {a.x + b.x, a.y + b.y}; }
+__device__ __forceinline__ D2 dsub(D2 a, D2 b) { return {a.x - b.x, a.y - b.y}; }
+__device__ __forceinline__ D2 dmul(D2 a, double2 w) { return {fma(a.x, w.x, -a.y * w.y), fma(a.x, w.y, a.y * w.x)}; }
+__device__ __forceinline__ D2 mul_mi(D2 a) { return {a.y, -a.x}; }      // times -i
+
+template <int NP> __device__ __forceinline__ void dft_regs(D2 (&v)[NP]);
+template <> __device__ __forceinline__ void dft_regs<1>(D2 (&)[1]) {}
+template <> __device__ __forceinline__ void dft_regs<2>(D2 (&v)[2]) {
+    const D2 a = v[0], b = v[1];
+    v[0] = dadd(a, b); v[1] = dsub(a, b);
+}
+template <> __device__ __forceinline__ void dft_regs<4>(D2 (&v)[4]) {
+    const D2 s02 = dadd(v[0], v[2]), d02 = dsub(v[0], v[2]), s13 = dadd(v[1], v[3]), d13 = mul_mi(dsub(v[1], v[3]));
+    v[0] = dadd(s02, s13); v[1] = dadd(d02, d13); v[2] = dsub(s02, s13); v[3] = dsub(d02, d13);
+}
+template <> __device__ __forceinline__ void dft_regs<8>(D2 (&v)[8]) {
+    D2 e[4] = {v[0], v[2], v[4], v[6]}, o[4] = {v[1], v[3], v[5], v[7]};
+    dft_regs<4>(e);
+    dft_regs<4>(o);
+    const double q = 0.70710678118654752440;
+    const D2 o1 = {q * (o[1].x + o[1].y), q * (o[1].y - o[1].x)};      // o[1] W8^1
+    const D2 o2 = mul_mi(o[2]);                                          // o[2] W8^2
+    const D2 o3 = {q * (o[3].y - o[3].x), -q * (o[3].x + o[3].y)};     // o[3] W8^3
+    v[0] = dadd(e[0], o[0]); v[4] = dsub(e[0], o[0]);
+    v[1] = dadd(e[1], o1);   v[5] = dsub(e[1], o1);
+    v[2] = dadd(e[2], o2);   v[6] = dsub(e[2], o2);
+    v[3] = dadd(e[3], o3);   v[7] = dsub(e[3], o3);
+}
+
+// first argmax over the (optionally shifted) output index of | zero-padded A-point DFT of z[0..n) |, n <= NP
+template <int NP>
+__device__ __forceinline__ int angle_argmax_thread(const cf* __restrict__ cube, long long plane, long long cell,
+                                                   const int32_t* __restrict__ ant, int n, int A, bool shift,
+                                                   const double2* tw) {
+    D2 z[NP];
+#pragma unroll
+    for (int j = 0; j < NP; ++j) {
+        z[j] = {0.0, 0.0};
+        if (j < n) { const cf v = __ldg(cube + ant[j] * plane + cell); z[j] = {(double)v.x, (double)v.y}; }
+    }
+    if (NP == 1) return 0;                                  // every bin has the magnitude of the one sample
+    const int M = A / NP, half = shift ? A / 2 : 0;
+    double best = -1.0;
+    int best_a = 0;
+    for (int r = 0; r < M; ++r) {
+        D2 v[NP];
+        v[0] = z[0];
+#pragma unroll
+        for (int j = 1; j < NP; ++j) v[j] = dmul(z[j], tw[(j * r) & (A - 1)]);
+        dft_regs<NP>(v);
+#pragma unroll
+        for (int q = 0; q < NP; ++q) {
+            const double mag = fma(v[q].x, v[q].x, v[q].y * v[q].y);
+            const int ao = (r + M * q + half) & (A - 1);
+            if (mag > best || (mag == best && ao < best_a)) { best = mag; best_a = ao; }
+        }
+    }
+    return best_a;
+}
+
+__device__ __forceinline__ int angle_argmax_thread_any(const cf* cube, long long plane, long long cell, const int32_t* ant,
+                                                       int n, int A, bool shift, const double2* tw) {
+    if (n <= 1) return angle_argmax_thread<1>(cube, plane, cell, ant, n, A, shift, tw);
+    if (n == 2) return angle_argmax_thread<2>(cube, plane, cell, ant, n, A, shift, tw);
+    if (n <= 4) return angle_argmax_thread<4>(cube, plane, cell, ant, n, A, shift, tw);
+    return angle_argmax_thread<8>(cube, plane, cell, ant, n, A, shift, tw);
+}
+
+constexpr int kPcTThreads = 64;
+
+__global__ void __launch_bounds__(kPcTThreads) point_cloud_thread_kernel(const __grid_constant__ PcArgs a, int n_frames) {
+    __shared__ double2 tw_s[kPcTwMax];
+    const bool tw_in_smem = a.A <= kPcTwMax;
+    if (tw_in_smem)
+        for (int i = threadIdx.x; i < a.A; i += kPcTThreads) tw_s[i] = a.tw64[i];
+    __syncthreads();
+    const double2* tw = tw_in_smem ? tw_s : a.tw64;
+    const long long plane = (long long)a.S * a.L;
+    for (int frame = blockIdx.x; frame < n_frames; frame += gridDim.x) {
+        const int n = min(a.counts[frame], a.max_dets);
+        const long long slot0 = (long long)frame * a.max_dets;
+        const long long row0 = a.offsets ? (long long)a.offsets[frame] : slot0;
+        const cf* cube = a.rd + (long long)frame * a.V * plane;
+        for (int slot = threadIdx.x; slot < n; slot += kPcTThreads) {
+            const int2 rdx = reinterpret_cast<const int2*>(a.dets)[slot0 + slot];
+            const long long cell = (long long)rdx.x * a.L + rdx.y;
+            int az_i = 0, el_i = 0;
+            if (a.n_az > 0) az_i = angle_argmax_thread_any(cube, plane, cell, a.az_idx, a.n_az, a.A, a.shift_az != 0, tw);
+            if (a.n_el > 0) el_i = angle_argmax_thread_any(cube, plane, cell, a.el_idx, a.n_el, a.A, a.shift_el != 0, tw);
+            const double ca = a.n_az > 0 ? a.angle_cos[az_i] : 1.0, sa = a.n_az > 0 ? a.angle_sin[az_i] : 0.0;
+            const double ce = a.n_el > 0 ? a.angle_cos[el_i] : 1.0, se = a.n_el > 0 ? a.angle_sin[el_i] : 0.0;
+            const double rng = a.range_bins[rdx.x], vel = a.vel_bins[rdx.y];
+            double4 p;
+            p.x = rng * ce * ca;
+            p.y = rng * ce * sa;
+            p.z = rng * se;
+            p.w = vel;
+            const long long row = row0 + slot;
+            reinterpret_cast<double4*>(a.points)[row] = p;
+            if (a.az_bin) a.az_bin[row] = az_i;
+            if (a.el_bin) a.el_bin[row] = el_i;
+        }
+    }
+}
+
 int launch_point_cloud(radar_ctx* ctx, const cf* rd, int n_frames, const int32_t* dets, const int32_t* counts,
                        int max_dets, const int32_t* az_idx, int n_az, const int32_t* el_idx, int n_el, int shift_az,
                        int shift_el, int num_angle_bins, const int32_t* offsets, double* points_out, int32_t* az_bin_out,
@@ -170,7 +284,11 @@ int launch_point_cloud(radar_ctx* ctx, const cf* rd, int n_frames, const int32_t
     a.points = points_out; a.az_bin = az_bin_out; a.el_bin = el_bin_out;
     a.offsets = offsets;
     const int grid = n_frames < ctx->sm_count * 64 ? n_frames : ctx->sm_count * 64;
-    point_cloud_kernel<<<(unsigned)grid, kPcThreads, 0, st>>>(a, n_frames);
+    const bool pow2_bins = (num_angle_bins & (num_angle_bins - 1)) == 0 && num_angle_bins >= 8;
+    if (pow2_bins && n_az <= 8 && n_el <= 8 && ctx->pc_mode != 1)
+        point_cloud_thread_kernel<<<(unsigned)grid, kPcTThreads, 0, st>>>(a, n_frames);
+    else
+        point_cloud_kernel<<<(unsigned)grid, kPcThreads, 0, st>>>(a, n_frames);
     RB_CUDA_OK(ctx, cudaGetLastError());
     return RADAR_OK;
 }
