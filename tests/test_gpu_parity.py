@@ -5,6 +5,8 @@ Tolerances (BASELINE.json north_star): bin / peak indices bit-exact; RD and RA m
 L2 (fp32 device arithmetic vs fp64 reference); CFAR masks identical except cells within 1e-5 (relative) of
 the threshold, which are counted and reported.
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -410,3 +412,64 @@ def test_error_paths(torch_cuda):
     e = RadarEngine(4, 64, 1, 8)
     with pytest.raises(ValueError):
         e.range_doppler(torch.zeros((1, 8, 4, 63, 2), dtype=torch.int16, device="cuda"))
+
+
+# ------------------------------------------------------------------------------------------------ point-cloud kernels
+def _engine_with_env(cm, var, value):
+    """A private engine created with an environment switch set (switches are read when the context is created)."""
+    from mmwave_radar_processing_b200.engine import RadarEngine
+    old = os.environ.get(var)
+    os.environ[var] = str(value)
+    try:
+        return RadarEngine(cm.num_rx_antennas, cm.get_num_adc_samples(0), cm.chirp_cfgs_per_loop, cm.frameCfg_loops)
+    finally:
+        if old is None:
+            del os.environ[var]
+        else:
+            os.environ[var] = old
+
+
+@pytest.mark.parametrize("name", ["6843_RadVel_ods_20Hz", "1843_RadVel"])
+def test_point_cloud_kernels_agree_and_match_oracle(torch_cuda, name):
+    """Thread-per-detection kernel (default) and warp-per-detection kernel (RADAR_B200_PC=1): identical angle bins and
+    points, both equal to the oracle's fp64 FFT argmax, over antenna sets of 1..8 (padded / exact powers of two), 12
+    (warp kernel only), 8..256 bins, both shift flags, ragged per-frame counts."""
+    torch = torch_cuda
+    from oracle import radar_oracle as orc
+    from mmwave_radar_processing_b200.pipeline import reference_axes
+    cm = load_cfg(name)
+    frames = [_oracle_frame(cm, 40 + f) for f in range(3)]
+    iq = torch.from_numpy(np.stack([f[0] for f in frames])).cuda()
+    v, s, l = frames[0][2].shape
+    rng = np.random.default_rng(17)
+    max_dets = 200
+    counts = np.array([200, 0, 77], dtype=np.int32)
+    dets = np.zeros((3, max_dets, 2), dtype=np.int32)
+    dets[..., 0] = rng.integers(0, s, (3, max_dets))
+    dets[..., 1] = rng.integers(0, l, (3, max_dets))
+    engines = {"thread": _engine(cm), "warp": _engine_with_env(cm, "RADAR_B200_PC", 1)}
+    cases = [([0], [], 64), ([1, 0], [3], 64), ([0, 1, 2], [3, 2, 1, 0], 128), ([0, 3, 1, 2], [2, 3], 8),
+             (list(range(min(v, 8))), [1, 2, 3, 0, 2], 256), ([3, 2, 1, 0, 1, 2], list(range(min(v, 7))), 32)]
+    if v >= 12:
+        cases.append((list(range(12)), [9, 8, 5, 4], 64))            # 12 antennas: warp kernel on both engines
+    for az, el, bins in cases:
+        rb, vb, ab = reference_axes(cm, bins)
+        got = {}
+        for tag, eng in engines.items():
+            eng.set_axes(rb, vb)
+            eng.set_angle_bins(ab)
+            rd, _ = eng.range_doppler(iq, want_rd=True, mag_antenna=0)
+            rd_host = rd.cpu().numpy().astype(np.complex128)             # the oracle runs on the SAME fp32 cube
+            for sh_az, sh_el in ((True, False), (False, True)):
+                pts, az_bin, el_bin = eng.point_cloud(rd, torch.from_numpy(dets).cuda(), torch.from_numpy(counts).cuda(),
+                                                      az, el, sh_az, sh_el, bins)
+                got[tag, sh_az] = (pts.cpu().numpy(), az_bin.cpu().numpy(), el_bin.cpu().numpy())
+        for sh_az, sh_el in ((True, False), (False, True)):
+            a, b = got["thread", sh_az], got["warp", sh_az]
+            for x, y in zip(a, b):
+                np.testing.assert_array_equal(x, y)
+            for f in range(3):
+                n = counts[f]
+                rd_ref = rd_host[f]
+                np.testing.assert_array_equal(a[1][f, :n], orc.angle_indices(rd_ref, dets[f, :n, 0], dets[f, :n, 1], az, bins, sh_az))
+                np.testing.assert_array_equal(a[2][f, :n], orc.angle_indices(rd_ref, dets[f, :n, 0], dets[f, :n, 1], el, bins, sh_el))
