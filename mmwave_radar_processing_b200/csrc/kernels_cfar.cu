@@ -39,6 +39,7 @@ struct CfarArgs {
     int pitch;            // row pitch of the map in shared memory: == nvd (mod 32) so consecutive cells under test, which run
                           // across valid rows, read consecutive banks (>= cols)
     FastDiv div_cols, div_vd, div_wd;
+    int ph1_extra;        // OS counting path: full rows counted before the first decision, beyond the minimum that can reject
 };
 
 template <int MAXV>
@@ -147,7 +148,7 @@ __device__ __forceinline__ void os_count_cells(const CfarArgs& a, const float* m
     const int g_lo = a.tr, g_hi = a.tr + 2 * a.gr;                 // window rows crossing the guard band
     const int seg2 = td + 2 * gd + 1;
     // rows of phase 1: enough that "all of them above the bound" already rules a detection out, plus two, all full rows
-    int ph1 = (a.n_train - a.k_rank + wd) / wd + 2;
+    int ph1 = (a.n_train - a.k_rank + wd) / wd + a.ph1_extra;
     ph1 = ph1 < g_lo ? ph1 : g_lo;
     const int lane = threadIdx.x & 31;
     for (int c0 = 0; c0 < n_cut; c0 += blockDim.x) {
@@ -367,6 +368,7 @@ static int resolve_params(radar_ctx* ctx, const radar_cfar_params& p, bool one_d
             return set_error(ctx, RADAR_E_INVALID, "unknown CFAR kind %d", p.kind);
     }
     a->div_wd = make_fastdiv((uint32_t)wd);
+    a->ph1_extra = ctx->cfar_ph1 >= 0 ? ctx->cfar_ph1 : 2;
     return RADAR_OK;
 }
 
