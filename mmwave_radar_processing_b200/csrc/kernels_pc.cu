@@ -221,9 +221,9 @@ __device__ __forceinline__ int angle_argmax_thread_any(const cf* cube, long long
     return angle_argmax_thread<8>(cube, plane, cell, ant, n, A, shift, tw);
 }
 
-constexpr int kPcTThreads = 64;
+constexpr int kPcTThreads = 128;
 
-__global__ void __launch_bounds__(kPcTThreads) point_cloud_thread_kernel(const __grid_constant__ PcArgs a, int n_frames) {
+__global__ void __launch_bounds__(kPcTThreads, 8) point_cloud_thread_kernel(const __grid_constant__ PcArgs a, int n_frames) {
     __shared__ double2 tw_s[kPcTwMax];
     const bool tw_in_smem = a.A <= kPcTwMax;
     if (tw_in_smem)
