@@ -7,7 +7,8 @@ A *step* is one pass of the hot path over one batch of F synthetic int16 ADC fra
 
     radar_range_doppler (all V antennas, complex RD cube + |RD[0]|)  ->  radar_range_angle (heat map)
       ->  radar_cfar_2d (OS-CFAR-2D + ordered compaction)  ->  radar_det_offsets  ->  radar_point_cloud
-      [-> NCCL all-gather of the variable-length point clouds when N > 1]
+      [N > 1: radar_point_cloud also stores every packed row into the gathered buffer of every rank (NVLink peer memory);
+       counts / totals by peer copies + a cross-rank barrier on a side stream.  --exchange nccl: NCCL all-gathers instead]
 
 ``value`` is whole-job frames/s with the inputs resident in HBM; ``e2e`` is the same metric through the host-facing
 call (``FramePipeline.run_host``): pinned host int16 frames in, host point clouds out, copies inside the timed
@@ -213,14 +214,14 @@ def run_reference_arm(a):
     return 0
 
 
-def workload_config(cm, wl, frames_per_gpu, n_gpus):
+def workload_config(cm, wl, frames_per_gpu, n_gpus, exchange="peer"):
     r, s, cpl, l = cm.num_rx_antennas, cm.get_num_adc_samples(0), cm.chirp_cfgs_per_loop, cm.frameCfg_loops
     return {"workload": f"configs/{WORKLOADS[wl][0]}.cfg batched synthetic int16 ADC cubes", "num_rx": r,
             "chirps_per_loop": cpl, "virtual_antennas": r * cpl, "samples": s, "loops": l,
             "frames_per_gpu_per_step": frames_per_gpu, "global_frames_per_step": frames_per_gpu * n_gpus,
             "detector": "os_cfar_2d num_train=(8,4) num_guard=(2,1) rho=0.75 alpha=3.5",
             "stages": "range_doppler+range_angle+cfar_2d+det_offsets+point_cloud",
-            "parallelism": f"frame-sharded x{n_gpus}" + (" + NCCL all-gather of point clouds (own stream, under the next step)" if n_gpus > 1 else ""),
+            "parallelism": f"frame-sharded x{n_gpus}" + ((" + point rows stored into every rank's gathered buffer by the point-cloud kernel (NVLink peer memory), counts by peer copies + barrier on a side stream" if exchange == "peer" else " + NCCL all-gather of point clouds (own stream, under the next step)") if n_gpus > 1 else ""),
             "l2_policy": "per-step working set (int16 in + complex RD out) exceeds the 126 MB L2; no explicit flush"}
 
 
@@ -237,6 +238,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 -> min(steps, 10)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-range-angle", action="store_true")
+    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
+                    help="N > 1: point rows stored into peer memory by the point-cloud kernel (default) or NCCL all-gathers")
     a = ap.parse_args()
     a.warmup = max(a.warmup, 3) if a.impl == "b200" else a.warmup
     if a.impl == "reference":
@@ -273,15 +276,37 @@ def main():
     iq_host.copy_(torch.from_numpy(iq_host_np))
     iq_dev = iq_host.to(dev)
 
-    # ---- N > 1: the all-gather of step i runs on its own stream under the kernels of step i+1 (double-buffered staging);
-    # its fixed capacity is sized from a first, synchronous step (largest per-rank total + 25 %) and checked at the end
+    # ---- N > 1: the exchange of the point clouds.  Default ("peer"): the point-cloud kernel stores every packed row straight
+    # into the gathered buffers of all ranks over NVLink peer memory (radar_ctx_set_point_mirrors + PeerPointExchange); per
+    # step only the counts / totals travel by peer copies, followed by the cross-rank barrier, on a side stream under the
+    # kernels of the next step.  "--exchange nccl": staging copy + NCCL all-gathers on the side stream (the previous scheme).
+    # The fixed capacity is sized from a first, synchronous step (largest per-rank total + 25 %) and checked at the end.
     cap_rows = 0
     comm = torch.cuda.Stream(device=dev) if world > 1 else None
-    staging, gathered, done_ev = [None, None], [None, None], [None, None]
+    staging, gathered, done_ev = [None, None, None], [None, None, None], [None, None, None]
     step_no = 0
+    peer_ex = None
+    DEPTH = 3                                                    # gathered slots in flight (peer exchange)
 
     def step(mark=None):
         nonlocal step_no
+        if world > 1 and peer_ex is not None:
+            k = step_no % DEPTH
+            main = torch.cuda.current_stream()
+            if step_no >= 2 and done_ev[(step_no - 2) % DEPTH] is not None:
+                main.wait_event(done_ev[(step_no - 2) % DEPTH])   # every rank is past step i-2: slot k (step i-3) is free
+            peer_ex.arm(k)
+            out = pipe.run(iq_dev, mark)
+            ready = torch.cuda.Event()
+            ready.record(main)
+            with torch.cuda.stream(comm):
+                comm.wait_event(ready)
+                peer_ex.publish(k, out["counts"], out["offsets"][F:F + 1])
+                done_ev[k] = torch.cuda.Event()
+                done_ev[k].record(comm)
+            gathered[k] = peer_ex.gathered(k)
+            step_no += 1
+            return out
         out = pipe.run(iq_dev, mark)
         if world > 1:
             k = step_no & 1
@@ -312,6 +337,8 @@ def main():
         t = first["offsets"][F:F + 1].to(torch.int64).clone()
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         cap_rows = int((int(t.item()) * 5 // 4 + 1023) // 1024 * 1024)
+        if a.exchange == "peer":
+            peer_ex = rdist.PeerPointExchange(pipe.engine, F, cap_rows, depth=DEPTH)
 
     stage_names = ["range_doppler"] + ([] if a.no_range_angle else ["range_angle"]) + ["cfar", "point_cloud"]
 
@@ -356,6 +383,8 @@ def main():
         for g in gathered:
             if g is not None:
                 rdist.check_capacity(g[2], cap_rows)
+        if peer_ex is not None:
+            peer_ex.disarm()                                     # the end-to-end region below is per rank
     stage_ms = {n: 0.0 for n in stage_names}
     for (n0, e0), (n1, e1) in zip(marks[:-1], marks[1:]):
         if n1 != "begin":
@@ -397,7 +426,7 @@ def main():
             "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": f"synthetic ({min(N_UNIQUE, F)} distinct seeded frames per rank tiled to the batch)",
-            "config": workload_config(cm, a.workload, F, world),
+            "config": workload_config(cm, a.workload, F, world, a.exchange),
             "roofline": {"kernel": "rd_stream_kernel", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": (traffic * F if traffic else None),
                          "peak_source": peak_src, "algorithmic_bytes_per_frame": rd_bytes_per_frame,

@@ -185,6 +185,15 @@ int radar_point_cloud(radar_ctx* ctx, const void* rd, int n_frames,
                       int shift_az, int shift_el, int num_angle_bins, const int32_t* offsets,
                       double* points_out, int32_t* az_bin_out, int32_t* el_bin_out, void* stream);
 
+/* Multi-GPU exchange fused into the point-cloud kernel (the variable-length point clouds are the one
+ * exchange of the streaming path).  After this call every PACKED row (offsets != NULL) radar_point_cloud writes is also
+ * stored at mirrors[i] + 4*row for row < cap_rows: mirrors are device pointers the kernel can store to - peer-mapped
+ * buffers of the other ranks (NVLink / NVSwitch peer memory, e.g. torch symmetric memory) and this rank's own slot of
+ * the gathered array - so the all-gather of the points happens inside the kernel, row by row, with no staging copy and
+ * no collective kernel.  h_mirrors: host array of n_mirrors (<= 16) device pointers; n_mirrors = 0 switches it off.
+ * Completion across ranks is the caller's barrier. */
+int radar_ctx_set_point_mirrors(radar_ctx* ctx, const uint64_t* h_mirrors, int n_mirrors, int cap_rows);
+
 /* Exclusive scan of min(counts[f], max_dets): offsets_out int32 [n_frames+1], offsets_out[n_frames] = total
  * number of points of the batch (the per-frame list lengths of PointCloudGenerator.process,
  * processors/point_cloud_generator.py:108-140, laid end to end). */

@@ -208,6 +208,19 @@ int radar_ctx_set_angle_bins(radar_ctx* ctx, const double* h_angle_bins, int n_b
     return upload_doubles(ctx, s.data(), n_bins, &ctx->angle_sin, &n_tmp);
 }
 
+int radar_ctx_set_point_mirrors(radar_ctx* ctx, const uint64_t* h_mirrors, int n_mirrors, int cap_rows) {
+    RB_ENTER(ctx);
+    if (n_mirrors < 0 || n_mirrors > 16) return set_error(ctx, RADAR_E_INVALID, "n_mirrors %d outside 0..16", n_mirrors);
+    if (n_mirrors > 0 && (!h_mirrors || cap_rows <= 0)) return set_error(ctx, RADAR_E_INVALID, "mirrors need pointers and a positive capacity");
+    for (int i = 0; i < n_mirrors; ++i) {
+        if (!h_mirrors[i] || (h_mirrors[i] & 31u)) return set_error(ctx, RADAR_E_INVALID, "mirror %d is null or not 32-byte aligned", i);
+        ctx->point_mirrors[i] = reinterpret_cast<double*>(h_mirrors[i]);
+    }
+    ctx->n_point_mirrors = n_mirrors;
+    ctx->point_mirror_cap = n_mirrors > 0 ? cap_rows : 0;
+    return RADAR_OK;
+}
+
 int radar_range_doppler(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, const int32_t* ant_list, int n_ant,
                         int window_flags, void* rd_out, float* mag_out, int mag_antenna, void* stream) {
     RB_ENTER(ctx);

@@ -29,7 +29,16 @@ struct PcArgs {
     const double* angle_cos; const double* angle_sin;     // cos / sin of angle_bins (host fp64, uploaded with the bins)
     double* points; int32_t* az_bin; int32_t* el_bin;
     const int32_t* offsets;      // optional exclusive scan of the clamped counts: packed output rows
+    double* mirrors[16];         // radar_ctx_set_point_mirrors: every packed row below mirror_cap is stored there too
+    int n_mirrors, mirror_cap;   // (peer-mapped gathered buffers: the all-gather of the points, done by these stores)
 };
+
+__device__ __forceinline__ void store_point(const PcArgs& a, long long row, double4 p) {
+    reinterpret_cast<double4*>(a.points)[row] = p;
+    if (a.n_mirrors > 0 && row < a.mirror_cap) {
+        for (int m = 0; m < a.n_mirrors; ++m) reinterpret_cast<double4*>(a.mirrors[m])[row] = p;
+    }
+}
 
 // argmax_a | sum_j z[j] w^j |, w = W_A^{a'}, a' = (a - A/2) mod A when shifted; first maximum wins.  z: this detection's n
 // gathered RD samples (shared memory), tw: W_A^e in fp64.  The sum is evaluated by Horner's rule in fp64 (one twiddle per
@@ -135,7 +144,7 @@ __global__ void __launch_bounds__(kPcThreads) point_cloud_kernel(const __grid_co
                     p.z = rng * se;
                     p.w = vel;
                     const long long row = row0 + c0 + slot;
-                    reinterpret_cast<double4*>(a.points)[row] = p;
+                    store_point(a, row, p);
                     if (a.az_bin) a.az_bin[row] = az_i;
                     if (a.el_bin) a.el_bin[row] = el_i;
                 }
@@ -251,7 +260,7 @@ __global__ void __launch_bounds__(kPcTThreads, 8) point_cloud_thread_kernel(cons
             p.z = rng * se;
             p.w = vel;
             const long long row = row0 + slot;
-            reinterpret_cast<double4*>(a.points)[row] = p;
+            store_point(a, row, p);
             if (a.az_bin) a.az_bin[row] = az_i;
             if (a.el_bin) a.el_bin[row] = el_i;
         }
@@ -283,6 +292,9 @@ int launch_point_cloud(radar_ctx* ctx, const cf* rd, int n_frames, const int32_t
     a.angle_cos = ctx->angle_cos; a.angle_sin = ctx->angle_sin;
     a.points = points_out; a.az_bin = az_bin_out; a.el_bin = el_bin_out;
     a.offsets = offsets;
+    a.n_mirrors = offsets ? ctx->n_point_mirrors : 0;       // mirrors follow the packed layout only
+    a.mirror_cap = ctx->point_mirror_cap;
+    for (int i = 0; i < 16; ++i) a.mirrors[i] = ctx->point_mirrors[i];
     const int grid = n_frames < ctx->sm_count * 64 ? n_frames : ctx->sm_count * 64;
     const bool pow2_bins = (num_angle_bins & (num_angle_bins - 1)) == 0 && num_angle_bins >= 8;
     if (pow2_bins && n_az <= 8 && n_el <= 8 && ctx->pc_mode != 1)

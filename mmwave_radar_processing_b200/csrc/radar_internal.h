@@ -46,6 +46,8 @@ struct radar_ctx {
     int sar_dbg = 0;                              // RADAR_B200_SAR_DBG: timing experiments of the tensor-core SAR kernel (results invalid)
     int sar_tpr = 0;                              // RADAR_B200_SAR_TPR: threads per direction row of the tensor-core SAR kernel (0 = default)
     int sar_seg_chunks = 0;                       // RADAR_B200_SAR_SEG: chunks (16 elements) per accumulation segment, 0 = automatic
+    double* point_mirrors[16] = {nullptr};       // radar_ctx_set_point_mirrors: extra destinations of every packed point row
+    int n_point_mirrors = 0, point_mirror_cap = 0;
     int cfar_ph1 = -1;                            // RADAR_B200_CFAR_PH1: extra full rows of the OS-CFAR first counting phase (-1 = default)
     int pc_mode = 0;                              // RADAR_B200_PC=1: warp-per-detection point-cloud kernel only (tests / comparison)
     int ra_fc = 0;                                // RADAR_B200_RA_FC: frames per pass of the range-angle kernel (0 = cost model)

@@ -138,3 +138,60 @@ def sar_image_sharded(compute_slice: Callable[[torch.Tensor, torch.Tensor, torch
         rlo, rhi = shard_range(g, r, w)
         cols.append(allt[r, :rhi - rlo])
     return torch.cat(cols, dim=0).transpose(0, 1).contiguous(), (lo, hi)
+
+
+class PeerPointExchange:
+    """The all-gather of the streaming path's point clouds over NVLink peer memory, with the point rows stored by the
+    point-cloud kernel itself (``radar_ctx_set_point_mirrors``): no staging copy and no collective kernel competing with
+    the next step for SMs.  One symmetric allocation (``torch.distributed._symmetric_memory``) holds ``depth`` gathered
+    slots on every rank; slot layout per (k, source rank): points float64 [cap_rows, 4] | counts int32 [F_local] |
+    total int32 [1].  Per step:
+
+        ex.arm(k)                      # the next radar_point_cloud call also stores its packed rows into slot k of every rank
+        out = pipe.run(...)            # kernels (main stream)
+        ex.publish(k, out["counts"], out["offsets"][F:F+1])   # counts / total by peer copies, then the cross-rank barrier
+
+    ``gathered(k)`` are views of this rank's slot k: valid once ``publish(k)`` has completed on the stream it ran on; the
+    reader must be done with slot k before this rank's ``publish`` of the step after next (depth 2)."""
+
+    def __init__(self, engine, n_frames_local: int, cap_rows: int, depth: int = 2):
+        import torch.distributed._symmetric_memory as symm
+        self.engine, self.f, self.cap, self.depth = engine, int(n_frames_local), int(cap_rows), int(depth)
+        self.world, self.rank = world_size(), dist.get_rank()
+        self.pts_bytes = self.cap * 32
+        self.cnt_off = self.pts_bytes
+        self.tot_off = self.cnt_off + 4 * self.f
+        self.slot = (self.tot_off + 4 + 255) // 256 * 256
+        dev = engine.device
+        self.buf = symm.empty((self.depth, self.world, self.slot), dtype=torch.uint8, device=dev)
+        self.buf.zero_()
+        self.hdl = symm.rendezvous(self.buf, dist.group.WORLD)
+        self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        self.peers = [self.hdl.get_buffer(r, self.buf.shape, torch.uint8) for r in range(self.world)]
+        torch.cuda.synchronize(dev)
+        self.hdl.barrier(channel=0)
+
+    def arm(self, k: int):
+        off = (k * self.world + self.rank) * self.slot
+        self.engine.set_point_mirrors([p + off for p in self.ptrs], self.cap)
+
+    def disarm(self):
+        self.engine.set_point_mirrors([], 0)
+
+    def publish(self, k: int, counts: torch.Tensor, total: torch.Tensor):
+        """On the current stream, after the point-cloud kernel of this step (stream order or an event wait)."""
+        c8 = counts.contiguous().view(torch.uint8)
+        t8 = total.contiguous().view(torch.uint8)
+        for i in range(self.world):
+            dst = self.peers[(self.rank + i) % self.world][k, self.rank]
+            dst[self.cnt_off:self.cnt_off + c8.numel()].copy_(c8, non_blocking=True)
+            dst[self.tot_off:self.tot_off + 4].copy_(t8, non_blocking=True)
+        self.hdl.barrier(channel=k % 8)
+
+    def gathered(self, k: int):
+        """-> (points [W, cap_rows, 4] f64, counts [W, F_local] i32, totals [W] i32) views of this rank's slot k."""
+        s = self.buf[k]
+        pts = s[:, :self.pts_bytes].view(torch.float64).view(self.world, self.cap, 4)
+        cnt = s[:, self.cnt_off:self.tot_off].view(torch.int32)
+        tot = s[:, self.tot_off:self.tot_off + 4].view(torch.int32).view(self.world)
+        return pts, cnt, tot

@@ -118,6 +118,12 @@ class RadarEngine:
                                                         ab.shape[0]), self.ctx)
             self._angle_key = key
 
+    def set_point_mirrors(self, pointers, cap_rows: int = 0):
+        """Device pointers (ints) every packed point row is also stored to (peer-mapped gathered buffers); [] switches off."""
+        arr = (C.c_uint64 * max(1, len(pointers)))(*[int(p) for p in pointers])
+        nat.check(self.lib.radar_ctx_set_point_mirrors(self.ctx, C.cast(arr, C.c_void_p), len(pointers), int(cap_rows)),
+                  self.ctx)
+
     # ------------------------------------------------------------------ kernels
     def range_doppler(self, adc: torch.Tensor, ant_list=None, window_flags: int = 3, want_rd: bool = True,
                       mag_antenna: Optional[int] = None, rd_out=None, mag_out=None):
