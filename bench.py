@@ -7,8 +7,10 @@ A *step* is one pass of the hot path over one batch of F synthetic int16 ADC fra
 
     radar_range_doppler (all V antennas, complex RD cube + |RD[0]|)  ->  radar_range_angle (heat map)
       ->  radar_cfar_2d (OS-CFAR-2D + ordered compaction)  ->  radar_det_offsets  ->  radar_point_cloud
-      [N > 1: radar_point_cloud also stores every packed row into the gathered buffer of every rank (NVLink peer memory);
-       counts / totals by peer copies + a cross-rank barrier on a side stream.  --exchange nccl: NCCL all-gathers instead]
+      [N > 1: radar_point_cloud also stores every packed row into this rank's slot of a symmetric gathered buffer; the slot,
+       the counts and the total are pushed to the peers by copy-engine peer copies over NVLink + a cross-rank barrier on a
+       side stream, under the kernels of the next step (--exchange peer: the kernel stores to every rank itself;
+       --exchange nccl: staging copy + NCCL all-gathers)]
 
 ``value`` is whole-job frames/s with the inputs resident in HBM; ``e2e`` is the same metric through the host-facing
 call (``FramePipeline.run_host``): pinned host int16 frames in, host point clouds out, copies inside the timed
@@ -221,7 +223,7 @@ def workload_config(cm, wl, frames_per_gpu, n_gpus, exchange="peer"):
             "frames_per_gpu_per_step": frames_per_gpu, "global_frames_per_step": frames_per_gpu * n_gpus,
             "detector": "os_cfar_2d num_train=(8,4) num_guard=(2,1) rho=0.75 alpha=3.5",
             "stages": "range_doppler+range_angle+cfar_2d+det_offsets+point_cloud",
-            "parallelism": f"frame-sharded x{n_gpus}" + ((" + point rows stored into every rank's gathered buffer by the point-cloud kernel (NVLink peer memory), counts by peer copies + barrier on a side stream" if exchange == "peer" else " + NCCL all-gather of point clouds (own stream, under the next step)") if n_gpus > 1 else ""),
+            "parallelism": f"frame-sharded x{n_gpus}" + ({"copy": " + point rows stored into a symmetric gathered buffer by the point-cloud kernel, pushed to the peers by copy-engine peer copies over NVLink + barrier (side stream, under the next step)", "peer": " + point rows stored into every rank's gathered buffer by the point-cloud kernel (NVLink peer memory), counts by peer copies + barrier on a side stream", "nccl": " + NCCL all-gather of point clouds (own stream, under the next step)"}[exchange] if n_gpus > 1 else ""),
             "l2_policy": "per-step working set (int16 in + complex RD out) exceeds the 126 MB L2; no explicit flush"}
 
 
@@ -238,8 +240,10 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=0, help="0 -> min(steps, 10)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-range-angle", action="store_true")
-    ap.add_argument("--exchange", default="peer", choices=["peer", "nccl"],
-                    help="N > 1: point rows stored into peer memory by the point-cloud kernel (default) or NCCL all-gathers")
+    ap.add_argument("--exchange", default="copy", choices=["copy", "peer", "nccl"],
+                    help="N > 1 exchange of the point clouds: copy = kernel stores into this rank's gathered slot + copy-engine "
+                         "pushes to the peers over NVLink (default); peer = the kernel stores into every rank's slot itself; "
+                         "nccl = staging copy + NCCL all-gathers")
     a = ap.parse_args()
     a.warmup = max(a.warmup, 3) if a.impl == "b200" else a.warmup
     if a.impl == "reference":
@@ -276,10 +280,12 @@ def main():
     iq_host.copy_(torch.from_numpy(iq_host_np))
     iq_dev = iq_host.to(dev)
 
-    # ---- N > 1: the exchange of the point clouds.  Default ("peer"): the point-cloud kernel stores every packed row straight
-    # into the gathered buffers of all ranks over NVLink peer memory (radar_ctx_set_point_mirrors + PeerPointExchange); per
-    # step only the counts / totals travel by peer copies, followed by the cross-rank barrier, on a side stream under the
-    # kernels of the next step.  "--exchange nccl": staging copy + NCCL all-gathers on the side stream (the previous scheme).
+    # ---- N > 1: the exchange of the point clouds (PeerPointExchange: one symmetric allocation, 3 gathered slots per rank).
+    # "copy" (default): the point-cloud kernel stores every packed row into this rank's own slot (radar_ctx_set_point_mirrors)
+    # and the slot, the counts and the total go to the peers by copy-engine peer copies over NVLink, then the cross-rank
+    # barrier - all on a side stream under the kernels of the next step, no SM time.  "peer": the kernel stores the rows into
+    # every rank's slot itself (best at N = 2, loses at N = 8: 32-byte remote stores per thread).  "nccl": staging copy +
+    # NCCL all-gathers on the side stream (the NCCL kernels take SMs from the next step's range-Doppler / range-angle).
     # The fixed capacity is sized from a first, synchronous step (largest per-rank total + 25 %) and checked at the end.
     cap_rows = 0
     comm = torch.cuda.Stream(device=dev) if world > 1 else None
@@ -295,13 +301,13 @@ def main():
             main = torch.cuda.current_stream()
             if step_no >= 2 and done_ev[(step_no - 2) % DEPTH] is not None:
                 main.wait_event(done_ev[(step_no - 2) % DEPTH])   # every rank is past step i-2: slot k (step i-3) is free
-            peer_ex.arm(k)
+            peer_ex.arm(k, remote=a.exchange == "peer")
             out = pipe.run(iq_dev, mark)
             ready = torch.cuda.Event()
             ready.record(main)
             with torch.cuda.stream(comm):
                 comm.wait_event(ready)
-                peer_ex.publish(k, out["counts"], out["offsets"][F:F + 1])
+                peer_ex.publish(k, out["counts"], out["offsets"][F:F + 1], push_points=a.exchange == "copy")
                 done_ev[k] = torch.cuda.Event()
                 done_ev[k].record(comm)
             gathered[k] = peer_ex.gathered(k)
@@ -337,7 +343,7 @@ def main():
         t = first["offsets"][F:F + 1].to(torch.int64).clone()
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         cap_rows = int((int(t.item()) * 5 // 4 + 1023) // 1024 * 1024)
-        if a.exchange == "peer":
+        if a.exchange in ("peer", "copy"):
             peer_ex = rdist.PeerPointExchange(pipe.engine, F, cap_rows, depth=DEPTH)
 
     stage_names = ["range_doppler"] + ([] if a.no_range_angle else ["range_angle"]) + ["cfar", "point_cloud"]

@@ -171,19 +171,27 @@ class PeerPointExchange:
         torch.cuda.synchronize(dev)
         self.hdl.barrier(channel=0)
 
-    def arm(self, k: int):
+    def arm(self, k: int, remote: bool = True):
+        """remote False: only this rank's own gathered slot is a mirror; the peers get the rows from ``publish(points=...)``."""
         off = (k * self.world + self.rank) * self.slot
-        self.engine.set_point_mirrors([p + off for p in self.ptrs], self.cap)
+        ptrs = self.ptrs if remote else [self.ptrs[self.rank]]
+        self.engine.set_point_mirrors([p + off for p in ptrs], self.cap)
 
     def disarm(self):
         self.engine.set_point_mirrors([], 0)
 
-    def publish(self, k: int, counts: torch.Tensor, total: torch.Tensor):
-        """On the current stream, after the point-cloud kernel of this step (stream order or an event wait)."""
+    def publish(self, k: int, counts: torch.Tensor, total: torch.Tensor, push_points: bool = False):
+        """On the current stream, after the point-cloud kernel of this step (stream order or an event wait).
+        ``push_points``: this rank's rows (its own slot k, filled by the kernel's local mirror) are pushed to the OTHER
+        ranks by peer-to-peer copies (copy engines) - the variant for ``arm(k, remote=False)``, where the kernel's own
+        stores stay on the local GPU."""
         c8 = counts.contiguous().view(torch.uint8)
         t8 = total.contiguous().view(torch.uint8)
+        p8 = self.buf[k, self.rank, :self.pts_bytes] if push_points else None
         for i in range(self.world):
             dst = self.peers[(self.rank + i) % self.world][k, self.rank]
+            if p8 is not None and i > 0:
+                dst[:self.pts_bytes].copy_(p8, non_blocking=True)
             dst[self.cnt_off:self.cnt_off + c8.numel()].copy_(c8, non_blocking=True)
             dst[self.tot_off:self.tot_off + 4].copy_(t8, non_blocking=True)
         self.hdl.barrier(channel=k % 8)

@@ -45,6 +45,21 @@ def main():
             n = int(tot[r])
             assert n > 0 and torch.equal(pts[r, :n], want[0][r, :n]), (rank, step, r)
         dist.barrier()
+    for step in range(3):                                   # kernel stores stay local, the peers get copy-engine pushes
+        k = step % 2
+        ex.buf[k].zero_()
+        torch.cuda.synchronize()
+        dist.barrier()
+        ex.arm(k, remote=False)
+        out = pipe.run(iq)
+        ex.publish(k, out["counts"], out["offsets"][f:f + 1], push_points=True)
+        torch.cuda.synchronize()
+        pts, cnt, tot = ex.gathered(k)
+        assert torch.equal(tot, want[2]) and torch.equal(cnt, want[1]), (rank, step)
+        for r in range(world):
+            n = int(tot[r])
+            assert torch.equal(pts[r, :n], want[0][r, :n]), (rank, step, r)
+        dist.barrier()
     ex.disarm()
     # capacity smaller than the rank's rows: rows beyond it are dropped on the mirrors, the local output is complete
     small = rdist.PeerPointExchange(pipe.engine, f, 64)
