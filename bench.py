@@ -344,7 +344,19 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         cap_rows = int((int(t.item()) * 5 // 4 + 1023) // 1024 * 1024)
         if a.exchange in ("peer", "copy"):
-            peer_ex = rdist.PeerPointExchange(pipe.engine, F, cap_rows, depth=DEPTH)
+            # symmetric memory needs peer access between all GPUs of the node; every rank must take the same branch
+            ok = torch.ones((1,), dtype=torch.int32, device=dev)
+            try:
+                peer_ex = rdist.PeerPointExchange(pipe.engine, F, cap_rows, depth=DEPTH)
+            except Exception as exc:  # noqa: BLE001
+                print(f"[bench] rank {rank}: peer exchange unavailable ({exc}); using NCCL all-gathers", file=sys.stderr)
+                ok.zero_()
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if int(ok.item()) == 0:
+                if peer_ex is not None:
+                    peer_ex.disarm()
+                peer_ex = None
+                a.exchange = "nccl"
 
     stage_names = ["range_doppler"] + ([] if a.no_range_angle else ["range_angle"]) + ["cfar", "point_cloud"]
 
