@@ -230,8 +230,9 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
     SmemArena ar(smem_raw);
     float* map = ar.take<float>(a.rows * a.pitch);
     uint8_t* mask = ar.take<uint8_t>(n_cells);
-    int* work_cell = ar.take<int>(n_cells);              // OS counting path: undecided cells after phase 1
-    float* work_t = ar.take<float>(n_cells);
+    const int n_work_max = max(a.rows - 2 * (a.tr + a.gr), 0) * max(a.cols - 2 * (a.td + a.gd), 0);   // cells under test
+    int* work_cell = ar.take<int>(n_work_max);           // OS counting path: undecided cells after phase 1
+    float* work_t = ar.take<float>(n_work_max);
     __shared__ int work_n;
     if (threadIdx.x == 0) work_n = 0;
     const long long m = blockIdx.x;
@@ -389,7 +390,9 @@ static int launch_cfar(radar_ctx* ctx, const float* maps, int n_maps, int rows, 
     const size_t n_cells = (size_t)rows * cols;
     a.pitch = cols;
     if (nvd > 0) while ((a.pitch - nvd) % 32 != 0) ++a.pitch;
-    const size_t smem = arena_bytes((size_t)rows * a.pitch, 4) + arena_bytes(n_cells, 1) + 2 * arena_bytes(n_cells, 4);
+    const int nvr = rows - 2 * (a.tr + a.gr);
+    const size_t n_work_max = (size_t)(nvr > 0 ? nvr : 0) * (size_t)(nvd > 0 ? nvd : 0);
+    const size_t smem = arena_bytes((size_t)rows * a.pitch, 4) + arena_bytes(n_cells, 1) + 2 * arena_bytes(n_work_max, 4);
     if (smem > (size_t)ctx->max_smem_optin)
         return set_error(ctx, RADAR_E_UNSUPPORTED, "CFAR map of %d x %d cells exceeds shared memory", rows, cols);
     RB_CUDA_OK(ctx, cudaFuncSetAttribute(cfar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
