@@ -46,6 +46,8 @@ struct SarPrepArgs {
     float* bblk;          // [n_chunks][2][NB * kTcKC]
     double* posl;         // [3][n_chunks * kTcElems]  positions / lambda, zero padded
     float* posf;          // [6][n_chunks * kTcElems]  the same as float pairs: rows 2a = hi, 2a+1 = lo of axis a
+    float* stepf;         // [6][n_chunks]  per-axis element spacing / lambda (float hi / lo pairs) of an equispaced chunk
+    uint8_t* lin;         // [n_chunks]     1 = the chunk is an arithmetic progression to 1e-9 wavelengths (and has no padding)
 };
 
 __device__ __forceinline__ float tf32_round(float v) {
@@ -64,6 +66,26 @@ __global__ void __launch_bounds__(256) sar_tc_prep_kernel(const __grid_constant_
         const float vh = (float)v;
         a.posf[(size_t)(2 * axis) * npad + n] = vh;
         a.posf[(size_t)(2 * axis + 1) * npad + n] = (float)(v - (double)vh);
+    }
+    if (threadIdx.x == 0) {
+        // equispaced chunk (constant platform velocity inside a frame): the generators may then step the phase by a constant
+        bool lin = (c + 1) * kTcElems <= a.N;
+        double step[3] = {0.0, 0.0, 0.0};
+        if (lin) {
+            for (int axis = 0; axis < 3; ++axis) {
+                const double* v = a.pos + (size_t)axis * a.N + (size_t)c * kTcElems;
+                const double v0 = v[0] * a.inv_lambda;
+                step[axis] = (v[kTcElems - 1] * a.inv_lambda - v0) / (double)(kTcElems - 1);
+                for (int e = 1; e < kTcElems; ++e)
+                    lin = lin && fabs(v[e] * a.inv_lambda - (v0 + (double)e * step[axis])) <= 1e-9;
+            }
+        }
+        a.lin[c] = lin ? 1 : 0;
+        for (int axis = 0; axis < 3; ++axis) {
+            const float sh = (float)step[axis];
+            a.stepf[(size_t)(2 * axis) * a.n_chunks + c] = sh;
+            a.stepf[(size_t)(2 * axis + 1) * a.n_chunks + c] = (float)(step[axis] - (double)sh);
+        }
     }
     float* hi = a.bblk + (size_t)c * 2 * a.NB * kTcKC;
     float* lo = hi + a.NB * kTcKC;
@@ -120,6 +142,29 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
                  : "r"(taddr));
 }
 
+// Fractional part of (d . p) in turns as a float pair, WITHOUT the fp64 pipe: d = dh + dl and p = ph + pl per axis as float
+// pairs.  dh*ph splits exactly into a rounded product and its FMA remainder; the rounded product (up to 1e4 turns) loses its
+// integer part exactly (x - rint(x) is exact below 2^22, rint by the magic-number add); the three fractions are summed with
+// error-free TwoSums, everything below goes into the low word.  th + tl is good to ~1e-9 turns; |th| <= 1/2 + ulp.
+__device__ __forceinline__ void phase_pair(const float (&dh)[3], const float (&dl)[3], const float (&ph)[3], const float (&pl)[3],
+                                           float* th, float* tl) {
+    float fr[3], small = 0.0f;
+#pragma unroll
+    for (int ax = 0; ax < 3; ++ax) {
+        const float hi = dh[ax] * ph[ax];
+        const float lo = fmaf(dh[ax], ph[ax], -hi);
+        fr[ax] = hi - ((hi + 12582912.0f) - 12582912.0f);
+        small += fmaf(dh[ax], pl[ax], fmaf(dl[ax], ph[ax], lo));
+    }
+    const float s1 = fr[0] + fr[1], b1 = s1 - fr[0], e1 = (fr[0] - (s1 - b1)) + (fr[1] - b1);
+    const float s2 = s1 + fr[2], b2 = s2 - s1, e2 = (s1 - (s2 - b2)) + (fr[2] - b2);
+    const float h = s2 - ((s2 + 12582912.0f) - 12582912.0f);
+    const float l = (e1 + e2) + small;
+    const float t = h + l;
+    *th = t;
+    *tl = (h - t) + l;
+}
+
 // exp(2 pi i t) for t in [-1/2, 1/2] turns: quadrant by the magic-number round (no conversion-unit instructions), Taylor
 // polynomials on |2 pi r| <= pi/4 (sin to x^9, cos to x^8: truncation error < 3e-8), quadrant rotation by sign-bit XORs.
 __device__ __forceinline__ void sincos_turns(float t, float* sn, float* cs) {
@@ -147,6 +192,8 @@ struct SarTcArgs {
     const float* bblk;    // prepared B chunks
     const double* posl;   // [3][npad] positions / lambda
     const float* posf;    // [6][npad] hi / lo float pairs of the same
+    const float* stepf;   // [6][n_chunks] element spacing / lambda of the equispaced chunks, float hi / lo pairs
+    const uint8_t* lin;   // [n_chunks] chunk is equispaced (null: never use the stepping path)
     const double* dirs;   // [3][G]
     int npad, n_chunks, seg_chunks, G, S, SP, NB;
     int g_begin, g_end;
@@ -261,6 +308,58 @@ __global__ void __launch_bounds__(128 * MT * TPR + 64, 1) sar_tc_kernel(const __
             if (c >= 2) mbar_wait(&empty[s], ((c >> 1) - 1) & 1);            // the MMAs of chunk c-2 have finished reading this stage
             const double* px = a.posl + (size_t)c * kTcElems;
             const float* pf = a.posf + (size_t)c * kTcElems;
+            constexpr int W = kTcElems / TPR;                      // elements of a chunk this thread generates
+            if (CS && a.lin && a.lin[c]) {
+                // Equispaced chunk: phase(e) = t0 + e * delta.  Per group of 8 elements: the group's first phase and delta as
+                // float pairs (phase_pair, once per group / chunk instead of once per element), exp(2 pi i delta 2^k) by
+                // sincos_turns of the exactly doubled and re-reduced pair (no squaring error), and every coefficient is the
+                // group's first one times at most three of those powers: ~12 instructions per element instead of ~46.  The
+                // arithmetic of an element does not depend on TPR (bit-identical tilings).
+                float sh[3], sl[3];
+#pragma unroll
+                for (int ax = 0; ax < 3; ++ax) {
+                    sh[ax] = __ldg(a.stepf + (size_t)(2 * ax) * a.n_chunks + c);
+                    sl[ax] = __ldg(a.stepf + (size_t)(2 * ax + 1) * a.n_chunks + c);
+                }
+                float uh, ul, ur[3], ui[3];
+                phase_pair(dh, dl, sh, sl, &uh, &ul);
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    sincos_turns(uh + ul, &ui[k], &ur[k]);
+                    uh *= 2.0f; ul *= 2.0f;
+                    uh -= (uh + 12582912.0f) - 12582912.0f;
+                }
+#pragma unroll
+                for (int grp = 0; grp < W / 8; ++grp) {
+                    const int nl0 = part * W + grp * 8;
+                    float ph[3], pl[3], t0h, t0l, wr[8], wi[8];
+#pragma unroll
+                    for (int ax = 0; ax < 3; ++ax) {
+                        ph[ax] = __ldg(pf + (size_t)(2 * ax) * a.npad + nl0);
+                        pl[ax] = __ldg(pf + (size_t)(2 * ax + 1) * a.npad + nl0);
+                    }
+                    phase_pair(dh, dl, ph, pl, &t0h, &t0l);
+                    sincos_turns(t0h + t0l, &wi[0], &wr[0]);
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) {
+#pragma unroll
+                        for (int e = 0; e < (1 << k); ++e) {
+                            wr[(1 << k) + e] = fmaf(wr[e], ur[k], -wi[e] * ui[k]);
+                            wi[(1 << k) + e] = fmaf(wr[e], ui[k], wi[e] * ur[k]);
+                        }
+                    }
+#pragma unroll
+                    for (int nq = 0; nq < 8; nq += 2) {
+                        const int nl = nl0 + nq;
+                        float4 h, l;
+                        h.x = tf32_round(wr[nq]); h.y = tf32_round(wi[nq]); h.z = tf32_round(wr[nq + 1]); h.w = tf32_round(wi[nq + 1]);
+                        l.x = wr[nq] - h.x; l.y = wi[nq] - h.y; l.z = wr[nq + 1] - h.z; l.w = wi[nq + 1] - h.w;
+                        const int idx = ((row >> 3) * (kTcKC / 4) + (nl >> 1)) * 32 + (row & 7) * 4;
+                        *reinterpret_cast<float4*>(a_hi + idx) = h;
+                        *reinterpret_cast<float4*>(a_lo + idx) = l;
+                    }
+                }
+            } else
 #pragma unroll UNR
             for (int nq = 0; nq < kTcElems / TPR; nq += 2) {
                 const int nl = part * (kTcElems / TPR) + nq;
@@ -392,15 +491,18 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
     const size_t posl_bytes = (size_t)3 * npad * sizeof(double);
     const size_t posf_bytes = (size_t)6 * npad * sizeof(float);
     const size_t beams_bytes = (size_t)S * width * sizeof(cf);
+    const size_t step_bytes = (size_t)6 * n_chunks * sizeof(float), lin_bytes = (size_t)n_chunks;
     auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
-    if (int rc = ensure_scratch(ctx, up(bblk_bytes) + up(posl_bytes) + up(posf_bytes) + up(beams_bytes))) return rc;
+    if (int rc = ensure_scratch(ctx, up(bblk_bytes) + up(posl_bytes) + up(posf_bytes) + up(beams_bytes) + up(step_bytes) + up(lin_bytes))) return rc;
     unsigned char* base = reinterpret_cast<unsigned char*>(ctx->scratch);
     float* bblk = reinterpret_cast<float*>(base);
     double* posl = reinterpret_cast<double*>(base + up(bblk_bytes));
     float* posf = reinterpret_cast<float*>(base + up(bblk_bytes) + up(posl_bytes));
     cf* beams = reinterpret_cast<cf*>(base + up(bblk_bytes) + up(posl_bytes) + up(posf_bytes));
+    float* stepf = reinterpret_cast<float*>(base + up(bblk_bytes) + up(posl_bytes) + up(posf_bytes) + up(beams_bytes));
+    uint8_t* lin = reinterpret_cast<uint8_t*>(stepf) + up(step_bytes);
 
-    SarPrepArgs p{aperture, S, N, SP, NB, n_chunks, positions, 1.0 / lambda_m, bblk, posl, posf};
+    SarPrepArgs p{aperture, S, N, SP, NB, n_chunks, positions, 1.0 / lambda_m, bblk, posl, posf, stepf, lin};
     sar_tc_prep_kernel<<<n_chunks, 256, 0, st>>>(p);
     RB_CUDA_OK(ctx, cudaGetLastError());
 
@@ -408,7 +510,7 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
     int seg_chunks = (int)(6.0e5 / (double)N) / kTcElems;
     seg_chunks = seg_chunks < 4 ? 4 : (seg_chunks > n_chunks ? n_chunks : seg_chunks);
     if (ctx->sar_seg_chunks > 0) seg_chunks = ctx->sar_seg_chunks;
-    SarTcArgs a{bblk, posl, posf, dirs, npad, n_chunks, seg_chunks, G, S, SP, NB, g_begin, g_end, beams};
+    SarTcArgs a{bblk, posl, posf, stepf, (ctx->sar_dbg & 32) ? nullptr : lin, dirs, npad, n_chunks, seg_chunks, G, S, SP, NB, g_begin, g_end, beams};
     auto smem_for = [&](int tiles) {
         const size_t stage_floats = (size_t)tiles * 2 * kTcATile + 2 * (size_t)NB * kTcKC;
         return 2 * stage_floats * sizeof(float) + 8 * sizeof(uint64_t) + 16;

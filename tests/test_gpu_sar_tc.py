@@ -40,17 +40,21 @@ def sar_direct(x, pos, dirs, lam, cols):
     return np.fft.fft((x.astype(np.complex128) @ w) * np.hanning(s)[:, None], axis=0)
 
 
-def engine_with_mode(mode, s):
+def engine_with_mode(mode, s, dbg=None):
     from mmwave_radar_processing_b200.engine import RadarEngine
-    old = os.environ.get("RADAR_B200_SAR")
-    os.environ["RADAR_B200_SAR"] = str(mode)
+    env = {"RADAR_B200_SAR": str(mode)}
+    if dbg is not None:
+        env["RADAR_B200_SAR_DBG"] = str(dbg)
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)
     try:
         return RadarEngine(1, s, 1, 1)
     finally:
-        if old is None:
-            del os.environ["RADAR_B200_SAR"]
-        else:
-            os.environ["RADAR_B200_SAR"] = old
+        for k, v in old.items():
+            if v is None:
+                del os.environ[k]
+            else:
+                os.environ[k] = v
 
 
 @pytest.mark.parametrize("s,n,g", [(90, 500, 300), (63, 210, 129), (64, 37, 128), (100, 333, 200), (128, 100, 64), (120, 65, 257)])
@@ -88,3 +92,35 @@ def test_fallback_shape_and_throughput_grid(torch_cuda):
     cols[:4] = [0, 127, 128, 32767]
     assert rel_l2(out[:, torch.from_numpy(cols).cuda()].cpu().numpy(), sar_direct(x, pos, dirs, lam, cols)) < TOL
     assert torch.isfinite(torch.view_as_real(out)).all()
+
+
+@pytest.mark.parametrize("s,frames,per_frame,g", [(90, 5, 100, 300), (64, 7, 37, 200), (100, 3, 160, 129), (72, 4, 16, 140)])
+def test_equispaced_chunks_step_the_phase(torch_cuda, s, frames, per_frame, g):
+    """Constant velocity inside a frame (the reference's geometry): chunks of 16 equispaced elements take the stepping path
+    (t0 + e delta), chunks straddling a frame boundary the general one.  Both against fp64 and against the general path
+    alone (RADAR_B200_SAR_DBG=32), both tilings."""
+    torch = torch_cuda
+    rng = np.random.default_rng(s + per_frame)
+    n = frames * per_frame
+    lam = 0.0039
+    x = (rng.integers(-2000, 2000, (s, n)) + 1j * rng.integers(-2000, 2000, (s, n))).astype(np.complex64)
+    pos = np.zeros((3, n))
+    start = np.zeros(3)
+    for f in range(frames):
+        vel = np.array([0.01, 0.5, 0.0]) + 0.05 * rng.standard_normal(3)
+        t = np.arange(per_frame) * 1.1e-4
+        pos[:, f * per_frame:(f + 1) * per_frame] = start[:, None] + vel[:, None] * t[None, :]
+        start = pos[:, (f + 1) * per_frame - 1] + vel * 3e-3                     # inter-frame gap
+    az = rng.uniform(-1.0, 1.0, g)
+    el = rng.uniform(-0.3, 0.3, g)
+    dirs = np.stack([np.cos(az) * np.cos(el), np.sin(az) * np.cos(el), np.sin(el)])
+    want = sar_direct(x, pos, dirs, lam, np.arange(g))
+    xs, ps, ds = torch.from_numpy(x).cuda(), torch.from_numpy(pos).cuda(), torch.from_numpy(dirs).cuda()
+    step2 = engine_with_mode(2, s).sar_image(xs, ps, ds, lam).cpu().numpy()
+    step3 = engine_with_mode(3, s).sar_image(xs, ps, ds, lam).cpu().numpy()
+    general = engine_with_mode(2, s, dbg=32).sar_image(xs, ps, ds, lam).cpu().numpy()
+    assert rel_l2(step2, want) < 1e-5, rel_l2(step2, want)
+    assert rel_l2(general, want) < 1e-5
+    assert rel_l2(step2, general) < 5e-6, rel_l2(step2, general)
+    np.testing.assert_array_equal(step2, step3)
+    assert not np.array_equal(step2, general)                # the stepping path really ran
