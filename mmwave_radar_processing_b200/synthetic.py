@@ -45,6 +45,30 @@ def synth_frame_iq(num_rx: int, num_samples: int, cpl: int, loops: int, seed: in
     return iq
 
 
+def synth_scene_iq(num_rx: int, num_samples: int, cpl: int, loops: int, seed: int, targets,
+                   noise_sigma: float = 30.0) -> np.ndarray:
+    """One frame with EXPLICIT point targets ``[(amplitude, range_bin, doppler_bin, sin_theta), ...]`` (fractional bins
+    allowed) plus seeded white noise; int16 ``[chirp][rx][sample][2]``.  Used for scripted sequences (a ground return whose
+    range drifts from frame to frame drives the altimeter recurrence of the ground detector)."""
+    rng = np.random.default_rng(seed)
+    r, s, l = num_rx, num_samples, loops
+    c = cpl * l
+    chirp = np.arange(c)
+    loop = chirp // cpl
+    v = (chirp % cpl)[:, None] * r + np.arange(r)[None, :]      # (C, R) virtual index
+    n = np.arange(s)
+    x = np.zeros((c, r, s), dtype=np.complex128)
+    for amp, rho, dlt, sin_t in targets:
+        ph = rho * n[None, None, :] / s + dlt * loop[:, None, None] / l + 0.5 * sin_t * v[:, :, None]
+        x += amp * np.exp(2j * np.pi * ph)
+    if noise_sigma > 0:
+        x += noise_sigma * (rng.standard_normal(x.shape) + 1j * rng.standard_normal(x.shape))
+    iq = np.empty((c, r, s, 2), dtype=np.int16)
+    iq[..., 0] = np.clip(np.rint(x.real), -32768, 32767).astype(np.int16)
+    iq[..., 1] = np.clip(np.rint(x.imag), -32768, 32767).astype(np.int16)
+    return iq
+
+
 def synth_batch_iq(num_rx, num_samples, cpl, loops, seeds, **kw) -> np.ndarray:
     """Stack of frames ``[frame][chirp][rx][sample][2]`` for the given seeds."""
     return np.stack([synth_frame_iq(num_rx, num_samples, cpl, loops, int(sd), **kw) for sd in seeds])
