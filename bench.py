@@ -3,20 +3,24 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--workload NAME] [--frames F] [--impl reference]
 
-A *step* is one pass of the hot path over one batch of F synthetic int16 ADC frames per GPU:
+Default workload (BASELINE.json configs[4], the shape north_star targets): the **6843 ODS synthetic stream of 100 000
+frames** (configs/6843_RadVel_ods_20Hz.cfg: 63 samples x 70 loops, 3 TX x 4 RX = 12 virtual antennas).  A *step* is one
+pass of the hot path over the whole stream; with N > 1 the stream is cut into N contiguous frame blocks (strong scaling):
 
     radar_range_doppler (all V antennas, complex RD cube + |RD[0]|)  ->  radar_range_angle (heat map)
       ->  radar_cfar_2d (OS-CFAR-2D + ordered compaction)  ->  radar_det_offsets  ->  radar_point_cloud
-      [N > 1: radar_point_cloud also stores every packed row into this rank's slot of a symmetric gathered buffer; the slot,
-       the counts and the total are pushed to the peers by copy-engine peer copies over NVLink + a cross-rank barrier on a
-       side stream, under the kernels of the next step (--exchange peer: the kernel stores to every rank itself;
-       --exchange nccl: staging copy + NCCL all-gathers)]
+      [N > 1: radar_point_cloud also stores every packed row into this rank's slot of a symmetric-memory gathered buffer;
+       the slot, the counts and the total go to the peers by copy-engine peer copies over NVLink + a cross-rank signal-pad
+       barrier on a side stream, under the kernels of the next step (--exchange peer: the kernel stores to every rank
+       itself; --exchange nccl: staging copy + NCCL all-gathers).  NCCL itself only carries the sizing all-reduces.]
 
 ``value`` is whole-job frames/s with the inputs resident in HBM; ``e2e`` is the same metric through the host-facing
-call (``FramePipeline.run_host``): pinned host int16 frames in, host point clouds out, copies inside the timed
-region.  ``roofline`` is for the dominant kernel (the fused range-Doppler kernel), ``cpu_baseline`` is the numpy
-oracle port timed on this box's host cores (rank 0, N=1 only).  ``--impl reference`` times that CPU path on all
-host cores and prints the same line shape.
+call (``FramePipeline.run_host``): pinned host int16 frames in, host point clouds out, copies inside the timed region.
+``roofline`` is for the dominant kernel (the fused range-Doppler kernel) and lists every stage kernel under ``kernels``;
+``cpu_baseline`` is the numpy oracle port timed on this box's host cores (rank 0, N=1 only).  ``extra`` (N=1) carries
+the second single-GPU workload (configs/1843_RadVel.cfg, BASELINE.json configs[1]) and the CA-CFAR-2D detector timing.
+``--impl reference`` times the CPU path on all host cores and prints the same line shape.
+``--workload sar``: the voxel-sharded synthetic-array image (BASELINE.json configs[3]), images/s + tensor-pipe roofline.
 """
 from __future__ import annotations
 
@@ -41,10 +45,14 @@ WORKLOADS = {
     "RadCloud": ("RadCloud", "standard", (0, 1, 2, 3), (), (0, 1, 2, 3)),
     "RadarHD": ("RadarHD", "standard", (0, 1, 2, 3), (), (0, 1, 2, 3)),
 }
+DEFAULT_WORKLOAD = "6843_RadVel_ods_20Hz"
+STREAM_FRAMES = 100_000          # BASELINE.json configs[4]: the whole stream is one step, split over the ranks
 # detector of the reference's PointCloudGenerator integration test (tests/verify_processors.py:121-143)
 DETECTOR = dict(kind="os", num_train=(8, 4), num_guard=(2, 1), rho=0.75, alpha=3.5)
+DETECTOR_CA = dict(kind="ca", num_train=(4, 4), num_guard=(2, 2), pfa=1e-5)      # verify_processors.py:156-191
 MAX_DETS = 256
 N_UNIQUE = 256          # distinct synthetic frames per rank, tiled to the batch
+E2E_FRAMES_MAX = 16384  # frames per rank of the end-to-end (host buffers) region: bounds the pinned allocation
 FALLBACK_HBM_GBS = 6650.0
 
 
@@ -55,22 +63,29 @@ def load_cfg(name, geometry):
     return cm
 
 
-def hbm_peak():
-    path = os.path.join(REPO, "MEASURED_PEAKS.json")
+def measured_peaks():
     try:
-        with open(path) as fh:
-            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+        with open(os.path.join(REPO, "MEASURED_PEAKS.json")) as fh:
+            return json.load(fh)
     except Exception:  # noqa: BLE001
-        return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+        return {}
+
+
+def hbm_peak():
+    p = measured_peaks()
+    if "hbm_gbs" in p:
+        return float(p["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
 
 
 def ncu_traffic(kernel: str, workload: str):
-    """dram bytes per launch per frame from the committed ncu capture (profiles/traffic.json), or None."""
+    """(dram bytes per launch per frame, capture tag) from the committed ncu capture (profiles/traffic.json), or None."""
     try:
         with open(os.path.join(REPO, "profiles", "traffic.json")) as fh:
-            return json.load(fh).get(workload, {}).get(kernel)
+            d = json.load(fh)
+        return d.get(workload, {}).get(kernel), d.get("_capture", "static ncu capture (profiles/traffic.json)")
     except Exception:  # noqa: BLE001
-        return None
+        return None, None
 
 
 # ------------------------------------------------------------------------------------------------ clocks
@@ -80,7 +95,7 @@ class ClockSampler(threading.Thread):
     REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
                0x80: "hw_power_brake_slowdown"}
 
-    def __init__(self, index: int, period_s: float = 0.01):
+    def __init__(self, index: int, period_s: float = 0.004):
         super().__init__(daemon=True)
         self.index, self.period = index, period_s
         self.samples, self.reasons, self.max_mhz = [], set(), None
@@ -121,7 +136,7 @@ class ClockSampler(threading.Thread):
             return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": 0}
         loaded = [m for m, u in self.samples if u > 0] or [m for m, _ in self.samples]
         return {"sm_mhz": statistics.median(loaded), "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(self.samples)}
+                "samples": len(self.samples), "samples_under_load": len(loaded)}
 
 
 # ------------------------------------------------------------------------------------------------ CPU path
@@ -172,6 +187,16 @@ def cpu_baseline_single(cm, wl, frames_iq, budget_s=12.0):
             "sample": f"{n} frames of {wl} through oracle/radar_oracle.py (numpy fp64, 1 thread), {dt:.1f} s"}
 
 
+def frames_per_rank(a, world, rank=0):
+    """(frames of this rank per step, global frames per step, scaling).  --frames 0: the 100k-frame stream in contiguous
+    blocks (strong scaling); --frames F: F frames per GPU (weak scaling)."""
+    from mmwave_radar_processing_b200.distributed import shard_range
+    if a.frames > 0:
+        return a.frames, a.frames * world, "weak"
+    lo, hi = shard_range(STREAM_FRAMES, rank, world)
+    return hi - lo, STREAM_FRAMES, "strong"
+
+
 def run_reference_arm(a):
     """--impl reference: the CPU path on all host cores (process pool sharded by frame), rank 0 only."""
     rank = int(os.environ.get("RANK", "0"))
@@ -201,13 +226,15 @@ def run_reference_arm(a):
             pool.map(_cpu_frame, batch, chunksize=max(1, frames_per_step // (cores * 4)))
         dt = time.perf_counter() - t0
     val = a.steps * frames_per_step / dt
-    sample = (f"{frames_per_step} frames/step of {a.workload} through oracle/radar_oracle.py (numpy fp64), "
-              f"{cores}-process pool sharded by frame")
+    sample = (f"{frames_per_step} frames per timed step (a bounded sample of the workload in config) of {a.workload} through "
+              f"oracle/radar_oracle.py (numpy fp64), {cores}-process pool sharded by frame")
+    world = max(1, a.gpus)
+    f_rank, f_global, scaling = frames_per_rank(a, world)
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": "frames/s", "n_gpus": a.gpus, "steps": a.steps,
-        "warmup": a.warmup, "ms_per_step": 1e3 * dt / a.steps, "higher_is_better": True, "scaling": "weak",
+        "warmup": a.warmup, "ms_per_step": 1e3 * dt / a.steps, "higher_is_better": True, "scaling": scaling,
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": workload_config(cm, a.workload, frames_per_step, 1),
+        "config": workload_config(cm, a.workload, f_rank, f_global, world, a.exchange),
         "cpu_baseline": {"value": val, "unit": "frames/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -216,29 +243,256 @@ def run_reference_arm(a):
     return 0
 
 
-def workload_config(cm, wl, frames_per_gpu, n_gpus, exchange="peer"):
+EXCHANGE_TEXT = {
+    "copy": " + point rows stored by the point-cloud kernel into this rank's slot of a symmetric-memory gathered buffer, "
+            "pushed to the peers by copy-engine peer copies over NVLink + signal-pad barrier (side stream, under the next "
+            "step); NCCL carries only the sizing all-reduces",
+    "peer": " + point rows stored into every rank's symmetric-memory gathered buffer by the point-cloud kernel (NVLink "
+            "peer stores), counts by copy-engine peer copies + signal-pad barrier on a side stream",
+    "nccl": " + NCCL all-gather of point clouds (own stream, under the next step)",
+}
+
+
+def workload_config(cm, wl, frames_per_gpu, global_frames, n_gpus, exchange="copy"):
     r, s, cpl, l = cm.num_rx_antennas, cm.get_num_adc_samples(0), cm.chirp_cfgs_per_loop, cm.frameCfg_loops
-    return {"workload": f"configs/{WORKLOADS[wl][0]}.cfg batched synthetic int16 ADC cubes", "num_rx": r,
-            "chirps_per_loop": cpl, "virtual_antennas": r * cpl, "samples": s, "loops": l,
-            "frames_per_gpu_per_step": frames_per_gpu, "global_frames_per_step": frames_per_gpu * n_gpus,
+    stream = global_frames == STREAM_FRAMES
+    return {"workload": (f"configs/{WORKLOADS[wl][0]}.cfg synthetic int16 ADC stream of {global_frames} frames" +
+                         (" cut into contiguous frame blocks, one per GPU" if stream else " (batched cubes)")),
+            "num_rx": r, "chirps_per_loop": cpl, "virtual_antennas": r * cpl, "samples": s, "loops": l,
+            "frames_per_gpu_per_step": frames_per_gpu, "global_frames_per_step": global_frames,
             "detector": "os_cfar_2d num_train=(8,4) num_guard=(2,1) rho=0.75 alpha=3.5",
             "stages": "range_doppler+range_angle+cfar_2d+det_offsets+point_cloud",
-            "parallelism": f"frame-sharded x{n_gpus}" + ({"copy": " + point rows stored into a symmetric gathered buffer by the point-cloud kernel, pushed to the peers by copy-engine peer copies over NVLink + barrier (side stream, under the next step)", "peer": " + point rows stored into every rank's gathered buffer by the point-cloud kernel (NVLink peer memory), counts by peer copies + barrier on a side stream", "nccl": " + NCCL all-gather of point clouds (own stream, under the next step)"}[exchange] if n_gpus > 1 else ""),
+            "parallelism": f"frame-sharded x{n_gpus}" + (EXCHANGE_TEXT[exchange] if n_gpus > 1 else ""),
             "l2_policy": "per-step working set (int16 in + complex RD out) exceeds the 126 MB L2; no explicit flush"}
+
+
+def stage_rooflines(cm, wl, F, stage_ms, ms_per_step, points, peak):
+    """Algorithmic bytes per frame (DESIGN.md section 4 / SURVEY.md section 8d) and achieved fraction of the HBM peak for
+    every stage kernel of one step."""
+    R, S, cpl, L = cm.num_rx_antennas, cm.get_num_adc_samples(0), cm.chirp_cfgs_per_loop, cm.frameCfg_loops
+    V, C = R * cpl, cpl * L
+    _, _, az, el, ra_ants = WORKLOADS[wl]
+    ppf = points / max(1, F)
+    bytes_pf = {
+        "range_doppler": 4 * R * S * C + 8 * V * S * L + 4 * S * L,
+        "range_angle": 4 * R * S * cpl + 4 * S * 64,
+        "cfar": 4 * S * L + 8 * ppf + 4,
+        "point_cloud": (8 * (len(az) + len(el)) + 8 + 32) * ppf,
+    }
+    names = {"range_doppler": "rd_stream_kernel", "range_angle": "range_angle_kernel", "cfar": "cfar_kernel",
+             "point_cloud": "point_cloud_thread_kernel"}
+    out = []
+    for st, ms in stage_ms.items():
+        b = bytes_pf[st]
+        ach = b * F / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
+        out.append({"stage": st, "kernel": names[st], "algorithmic_bytes_per_frame": b, "ms_per_launch": ms,
+                    "achieved_gbs": ach, "frac": ach / peak, "share_of_step": ms / ms_per_step})
+    step_bytes = sum(bytes_pf[st] for st in stage_ms)
+    return out, bytes_pf, step_bytes
+
+
+def time_stage_loop(torch, pipe, iq_dev, steps, warmup):
+    """Plain single-GPU loop with per-stage events -> (ms_total, stage_ms, last out)."""
+    for _ in range(warmup):
+        pipe.run(iq_dev)
+    torch.cuda.synchronize()
+    marks = []
+
+    def mark(name):
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        marks.append((name, ev))
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    out = None
+    for _ in range(steps):
+        mark("begin")
+        out = pipe.run(iq_dev, mark)
+    t1.record()
+    torch.cuda.synchronize()
+    stage = {}
+    for (n0, e0), (n1, e1) in zip(marks[:-1], marks[1:]):
+        if n1 != "begin":
+            stage[n1] = stage.get(n1, 0.0) + e0.elapsed_time(e1)
+    return t0.elapsed_time(t1), {k: v / steps for k, v in stage.items()}, out
+
+
+def extra_single_gpu_lines(torch, dev, peak):
+    """N=1 extras: (a) configs/1843_RadVel.cfg, 4096 frames per step (BASELINE.json configs[1]; round-1 headline, kept for
+    continuity); (b) the CA-CFAR-2D detector of tests/verify_processors.py:156-191 on both shapes."""
+    import numpy as np
+    from mmwave_radar_processing_b200.pipeline import DetectorSpec, FramePipeline
+    from mmwave_radar_processing_b200.synthetic import synth_batch_for_cfg
+    extras = []
+    for wl, det_name, det in (("1843_RadVel", "os_cfar_2d", DETECTOR), ("1843_RadVel", "ca_cfar_2d", DETECTOR_CA),
+                              (DEFAULT_WORKLOAD, "ca_cfar_2d", DETECTOR_CA)):
+        cfg_name, geom, az, el, ra_ants = WORKLOADS[wl]
+        cm = load_cfg(cfg_name, geom)
+        F = 4096
+        pipe = FramePipeline(cm, detector=DetectorSpec(**det), az_antenna_idxs=az, el_antenna_idxs=el, max_dets=MAX_DETS,
+                             with_range_angle=True, ra_antennas=ra_ants, device=dev)
+        uniq = synth_batch_for_cfg(cm, range(N_UNIQUE))
+        iq_dev = torch.from_numpy(np.concatenate([uniq] * (F // N_UNIQUE))).to(dev)
+        steps = 50
+        ms_total, stage_ms, out = time_stage_loop(torch, pipe, iq_dev, steps, 5)
+        pts = int(out["offsets"][F].item())
+        kernels, bytes_pf, step_bytes = stage_rooflines(cm, wl, F, stage_ms, ms_total / steps, pts, peak)
+        if det_name == "ca_cfar_2d":
+            extras.append({"workload": f"configs/{cfg_name}.cfg", "detector": "ca_cfar_2d num_train=(4,4) num_guard=(2,2) pfa=1e-5",
+                           "frames_per_step": F, "cfar_ms_per_launch": stage_ms["cfar"],
+                           "cfar_frac_of_hbm": [k for k in kernels if k["stage"] == "cfar"][0]["frac"],
+                           "points_per_step": pts})
+        else:
+            extras.append({"workload": f"configs/{cfg_name}.cfg batched synthetic int16 ADC cubes", "frames_per_step": F,
+                           "steps": steps, "value": F * steps / (ms_total * 1e-3), "unit": "frames/s",
+                           "ms_per_step": ms_total / steps, "stage_ms_per_step": stage_ms,
+                           "roofline": {"kernel": "rd_stream_kernel", "frac": kernels[0]["frac"],
+                                        "achieved": kernels[0]["achieved_gbs"], "peak": peak, "unit": "GB/s",
+                                        "algorithmic_bytes_per_frame": bytes_pf["range_doppler"], "kernels": kernels,
+                                        "step_hbm_frac": step_bytes * F / (ms_total / steps * 1e-3) / 1e9 / peak},
+                           "points_per_step": pts})
+        del pipe, iq_dev, out
+        torch.cuda.empty_cache()
+    return extras
+
+
+# ------------------------------------------------------------------------------------------------ SAR workload
+def run_sar(a):
+    """--workload sar: BASELINE.json configs[3] - one synthetic-array image (configs/RadSAR_1843_official.cfg: S = 90 range
+    bins, N = 2000 aperture elements, G = 512 x 64 directions), the direction grid sharded over the ranks after a broadcast
+    of the aperture cube + geometry; every rank ends with the full image (all-gather of the tiles).  A step = one image."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from mmwave_radar_processing_b200 import distributed as rdist
+    from mmwave_radar_processing_b200.engine import RadarEngine
+
+    rank, local_rank, world = rdist.init_from_env()
+    dev = torch.device("cuda", local_rank)
+    torch.cuda.set_device(dev)
+    s, n, g = 90, 2000, 512 * 64
+    rng = np.random.default_rng(0)
+    x = (rng.integers(-2000, 2000, (s, n)) + 1j * rng.integers(-2000, 2000, (s, n))).astype(np.complex64)
+    t = np.arange(n) * 1e-4
+    pos = np.stack([0.01 * t, 0.5 * t, np.zeros(n)])
+    az = np.repeat(np.linspace(-1.0, 1.0, 512), 64)
+    el = np.tile(np.linspace(-0.3, 0.3, 64), 512)
+    dirs = np.stack([np.cos(az) * np.cos(el), np.sin(az) * np.cos(el), np.sin(el)])
+    lam = 0.0039
+    eng = RadarEngine(1, s, 1, 1, device=dev)
+    if rank == 0:
+        xs, ps = torch.from_numpy(x).to(dev), torch.from_numpy(pos).to(dev)
+    else:
+        xs = torch.empty((s, n), dtype=torch.complex64, device=dev)
+        ps = torch.empty((3, n), dtype=torch.float64, device=dev)
+    ds = torch.from_numpy(dirs).to(dev)
+
+    def step():
+        # broadcast of the aperture cube + geometry from rank 0, this rank's direction slice, all-gather of the tiles
+        img, _ = rdist.sar_image_sharded(lambda ap, po, di, lo, hi: eng.sar_image(ap, po, di, lam, lo, hi),
+                                         xs, ps, ds, src=0, gather=True)
+        return img
+
+    for _ in range(max(3, a.warmup)):
+        img = step()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    k0, k1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(a.steps):
+        img = step()
+    e1.record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    ms_total = e0.elapsed_time(e1)
+    # kernel-only time of this rank's slice (no collectives)
+    lo, hi = rdist.shard_range(g, rank, world)
+    k0.record()
+    for _ in range(a.steps):
+        eng.sar_image(xs, ps, ds, lam, lo, hi)
+    k1.record()
+    torch.cuda.synchronize()
+    k_ms = k0.elapsed_time(k1) / a.steps
+    if world > 1:
+        tt = torch.tensor([ms_total, k_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms_total, k_ms = float(tt[0].item()), float(tt[1].item())
+    # end to end: host aperture + geometry in, host image out (rank 0 feeds, every rank reads its copy back)
+    xh, ph = torch.from_numpy(x).pin_memory(), torch.from_numpy(pos).pin_memory()
+    ih = torch.empty((s, g), dtype=torch.complex64).pin_memory()
+    e2e_steps = min(a.steps, 10)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(e2e_steps):
+        if rank == 0:
+            xs.copy_(xh, non_blocking=True)
+            ps.copy_(ph, non_blocking=True)
+        ih.copy_(step(), non_blocking=True)
+    e1.record()
+    torch.cuda.synchronize()
+    e2e_ms = e0.elapsed_time(e1)
+    if world > 1:
+        tt = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e_ms = float(tt.item())
+    clocks = sampler.stop() if sampler else None
+    if rank == 0:
+        peaks = measured_peaks()
+        bf16 = float(peaks.get("bf16_tflops", 0.0) or 0.0)
+        per = ms_total / a.steps
+        g_rank = hi - lo
+        sp2 = 2 * ((s + 7) // 8 * 8)
+        useful = 8.0 * s * n * g_rank / (k_ms * 1e-3) / 1e12
+        executed = 3 * 2.0 * sp2 * (2 * n) * ((g_rank + 127) // 128 * 128) / (k_ms * 1e-3) / 1e12
+        line = {"metric": "images/s synthetic-array (SAR) beamformer, direction grid sharded by voxel", "value": 1e3 / per,
+                "unit": "images/s", "n_gpus": world, "steps": a.steps, "warmup": max(3, a.warmup), "ms_per_step": per,
+                "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "tf32x3 (split fp32) -> f32",
+                "data": "synthetic aperture cube (seeded integers), linear platform track",
+                "config": {"workload": "configs/RadSAR_1843_official.cfg multi-frame synthetic array: S=90 range bins, N=2000 "
+                                       "aperture elements, G=512x64 directions", "S": s, "N": n, "G": g,
+                           "parallelism": f"voxel-sharded x{world}: NCCL broadcast of aperture cube + geometry, "
+                                          "radar_sar_image(g_begin, g_end) per rank, NCCL all-gather of the image tiles",
+                           "l2_policy": "operands (1.4 MB) are L2-resident by design; output tiles are written once"},
+                "roofline": {"kernel": "sar_tc_kernel", "bound": "tensor", "achieved": executed,
+                             "peak": bf16 / 2 if bf16 else None, "unit": "TFLOP/s",
+                             "frac": executed / (bf16 / 2) if bf16 else None, "traffic": None,
+                             "peak_source": "half of the measured dense bf16 peak (TF32 rate), MEASURED_PEAKS.json",
+                             "useful_tflops": useful, "kernel_ms_per_launch": k_ms,
+                             "executed_flops_note": "3 tcgen05.mma kind::tf32 per product (hi*hi + hi*lo + lo*hi), K = 2N, 192 columns"},
+                "e2e": {"value": 1e3 * e2e_steps / e2e_ms, "unit": "images/s",
+                        "h2d_bytes_per_step": int(x.nbytes + pos.nbytes), "d2h_bytes_per_step": int(s * g * 8),
+                        "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps,
+                        "api": "distributed.sar_image_sharded over RadarEngine.sar_image (pinned host aperture in, host image out)"},
+                "gpu_launches": a.steps * 3, "clocks": clocks}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
 
 
 # ------------------------------------------------------------------------------------------------ GPU arm
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="1843_RadVel", choices=sorted(WORKLOADS))
-    ap.add_argument("--frames", type=int, default=4096, help="frames per GPU per step")
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS) + ["sar"])
+    ap.add_argument("--frames", type=int, default=0,
+                    help="frames per GPU per step (weak scaling); 0 = the 100k-frame stream split over the GPUs (strong)")
     ap.add_argument("--chunk", type=int, default=512, help="frames per H2D/D2H chunk of the end-to-end path")
-    ap.add_argument("--e2e-steps", type=int, default=0, help="0 -> min(steps, 10)")
+    ap.add_argument("--e2e-steps", type=int, default=0, help="0 -> min(steps, 5)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extra", action="store_true", help="skip the N=1 extra workloads (1843_RadVel, CA-CFAR)")
     ap.add_argument("--no-range-angle", action="store_true")
     ap.add_argument("--exchange", default="copy", choices=["copy", "peer", "nccl"],
                     help="N > 1 exchange of the point clouds: copy = kernel stores into this rank's gathered slot + copy-engine "
@@ -247,7 +501,11 @@ def main():
     a = ap.parse_args()
     a.warmup = max(a.warmup, 3) if a.impl == "b200" else a.warmup
     if a.impl == "reference":
+        if a.workload == "sar":
+            a.workload = DEFAULT_WORKLOAD
         return run_reference_arm(a)
+    if a.workload == "sar":
+        return run_sar(a)
 
     import numpy as np
     import torch
@@ -267,18 +525,21 @@ def main():
     cfg_name, geom, az, el, ra_ants = WORKLOADS[a.workload]
     cm = load_cfg(cfg_name, geom)
     R, S, cpl, L = cm.num_rx_antennas, cm.get_num_adc_samples(0), cm.chirp_cfgs_per_loop, cm.frameCfg_loops
-    V, C = R * cpl, cpl * L
-    F = a.frames
+    F, F_global, scaling = frames_per_rank(a, world, rank)
+    if world > 1 and a.frames == 0 and STREAM_FRAMES % world != 0:
+        raise SystemExit("the stream must split evenly over the ranks (the gathered buffer has equal slots)")
     pipe = FramePipeline(cm, detector=DetectorSpec(**DETECTOR), az_antenna_idxs=az, el_antenna_idxs=el,
                          max_dets=MAX_DETS, with_range_angle=not a.no_range_angle, ra_antennas=ra_ants, device=dev)
 
-    # synthetic frames: N_UNIQUE distinct seeded frames per rank, tiled to the batch
+    # synthetic frames: N_UNIQUE distinct seeded frames per rank, tiled to the rank's block ON THE DEVICE
     uniq = synth_batch_for_cfg(cm, range(rank * N_UNIQUE, rank * N_UNIQUE + min(N_UNIQUE, F)))
     reps = (F + uniq.shape[0] - 1) // uniq.shape[0]
-    iq_host_np = np.concatenate([uniq] * reps)[:F]
-    iq_host, counts_host, points_host = pipe.host_buffers(F, points_per_frame=MAX_DETS // 2)
-    iq_host.copy_(torch.from_numpy(iq_host_np))
-    iq_dev = iq_host.to(dev)
+    uniq_dev = torch.from_numpy(uniq).to(dev)
+    iq_dev = uniq_dev.repeat((reps, 1, 1, 1, 1))[:F].contiguous()
+    del uniq_dev
+    Fe = min(F, E2E_FRAMES_MAX)
+    iq_host, counts_host, points_host = pipe.host_buffers(Fe, points_per_frame=MAX_DETS // 2)
+    iq_host.copy_(iq_dev[:Fe])
 
     # ---- N > 1: the exchange of the point clouds (PeerPointExchange: one symmetric allocation, 3 gathered slots per rank).
     # "copy" (default): the point-cloud kernel stores every packed row into this rank's own slot (radar_ctx_set_point_mirrors)
@@ -286,8 +547,10 @@ def main():
     # barrier - all on a side stream under the kernels of the next step, no SM time.  "peer": the kernel stores the rows into
     # every rank's slot itself (best at N = 2, loses at N = 8: 32-byte remote stores per thread).  "nccl": staging copy +
     # NCCL all-gathers on the side stream (the NCCL kernels take SMs from the next step's range-Doppler / range-angle).
-    # The fixed capacity is sized from a first, synchronous step (largest per-rank total + 25 %) and checked at the end.
+    # The fixed capacity is sized from a first, synchronous step (largest per-rank total + 25 %) and checked at the end;
+    # the copy-engine pushes carry only the rows the previous steps produced (+10 %, rounded up to 256 rows).
     cap_rows = 0
+    push_rows = None
     comm = torch.cuda.Stream(device=dev) if world > 1 else None
     staging, gathered, done_ev = [None, None, None], [None, None, None], [None, None, None]
     step_no = 0
@@ -307,7 +570,7 @@ def main():
             ready.record(main)
             with torch.cuda.stream(comm):
                 comm.wait_event(ready)
-                peer_ex.publish(k, out["counts"], out["offsets"][F:F + 1], push_points=a.exchange == "copy")
+                peer_ex.publish(k, out["counts"], out["offsets"][F:F + 1], push_points=a.exchange == "copy", rows=push_rows)
                 done_ev[k] = torch.cuda.Event()
                 done_ev[k].record(comm)
             gathered[k] = peer_ex.gathered(k)
@@ -342,7 +605,9 @@ def main():
         first = pipe.run(iq_dev)
         t = first["offsets"][F:F + 1].to(torch.int64).clone()
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        cap_rows = int((int(t.item()) * 5 // 4 + 1023) // 1024 * 1024)
+        largest = int(t.item())
+        cap_rows = int((largest * 5 // 4 + 1023) // 1024 * 1024)
+        push_rows = min(cap_rows, int((largest * 11 // 10 + 255) // 256 * 256))
         if a.exchange in ("peer", "copy"):
             # symmetric memory needs peer access between all GPUs of the node; every rank must take the same branch
             ok = torch.ones((1,), dtype=torch.int32, device=dev)
@@ -400,7 +665,7 @@ def main():
         ms_total = float(t.item())
         for g in gathered:
             if g is not None:
-                rdist.check_capacity(g[2], cap_rows)
+                rdist.check_capacity(g[2], push_rows if (peer_ex is not None and a.exchange == "copy") else cap_rows)
         if peer_ex is not None:
             peer_ex.disarm()                                     # the end-to-end region below is per rank
     stage_ms = {n: 0.0 for n in stage_names}
@@ -411,8 +676,8 @@ def main():
     total_points = int(out["offsets"][F].item())
 
     # ---- end-to-end timed region through the host-facing call
-    e2e_steps = a.e2e_steps or min(a.steps, 10)
-    for _ in range(3):
+    e2e_steps = a.e2e_steps or min(a.steps, 5)
+    for _ in range(2):
         pipe.run_host(iq_host, counts_host, points_host, chunk_frames=a.chunk)
     barrier()
     torch.cuda.synchronize()
@@ -429,37 +694,73 @@ def main():
         t = torch.tensor([e2e_ms], dtype=torch.float64, device=dev)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_ms = float(t.item())
+    # plain pinned-host -> device copy of the same bytes, every rank at once: the ceiling of the end-to-end number
+    h2d_dst = pipe._chunks[0].iq
+    barrier()
+    torch.cuda.synchronize()
+    e_start.record()
+    for _ in range(e2e_steps):
+        for lo in range(0, Fe, h2d_dst.shape[0]):
+            n = min(h2d_dst.shape[0], Fe - lo)
+            h2d_dst[:n].copy_(iq_host[lo:lo + n], non_blocking=True)
+    e_end.record()
+    torch.cuda.synchronize()
+    barrier()
+    h2d_ms = e_start.elapsed_time(e_end)
+    if world > 1:
+        t = torch.tensor([h2d_ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        h2d_ms = float(t.item())
     clocks = sampler.stop() if sampler else None
 
     if rank == 0:
         ms_per_step = ms_total / a.steps
-        value = world * F * a.steps / (ms_total * 1e-3)
+        value = F_global * a.steps / (ms_total * 1e-3)
         peak, peak_src = hbm_peak()
-        rd_bytes_per_frame = 4 * R * S * C + 8 * V * S * L + 4 * S * L
+        kernels, bytes_pf, step_bytes = stage_rooflines(cm, a.workload, F, stage_ms, ms_per_step, total_points, peak)
         rd_ms = stage_ms["range_doppler"]
-        achieved = rd_bytes_per_frame * F / (rd_ms * 1e-3) / 1e9
-        traffic = ncu_traffic("rd_stream_kernel", a.workload)
-        step_bytes_per_frame = rd_bytes_per_frame + 4 * S * L + S * L
+        achieved = bytes_pf["range_doppler"] * F / (rd_ms * 1e-3) / 1e9
+        traffic, traffic_src = ncu_traffic("rd_stream_kernel", a.workload)
+        e2e_value = world * Fe * e2e_steps / (e2e_ms * 1e-3)
+        h2d_gbs = world * h2d * e2e_steps / (h2d_ms * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": f"synthetic ({min(N_UNIQUE, F)} distinct seeded frames per rank tiled to the batch)",
-            "config": workload_config(cm, a.workload, F, world, a.exchange),
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
+            "dtype": "f32", "data": f"synthetic ({min(N_UNIQUE, F)} distinct seeded frames per rank tiled to the rank's block)",
+            "config": workload_config(cm, a.workload, F, F_global, world, a.exchange),
             "roofline": {"kernel": "rd_stream_kernel", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": (traffic * F if traffic else None),
-                         "peak_source": peak_src, "algorithmic_bytes_per_frame": rd_bytes_per_frame,
-                         "kernel_ms_per_launch": rd_ms,
-                         "step_hbm_frac": step_bytes_per_frame * F / (ms_per_step * 1e-3) / 1e9 / peak},
+                         "frac": achieved / peak, "traffic": (traffic * F if traffic else None), "traffic_source": traffic_src,
+                         "peak_source": peak_src, "algorithmic_bytes_per_frame": bytes_pf["range_doppler"],
+                         "kernel_ms_per_launch": rd_ms, "kernels": kernels,
+                         "step_algorithmic_bytes_per_frame": step_bytes,
+                         "step_hbm_frac": step_bytes * F / (ms_per_step * 1e-3) / 1e9 / peak},
             "stage_ms_per_step": stage_ms,
-            "e2e": {"value": world * F * e2e_steps / (e2e_ms * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": h2d,
+            "e2e": {"value": e2e_value, "unit": "frames/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps,
-                    "chunk_frames": a.chunk, "api": "FramePipeline.run_host (pinned host int16 -> host point clouds)"},
+                    "frames_per_gpu_per_step": Fe, "chunk_frames": a.chunk,
+                    "api": "FramePipeline.run_host (pinned host int16 -> host point clouds)",
+                    "h2d_ceiling": {"aggregate_gbs": h2d_gbs, "frames_per_s": world * Fe * e2e_steps / (h2d_ms * 1e-3),
+                                    "frac": e2e_value / (world * Fe * e2e_steps / (h2d_ms * 1e-3)),
+                                    "what": "the same pinned host buffers copied to the device by every rank at once, no kernels"}},
             "gpu_launches": a.steps * pipe.launches_per_batch,
             "points_per_step_rank0": total_points,
             "clocks": clocks,
         }
+        if world > 1:
+            line["exchange"] = {"variant": a.exchange, "capacity_rows": cap_rows,
+                                "pushed_rows_per_peer": push_rows if a.exchange == "copy" else None,
+                                "bytes_pushed_per_rank_per_step": (push_rows * 32 + 4 * F + 4) * (world - 1) if a.exchange == "copy" else None}
         if world == 1 and not a.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_single(cm, a.workload, uniq[:64])
+        if world == 1 and not a.no_extra:
+            del iq_dev, out
+            pipe._main = None
+            pipe._chunks = []
+            torch.cuda.empty_cache()
+            try:
+                line["extra"] = extra_single_gpu_lines(torch, dev, peak)
+            except Exception as exc:  # noqa: BLE001
+                line["extra"] = [{"error": f"{type(exc).__name__}: {exc}"}]
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

@@ -106,7 +106,7 @@ def split_gathered(points: torch.Tensor, counts: torch.Tensor, max_dets: int) ->
 # -------------------------------------------------------------------------------------------- SAR / DBS grids
 def sar_image_sharded(compute_slice: Callable[[torch.Tensor, torch.Tensor, torch.Tensor, int, int], torch.Tensor],
                       aperture: torch.Tensor, positions: torch.Tensor, dirs: torch.Tensor, src: int = 0,
-                      gather: bool = True):
+                      gather: bool = True, broadcast: bool = True):
     """Voxel-sharded synthetic-array image.
 
     Rank ``src`` holds the aperture cube [S, N] c64 and the geometry [3, N] f64; they are broadcast, every rank
@@ -115,8 +115,9 @@ def sar_image_sharded(compute_slice: Callable[[torch.Tensor, torch.Tensor, torch
     the widest shard for the collective)."""
     w = world_size()
     rank = dist.get_rank() if dist.is_initialized() else 0
-    if w > 1:
-        dist.broadcast(aperture, src=src)
+    if w > 1 and broadcast:
+        # complex tensors travel as their real view (NCCL / gloo have no complex type)
+        dist.broadcast(torch.view_as_real(aperture) if aperture.is_complex() else aperture, src=src)
         dist.broadcast(positions, src=src)
     g = dirs.shape[1]
     lo, hi = shard_range(g, rank, w)
@@ -180,18 +181,22 @@ class PeerPointExchange:
     def disarm(self):
         self.engine.set_point_mirrors([], 0)
 
-    def publish(self, k: int, counts: torch.Tensor, total: torch.Tensor, push_points: bool = False):
+    def publish(self, k: int, counts: torch.Tensor, total: torch.Tensor, push_points: bool = False,
+                rows: Optional[int] = None):
         """On the current stream, after the point-cloud kernel of this step (stream order or an event wait).
         ``push_points``: this rank's rows (its own slot k, filled by the kernel's local mirror) are pushed to the OTHER
         ranks by peer-to-peer copies (copy engines) - the variant for ``arm(k, remote=False)``, where the kernel's own
-        stores stay on the local GPU."""
+        stores stay on the local GPU.  ``rows``: push only the first ``rows`` rows of the slot instead of its whole
+        capacity (the caller's estimate from earlier steps); the totals travel with the barrier, so a reader that finds
+        ``totals.max() > rows`` (``check_capacity(totals, rows)``) must ask for that step again with ``rows=None``."""
         c8 = counts.contiguous().view(torch.uint8)
         t8 = total.contiguous().view(torch.uint8)
-        p8 = self.buf[k, self.rank, :self.pts_bytes] if push_points else None
+        nbytes = self.pts_bytes if rows is None else min(self.pts_bytes, int(rows) * 32)
+        p8 = self.buf[k, self.rank, :nbytes] if push_points else None
         for i in range(self.world):
             dst = self.peers[(self.rank + i) % self.world][k, self.rank]
             if p8 is not None and i > 0:
-                dst[:self.pts_bytes].copy_(p8, non_blocking=True)
+                dst[:nbytes].copy_(p8, non_blocking=True)
             dst[self.cnt_off:self.cnt_off + c8.numel()].copy_(c8, non_blocking=True)
             dst[self.tot_off:self.tot_off + 4].copy_(t8, non_blocking=True)
         self.hdl.barrier(channel=k % 8)

@@ -473,3 +473,36 @@ def test_point_cloud_kernels_agree_and_match_oracle(torch_cuda, name):
                 rd_ref = rd_host[f]
                 np.testing.assert_array_equal(a[1][f, :n], orc.angle_indices(rd_ref, dets[f, :n, 0], dets[f, :n, 1], az, bins, sh_az))
                 np.testing.assert_array_equal(a[2][f, :n], orc.angle_indices(rd_ref, dets[f, :n, 0], dets[f, :n, 1], el, bins, sh_el))
+
+
+def test_stream_sized_batch_matches_small_batches(torch_cuda):
+    """BASELINE.json configs[4] runs 100k-frame blocks through ONE launch per stage: element offsets pass 2^31 (60 000 frames
+    x 12 antennas x 63 x 70 = 3.2e9 complex cells).  Frames at the far end of such a batch must equal the same frames run as a
+    small batch, bit for bit (same kernels, same per-frame arithmetic)."""
+    torch = torch_cuda
+    from mmwave_radar_processing_b200.pipeline import DetectorSpec, FramePipeline
+    from mmwave_radar_processing_b200.synthetic import synth_batch_for_cfg
+    if torch.cuda.mem_get_info()[0] < 60e9:
+        pytest.skip("needs 60 GB of free device memory")
+    cm = load_cfg("6843_RadVel_ods_20Hz", "ods")
+    uniq = torch.from_numpy(synth_batch_for_cfg(cm, range(32))).cuda()
+    f_big = 60000
+    iq = uniq.repeat((f_big // 32, 1, 1, 1, 1))
+    spec = DetectorSpec("os", (8, 4), (2, 1), rho=0.75, alpha=3.5)
+    kw = dict(detector=spec, az_antenna_idxs=(0, 3, 4, 7), el_antenna_idxs=(9, 8, 5, 4), max_dets=256,
+              with_range_angle=True, ra_antennas=(0, 3, 4, 7))
+    small = FramePipeline(cm, **kw).run(uniq)
+    ref = {k: small[k].clone() for k in ("counts", "offsets", "rd", "mag", "ra", "dets")}
+    ref_pts = small["points"][:int(small["offsets"][32])].clone()
+    big = FramePipeline(cm, **kw).run(iq)
+    torch.cuda.synchronize()
+    for lo in (0, f_big // 2, f_big - 32):          # f_big and f_big/2 are multiples of 32: the same 32 frames
+        lo -= lo % 32
+        assert torch.equal(big["counts"][lo:lo + 32], ref["counts"])
+        assert torch.equal(big["rd"][lo:lo + 32], ref["rd"])
+        assert torch.equal(big["mag"][lo:lo + 32], ref["mag"])
+        assert torch.equal(big["ra"][lo:lo + 32], ref["ra"])
+        assert torch.equal(big["dets"][lo:lo + 32], ref["dets"])
+        o0, o1 = int(big["offsets"][lo]), int(big["offsets"][lo + 32])
+        assert o1 - o0 == ref_pts.shape[0] and torch.equal(big["points"][o0:o1], ref_pts)
+    assert int(big["offsets"][f_big]) == (f_big // 32) * ref_pts.shape[0]
