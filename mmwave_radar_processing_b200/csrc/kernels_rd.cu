@@ -181,6 +181,10 @@ int launch_range_doppler(radar_ctx* ctx, const void* adc, int in_kind, int n_fra
     if (mag_out && mag_antenna >= a.n_out_ant) return set_error(ctx, RADAR_E_INVALID, "mag_antenna %d out of range", mag_antenna);
     const bool range_only = (window_flags & RADAR_RD_RANGE_ONLY) != 0;
     a.range_only = range_only ? 1 : 0;
+    if (!range_only && in_kind == RADAR_IN_IQ16 && !ant_weight && !ant_list && ctx->force_generic == 0 && ctx->rd_reg) {
+        const int rc = launch_range_doppler_reg(ctx, adc, n_frames, window_flags, rd_out, mag_out, mag_antenna, st);
+        if (rc <= 0) return rc;            // launched (0) or failed (<0); 1 = no register-resident instantiation for this shape
+    }
     if (!range_only && in_kind == RADAR_IN_IQ16 && !ant_weight && !ant_list && ctx->force_generic == 0) {
         const int rc = launch_range_doppler_stream(ctx, adc, n_frames, window_flags, rd_out, mag_out, mag_antenna, st);
         if (rc <= 0) return rc;            // launched (0) or failed (<0); 1 = no streaming instantiation for this shape

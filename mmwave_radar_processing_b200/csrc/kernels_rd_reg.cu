@@ -1,0 +1,156 @@
+// Register-resident range-Doppler kernel: warp-specialised device wrapper and launcher for the phases in rd_reg.cuh.
+//
+// One persistent CTA per SM.  Item i = antenna group (i mod IPF) of frame (i div IPF); a group is G consecutive RX
+// antennas of one TX slot, whose raw words form one contiguous run of G*S words in every chirp row.
+//   TMA warp : per item L bulk copies (one per loop, 16-byte aligned window around the run) into stage j mod NSTAGE of the
+//              raw ring; waits on raw_empty, completes on raw_full (expect_tx).
+//   A warps  : one thread per (antenna, sample) column: ring -> registers (stage released as soon as the words are read),
+//              L-point Doppler transform, row of the tile; waits on tile_empty, arrives on tile_full.
+//   B warps  : one thread per (antenna, Doppler bin) column: tile -> registers (tile released at once), S-point range
+//              transform, stores to rd_out / the magnitude map.
+#include <cmath>
+#include "radar_internal.h"
+#include "rd_reg.cuh"
+#include "mbar.cuh"
+
+namespace rb {
+
+template <class C>
+__global__ void __launch_bounds__(C::NT, 1) rd_reg_kernel(const __grid_constant__ RdRegParams<C> a) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    cf* tile = reinterpret_cast<cf*>(smem_raw);
+    uint32_t* ring = reinterpret_cast<uint32_t*>(smem_raw + (size_t)C::TILE * sizeof(cf));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + (size_t)C::TILE * sizeof(cf) + (size_t)C::NSTAGE * C::RAW_STAGE_W * 4);
+    uint64_t* raw_full = bars;
+    uint64_t* raw_empty = bars + C::NSTAGE;
+    uint64_t* tile_full = bars + 2 * C::NSTAGE;
+    uint64_t* tile_empty = tile_full + 1;
+    constexpr unsigned IPF = C::CR / C::G;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    if (tid == 0) {
+        for (int s = 0; s < C::NSTAGE; ++s) {
+            mb::init(raw_full + s, 1);
+            mb::init(raw_empty + s, C::NA * 32);
+        }
+        mb::init(tile_full, C::NA * 32);
+        mb::init(tile_empty, C::NB * 32);
+        mb::fence_init();
+    }
+    __syncthreads();
+    const unsigned n_items = a.n_items;
+
+    if (warp == C::NA + C::NB) {
+        // ===== TMA warp =====
+        unsigned j = 0;
+        for (unsigned item = blockIdx.x; item < n_items; item += gridDim.x, ++j) {
+            const unsigned st = j % C::NSTAGE, round = j / C::NSTAGE;
+            mb::wait(raw_empty + st, (round & 1) ^ 1);
+            const unsigned frame = item / IPF, grp = item - frame * IPF;
+            const unsigned off = grp * (C::G * C::S * 4);                      // byte offset of the run inside a chirp row
+            const unsigned a0 = off & ~15u;
+            const unsigned bytes = ((off - a0) + C::G * C::S * 4 + 15u) & ~15u;
+            if (lane == 0) mb::arrive_expect_tx(raw_full + st, bytes * C::L);
+            __syncwarp();
+            const unsigned char* src = reinterpret_cast<const unsigned char*>(a.iq) + (size_t)frame * ((size_t)C::ROW * C::L * 4) + a0;
+            uint32_t* dst = ring + st * C::RAW_STAGE_W;
+            for (int l = lane; l < C::L; l += 32)
+                mb::bulk_g2s(dst + l * C::RAW_PITCH_W, src + (size_t)l * (C::ROW * 4), bytes, raw_full + st);
+        }
+    } else if (warp < C::NA) {
+        // ===== phase A: Doppler =====
+        const int col = warp * 32 + lane;
+        const bool active = col < C::COLS_A;
+        const int colc = active ? col : C::COLS_A - 1;
+        const float ws = a.winS[colc % C::S];
+        unsigned j = 0;
+        for (unsigned item = blockIdx.x; item < n_items; item += gridDim.x, ++j) {
+            const unsigned st = j % C::NSTAGE, round = j / C::NSTAGE;
+            const unsigned grp = item % IPF;
+            const int shift = (int)((grp * (C::G * C::S * 4)) & 15u) >> 2;
+            cf v[C::L];
+            mb::wait(raw_full + st, round & 1);
+            rd_reg_doppler_load<C>(a, ring + st * C::RAW_STAGE_W, shift + colc, v);
+            mb::arrive(raw_empty + st);
+            rd_reg_doppler_finish<C>(ws, v);
+            mb::wait(tile_empty, (j & 1) ^ 1);
+            if (active) rd_reg_store_row<C>(v, tile + (size_t)col * C::P);
+            mb::arrive(tile_full);
+        }
+    } else {
+        // ===== phase B: range =====
+        const int col = (warp - C::NA) * 32 + lane;
+        const bool active = col < C::COLS_B;
+        const int colc = active ? col : C::COLS_B - 1;
+        const int g = colc / C::L, d = colc - g * C::L;
+        unsigned j = 0;
+        for (unsigned item = blockIdx.x; item < n_items; item += gridDim.x, ++j) {
+            const unsigned frame = item / IPF, grp = item - frame * IPF;
+            const int ant = (int)grp * C::G + g;
+            cf v[C::S];
+            mb::wait(tile_full, j & 1);
+            rd_reg_range_load<C>(tile, g, d, v);
+            mb::arrive(tile_empty);
+            if (active) {
+                const size_t o = ((size_t)frame * C::CR + ant) * (C::S * C::L) + d;
+                cf* out = a.rd_out ? a.rd_out + o : nullptr;
+                float* mag = nullptr;
+                if (a.mag_out) {
+                    if (a.mag_antenna < 0) mag = a.mag_out + o;
+                    else if (a.mag_antenna == ant) mag = a.mag_out + (size_t)frame * (C::S * C::L) + d;
+                }
+                rd_reg_range_store<C>(v, out, mag);
+            }
+        }
+    }
+}
+
+static void host_hann_f(int n, bool on, float* w) {
+    for (int k = 0; k < n; ++k)
+        w[k] = (on && n > 1) ? (float)(0.5 - 0.5 * std::cos(2.0 * M_PI * (double)k / (double)(n - 1))) : 1.0f;
+}
+
+template <class C>
+static int launch_reg(radar_ctx* ctx, const void* adc, int n_frames, int window_flags, cf* rd_out, float* mag_out,
+                      int mag_antenna, cudaStream_t st) {
+    constexpr size_t smem = C::smem_bytes();
+    static_assert(smem <= 227 * 1024, "tile + ring exceed shared memory");
+    static_assert(sizeof(RdRegParams<C>) <= 4000, "parameter block too large");
+    static_assert((C::ROW * 4) % 16 == 0, "chirp rows must keep the 16-byte alignment of the bulk copies");
+    static_assert(C::CR % C::G == 0, "antenna groups must tile the virtual array");
+    RdRegParams<C> a;
+    a.iq = reinterpret_cast<const uint32_t*>(adc);
+    a.rd_out = rd_out; a.mag_out = mag_out; a.mag_antenna = mag_antenna;
+    constexpr int IPF = C::CR / C::G;
+    if ((long long)n_frames * IPF > 0x7fffffffLL) return set_error(ctx, RADAR_E_INVALID, "too many frames in one call");
+    a.n_items = (unsigned)((long long)n_frames * IPF);
+    float wl[C::L];
+    host_hann_f(C::L, window_flags & RADAR_WIN_DOPPLER, wl);
+    for (int i = 0; i < C::L; ++i) a.winL[i] = make_float2(wl[i], wl[i]);
+    host_hann_f(C::S, window_flags & RADAR_WIN_RANGE, a.winS);
+    static bool configured[64] = {false};
+    if (!configured[ctx->device & 63]) {
+        RB_CUDA_OK(ctx, cudaFuncSetAttribute(rd_reg_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured[ctx->device & 63] = true;
+    }
+    unsigned grid = (unsigned)ctx->sm_count;
+    if (grid > a.n_items) grid = a.n_items;
+    rd_reg_kernel<C><<<grid, C::NT, smem, st>>>(a);
+    RB_CUDA_OK(ctx, cudaGetLastError());
+    return RADAR_OK;
+}
+
+// Returns RADAR_OK when the register-resident kernel was launched, 1 when the shape has no instantiation (caller falls back).
+int launch_range_doppler_reg(radar_ctx* ctx, const void* adc, int n_frames, int window_flags, cf* rd_out,
+                             float* mag_out, int mag_antenna, cudaStream_t st) {
+    const int S = ctx->shape.num_samples, L = ctx->shape.num_loops, R = ctx->shape.num_rx;
+    if (reinterpret_cast<uintptr_t>(adc) % 16 != 0) return 1;
+    const int CR = ctx->shape.chirps_per_loop * R;
+#define RB_REG(s, l, cr, g)                                                                                   \
+    if (S == s && L == l && CR == cr && R % g == 0)                                                           \
+        return launch_reg<RdRegShape<s, l, cr, g>>(ctx, adc, n_frames, window_flags, rd_out, mag_out, mag_antenna, st);
+    RB_REG(63, 70, 12, 2)
+#undef RB_REG
+    return 1;
+}
+
+}  // namespace rb

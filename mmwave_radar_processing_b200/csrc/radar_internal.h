@@ -51,6 +51,7 @@ struct radar_ctx {
     int cfar_ph1 = -1;                            // RADAR_B200_CFAR_PH1: extra full rows of the OS-CFAR first counting phase (-1 = default)
     int pc_mode = 0;                              // RADAR_B200_PC=1: warp-per-detection point-cloud kernel only (tests / comparison)
     int ra_fc = 0;                                // RADAR_B200_RA_FC: frames per pass of the range-angle kernel (0 = cost model)
+    int rd_reg = 1;                               // RADAR_B200_RD_REG=0: skip the register-resident range-Doppler kernel (tests / comparison)
     int stream_variant = 0;                       // RADAR_B200_STREAM_VARIANT: tuning candidate of the streaming kernel
     char err[512] = {0};
 };
@@ -78,6 +79,8 @@ int launch_range_doppler_spec(radar_ctx* ctx, const void* adc, int n_frames, con
                               int window_flags, cf* rd_out, float* mag_out, int mag_antenna, cudaStream_t st);
 int launch_range_doppler_stream(radar_ctx* ctx, const void* adc, int n_frames, int window_flags, cf* rd_out,
                                 float* mag_out, int mag_antenna, cudaStream_t st);
+int launch_range_doppler_reg(radar_ctx* ctx, const void* adc, int n_frames, int window_flags, cf* rd_out,
+                             float* mag_out, int mag_antenna, cudaStream_t st);
 int launch_range_profile(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx,
                          float* profile_out, cudaStream_t st);
 int launch_range_zoom(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx, const double* start_m,
