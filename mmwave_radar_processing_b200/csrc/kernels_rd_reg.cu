@@ -18,63 +18,71 @@ namespace rb {
 template <class C>
 __global__ void __launch_bounds__(C::NT, 1) rd_reg_kernel(const __grid_constant__ RdRegParams<C> a) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    cf* tile = reinterpret_cast<cf*>(smem_raw);
-    uint32_t* ring = reinterpret_cast<uint32_t*>(smem_raw + (size_t)C::TILE * sizeof(cf));
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + (size_t)C::TILE * sizeof(cf) + (size_t)C::NSTAGE * C::RAW_STAGE_W * 4);
+    cf* tiles = reinterpret_cast<cf*>(smem_raw);
+    uint32_t* ring = reinterpret_cast<uint32_t*>(smem_raw + (size_t)C::NTILE * C::TILE * sizeof(cf));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + (size_t)C::NTILE * C::TILE * sizeof(cf) + (size_t)C::NSTAGE * C::RAW_STAGE_W * 4);
     uint64_t* raw_full = bars;
     uint64_t* raw_empty = bars + C::NSTAGE;
     uint64_t* tile_full = bars + 2 * C::NSTAGE;
-    uint64_t* tile_empty = tile_full + 1;
+    uint64_t* tile_empty = tile_full + C::NTILE;
+    static_assert(2 * C::NSTAGE + 2 * C::NTILE <= 16, "barrier block");
     constexpr unsigned IPF = C::CR / C::G;
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);      // tells the compiler the role branches are warp uniform
     if (tid == 0) {
         for (int s = 0; s < C::NSTAGE; ++s) {
             mb::init(raw_full + s, 1);
             mb::init(raw_empty + s, C::NA * 32);
         }
-        mb::init(tile_full, C::NA * 32);
-        mb::init(tile_empty, C::NB * 32);
+        for (int t = 0; t < C::NTILE; ++t) {
+            mb::init(tile_full + t, C::NA * 32);
+            mb::init(tile_empty + t, C::NB * 32);
+        }
         mb::fence_init();
     }
     __syncthreads();
     const unsigned n_items = a.n_items;
 
     if (warp == C::NA + C::NB) {
-        // ===== TMA warp =====
-        unsigned j = 0;
-        for (unsigned item = blockIdx.x; item < n_items; item += gridDim.x, ++j) {
-            const unsigned st = j % C::NSTAGE, round = j / C::NSTAGE;
-            mb::wait(raw_empty + st, (round & 1) ^ 1);
-            const unsigned frame = item / IPF, grp = item - frame * IPF;
-            const unsigned off = grp * (C::G * C::S * 4);                      // byte offset of the run inside a chirp row
-            const unsigned a0 = off & ~15u;
-            const unsigned bytes = ((off - a0) + C::G * C::S * 4 + 15u) & ~15u;
-            if (lane == 0) mb::arrive_expect_tx(raw_full + st, bytes * C::L);
-            __syncwarp();
-            const unsigned char* src = reinterpret_cast<const unsigned char*>(a.iq) + (size_t)frame * ((size_t)C::ROW * C::L * 4) + a0;
-            uint32_t* dst = ring + st * C::RAW_STAGE_W;
-            for (int l = lane; l < C::L; l += 32)
-                mb::bulk_g2s(dst + l * C::RAW_PITCH_W, src + (size_t)l * (C::ROW * 4), bytes, raw_full + st);
+        // ===== TMA warp: one lane issues the L row copies of an item =====
+        if (lane == 0) {
+            unsigned j = 0;
+            for (unsigned item = blockIdx.x; item < n_items; item += gridDim.x, ++j) {
+                const unsigned st = j % C::NSTAGE, round = j / C::NSTAGE;
+                mb::wait(raw_empty + st, (round & 1) ^ 1);
+                const unsigned frame = item / IPF, grp = item - frame * IPF;
+                const unsigned off = grp * (C::G * C::S * 4);                      // byte offset of the run inside a chirp row
+                const unsigned a0 = off & ~15u;
+                const unsigned bytes = ((off - a0) + C::G * C::S * 4 + 15u) & ~15u;
+                mb::arrive_expect_tx(raw_full + st, bytes * C::L);
+                const unsigned char* src = reinterpret_cast<const unsigned char*>(a.iq) + (size_t)frame * ((size_t)C::ROW * C::L * 4) + a0;
+                uint32_t* dst = ring + st * C::RAW_STAGE_W;
+#pragma unroll 5
+                for (int l = 0; l < C::L; ++l)
+                    mb::bulk_g2s(dst + l * C::RAW_PITCH_W, src + (size_t)l * (C::ROW * 4), bytes, raw_full + st);
+            }
         }
     } else if (warp < C::NA) {
         // ===== phase A: Doppler =====
-        const int col = warp * 32 + lane;
+        const int h = C::DF == 1 ? 0 : warp / C::NA1;
+        const int col = (warp - h * C::NA1) * 32 + lane;
         const bool active = col < C::COLS_A;
         const int colc = active ? col : C::COLS_A - 1;
         const float ws = a.winS[colc % C::S];
         unsigned j = 0;
         for (unsigned item = blockIdx.x; item < n_items; item += gridDim.x, ++j) {
             const unsigned st = j % C::NSTAGE, round = j / C::NSTAGE;
+            const unsigned tb = j % C::NTILE, tround = j / C::NTILE;
             const unsigned grp = item % IPF;
             const int shift = (int)((grp * (C::G * C::S * 4)) & 15u) >> 2;
-            cf v[C::L];
+            cf v[C::LH];
             mb::wait(raw_full + st, round & 1);
-            rd_reg_doppler_load<C>(a, ring + st * C::RAW_STAGE_W, shift + colc, v);
+            rd_reg_doppler_load<C>(a, ring + st * C::RAW_STAGE_W, shift + colc, h, v);
             mb::arrive(raw_empty + st);
             rd_reg_doppler_finish<C>(ws, v);
-            mb::wait(tile_empty, (j & 1) ^ 1);
-            if (active) rd_reg_store_row<C>(v, tile + (size_t)col * C::P);
-            mb::arrive(tile_full);
+            mb::wait(tile_empty + tb, (tround & 1) ^ 1);
+            if (active) rd_reg_store_row<C>(v, tiles + (size_t)tb * C::TILE + (size_t)col * C::P, h);
+            mb::arrive(tile_full + tb);
         }
     } else {
         // ===== phase B: range =====
@@ -84,22 +92,21 @@ __global__ void __launch_bounds__(C::NT, 1) rd_reg_kernel(const __grid_constant_
         const int g = colc / C::L, d = colc - g * C::L;
         unsigned j = 0;
         for (unsigned item = blockIdx.x; item < n_items; item += gridDim.x, ++j) {
+            const unsigned tb = j % C::NTILE, tround = j / C::NTILE;
             const unsigned frame = item / IPF, grp = item - frame * IPF;
             const int ant = (int)grp * C::G + g;
             cf v[C::S];
-            mb::wait(tile_full, j & 1);
-            rd_reg_range_load<C>(tile, g, d, v);
-            mb::arrive(tile_empty);
-            if (active) {
-                const size_t o = ((size_t)frame * C::CR + ant) * (C::S * C::L) + d;
-                cf* out = a.rd_out ? a.rd_out + o : nullptr;
-                float* mag = nullptr;
-                if (a.mag_out) {
-                    if (a.mag_antenna < 0) mag = a.mag_out + o;
-                    else if (a.mag_antenna == ant) mag = a.mag_out + (size_t)frame * (C::S * C::L) + d;
-                }
-                rd_reg_range_store<C>(v, out, mag);
+            mb::wait(tile_full + tb, tround & 1);
+            rd_reg_range_load<C>(tiles + (size_t)tb * C::TILE, g, d, v);
+            mb::arrive(tile_empty + tb);
+            const size_t o = ((size_t)frame * C::CR + ant) * (C::S * C::L) + d;
+            cf* out = (a.rd_out && active) ? a.rd_out + o : nullptr;
+            float* mag = nullptr;
+            if (a.mag_out && active) {
+                if (a.mag_antenna < 0) mag = a.mag_out + o;
+                else if (a.mag_antenna == ant) mag = a.mag_out + (size_t)frame * (C::S * C::L) + d;
             }
+            rd_reg_range_store<C>(v, out, mag);
         }
     }
 }
@@ -125,7 +132,11 @@ static int launch_reg(radar_ctx* ctx, const void* adc, int n_frames, int window_
     a.n_items = (unsigned)((long long)n_frames * IPF);
     float wl[C::L];
     host_hann_f(C::L, window_flags & RADAR_WIN_DOPPLER, wl);
-    for (int i = 0; i < C::L; ++i) a.winL[i] = make_float2(wl[i], wl[i]);
+    for (int h = 0; h < C::DF; ++h)
+        for (int m = 0; m < C::LH; ++m) {
+            const float w = wl[(h * C::LH + C::DF * m) % C::L];
+            a.winL[h * C::LH + m] = make_float2(w, w);
+        }
     host_hann_f(C::S, window_flags & RADAR_WIN_RANGE, a.winS);
     static bool configured[64] = {false};
     if (!configured[ctx->device & 63]) {
@@ -145,10 +156,14 @@ int launch_range_doppler_reg(radar_ctx* ctx, const void* adc, int n_frames, int 
     const int S = ctx->shape.num_samples, L = ctx->shape.num_loops, R = ctx->shape.num_rx;
     if (reinterpret_cast<uintptr_t>(adc) % 16 != 0) return 1;
     const int CR = ctx->shape.chirps_per_loop * R;
-#define RB_REG(s, l, cr, g)                                                                                   \
-    if (S == s && L == l && CR == cr && R % g == 0)                                                           \
-        return launch_reg<RdRegShape<s, l, cr, g>>(ctx, adc, n_frames, window_flags, rd_out, mag_out, mag_antenna, st);
-    RB_REG(63, 70, 12, 2)
+    const int variant = ctx->rd_reg;
+#define RB_REG(var, s, l, cr, g, df, nstage, ntile)                                                           \
+    if (variant == var && S == s && L == l && CR == cr && R % g == 0)                                         \
+        return launch_reg<RdRegShape<s, l, cr, g, df, nstage, ntile>>(ctx, adc, n_frames, window_flags, rd_out, mag_out, mag_antenna, st);
+    // RB_REG(variant (RADAR_B200_RD_REG; 1 is the default), S, L, CR, G, DF, ring stages, tile buffers)
+    RB_REG(1, 63, 70, 12, 2, 1, 3, 1)      // 6843 ODS: 0.547 ms per 4096 frames (0.75 of measured HBM), 166 registers, 10 warps
+    RB_REG(2, 63, 70, 12, 2, 2, 3, 1)      //   split column: 14 warps are allocated as 16 -> 128 registers, phase B spills: 0.886
+    RB_REG(3, 63, 70, 12, 2, 2, 2, 2)      //   the same with two tile buffers: 0.976
 #undef RB_REG
     return 1;
 }
