@@ -21,6 +21,17 @@ def test_peer_point_exchange_matches_nccl_allgather():
     assert res.returncode == 0 and "PEER_EXCHANGE_OK" in res.stdout, res.stdout[-2000:] + res.stderr[-2000:]
 
 
+def test_sar_voxel_sharded_matches_single_gpu():
+    """BASELINE.json configs[3] on two GPUs: broadcast + per-rank direction slices + all-gather == one GPU's image."""
+    import torch
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs two CUDA devices")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29534", os.path.join(REPO, "tests", "multi_gpu_sar_sharded.py")]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=240)
+    assert res.returncode == 0 and "SAR_SHARDED_OK" in res.stdout, res.stdout[-2000:] + res.stderr[-2000:]
+
+
 def test_point_mirrors_single_device():
     """radar_ctx_set_point_mirrors on one GPU: two local mirrors receive every packed row below the capacity, nothing
     beyond it; the padded layout ignores the mirrors; switching off restores the plain call."""
