@@ -9,14 +9,16 @@
 //   and stops as soon as the decision is fixed (see os_count_cells).
 // * OS with noise estimates requested: one warp per cell under test; every lane keeps its share of the training window in registers
 //   and the exact k-th order statistic is built bit by bit (MSB->LSB) from warp-wide counts
-//   (__reduce_add_sync), which is an exact selection on the fp32 bit patterns (non-negative floats order
-//   like their unsigned encodings).
+//   (__reduce_add_sync), which is an exact selection on order-preserving integer keys of the fp32 values.
+//   Maps with a negative cell (detect() accepts signed data; the counting paths assume magnitudes) always take this path.
 // * decision in fp64: (double)x > alpha*(double)noise - the same expression the host layer uses to publish
 //   `thresholds`.
 // * compaction: warp ballots + popcounts, an exclusive scan over the warps' totals, then an ordered
 //   scatter - row-major (range, Doppler) like np.where, one global counter write per map.
+#include <cmath>
 #include "radar_internal.h"
 #include "rd_core.cuh"
+#include "mbar.cuh"
 
 namespace rb {
 
@@ -40,7 +42,19 @@ struct CfarArgs {
                           // across valid rows, read consecutive banks (>= cols)
     FastDiv div_cols, div_vd, div_wd;
     int ph1_extra;        // OS counting path: full rows counted before the first decision, beyond the minimum that can reject
+    int ladder;           // OS mask-only path: 1 = level-ladder screen (os_ladder_cells) before the exact count
+    int seg_d, seg_r;     // ladder: cells per sliding segment along Doppler / range
+    float lvl_mul[4];     // ladder: the four levels as multiples of the sampled map median
 };
+
+// order-preserving map of all floats (negative ones included: detect() accepts signed data) onto unsigned keys
+__device__ __forceinline__ unsigned float_key(float v) {
+    const unsigned b = __float_as_uint(v);
+    return b ^ ((b >> 31) ? 0xffffffffu : 0x80000000u);
+}
+__device__ __forceinline__ float key_float(unsigned k) {
+    return __uint_as_float(k ^ ((k >> 31) ? 0x80000000u : 0xffffffffu));
+}
 
 template <int MAXV>
 __device__ __forceinline__ void os_cells(const CfarArgs& a, const float* map, uint8_t* mask, double* noise_dst) {
@@ -70,10 +84,10 @@ __device__ __forceinline__ void os_cells(const CfarArgs& a, const float* map, ui
         const int base = vr * a.pitch + vd;     // top-left corner of the window
         unsigned vals[MAXV];
 #pragma unroll
-        for (int i = 0; i < MAXV; ++i) vals[i] = off[i] >= 0 ? __float_as_uint(map[base + off[i]]) : 0xffffffffu;
+        for (int i = 0; i < MAXV; ++i) vals[i] = off[i] >= 0 ? float_key(map[base + off[i]]) : 0xffffffffu;
         unsigned res = 0;
 #pragma unroll 1
-        for (int bit = 30; bit >= 0; --bit) {
+        for (int bit = 31; bit >= 0; --bit) {
             const unsigned cand = res | (1u << bit);
             int cnt = 0;
 #pragma unroll
@@ -83,7 +97,7 @@ __device__ __forceinline__ void os_cells(const CfarArgs& a, const float* map, ui
         }
         if (lane == 0) {
             const int cell = r * a.cols + d;
-            const double noise = (double)__uint_as_float(res);
+            const double noise = (double)key_float(res);
             mask[cell] = ((double)map[r * a.pitch + d] > a.alpha * noise) ? 1 : 0;
             if (noise_dst) noise_dst[cell] = noise;
         }
@@ -213,6 +227,195 @@ __device__ __forceinline__ void os_count_cells(const CfarArgs& a, const float* m
     }
 }
 
+
+// ---- OS-CFAR decision by a ladder of four levels -------------------------------------------------------------------
+// (reference: detectors/os_cfar.py:94-195; the decision x > alpha * v_k is the one os_count_cells makes.)
+// For a level l (a float) the number of training cells below l, n(l), brackets the number below the per-cell bound T:
+//   alpha*(double)l <  (double)x  =>  l <  T  =>  n(l) <= n(T)      (a "lower" level: n(l) >= k proves a detection)
+//   alpha*(double)l >= (double)x  =>  l >= T  =>  n(T) <= n(l)      (an "upper" level: n(l) < k rules one out)
+// because T is the smallest float whose rounded product with alpha reaches x and rounded multiplication is monotone.  The
+// window counts at FOUR levels are carried as the four bytes of one word: an indicator byte per level and map cell, sliding
+// sums along Doppler (full window width in the low 5 bits of each byte, guard width in the high 3) and then along range
+// (at most 255 cells per window), a handful of instructions per cell instead of ~100 compares.  The levels sit around the
+// expected order statistic of a noise window (multiples of a 64-sample median of the map), so a noise cell is ruled out by
+// the level between its T and its window's v_k and a strong cell is confirmed by the level between v_k and T; only cells
+// whose T and v_k share a bracket (0.5 % of the 6843 / 1843 bench maps, a few % with alpha = 2) are left to the exact
+// count, done by one warp per cell.  The mask is identical to the exact paths' (tests compare all three).
+__device__ __forceinline__ unsigned expand4(unsigned q) { return (q * 0x00204081u) & 0x01010101u; }
+
+// TD > 0: the detector's (train, guard) pairs compiled in (the reference's settings); TD == 0: run-time widths.
+template <int TR, int GR, int TD, int GD>
+__device__ __forceinline__ void os_ladder_cells(const CfarArgs& a, const float* map, uint8_t* mask, unsigned* lad,
+                                                int* work_cell, int* work_n, float* lvl /* [9]: levels, compare bounds, median */) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tr = TD > 0 ? TR : a.tr, gr = TD > 0 ? GR : a.gr, td = TD > 0 ? TD : a.td, gd = TD > 0 ? GD : a.gd;
+    const int cr = tr + gr, cd = td + gd;
+    const int wr = 2 * cr + 1, wd = 2 * cd + 1;
+    const int nvr = a.rows - 2 * cr, nvd = a.cols - 2 * cd;
+    const int n_cells = a.rows * a.cols;
+    // -- levels: median of 64 samples on a regular grid (rank by counting, ties by index), times lvl_mul
+    if (warp == 0) {
+        const int stride = n_cells / 64;
+        const int i0 = lane * stride + stride / 2, i1 = (lane + 32) * stride + stride / 2;
+        const int y0 = (int)a.div_cols.div((uint32_t)i0), y1 = (int)a.div_cols.div((uint32_t)i1);
+        const float v0 = map[y0 * a.pitch + (i0 - y0 * a.cols)], v1 = map[y1 * a.pitch + (i1 - y1 * a.cols)];
+        int r0 = 0, r1 = 0;
+        for (int src = 0; src < 32; ++src) {
+            const float s0 = __shfl_sync(0xffffffffu, v0, src), s1 = __shfl_sync(0xffffffffu, v1, src);
+            r0 += (s0 < v0 || (s0 == v0 && src < lane)) + (s1 < v0);
+            r1 += (s0 < v1 || s0 == v1) + (s1 < v1 || (s1 == v1 && src < lane));
+        }
+        if (lane == 0) lvl[8] = 0.0f;
+        __syncwarp();
+        if (r0 == 31) lvl[8] = v0;
+        if (r1 == 31) lvl[8] = v1;
+        __syncwarp();
+        if (lane < 4) {
+            float l = lvl[8] * a.lvl_mul[lane];
+            // a negative or NaN median (maps are magnitudes, but detect() takes anything): the level moves to +inf, where it
+            // is never a lower level and, with every finite cell below it, never rules a detection out
+            if (!(l >= 0.0f)) l = __int_as_float(0x7f800000);
+            const double th = a.alpha * (double)l;           // x > th  <=>  alpha*l < x  (l is a lower level for this cell)
+            float f = (float)th;                             // largest float <= th: x > th <=> x > f for float x
+            if ((double)f > th) f = __uint_as_float(__float_as_uint(f) - 1u);
+            lvl[lane] = l;
+            lvl[4 + lane] = f;
+        }
+    }
+    __syncthreads();
+    const float l0 = lvl[0], l1 = lvl[1], l2 = lvl[2], l3 = lvl[3];
+    uint8_t* qbuf = mask;                                    // the indicator bytes live in the mask buffer until the sums are built
+    for (int i = threadIdx.x; i < n_cells; i += blockDim.x) {            // ladder path: the map is unpadded (pitch == cols)
+        const float m = map[i];
+        qbuf[i] = (uint8_t)((m < l0 ? 1 : 0) | (m < l1 ? 2 : 0) | (m < l2 ? 4 : 0) | (m < l3 ? 8 : 0));
+    }
+    __syncthreads();
+    // -- sliding sums along Doppler: lad[r][d] = (cells below each level in [d-cd, d+cd]) | (in [d-gd, d+gd]) << 5, per byte
+    if (TD > 0) {
+        // compile-time widths: a thread takes SEG outputs of one row, its SEG + 2cd indicator bytes expanded once into registers
+        constexpr int SEG = 16, CD = TD + GD, NQ = SEG + 2 * CD;
+        const int nseg = (nvd + SEG - 1) / SEG;
+        for (int t = threadIdx.x; t < a.rows * nseg; t += blockDim.x) {
+            const int r = t / nseg, sg = t - r * nseg;
+            const int d0 = CD + sg * SEG;
+            const uint8_t* qr = qbuf + r * a.cols + d0 - CD;
+            const int n_ok = a.cols - (d0 - CD);             // bytes of this row from the segment's first input on
+            unsigned e[NQ];
+#pragma unroll
+            for (int x = 0; x < NQ; ++x) e[x] = x < n_ok ? expand4(qr[x]) : 0u;
+            unsigned A = 0, G = 0;
+#pragma unroll
+            for (int x = 0; x <= 2 * CD; ++x) A += e[x];
+#pragma unroll
+            for (int x = CD - GD; x <= CD + GD; ++x) G += e[x];
+            unsigned* out = lad + r * a.cols + d0;
+            const int n_out = min(SEG, a.cols - CD - d0);
+#pragma unroll
+            for (int o = 0; o < SEG; ++o) {
+                if (o > 0) {
+                    A += e[o + 2 * CD] - e[o - 1];
+                    G += e[o + CD + GD] - e[o + CD - GD - 1];
+                }
+                if (o < n_out) out[o] = A | (G << 5);
+            }
+        }
+    } else {
+        const int nseg = (nvd + a.seg_d - 1) / a.seg_d;
+        for (int t = threadIdx.x; t < a.rows * nseg; t += blockDim.x) {
+            const int r = t / nseg, sg = t - r * nseg;
+            const int d0 = cd + sg * a.seg_d, d1 = min(d0 + a.seg_d, a.cols - cd);
+            const uint8_t* qr = qbuf + r * a.cols;
+            unsigned* out = lad + r * a.cols;
+            unsigned A = 0, G = 0;
+            for (int x = d0 - cd; x <= d0 + cd; ++x) A += expand4(qr[x]);
+            for (int x = d0 - gd; x <= d0 + gd; ++x) G += expand4(qr[x]);
+            out[d0] = A | (G << 5);
+            for (int d = d0 + 1; d < d1; ++d) {
+                A += expand4(qr[d + cd]) - expand4(qr[d - cd - 1]);
+                G += expand4(qr[d + gd]) - expand4(qr[d - gd - 1]);
+                out[d] = A | (G << 5);
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < (n_cells + 3) / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(mask)[i] = 0u;
+    __syncthreads();
+    // -- sliding sums along range + decision
+    {
+        const float f0 = lvl[4], f1 = lvl[5], f2 = lvl[6], f3 = lvl[7];
+        const unsigned k4 = (unsigned)a.k_rank * 0x01010101u;
+        const int nseg = (nvr + a.seg_r - 1) / a.seg_r;
+        for (int t = threadIdx.x; t < nseg * nvd; t += blockDim.x) {
+            const int sg = t / nvd, vd = t - sg * nvd;
+            const int d = vd + cd;
+            const int r0 = cr + sg * a.seg_r, r1 = min(r0 + a.seg_r, a.rows - cr);
+            const unsigned* col = lad + d;
+            unsigned W = 0, Wg = 0;
+            if (TD > 0) {
+#pragma unroll
+                for (int y = -(TR + GR); y <= TR + GR; ++y) W += col[(r0 + y) * a.cols] & 0x1f1f1f1fu;
+#pragma unroll
+                for (int y = -GR; y <= GR; ++y) Wg += (col[(r0 + y) * a.cols] >> 5) & 0x07070707u;
+            } else {
+                for (int y = r0 - cr; y <= r0 + cr; ++y) W += col[y * a.cols] & 0x1f1f1f1fu;
+                for (int y = r0 - gr; y <= r0 + gr; ++y) Wg += (col[y * a.cols] >> 5) & 0x07070707u;
+            }
+            const unsigned* cr_in = col + (r0 + cr) * a.cols;      // row entering / leaving the window, entering / leaving the guard band
+            const unsigned* cr_out = col + (r0 - cr - 1) * a.cols;
+            const unsigned* gr_in = col + (r0 + gr) * a.cols;
+            const unsigned* gr_out = col + (r0 - gr - 1) * a.cols;
+            const float* xp = map + r0 * a.cols + d;
+            uint8_t* mp = mask + r0 * a.cols + d;
+            for (int r = r0; r < r1; ++r) {
+                if (r > r0) {
+                    W += (*cr_in & 0x1f1f1f1fu) - (*cr_out & 0x1f1f1f1fu);
+                    Wg += ((*gr_in >> 5) & 0x07070707u) - ((*gr_out >> 5) & 0x07070707u);
+                }
+                const unsigned Wt = W - Wg;                  // training cells below each level (no borrow: Wg <= W per byte)
+                const float x = *xp;
+                // bytes of the lower levels (alpha*l < x: the count below l is a lower bound of the count below T)
+                const unsigned lower = (x > f0 ? 0xffu : 0u) | (x > f1 ? 0xff00u : 0u) | (x > f2 ? 0xff0000u : 0u) | (x > f3 ? 0xff000000u : 0u);
+                const unsigned ge = __vcmpgeu4(Wt, k4);      // 0xff per level whose count reaches k
+                if (ge & lower) *mp = 1;                     // a lower level already has k cells below it: detection
+                else if ((~ge & ~lower) == 0u)               // no upper level rules it out: undecided
+                    work_cell[atomicAdd(work_n, 1)] = (r - cr) * nvd + vd;
+                cr_in += a.cols; cr_out += a.cols; gr_in += a.cols; gr_out += a.cols; xp += a.cols; mp += a.cols;
+            }
+        }
+    }
+    __syncthreads();
+    // -- exact count of the undecided cells, one warp per cell; every lane keeps its window offsets
+    const int n_work = *work_n;
+    if (n_work == 0) return;
+    constexpr int MAXW = 8;                                  // 255 window cells at most
+    int off[MAXW];
+#pragma unroll
+    for (int i = 0; i < MAXW; ++i) {
+        const int w = lane + 32 * i;
+        off[i] = -1;
+        if (w < wr * wd) {
+            const int y = (int)a.div_wd.div((uint32_t)w);
+            const int xx = w - y * wd;
+            const bool guard = (y >= tr && y <= tr + 2 * gr) && (xx >= td && xx <= td + 2 * gd);
+            if (!guard) off[i] = y * a.cols + xx;
+        }
+    }
+    for (int i = warp; i < n_work; i += kCfarWarps) {
+        const int c = work_cell[i];
+        const int vr = (int)a.div_vd.div((uint32_t)c);
+        const int vd = c - vr * nvd;
+        float t = 0.0f;
+        if (lane == 0) t = os_compare_bound(map[(vr + cr) * a.cols + vd + cd], a.alpha);
+        t = __shfl_sync(0xffffffffu, t, 0);
+        const float* win = map + vr * a.cols + vd;
+        int cnt = 0;
+#pragma unroll
+        for (int j = 0; j < MAXW; ++j) cnt += (off[j] >= 0 && win[off[j]] < t) ? 1 : 0;
+        cnt = __reduce_add_sync(0xffffffffu, cnt);
+        if (lane == 0) mask[(vr + cr) * a.cols + vd + cd] = cnt >= a.k_rank ? 1 : 0;
+    }
+}
+
 __device__ __forceinline__ void os_count_dispatch(const CfarArgs& a, const float* map, uint8_t* mask, int* wc, float* wt, int* wn) {
     // Doppler-axis (train, guard) of the reference's detector settings (tests/verify_processors.py:121-143,
     // gui_configs/processor_params.yaml:41-88)
@@ -228,12 +431,14 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
     __shared__ int warp_counts[kCfarWarps];
     const int n_cells = a.rows * a.cols;
     SmemArena ar(smem_raw);
-    float* map = ar.take<float>(a.rows * a.pitch);
+    float* map = ar.take<float>(a.rows * a.pitch + 8);      // + 32 bytes: alignment shift and round-up of the bulk copy
     uint8_t* mask = ar.take<uint8_t>(n_cells);
     const int n_work_max = max(a.rows - 2 * (a.tr + a.gr), 0) * max(a.cols - 2 * (a.td + a.gd), 0);   // cells under test
     int* work_cell = ar.take<int>(n_work_max);           // OS counting path: undecided cells after phase 1
-    float* work_t = ar.take<float>(n_work_max);
+    float* work_t = ar.take<float>(a.ladder ? n_cells : n_work_max);   // ladder: the packed sliding sums, one word per cell
     __shared__ int work_n;
+    __shared__ float ladder_lvl[9];
+    __shared__ uint64_t load_bar;
     if (threadIdx.x == 0) work_n = 0;
     const long long m = blockIdx.x;
     const float* src = a.maps + m * n_cells;
@@ -241,17 +446,64 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
     const uint8_t* rsel = a.row_select ? a.row_select + m * a.rows : nullptr;
     CfarArgs la = a;
     la.row_select = rsel;
-    for (int i = threadIdx.x; i < n_cells; i += blockDim.x) {
-        { const int y = (int)a.div_cols.div((uint32_t)i); map[y * a.pitch + (i - y * a.cols)] = src[i]; }
-        mask[i] = 0;
-        if (noise_dst) noise_dst[i] = 0.0;
+    // map -> shared memory.  Unpadded layout (ladder path): ONE bulk copy of the TMA engine from the 16-byte aligned address
+    // below the map (the copy may run a few bytes into the next map, so the last map of the batch takes the plain loop when
+    // its end is not aligned); otherwise batches of independent loads (one load latency per batch, not per cell).
+    const uintptr_t src_addr = reinterpret_cast<uintptr_t>(src);
+    const unsigned shift_b = (unsigned)(src_addr & 15u);
+    const unsigned copy_bytes = (shift_b + (unsigned)n_cells * 4u + 15u) & ~15u;
+    const bool want_counting = a.kind == RADAR_CFAR_OS && !noise_dst && a.alpha > 0.0;
+    int neg = 0;
+    const bool bulk = a.pitch == a.cols && (m + 1 < (long long)gridDim.x || copy_bytes == shift_b + (unsigned)n_cells * 4u);
+    if (bulk) {
+        map = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(map) + shift_b);
+        if (threadIdx.x == 0) {
+            mb::init(&load_bar, 1);
+            mb::fence_init();
+            mb::arrive_expect_tx(&load_bar, copy_bytes);
+            mb::bulk_g2s(reinterpret_cast<unsigned char*>(map) - shift_b, reinterpret_cast<const unsigned char*>(src) - shift_b,
+                         copy_bytes, &load_bar);
+        }
+        for (int i = threadIdx.x; i < n_cells; i += blockDim.x) {
+            mask[i] = 0;
+            if (noise_dst) noise_dst[i] = 0.0;
+        }
+        __syncthreads();                     // the barrier's initialisation is visible to every waiting thread
+        mb::wait(&load_bar, 0);
+        if (want_counting)
+            for (int i = threadIdx.x; i < n_cells; i += blockDim.x) neg |= map[i] < 0.0f ? 1 : 0;
+    } else {
+        for (int i0 = threadIdx.x; i0 < n_cells; i0 += 6 * kCfarThreads) {
+            float v[6];
+#pragma unroll
+            for (int j = 0; j < 6; ++j) { const int i = i0 + j * kCfarThreads; v[j] = i < n_cells ? __ldg(src + i) : 0.0f; }
+#pragma unroll
+            for (int j = 0; j < 6; ++j) {
+                const int i = i0 + j * kCfarThreads;
+                if (i < n_cells) {
+                    const int y = (int)a.div_cols.div((uint32_t)i);
+                    neg |= v[j] < 0.0f ? 1 : 0;
+                    map[y * a.pitch + (i - y * a.cols)] = v[j];
+                    mask[i] = 0;
+                    if (noise_dst) noise_dst[i] = 0.0;
+                }
+            }
+        }
     }
-    __syncthreads();
+    // the counting OS decisions rely on non-negative cells (magnitude maps); signed data takes the exact selection
+    const bool counting = want_counting && __syncthreads_or(neg) == 0;
+    if (!want_counting) __syncthreads();
 
     const int cr = a.tr + a.gr, cd = a.td + a.gd;
     const int nvr = a.rows - 2 * cr, nvd = a.cols - 2 * cd;
     if (nvr > 0 && nvd > 0) {      // window larger than the map: no valid cell (reference swallows the ValueError)
-        if (a.kind == RADAR_CFAR_OS && !noise_dst && a.alpha > 0.0) {
+        if (counting && a.ladder) {
+            unsigned* lad = reinterpret_cast<unsigned*>(work_t);
+            // (range, Doppler) settings of tests/verify_processors.py:121-143 and gui_configs/processor_params.yaml:41-47
+            if (a.tr == 8 && a.gr == 2 && a.td == 4 && a.gd == 1) os_ladder_cells<8, 2, 4, 1>(la, map, mask, lad, work_cell, &work_n, ladder_lvl);
+            else if (a.tr == 5 && a.gr == 3 && a.td == 5 && a.gd == 2) os_ladder_cells<5, 3, 5, 2>(la, map, mask, lad, work_cell, &work_n, ladder_lvl);
+            else os_ladder_cells<0, 0, 0, 0>(la, map, mask, lad, work_cell, &work_n, ladder_lvl);
+        } else if (counting) {
             os_count_dispatch(la, map, mask, work_cell, work_t, &work_n);
         } else if (a.kind == RADAR_CFAR_OS) {
             const int wcells = (2 * cr + 1) * (2 * cd + 1);
@@ -302,38 +554,49 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
     }
     if (!a.dets_out && !a.count_out) return;
 
-    // ordered compaction: each warp owns a contiguous, 32-aligned span of cells
+    // ordered compaction: every thread owns `ch` consecutive cells (whole 32-bit words of mask bytes), counts them with one
+    // popcount per word, an exclusive scan over the threads (shuffles inside a warp, shared memory across warps) gives its
+    // first slot, and it writes its detections in cell order - row-major (range, Doppler) like np.where.
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int span = (((n_cells + kCfarWarps - 1) / kCfarWarps) + 31) & ~31;
-    const int begin = warp * span;
-    const int end = min(begin + span, n_cells);
+    const int ch_words = ((n_cells + kCfarThreads - 1) / kCfarThreads + 3) / 4;
+    const int w_begin = threadIdx.x * ch_words;
+    const uint32_t* mw = reinterpret_cast<const uint32_t*>(mask);
+    auto mask_word = [&](int w) -> uint32_t {               // detections of cells 4w .. 4w+3 as bits 0, 8, 16, 24
+        const int left = n_cells - 4 * w;
+        if (left <= 0) return 0u;
+        const uint32_t v = mw[w] & 0x01010101u;
+        return left >= 4 ? v : v & ((1u << (8 * left)) - 1u);
+    };
     int cnt = 0;
-    for (int i = begin + lane; i < begin + span; i += 32) {
-        const bool hit = (i < end) && mask[i];
-        cnt += __popc(__ballot_sync(0xffffffffu, hit));
+    for (int w = w_begin; w < w_begin + ch_words; ++w) cnt += __popc(mask_word(w));
+    int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
     }
-    if (lane == 0) warp_counts[warp] = cnt;
+    if (lane == 31) warp_counts[warp] = incl;
     __syncthreads();
-    int offset = 0, total = 0;
+    int offset = incl - cnt, total = 0;
     for (int w = 0; w < kCfarWarps; ++w) {
         if (w < warp) offset += warp_counts[w];
         total += warp_counts[w];
     }
     if (threadIdx.x == 0 && a.count_out) a.count_out[m] = total;
-    if (!a.dets_out) return;
+    if (!a.dets_out || cnt == 0) return;
     int32_t* dets = a.dets_out + m * (long long)a.max_dets * 2;
-    for (int i = begin + lane; i < begin + span; i += 32) {
-        const bool hit = (i < end) && mask[i];
-        const unsigned ballot = __ballot_sync(0xffffffffu, hit);
-        if (hit) {
-            const int slot = offset + __popc(ballot & ((1u << lane) - 1u));
-            if (slot < a.max_dets) {
-                const int r = (int)a.div_cols.div((uint32_t)i);
-                dets[2 * slot] = r;
-                dets[2 * slot + 1] = i - r * a.cols;
+    for (int w = w_begin; w < w_begin + ch_words; ++w) {
+        uint32_t v = mask_word(w);
+        while (v) {
+            const int cell = 4 * w + ((__ffs(v) - 1) >> 3);
+            v &= v - 1u;
+            if (offset < a.max_dets) {
+                const int r = (int)a.div_cols.div((uint32_t)cell);
+                dets[2 * offset] = r;
+                dets[2 * offset + 1] = cell - r * a.cols;
             }
+            ++offset;
         }
-        offset += __popc(ballot);
     }
 }
 
@@ -388,11 +651,30 @@ static int launch_cfar(radar_ctx* ctx, const float* maps, int n_maps, int rows, 
     const int nvd = cols - 2 * (a.td + a.gd);
     a.div_vd = make_fastdiv((uint32_t)(nvd > 0 ? nvd : 1));
     const size_t n_cells = (size_t)rows * cols;
-    a.pitch = cols;
-    if (nvd > 0) while ((a.pitch - nvd) % 32 != 0) ++a.pitch;
     const int nvr = rows - 2 * (a.tr + a.gr);
+    // level-ladder screen: OS, mask only, every packed field wide enough (5 bits of window width, 3 of guard width, 8 of window
+    // cells), at least 64 cells to sample; RADAR_B200_CFAR_LADDER=0 switches it off (tests compare the paths)
+    {
+        const int wr = 2 * (a.tr + a.gr) + 1, wd = 2 * (a.td + a.gd) + 1;
+        a.ladder = (p.kind == RADAR_CFAR_OS && !noise_out && !row_select && a.alpha > 0.0 && ctx->cfar_ladder && nvr > 0 && nvd > 0 &&
+                    wd <= 31 && 2 * a.gd + 1 <= 7 && wr * wd <= 255 && n_cells >= 64) ? 1 : 0;
+        if (a.ladder) {
+            // expected order statistic of a Rayleigh noise window relative to the map median: sqrt(ln(1/(1-k/N)) / ln 2)
+            const double q = (double)a.k_rank / (double)a.n_train;
+            const double vk = q < 1.0 ? std::sqrt(std::log(1.0 / (1.0 - q)) / std::log(2.0)) : 2.0;
+            const double rel[4] = {0.57, 0.85, 1.28, 1.9};
+            for (int j = 0; j < 4; ++j) a.lvl_mul[j] = (float)(vk * rel[j]);
+            const int per_d = kCfarThreads / rows > 0 ? kCfarThreads / rows : 1;
+            a.seg_d = (nvd + per_d - 1) / per_d;
+            const int per_r = kCfarThreads / nvd > 0 ? kCfarThreads / nvd : 1;
+            a.seg_r = (nvr + per_r - 1) / per_r;
+        }
+    }
+    a.pitch = cols;
+    if (nvd > 0 && !a.ladder) while ((a.pitch - nvd) % 32 != 0) ++a.pitch;
     const size_t n_work_max = (size_t)(nvr > 0 ? nvr : 0) * (size_t)(nvd > 0 ? nvd : 0);
-    const size_t smem = arena_bytes((size_t)rows * a.pitch, 4) + arena_bytes(n_cells, 1) + 2 * arena_bytes(n_work_max, 4);
+    const size_t smem = arena_bytes((size_t)rows * a.pitch + 8, 4) + arena_bytes(n_cells, 1) + arena_bytes(n_work_max, 4) +
+                        arena_bytes(a.ladder ? n_cells : n_work_max, 4);
     if (smem > (size_t)ctx->max_smem_optin)
         return set_error(ctx, RADAR_E_UNSUPPORTED, "CFAR map of %d x %d cells exceeds shared memory", rows, cols);
     RB_CUDA_OK(ctx, cudaFuncSetAttribute(cfar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

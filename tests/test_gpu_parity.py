@@ -397,6 +397,42 @@ def test_os_cfar_counting_path_ties_and_edges(torch_cuda):
             assert np.array_equal(b["mask"][0, 3].cpu().numpy().astype(bool), mo)
 
 
+def test_os_cfar_ladder_equals_counting_path(torch_cuda):
+    """The level-ladder screen of the mask-only OS-CFAR (kernels_cfar.cu: os_ladder_cells) gives the mask of the plain
+    counting path (RADAR_B200_CFAR_LADDER=0) and of the oracle: range-Doppler maps of both bench cfgs, pure noise, signed
+    data (negative median), constant maps, a NaN / inf cell, detector settings of verify_processors.py and the GUI yaml."""
+    torch = torch_cuda
+    from oracle import radar_oracle as orc
+    from mmwave_radar_processing_b200.engine import cfar_params
+    from mmwave_radar_processing_b200.synthetic import synth_batch_for_cfg
+    rng = np.random.default_rng(11)
+    for name, geom in (("6843_RadVel_ods_20Hz", "ods"), ("1843_RadVel", "standard")):
+        cm = load_cfg(name, geom)
+        lad = _engine_with_env(cm, "RADAR_B200_CFAR_LADDER", 1)
+        ref = _engine_with_env(cm, "RADAR_B200_CFAR_LADDER", 0)
+        iq = torch.from_numpy(synth_batch_for_cfg(cm, range(12))).cuda()
+        _, mag = lad.range_doppler(iq, want_rd=False, mag_antenna=0)
+        s, l = mag.shape[-2:]
+        extra = [np.abs(rng.normal(size=(s, l)) + 1j * rng.normal(size=(s, l))) * 1e3,        # Rayleigh noise only
+                 rng.normal(size=(s, l)) - 0.5,                                               # signed, negative median
+                 np.full((s, l), 3.0), np.zeros((s, l)),                                      # constant maps
+                 rng.exponential(1.0, (s, l)) * np.exp(rng.normal(size=(s, l)) * 3.0)]        # heavy tailed
+        m = rng.exponential(1.0, (s, l)); m[s // 2, l // 2] = np.nan; m[s // 3, l // 3] = np.inf; extra.append(m)
+        maps = torch.cat([mag, torch.from_numpy(np.stack(extra).astype(np.float32)).cuda()])
+        for (t2, g2, rho, alpha) in (((8, 4), (2, 1), 0.75, 3.5), ((5, 5), (3, 2), 0.7, 2.0), ((4, 4), (2, 2), 0.5, 1.0),
+                                     ((2, 10), (1, 3), 0.9, 6.0), ((8, 4), (2, 1), 1.0, 0.25)):
+            p = cfar_params("os", t2, g2, rho=rho, alpha=alpha)
+            a = lad.cfar(maps, p, want_mask=True)
+            b = ref.cfar(maps, p, want_mask=True)
+            assert torch.equal(a["mask"], b["mask"]) and torch.equal(a["counts"], b["counts"]), (name, t2, g2, rho, alpha)
+            for i in range(maps.shape[0]):
+                n = int(a["counts"][i])
+                assert torch.equal(a["dets"][i, :n], b["dets"][i, :n])
+            for i in (0, 5, 12, 13, 16, 17):
+                _, _, mo = orc.cfar_2d(maps[i].cpu().numpy().astype(np.float64), "os", t2, g2, rho=rho, alpha=alpha)
+                assert np.array_equal(a["mask"][i].cpu().numpy().astype(bool), mo), (name, t2, i)
+
+
 def test_error_paths(torch_cuda):
     torch = torch_cuda
     from mmwave_radar_processing_b200 import _native as nat
