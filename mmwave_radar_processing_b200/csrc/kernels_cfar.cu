@@ -24,6 +24,7 @@ namespace rb {
 
 constexpr int kCfarThreads = 256;
 constexpr int kCfarWarps = kCfarThreads / 32;
+constexpr int kMapSpare = 48;         // floats behind the map in shared memory
 
 struct CfarArgs {
     const float* maps;
@@ -44,6 +45,8 @@ struct CfarArgs {
     int ph1_extra;        // OS counting path: full rows counted before the first decision, beyond the minimum that can reject
     int ladder;           // OS mask-only path: 1 = level-ladder screen (os_ladder_cells) before the exact count
     int seg_d, seg_r;     // ladder: cells per sliding segment along Doppler / range
+    int nseg_d, nseg_r;   // ladder: segments per row / per column
+    FastDiv div_nseg_d;
     float lvl_mul[4];     // ladder: the four levels as multiples of the sampled map median
 };
 
@@ -241,6 +244,7 @@ __device__ __forceinline__ void os_count_cells(const CfarArgs& a, const float* m
 // the level between its T and its window's v_k and a strong cell is confirmed by the level between v_k and T; only cells
 // whose T and v_k share a bracket (0.5 % of the 6843 / 1843 bench maps, a few % with alpha = 2) are left to the exact
 // count, done by one warp per cell.  The mask is identical to the exact paths' (tests compare all three).
+constexpr int kLadderSeg = 16;        // outputs per thread of the compile-time Doppler pass
 __device__ __forceinline__ unsigned expand4(unsigned q) { return (q * 0x00204081u) & 0x01010101u; }
 
 // TD > 0: the detector's (train, guard) pairs compiled in (the reference's settings); TD == 0: run-time widths.
@@ -284,25 +288,29 @@ __device__ __forceinline__ void os_ladder_cells(const CfarArgs& a, const float* 
     }
     __syncthreads();
     const float l0 = lvl[0], l1 = lvl[1], l2 = lvl[2], l3 = lvl[3];
-    uint8_t* qbuf = mask;                                    // the indicator bytes live in the mask buffer until the sums are built
-    for (int i = threadIdx.x; i < n_cells; i += blockDim.x) {            // ladder path: the map is unpadded (pitch == cols)
-        const float m = map[i];
-        qbuf[i] = (uint8_t)((m < l0 ? 1 : 0) | (m < l1 ? 2 : 0) | (m < l2 ? 4 : 0) | (m < l3 ? 8 : 0));
-    }
-    __syncthreads();
+    // indicator bytes of one cell: byte j = (m < level j)
+    auto indicators = [&](float m) -> unsigned {
+        unsigned e = m < l0 ? 1u : 0u;
+        if (m < l1) e |= 0x100u;
+        if (m < l2) e |= 0x10000u;
+        if (m < l3) e |= 0x1000000u;
+        return e;
+    };
     // -- sliding sums along Doppler: lad[r][d] = (cells below each level in [d-cd, d+cd]) | (in [d-gd, d+gd]) << 5, per byte
     if (TD > 0) {
-        // compile-time widths: a thread takes SEG outputs of one row, its SEG + 2cd indicator bytes expanded once into registers
-        constexpr int SEG = 16, CD = TD + GD, NQ = SEG + 2 * CD;
-        const int nseg = (nvd + SEG - 1) / SEG;
+        // compile-time widths: a thread takes SEG outputs of one row; the indicators of its SEG + 2cd cells stay in registers
+        constexpr int SEG = kLadderSeg, CD = TD + GD, NQ = SEG + 2 * CD;
+        const int nseg = a.nseg_d;
         for (int t = threadIdx.x; t < a.rows * nseg; t += blockDim.x) {
-            const int r = t / nseg, sg = t - r * nseg;
+            const int r = (int)a.div_nseg_d.div((uint32_t)t), sg = t - r * nseg;
             const int d0 = CD + sg * SEG;
-            const uint8_t* qr = qbuf + r * a.cols + d0 - CD;
-            const int n_ok = a.cols - (d0 - CD);             // bytes of this row from the segment's first input on
+            // a short last segment reads on into the next row (the map buffer has kMapSpare floats after its last row);
+            // those values only reach outputs that are not stored
+            static_assert(NQ <= kMapSpare, "spare floats behind the map");
+            const float* mr = map + r * a.cols + d0 - CD;
             unsigned e[NQ];
 #pragma unroll
-            for (int x = 0; x < NQ; ++x) e[x] = x < n_ok ? expand4(qr[x]) : 0u;
+            for (int x = 0; x < NQ; ++x) e[x] = indicators(mr[x]);
             unsigned A = 0, G = 0;
 #pragma unroll
             for (int x = 0; x <= 2 * CD; ++x) A += e[x];
@@ -320,33 +328,31 @@ __device__ __forceinline__ void os_ladder_cells(const CfarArgs& a, const float* 
             }
         }
     } else {
-        const int nseg = (nvd + a.seg_d - 1) / a.seg_d;
+        const int nseg = a.nseg_d;
         for (int t = threadIdx.x; t < a.rows * nseg; t += blockDim.x) {
-            const int r = t / nseg, sg = t - r * nseg;
+            const int r = (int)a.div_nseg_d.div((uint32_t)t), sg = t - r * nseg;
             const int d0 = cd + sg * a.seg_d, d1 = min(d0 + a.seg_d, a.cols - cd);
-            const uint8_t* qr = qbuf + r * a.cols;
+            const float* mr = map + r * a.cols;
             unsigned* out = lad + r * a.cols;
             unsigned A = 0, G = 0;
-            for (int x = d0 - cd; x <= d0 + cd; ++x) A += expand4(qr[x]);
-            for (int x = d0 - gd; x <= d0 + gd; ++x) G += expand4(qr[x]);
+            for (int x = d0 - cd; x <= d0 + cd; ++x) A += indicators(mr[x]);
+            for (int x = d0 - gd; x <= d0 + gd; ++x) G += indicators(mr[x]);
             out[d0] = A | (G << 5);
             for (int d = d0 + 1; d < d1; ++d) {
-                A += expand4(qr[d + cd]) - expand4(qr[d - cd - 1]);
-                G += expand4(qr[d + gd]) - expand4(qr[d - gd - 1]);
+                A += indicators(mr[d + cd]) - indicators(mr[d - cd - 1]);
+                G += indicators(mr[d + gd]) - indicators(mr[d - gd - 1]);
                 out[d] = A | (G << 5);
             }
         }
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < (n_cells + 3) / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(mask)[i] = 0u;
-    __syncthreads();
     // -- sliding sums along range + decision
     {
         const float f0 = lvl[4], f1 = lvl[5], f2 = lvl[6], f3 = lvl[7];
         const unsigned k4 = (unsigned)a.k_rank * 0x01010101u;
-        const int nseg = (nvr + a.seg_r - 1) / a.seg_r;
+        const int nseg = a.nseg_r;
         for (int t = threadIdx.x; t < nseg * nvd; t += blockDim.x) {
-            const int sg = t / nvd, vd = t - sg * nvd;
+            const int sg = (int)a.div_vd.div((uint32_t)t), vd = t - sg * nvd;
             const int d = vd + cd;
             const int r0 = cr + sg * a.seg_r, r1 = min(r0 + a.seg_r, a.rows - cr);
             const unsigned* col = lad + d;
@@ -431,8 +437,8 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
     __shared__ int warp_counts[kCfarWarps];
     const int n_cells = a.rows * a.cols;
     SmemArena ar(smem_raw);
-    float* map = ar.take<float>(a.rows * a.pitch + 8);      // + 32 bytes: alignment shift and round-up of the bulk copy
-    uint8_t* mask = ar.take<uint8_t>(n_cells);
+    float* map = ar.take<float>(a.rows * a.pitch + kMapSpare);   // spare: alignment shift + round-up of the bulk copy, ladder overreads
+    uint8_t* mask = ar.take<uint8_t>(n_cells + 32);
     const int n_work_max = max(a.rows - 2 * (a.tr + a.gr), 0) * max(a.cols - 2 * (a.td + a.gd), 0);   // cells under test
     int* work_cell = ar.take<int>(n_work_max);           // OS counting path: undecided cells after phase 1
     float* work_t = ar.take<float>(a.ladder ? n_cells : n_work_max);   // ladder: the packed sliding sums, one word per cell
@@ -464,14 +470,17 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
             mb::bulk_g2s(reinterpret_cast<unsigned char*>(map) - shift_b, reinterpret_cast<const unsigned char*>(src) - shift_b,
                          copy_bytes, &load_bar);
         }
-        for (int i = threadIdx.x; i < n_cells; i += blockDim.x) {
-            mask[i] = 0;
-            if (noise_dst) noise_dst[i] = 0.0;
-        }
+        for (int i = threadIdx.x; i < (n_cells + 3) / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(mask)[i] = 0u;
+        if (noise_dst)
+            for (int i = threadIdx.x; i < n_cells; i += blockDim.x) noise_dst[i] = 0.0;
         __syncthreads();                     // the barrier's initialisation is visible to every waiting thread
         mb::wait(&load_bar, 0);
-        if (want_counting)
-            for (int i = threadIdx.x; i < n_cells; i += blockDim.x) neg |= map[i] < 0.0f ? 1 : 0;
+        if (want_counting) {                 // sign bits OR-ed together (-0.0 and negative NaNs count as negative: exact path, still right)
+            int acc = 0;
+#pragma unroll 4
+            for (int i = threadIdx.x; i < n_cells; i += blockDim.x) acc |= __float_as_int(map[i]);
+            neg = acc < 0 ? 1 : 0;
+        }
     } else {
         for (int i0 = threadIdx.x; i0 < n_cells; i0 += 6 * kCfarThreads) {
             float v[6];
@@ -500,9 +509,9 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
         if (counting && a.ladder) {
             unsigned* lad = reinterpret_cast<unsigned*>(work_t);
             // (range, Doppler) settings of tests/verify_processors.py:121-143 and gui_configs/processor_params.yaml:41-47
-            if (a.tr == 8 && a.gr == 2 && a.td == 4 && a.gd == 1) os_ladder_cells<8, 2, 4, 1>(la, map, mask, lad, work_cell, &work_n, ladder_lvl);
-            else if (a.tr == 5 && a.gr == 3 && a.td == 5 && a.gd == 2) os_ladder_cells<5, 3, 5, 2>(la, map, mask, lad, work_cell, &work_n, ladder_lvl);
-            else os_ladder_cells<0, 0, 0, 0>(la, map, mask, lad, work_cell, &work_n, ladder_lvl);
+            if (a.tr == 8 && a.gr == 2 && a.td == 4 && a.gd == 1) os_ladder_cells<8, 2, 4, 1>(a, map, mask, lad, work_cell, &work_n, ladder_lvl);
+            else if (a.tr == 5 && a.gr == 3 && a.td == 5 && a.gd == 2) os_ladder_cells<5, 3, 5, 2>(a, map, mask, lad, work_cell, &work_n, ladder_lvl);
+            else os_ladder_cells<0, 0, 0, 0>(a, map, mask, lad, work_cell, &work_n, ladder_lvl);
         } else if (counting) {
             os_count_dispatch(la, map, mask, work_cell, work_t, &work_n);
         } else if (a.kind == RADAR_CFAR_OS) {
@@ -665,15 +674,19 @@ static int launch_cfar(radar_ctx* ctx, const float* maps, int n_maps, int rows, 
             const double rel[4] = {0.57, 0.85, 1.28, 1.9};
             for (int j = 0; j < 4; ++j) a.lvl_mul[j] = (float)(vk * rel[j]);
             const int per_d = kCfarThreads / rows > 0 ? kCfarThreads / rows : 1;
-            a.seg_d = (nvd + per_d - 1) / per_d;
+            const bool fixed = (a.tr == 8 && a.gr == 2 && a.td == 4 && a.gd == 1) || (a.tr == 5 && a.gr == 3 && a.td == 5 && a.gd == 2);
+            a.seg_d = fixed ? kLadderSeg : (nvd + per_d - 1) / per_d;   // the kernel's compile-time instantiations use kLadderSeg
+            a.nseg_d = (nvd + a.seg_d - 1) / a.seg_d;
+            a.div_nseg_d = make_fastdiv((uint32_t)a.nseg_d);
             const int per_r = kCfarThreads / nvd > 0 ? kCfarThreads / nvd : 1;
             a.seg_r = (nvr + per_r - 1) / per_r;
+            a.nseg_r = (nvr + a.seg_r - 1) / a.seg_r;
         }
     }
     a.pitch = cols;
     if (nvd > 0 && !a.ladder) while ((a.pitch - nvd) % 32 != 0) ++a.pitch;
     const size_t n_work_max = (size_t)(nvr > 0 ? nvr : 0) * (size_t)(nvd > 0 ? nvd : 0);
-    const size_t smem = arena_bytes((size_t)rows * a.pitch + 8, 4) + arena_bytes(n_cells, 1) + arena_bytes(n_work_max, 4) +
+    const size_t smem = arena_bytes((size_t)rows * a.pitch + kMapSpare, 4) + arena_bytes(n_cells + 32, 1) + arena_bytes(n_work_max, 4) +
                         arena_bytes(a.ladder ? n_cells : n_work_max, 4);
     if (smem > (size_t)ctx->max_smem_optin)
         return set_error(ctx, RADAR_E_UNSUPPORTED, "CFAR map of %d x %d cells exceeds shared memory", rows, cols);
