@@ -390,35 +390,36 @@ __device__ __forceinline__ void os_ladder_cells(const CfarArgs& a, const float* 
         }
     }
     __syncthreads();
-    // -- exact count of the undecided cells, one warp per cell; every lane keeps its window offsets
+    // -- exact count of the undecided cells: eight lanes per cell, each walking every eighth window cell (the decision's own
+    //    predicate alpha*(double)c < (double)x per cell was measured slower than deriving the float bound once)
     const int n_work = *work_n;
     if (n_work == 0) return;
-    constexpr int MAXW = 8;                                  // 255 window cells at most
-    int off[MAXW];
-#pragma unroll
-    for (int i = 0; i < MAXW; ++i) {
-        const int w = lane + 32 * i;
-        off[i] = -1;
-        if (w < wr * wd) {
-            const int y = (int)a.div_wd.div((uint32_t)w);
-            const int xx = w - y * wd;
-            const bool guard = (y >= tr && y <= tr + 2 * gr) && (xx >= td && xx <= td + 2 * gd);
-            if (!guard) off[i] = y * a.cols + xx;
+    const int sub = lane >> 3, l8 = lane & 7;
+    const int wcells = wr * wd;
+    int y0 = 0, x0 = l8;                                     // window cell w = l8 + 8j as (row, column)
+    while (x0 >= wd) { x0 -= wd; ++y0; }
+    for (int i0 = warp * 4; i0 < n_work; i0 += kCfarWarps * 4) {
+        const int i = i0 + sub;
+        int cnt = 0, cell = 0;
+        if (i < n_work) {
+            const int c = work_cell[i];
+            const int vr = (int)a.div_vd.div((uint32_t)c);
+            const int vd = c - vr * nvd;
+            cell = (vr + cr) * a.cols + vd + cd;
+            const float tb = os_compare_bound(map[cell], a.alpha);
+            const float* win = map + vr * a.cols + vd;
+            int y = y0, xx = x0;
+            for (int w = l8; w < wcells; w += 8) {
+                const bool guard = (y >= tr && y <= tr + 2 * gr) && (xx >= td && xx <= td + 2 * gd);
+                cnt += (!guard && win[y * a.cols + xx] < tb) ? 1 : 0;
+                xx += 8;
+                while (xx >= wd) { xx -= wd; ++y; }
+            }
         }
-    }
-    for (int i = warp; i < n_work; i += kCfarWarps) {
-        const int c = work_cell[i];
-        const int vr = (int)a.div_vd.div((uint32_t)c);
-        const int vd = c - vr * nvd;
-        float t = 0.0f;
-        if (lane == 0) t = os_compare_bound(map[(vr + cr) * a.cols + vd + cd], a.alpha);
-        t = __shfl_sync(0xffffffffu, t, 0);
-        const float* win = map + vr * a.cols + vd;
-        int cnt = 0;
-#pragma unroll
-        for (int j = 0; j < MAXW; ++j) cnt += (off[j] >= 0 && win[off[j]] < t) ? 1 : 0;
-        cnt = __reduce_add_sync(0xffffffffu, cnt);
-        if (lane == 0) mask[(vr + cr) * a.cols + vd + cd] = cnt >= a.k_rank ? 1 : 0;
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, 1);
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, 2);
+        cnt += __shfl_xor_sync(0xffffffffu, cnt, 4);
+        if (i < n_work && l8 == 0) mask[cell] = cnt >= a.k_rank ? 1 : 0;
     }
 }
 
@@ -473,8 +474,8 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
         for (int i = threadIdx.x; i < (n_cells + 3) / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(mask)[i] = 0u;
         if (noise_dst)
             for (int i = threadIdx.x; i < n_cells; i += blockDim.x) noise_dst[i] = 0.0;
-        __syncthreads();                     // the barrier's initialisation is visible to every waiting thread
-        mb::wait(&load_bar, 0);
+        if (threadIdx.x == 0) mb::wait(&load_bar, 0);        // one thread polls; the others sleep at the CTA barrier
+        __syncthreads();
         if (want_counting) {                 // sign bits OR-ed together (-0.0 and negative NaNs count as negative: exact path, still right)
             int acc = 0;
 #pragma unroll 4
@@ -499,6 +500,7 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
             }
         }
     }
+    if (!bulk && threadIdx.x < 4) mask[n_cells + threadIdx.x] = 0;       // the compaction reads whole words
     // the counting OS decisions rely on non-negative cells (magnitude maps); signed data takes the exact selection
     const bool counting = want_counting && __syncthreads_or(neg) == 0;
     if (!want_counting) __syncthreads();
@@ -570,11 +572,9 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
     const int ch_words = ((n_cells + kCfarThreads - 1) / kCfarThreads + 3) / 4;
     const int w_begin = threadIdx.x * ch_words;
     const uint32_t* mw = reinterpret_cast<const uint32_t*>(mask);
+    const int n_words = (n_cells + 3) / 4;                   // the bytes behind the last cell are zero (see the load above)
     auto mask_word = [&](int w) -> uint32_t {               // detections of cells 4w .. 4w+3 as bits 0, 8, 16, 24
-        const int left = n_cells - 4 * w;
-        if (left <= 0) return 0u;
-        const uint32_t v = mw[w] & 0x01010101u;
-        return left >= 4 ? v : v & ((1u << (8 * left)) - 1u);
+        return w < n_words ? mw[w] & 0x01010101u : 0u;
     };
     int cnt = 0;
     for (int w = w_begin; w < w_begin + ch_words; ++w) cnt += __popc(mask_word(w));
