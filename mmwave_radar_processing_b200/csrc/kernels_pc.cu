@@ -85,7 +85,8 @@ __device__ __forceinline__ int angle_argmax(const cf* z, int n_rt, int A, bool s
     const unsigned hi = (unsigned)(bits >> 32), lo = (unsigned)bits;
     const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
     const unsigned ml = __reduce_max_sync(0xffffffffu, hi == mh ? lo : 0u);
-    return (int)__reduce_min_sync(0xffffffffu, (hi == mh && lo == ml) ? (unsigned)best_a : 0x7fffffffu);
+    const unsigned arg = __reduce_min_sync(0xffffffffu, (hi == mh && lo == ml) ? (unsigned)best_a : 0x7fffffffu);
+    return arg < (unsigned)A ? (int)arg : 0;       // every |DFT| NaN (NaN / inf in the cube): no lane ever updated - stay in range
 }
 
 __device__ __forceinline__ int angle_argmax_any(const cf* z, int n, int A, bool shift, int lane, const double2* tw) {

@@ -17,6 +17,8 @@ Two entry points:
 """
 from __future__ import annotations
 
+import os
+
 from dataclasses import dataclass, field
 from typing import Callable, List, Optional, Sequence
 
@@ -74,6 +76,9 @@ class _Buffers:
         self.iq = (torch.empty((n_frames, e.C, e.R, e.S, 2), dtype=torch.int16, device=dev) if with_iq else None)
 
 
+_NVTX = os.environ.get("RADAR_B200_NVTX", "0") not in ("", "0")
+
+
 @dataclass
 class FramePipeline:
     cfg: object
@@ -107,20 +112,36 @@ class FramePipeline:
     def _stages(self, iq_dev: torch.Tensor, buf: _Buffers, mark: Optional[Callable[[str], None]] = None):
         f = iq_dev.shape[0]
         e = self.engine
+        push = None
+        if _NVTX:                       # RADAR_B200_NVTX=1: one NVTX range per stage (nsys / ncu --nvtx timelines)
+            user_mark = mark
+            push = torch.cuda.nvtx.range_push
+
+            def mark(name, _user=user_mark):            # the stage that just ended
+                torch.cuda.nvtx.range_pop()
+                if _user:
+                    _user(name)
+            push("radar_b200.range_doppler")
         rd, mag = buf.rd[:f], buf.mag[:f]
         e.range_doppler(iq_dev, want_rd=True, mag_antenna=0, rd_out=rd, mag_out=mag)
         if mark:
             mark("range_doppler")
         ra = None
         if self.with_range_angle:
+            if push:
+                push("radar_b200.range_angle")
             ra = e.range_angle(iq_dev, loop_idx=self.ra_chirp_idx, ant_list=list(self.ra_antennas) or None,
                                num_angle_bins=self.ra_angle_bins, out=buf.ra[:f])
             if mark:
                 mark("range_angle")
         dets, counts = buf.dets[:f], buf.counts[:f]
+        if push:
+            push("radar_b200.cfar")
         e.cfar(mag, self._params, one_d=False, max_dets=self.max_dets, dets_out=dets, count_out=counts)
         if mark:
             mark("cfar")
+        if push:
+            push("radar_b200.point_cloud")
         offsets = e.det_offsets(counts, self.max_dets, out=buf.offsets[:f + 1])
         pts, _, _ = e.point_cloud(rd, dets, counts, list(self.az_antenna_idxs), list(self.el_antenna_idxs),
                                   shift_az=self.shift_az_resp, shift_el=self.shift_el_resp,

@@ -84,6 +84,15 @@ class PointCloudGenerator(_Processor):
         if n == 0:
             return np.zeros(0), np.zeros(0)
         v, s, l = raw.shape
+        # numpy fancy indexing semantics of the reference's gather (:180-186): negative indices wrap, out-of-range ones raise
+        ri, di = np.asarray(det_range_idxs).astype(np.int64), np.asarray(det_velocity_idxs).astype(np.int64)
+        if ri.shape != di.shape:
+            raise IndexError("shape mismatch: range and velocity index arrays differ in length")
+        for idx, size, axis in ((ri, s, 1), (di, l, 2)):
+            if idx.size and (idx.min() < -size or idx.max() >= size):
+                bad = int(idx[(idx < -size) | (idx >= size)][0])
+                raise IndexError(f"index {bad} is out of bounds for axis {axis} with size {size}")
+        det_range_idxs, det_velocity_idxs = np.where(ri < 0, ri + s, ri), np.where(di < 0, di + l, di)
         eng = engine_for_cube_shape(v, s, l)
         eng.set_axes(np.zeros(s), np.zeros(l))
         eng.set_angle_bins(self.angle_bins)

@@ -5,8 +5,8 @@ range-Doppler kernel with window_flags = 0 - cut to the valid range rows and cro
 geometry, the slices and the ground-plane mesh are host fp64 with the reference's expressions.
 """
 import numpy as np
-import scipy.constants as constants
 
+from ..config_managers.cfgManager import SPEED_OF_LIGHT_M_S
 from ._device import is_device_tensor, stage_cube, to_host_c128
 from ._processor import _Processor
 from .virtual_array_reformater import VirtualArrayReformatter
@@ -47,7 +47,7 @@ class StripMapSARProcessor(_Processor):
         self.num_range_bins = cm.get_num_adc_samples(profile_idx=0)
         self.range_bins = np.linspace(start=0, stop=cm.range_max_m, num=self.num_range_bins)
         start_freq_GHz = float(cm.profile_cfgs[0]["startFreq_GHz"])
-        self.lambda_m = constants.c / (start_freq_GHz * 1e9)
+        self.lambda_m = SPEED_OF_LIGHT_M_S / (start_freq_GHz * 1e9)
         chirp_cfgs_per_loop = cm.frameCfg_end_index - cm.frameCfg_start_index + 1
         self.chirps_per_frame = cm.frameCfg_loops * chirp_cfgs_per_loop
         self.phase_shifts = np.linspace(start=np.pi, stop=-np.pi, num=cm.frameCfg_loops)

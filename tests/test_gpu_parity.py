@@ -542,3 +542,35 @@ def test_stream_sized_batch_matches_small_batches(torch_cuda):
         o0, o1 = int(big["offsets"][lo]), int(big["offsets"][lo + 32])
         assert o1 - o0 == ref_pts.shape[0] and torch.equal(big["points"][o0:o1], ref_pts)
     assert int(big["offsets"][f_big]) == (f_big // 32) * ref_pts.shape[0]
+
+
+def test_frame_file_to_point_clouds(torch_cuda, tmp_path):
+    """int16 frame file -> memmap -> pinned chunks -> FramePipeline.run_host gives the clouds of the frames
+    run directly from device memory (and of the oracle for the first frames)."""
+    torch = torch_cuda
+    from oracle import radar_oracle as orc
+    from mmwave_radar_processing_b200 import ingest
+    from mmwave_radar_processing_b200.pipeline import DetectorSpec, FramePipeline
+    from mmwave_radar_processing_b200.synthetic import synth_batch_for_cfg
+    cm = load_cfg("6843_RadVel_ods_20Hz", "ods")
+    iq = synth_batch_for_cfg(cm, range(37))
+    path = str(tmp_path / "stream.rb2")
+    ingest.FrameFile.write(path, iq)
+    pipe = FramePipeline(cm, detector=DetectorSpec(kind="os", num_train=(8, 4), num_guard=(2, 1), rho=0.75, alpha=3.5),
+                         az_antenna_idxs=(0, 3, 4, 7), el_antenna_idxs=(9, 8, 5, 4), max_dets=256)
+    clouds = ingest.process_file(pipe, path, batch_frames=16, chunk_frames=8, points_per_frame=256)
+    direct = pipe.gather_host(pipe.run(torch.from_numpy(iq).cuda()))
+    assert len(clouds) == len(direct) == 37
+    for a, b in zip(clouds, direct):
+        assert a.shape == b.shape and np.array_equal(a, b)
+    for i in range(3):
+        cube = orc.virtual_array(orc.iq_to_cube(iq[i]), cm.num_rx_antennas, cm.chirp_cfgs_per_loop, cm.frameCfg_loops)
+        rd = orc.range_doppler(cube)
+        _, _, mask = orc.cfar_2d(np.abs(rd[0]), "os", (8, 4), (2, 1), rho=0.75, alpha=3.5)
+        pts, _, _ = orc.point_cloud(rd, orc.mask_to_dets(mask), pipe.range_bins, pipe.vel_bins, [0, 3, 4, 7], [9, 8, 5, 4])
+        assert clouds[i].shape == pts.shape and np.allclose(clouds[i], pts, rtol=1e-9, atol=1e-9)
+    wrong = load_cfg("1843_RadVel")
+    pipe2 = FramePipeline(wrong, detector=DetectorSpec(kind="os", num_train=(8, 4), num_guard=(2, 1), rho=0.75, alpha=3.5),
+                          az_antenna_idxs=(0, 1, 2, 3), el_antenna_idxs=(), max_dets=64)
+    with pytest.raises(ValueError):
+        ingest.process_file(pipe2, path)

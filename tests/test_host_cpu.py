@@ -77,6 +77,47 @@ def test_native_stream_kernel_phases_on_cpu():
     assert worst < 2e-6
 
 
+def test_native_register_resident_kernel_phases_on_cpu():
+    out = _native_check("host_rd_reg_check")
+    worst = float(re.search(r"worst rel_l2 = ([0-9.e+-]+)", out).group(1))
+    assert worst < 2e-6
+
+
+def test_frame_file_round_trip_and_errors(tmp_path):
+    """ingest.FrameFile: header + int16 [frame][chirp][rx][sample][2] body, memory-mapped back bit for bit; chunks cover
+    every frame once; truncated / foreign files and non-integer cubes are refused."""
+    import numpy as np
+    import pytest
+    from mmwave_radar_processing_b200 import ingest
+    rng = np.random.default_rng(3)
+    frames = rng.integers(-32768, 32767, (11, 6, 4, 16, 2)).astype(np.int16)
+    path = str(tmp_path / "frames.rb2")
+    ingest.FrameFile.write(path, frames)
+    ff = ingest.FrameFile(path)
+    assert (ff.n_frames, ff.chirps_per_frame, ff.num_rx, ff.num_samples) == (11, 6, 4, 16)
+    assert np.array_equal(np.asarray(ff.data), frames)
+    seen = []
+    for lo, buf in ff.chunks(4, pinned=False):
+        assert np.array_equal(buf.numpy(), frames[lo:lo + buf.shape[0]])
+        seen.extend(range(lo, lo + buf.shape[0]))
+    assert seen == list(range(11))
+    with open(path, "r+b") as f:
+        f.truncate(ingest.HEADER_BYTES + 100)
+    with pytest.raises(ValueError):
+        ingest.FrameFile(path)
+    bad = str(tmp_path / "bad.bin")
+    open(bad, "wb").write(b"x" * 200)
+    with pytest.raises(ValueError):
+        ingest.FrameFile(bad)
+    cube = (rng.integers(-500, 500, (4, 16, 6)) + 1j * rng.integers(-500, 500, (4, 16, 6))).astype(np.complex128)
+    iq = ingest.cube_to_iq16(cube)
+    assert iq.shape == (6, 4, 16, 2) and iq[2, 1, 5, 0] == cube[1, 5, 2].real and iq[2, 1, 5, 1] == cube[1, 5, 2].imag
+    with pytest.raises(ValueError):
+        ingest.cube_to_iq16(cube + 0.25)
+    with pytest.raises(ValueError):
+        ingest.cube_to_iq16(cube * 1000)
+
+
 def test_native_ego_velocity_solvers_on_cpu():
     assert "ok" in _native_check("host_vel_solve_check")
 
