@@ -48,6 +48,11 @@ struct CfarArgs {
     int nseg_d, nseg_r;   // ladder: segments per row / per column
     FastDiv div_nseg_d;
     float lvl_mul[4];     // ladder: the four levels as multiples of the sampled map median
+    // maps that do not fit one CTA's shared memory: rows x cols above is one TILE (valid cells + halo), the map is full_rows x
+    // full_cols, tile (i, j) starts at min(i*tile_r, full_rows - rows), min(j*tile_c, full_cols - cols) - edge tiles move
+    // inward, so every tile has the same shape and overlapping cells are computed twice with identical results
+    int tiled, full_rows, full_cols, tile_r, tile_c, n_tr, n_tc;
+    uint8_t* mask_glob;   // tiled: full-size mask the tiles write (mask_out or scratch); cfar_compact_kernel reads it
 };
 
 // order-preserving map of all floats (negative ones included: detect() accepts signed data) onto unsigned keys
@@ -60,7 +65,7 @@ __device__ __forceinline__ float key_float(unsigned k) {
 }
 
 template <int MAXV>
-__device__ __forceinline__ void os_cells(const CfarArgs& a, const float* map, uint8_t* mask, double* noise_dst) {
+__device__ __forceinline__ void os_cells(const CfarArgs& a, const float* map, uint8_t* mask, double* noise_dst, int npitch) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int cr = a.tr + a.gr, cd = a.td + a.gd;
     const int wr = 2 * cr + 1, wd = 2 * cd + 1;
@@ -102,7 +107,7 @@ __device__ __forceinline__ void os_cells(const CfarArgs& a, const float* map, ui
             const int cell = r * a.cols + d;
             const double noise = (double)key_float(res);
             mask[cell] = ((double)map[r * a.pitch + d] > a.alpha * noise) ? 1 : 0;
-            if (noise_dst) noise_dst[cell] = noise;
+            if (noise_dst) noise_dst[r * npitch + d] = noise;
         }
     }
 }
@@ -447,10 +452,22 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
     __shared__ float ladder_lvl[9];
     __shared__ uint64_t load_bar;
     if (threadIdx.x == 0) work_n = 0;
-    const long long m = blockIdx.x;
-    const float* src = a.maps + m * n_cells;
-    double* noise_dst = a.noise_out ? a.noise_out + m * n_cells : nullptr;
-    const uint8_t* rsel = a.row_select ? a.row_select + m * a.rows : nullptr;
+    long long m = blockIdx.x;
+    int R0 = 0, C0 = 0, src_pitch = a.cols, npitch = a.cols;
+    long long map_cells = n_cells, map_rows = a.rows;
+    if (a.tiled) {
+        const int tiles = a.n_tr * a.n_tc;
+        const int t = (int)(blockIdx.x % (unsigned)tiles);
+        m = blockIdx.x / (unsigned)tiles;
+        R0 = min((t / a.n_tc) * a.tile_r, a.full_rows - a.rows);
+        C0 = min((t % a.n_tc) * a.tile_c, a.full_cols - a.cols);
+        src_pitch = npitch = a.full_cols;
+        map_cells = (long long)a.full_rows * a.full_cols;
+        map_rows = a.full_rows;
+    }
+    const float* src = a.maps + m * map_cells + (long long)R0 * src_pitch + C0;
+    double* noise_dst = a.noise_out ? a.noise_out + m * map_cells + (long long)R0 * npitch + C0 : nullptr;
+    const uint8_t* rsel = a.row_select ? a.row_select + m * map_rows + R0 : nullptr;
     CfarArgs la = a;
     la.row_select = rsel;
     // map -> shared memory.  Unpadded layout (ladder path): ONE bulk copy of the TMA engine from the 16-byte aligned address
@@ -461,7 +478,7 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
     const unsigned copy_bytes = (shift_b + (unsigned)n_cells * 4u + 15u) & ~15u;
     const bool want_counting = a.kind == RADAR_CFAR_OS && !noise_dst && a.alpha > 0.0;
     int neg = 0;
-    const bool bulk = a.pitch == a.cols && (m + 1 < (long long)gridDim.x || copy_bytes == shift_b + (unsigned)n_cells * 4u);
+    const bool bulk = !a.tiled && a.pitch == a.cols && (m + 1 < (long long)gridDim.x || copy_bytes == shift_b + (unsigned)n_cells * 4u);
     if (bulk) {
         map = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(map) + shift_b);
         if (threadIdx.x == 0) {
@@ -486,7 +503,11 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
         for (int i0 = threadIdx.x; i0 < n_cells; i0 += 6 * kCfarThreads) {
             float v[6];
 #pragma unroll
-            for (int j = 0; j < 6; ++j) { const int i = i0 + j * kCfarThreads; v[j] = i < n_cells ? __ldg(src + i) : 0.0f; }
+            for (int j = 0; j < 6; ++j) {
+                const int i = i0 + j * kCfarThreads;
+                const int y = (int)a.div_cols.div((uint32_t)i);
+                v[j] = i < n_cells ? __ldg(src + (long long)y * src_pitch + (i - y * a.cols)) : 0.0f;
+            }
 #pragma unroll
             for (int j = 0; j < 6; ++j) {
                 const int i = i0 + j * kCfarThreads;
@@ -495,7 +516,7 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
                     neg |= v[j] < 0.0f ? 1 : 0;
                     map[y * a.pitch + (i - y * a.cols)] = v[j];
                     mask[i] = 0;
-                    if (noise_dst) noise_dst[i] = 0.0;
+                    if (noise_dst && !a.tiled) noise_dst[i] = 0.0;      // tiled: the launcher cleared the whole array
                 }
             }
         }
@@ -518,9 +539,9 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
             os_count_dispatch(la, map, mask, work_cell, work_t, &work_n);
         } else if (a.kind == RADAR_CFAR_OS) {
             const int wcells = (2 * cr + 1) * (2 * cd + 1);
-            if (wcells <= 32 * 8) os_cells<8>(la, map, mask, noise_dst);
-            else if (wcells <= 32 * 16) os_cells<16>(la, map, mask, noise_dst);
-            else os_cells<32>(la, map, mask, noise_dst);
+            if (wcells <= 32 * 8) os_cells<8>(la, map, mask, noise_dst, npitch);
+            else if (wcells <= 32 * 16) os_cells<16>(la, map, mask, noise_dst, npitch);
+            else os_cells<32>(la, map, mask, noise_dst, npitch);
         } else {
             const int n_cut = nvr * nvd;
             for (int c = threadIdx.x; c < n_cut; c += blockDim.x) {
@@ -553,12 +574,23 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
                 }
                 const int cell = r * a.cols + d;
                 mask[cell] = ((double)map[r * a.pitch + d] > a.alpha * noise) ? 1 : 0;
-                if (noise_dst) noise_dst[cell] = noise;
+                if (noise_dst) noise_dst[r * npitch + d] = noise;
             }
         }
     }
     __syncthreads();
 
+    if (a.tiled) {
+        // the tile's valid cells plus the map's own edge rows / columns it touches; the ordered compaction runs afterwards
+        const int r_lo = R0 == 0 ? 0 : cr, r_hi = R0 + a.rows == a.full_rows ? a.rows : a.rows - cr;
+        const int c_lo = C0 == 0 ? 0 : cd, c_hi = C0 + a.cols == a.full_cols ? a.cols : a.cols - cd;
+        uint8_t* dst = a.mask_glob + m * map_cells + (long long)R0 * a.full_cols + C0;
+        for (int i = threadIdx.x; i < n_cells; i += blockDim.x) {
+            const int y = (int)a.div_cols.div((uint32_t)i), x = i - y * a.cols;
+            if (y >= r_lo && y < r_hi && x >= c_lo && x < c_hi) dst[(long long)y * a.full_cols + x] = mask[i];
+        }
+        return;
+    }
     if (a.mask_out) {
         uint8_t* dst = a.mask_out + m * n_cells;
         for (int i = threadIdx.x; i < n_cells; i += blockDim.x) dst[i] = mask[i];
@@ -645,6 +677,80 @@ static int resolve_params(radar_ctx* ctx, const radar_cfar_params& p, bool one_d
     return RADAR_OK;
 }
 
+// Ordered compaction of full-size masks in global memory (tiled maps): one CTA per map, every thread a contiguous run of cells.
+__global__ void __launch_bounds__(kCfarThreads) cfar_compact_kernel(const uint8_t* __restrict__ masks, long long n_cells, FastDiv div_cols,
+                                                                     int cols, int32_t* dets_out, int32_t* count_out, int max_dets) {
+    __shared__ int warp_counts[kCfarWarps];
+    const long long m = blockIdx.x;
+    const uint8_t* mask = masks + m * n_cells;
+    const long long ch = (n_cells + kCfarThreads - 1) / kCfarThreads;
+    const long long begin = (long long)threadIdx.x * ch, end = begin + ch < n_cells ? begin + ch : n_cells;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int cnt = 0;
+    for (long long i = begin; i < end; ++i) cnt += mask[i] ? 1 : 0;
+    int incl = cnt;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) warp_counts[warp] = incl;
+    __syncthreads();
+    int offset = incl - cnt, total = 0;
+    for (int w = 0; w < kCfarWarps; ++w) {
+        if (w < warp) offset += warp_counts[w];
+        total += warp_counts[w];
+    }
+    if (threadIdx.x == 0 && count_out) count_out[m] = total;
+    if (!dets_out || cnt == 0) return;
+    int32_t* dets = dets_out + m * (long long)max_dets * 2;
+    for (long long i = begin; i < end; ++i) {
+        if (!mask[i]) continue;
+        if (offset < max_dets) {
+            const int r = (int)div_cols.div((uint32_t)i);
+            dets[2 * offset] = r;
+            dets[2 * offset + 1] = (int)(i - (long long)r * cols);
+        }
+        ++offset;
+    }
+}
+
+// Per-shape launch state: everything that depends on the (tile) shape the CTA holds in shared memory.
+static size_t configure_shape(radar_ctx* ctx, const radar_cfar_params& p, bool mask_only, bool has_row_select, int rows, int cols,
+                              CfarArgs* a) {
+    a->rows = rows; a->cols = cols;
+    a->div_cols = make_fastdiv((uint32_t)cols);
+    const int nvd = cols - 2 * (a->td + a->gd);
+    a->div_vd = make_fastdiv((uint32_t)(nvd > 0 ? nvd : 1));
+    const size_t n_cells = (size_t)rows * cols;
+    const int nvr = rows - 2 * (a->tr + a->gr);
+    // level-ladder screen: OS, mask only, every packed field wide enough (5 bits of window width, 3 of guard width, 8 of window
+    // cells), at least 64 cells to sample; RADAR_B200_CFAR_LADDER=0 switches it off (tests compare the paths)
+    const int wr = 2 * (a->tr + a->gr) + 1, wd = 2 * (a->td + a->gd) + 1;
+    a->ladder = (p.kind == RADAR_CFAR_OS && mask_only && !has_row_select && a->alpha > 0.0 && ctx->cfar_ladder && nvr > 0 && nvd > 0 &&
+                 wd <= 31 && 2 * a->gd + 1 <= 7 && wr * wd <= 255 && n_cells >= 64) ? 1 : 0;
+    if (a->ladder) {
+        // expected order statistic of a Rayleigh noise window relative to the map median: sqrt(ln(1/(1-k/N)) / ln 2)
+        const double q = (double)a->k_rank / (double)a->n_train;
+        const double vk = q < 1.0 ? std::sqrt(std::log(1.0 / (1.0 - q)) / std::log(2.0)) : 2.0;
+        const double rel[4] = {0.57, 0.85, 1.28, 1.9};
+        for (int j = 0; j < 4; ++j) a->lvl_mul[j] = (float)(vk * rel[j]);
+        const int per_d = kCfarThreads / rows > 0 ? kCfarThreads / rows : 1;
+        const bool fixed = (a->tr == 8 && a->gr == 2 && a->td == 4 && a->gd == 1) || (a->tr == 5 && a->gr == 3 && a->td == 5 && a->gd == 2);
+        a->seg_d = fixed ? kLadderSeg : (nvd + per_d - 1) / per_d;   // the kernel's compile-time instantiations use kLadderSeg
+        a->nseg_d = (nvd + a->seg_d - 1) / a->seg_d;
+        a->div_nseg_d = make_fastdiv((uint32_t)a->nseg_d);
+        const int per_r = kCfarThreads / nvd > 0 ? kCfarThreads / nvd : 1;
+        a->seg_r = (nvr + per_r - 1) / per_r;
+        a->nseg_r = (nvr + a->seg_r - 1) / a->seg_r;
+    }
+    a->pitch = cols;
+    if (nvd > 0 && !a->ladder) while ((a->pitch - nvd) % 32 != 0) ++a->pitch;
+    const size_t n_work_max = (size_t)(nvr > 0 ? nvr : 0) * (size_t)(nvd > 0 ? nvd : 0);
+    return arena_bytes((size_t)rows * a->pitch + kMapSpare, 4) + arena_bytes(n_cells + 32, 1) + arena_bytes(n_work_max, 4) +
+           arena_bytes(a->ladder ? n_cells : n_work_max, 4);
+}
+
 static int launch_cfar(radar_ctx* ctx, const float* maps, int n_maps, int rows, int cols, const radar_cfar_params& p,
                        bool one_d, const uint8_t* row_select, double* noise_out, uint8_t* mask_out,
                        int32_t* dets_out, int32_t* count_out, int max_dets, cudaStream_t st) {
@@ -653,46 +759,61 @@ static int launch_cfar(radar_ctx* ctx, const float* maps, int n_maps, int rows, 
     if (n_maps <= 0) return RADAR_OK;
     CfarArgs a{};
     if (int rc = resolve_params(ctx, p, one_d, &a)) return rc;
-    a.maps = maps; a.rows = rows; a.cols = cols;
+    a.maps = maps;
     a.row_select = row_select;
     a.noise_out = noise_out; a.mask_out = mask_out; a.dets_out = dets_out; a.count_out = count_out; a.max_dets = max_dets;
-    a.div_cols = make_fastdiv((uint32_t)cols);
-    const int nvd = cols - 2 * (a.td + a.gd);
-    a.div_vd = make_fastdiv((uint32_t)(nvd > 0 ? nvd : 1));
-    const size_t n_cells = (size_t)rows * cols;
-    const int nvr = rows - 2 * (a.tr + a.gr);
-    // level-ladder screen: OS, mask only, every packed field wide enough (5 bits of window width, 3 of guard width, 8 of window
-    // cells), at least 64 cells to sample; RADAR_B200_CFAR_LADDER=0 switches it off (tests compare the paths)
-    {
-        const int wr = 2 * (a.tr + a.gr) + 1, wd = 2 * (a.td + a.gd) + 1;
-        a.ladder = (p.kind == RADAR_CFAR_OS && !noise_out && !row_select && a.alpha > 0.0 && ctx->cfar_ladder && nvr > 0 && nvd > 0 &&
-                    wd <= 31 && 2 * a.gd + 1 <= 7 && wr * wd <= 255 && n_cells >= 64) ? 1 : 0;
-        if (a.ladder) {
-            // expected order statistic of a Rayleigh noise window relative to the map median: sqrt(ln(1/(1-k/N)) / ln 2)
-            const double q = (double)a.k_rank / (double)a.n_train;
-            const double vk = q < 1.0 ? std::sqrt(std::log(1.0 / (1.0 - q)) / std::log(2.0)) : 2.0;
-            const double rel[4] = {0.57, 0.85, 1.28, 1.9};
-            for (int j = 0; j < 4; ++j) a.lvl_mul[j] = (float)(vk * rel[j]);
-            const int per_d = kCfarThreads / rows > 0 ? kCfarThreads / rows : 1;
-            const bool fixed = (a.tr == 8 && a.gr == 2 && a.td == 4 && a.gd == 1) || (a.tr == 5 && a.gr == 3 && a.td == 5 && a.gd == 2);
-            a.seg_d = fixed ? kLadderSeg : (nvd + per_d - 1) / per_d;   // the kernel's compile-time instantiations use kLadderSeg
-            a.nseg_d = (nvd + a.seg_d - 1) / a.seg_d;
-            a.div_nseg_d = make_fastdiv((uint32_t)a.nseg_d);
-            const int per_r = kCfarThreads / nvd > 0 ? kCfarThreads / nvd : 1;
-            a.seg_r = (nvr + per_r - 1) / per_r;
-            a.nseg_r = (nvr + a.seg_r - 1) / a.seg_r;
+    const size_t limit = (size_t)ctx->max_smem_optin - 1024;        // static shared memory of the kernel
+    size_t smem = configure_shape(ctx, p, noise_out == nullptr, row_select != nullptr, rows, cols, &a);
+    unsigned grid = (unsigned)n_maps;
+    if (smem > limit || ctx->cfar_tile > 0) {
+        // the map does not fit one CTA: tiles of valid cells plus halo, masks into a full-size array, compaction afterwards
+        const int cr = a.tr + a.gr, cd = a.td + a.gd;
+        int cols_t = cols, rows_t = rows;
+        if (ctx->cfar_tile > 0) {                                   // RADAR_B200_CFAR_TILE=n: tiles of n x n valid cells (tests)
+            cols_t = cols < ctx->cfar_tile + 2 * cd ? cols : ctx->cfar_tile + 2 * cd;
+            rows_t = rows < ctx->cfar_tile + 2 * cr ? rows : ctx->cfar_tile + 2 * cr;
+        } else {
+            for (;;) {
+                // the tallest tile of this width that fits; narrower tiles when not even one window row band does
+                int lo = 2 * cr + 1 < rows ? 2 * cr + 1 : rows, hi = rows;
+                if (configure_shape(ctx, p, noise_out == nullptr, row_select != nullptr, lo, cols_t, &a) <= limit) {
+                    while (lo < hi) {
+                        const int mid = (lo + hi + 1) / 2;
+                        if (configure_shape(ctx, p, noise_out == nullptr, row_select != nullptr, mid, cols_t, &a) <= limit) lo = mid; else hi = mid - 1;
+                    }
+                    rows_t = lo;
+                    break;
+                }
+                if (cols_t <= 2 * cd + 1) return set_error(ctx, RADAR_E_UNSUPPORTED, "CFAR window of %d x %d cells exceeds shared memory", 2 * cr + 1, 2 * cd + 1);
+                cols_t = (cols_t + 2 * cd + 1) / 2 > 2 * cd + 1 ? (cols_t + 2 * cd + 1) / 2 : 2 * cd + 1;
+            }
         }
+        smem = configure_shape(ctx, p, noise_out == nullptr, row_select != nullptr, rows_t, cols_t, &a);
+        if (smem > limit) return set_error(ctx, RADAR_E_UNSUPPORTED, "CFAR tile of %d x %d cells exceeds shared memory", rows_t, cols_t);
+        a.tiled = 1; a.full_rows = rows; a.full_cols = cols;
+        a.tile_r = rows_t - 2 * cr > 0 ? rows_t - 2 * cr : 1;
+        a.tile_c = cols_t - 2 * cd > 0 ? cols_t - 2 * cd : 1;
+        a.n_tr = rows_t >= rows ? 1 : (rows - 2 * cr + a.tile_r - 1) / a.tile_r;
+        a.n_tc = cols_t >= cols ? 1 : (cols - 2 * cd + a.tile_c - 1) / a.tile_c;
+        const long long blocks = (long long)n_maps * a.n_tr * a.n_tc;
+        if (blocks > 0x7fffffffLL) return set_error(ctx, RADAR_E_INVALID, "too many CFAR tiles in one call");
+        grid = (unsigned)blocks;
+        const size_t full = (size_t)rows * cols;
+        a.mask_glob = mask_out;
+        if (!a.mask_glob) {
+            if (int rc = ensure_scratch(ctx, (size_t)n_maps * full)) return rc;
+            a.mask_glob = reinterpret_cast<uint8_t*>(ctx->scratch);
+        }
+        if (noise_out) RB_CUDA_OK(ctx, cudaMemsetAsync(noise_out, 0, (size_t)n_maps * full * sizeof(double), st));
     }
-    a.pitch = cols;
-    if (nvd > 0 && !a.ladder) while ((a.pitch - nvd) % 32 != 0) ++a.pitch;
-    const size_t n_work_max = (size_t)(nvr > 0 ? nvr : 0) * (size_t)(nvd > 0 ? nvd : 0);
-    const size_t smem = arena_bytes((size_t)rows * a.pitch + kMapSpare, 4) + arena_bytes(n_cells + 32, 1) + arena_bytes(n_work_max, 4) +
-                        arena_bytes(a.ladder ? n_cells : n_work_max, 4);
-    if (smem > (size_t)ctx->max_smem_optin)
-        return set_error(ctx, RADAR_E_UNSUPPORTED, "CFAR map of %d x %d cells exceeds shared memory", rows, cols);
     RB_CUDA_OK(ctx, cudaFuncSetAttribute(cfar_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    cfar_kernel<<<(unsigned)n_maps, kCfarThreads, smem, st>>>(a);
+    cfar_kernel<<<grid, kCfarThreads, smem, st>>>(a);
     RB_CUDA_OK(ctx, cudaGetLastError());
+    if (a.tiled && (dets_out || count_out)) {
+        cfar_compact_kernel<<<(unsigned)n_maps, kCfarThreads, 0, st>>>(a.mask_glob, (long long)rows * cols, make_fastdiv((uint32_t)cols), cols,
+                                                                       dets_out, count_out, max_dets);
+        RB_CUDA_OK(ctx, cudaGetLastError());
+    }
     return RADAR_OK;
 }
 

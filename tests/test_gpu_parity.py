@@ -433,6 +433,54 @@ def test_os_cfar_ladder_equals_counting_path(torch_cuda):
                 assert np.array_equal(a["mask"][i].cpu().numpy().astype(bool), mo), (name, t2, i)
 
 
+def test_cfar_tiled_large_maps(torch_cuda):
+    """Maps beyond one CTA's shared memory run as tiles with halo + a separate ordered compaction: forced small tiles
+    (RADAR_B200_CFAR_TILE) reproduce the single-CTA results bit for bit for every detector family, and genuinely large
+    maps (300 x 200 2-D, a 50 000-cell 1-D signal) match the oracle."""
+    torch = torch_cuda
+    from oracle import radar_oracle as orc
+    from mmwave_radar_processing_b200.engine import cfar_params
+    cm = load_cfg("1843_RadVel")
+    plain = _engine_with_env(cm, "RADAR_B200_CFAR_TILE", 0)
+    rng = np.random.default_rng(5)
+    maps = torch.from_numpy(rng.exponential(1.0, (5, 61, 47)).astype(np.float32) *
+                            np.exp(rng.normal(size=(5, 61, 47)) * 1.5).astype(np.float32)).cuda()
+    sel = torch.from_numpy((rng.random((5, 61)) < 0.6).astype(np.uint8)).cuda()
+    for tile in (7, 16, 23):
+        tiled = _engine_with_env(cm, "RADAR_B200_CFAR_TILE", tile)
+        for p, kw in ((cfar_params("os", (8, 4), (2, 1), rho=0.75, alpha=2.0), {}),
+                      (cfar_params("os", (3, 2), (1, 1), rho=0.5, alpha=1.5), dict(want_noise=True)),
+                      (cfar_params("ca", (4, 4), (2, 2), pfa=1e-2), dict(want_noise=True)),
+                      (cfar_params("os", 6, 2, rho=0.75, alpha=2.0), dict(one_d=True, row_select=sel)),
+                      (cfar_params("go", 5, 1, pfa=1e-2), dict(one_d=True, want_noise=True)),
+                      (cfar_params("so", 5, 1, pfa=1e-1), dict(one_d=True, row_select=sel, want_noise=True))):
+            a = tiled.cfar(maps, p, want_mask=True, **kw)
+            b = plain.cfar(maps, p, want_mask=True, **kw)
+            assert torch.equal(a["mask"], b["mask"]) and torch.equal(a["counts"], b["counts"]), (tile, kw)
+            assert int(b["counts"].sum()) > 0
+            if kw.get("want_noise"):
+                assert torch.equal(a["noise"], b["noise"])
+            for i in range(maps.shape[0]):
+                n = int(a["counts"][i])
+                assert torch.equal(a["dets"][i, :n], b["dets"][i, :n])
+    big = rng.exponential(1.0, (2, 300, 200)).astype(np.float32)
+    big[0, 150, 100] = 60.0; big[1, 20:24, 30] = 40.0
+    x = torch.from_numpy(big).cuda()
+    for kind, kw in (("os", dict(rho=0.75, alpha=3.5)), ("ca", dict(pfa=1e-4))):
+        out = plain.cfar(x, cfar_params(kind, (8, 4), (2, 1), **kw), want_mask=True, want_noise=(kind == "ca"))
+        for i in range(2):
+            thr, noise, mo = orc.cfar_2d(big[i].astype(np.float64), kind, (8, 4), (2, 1), **kw)
+            assert np.array_equal(out["mask"][i].cpu().numpy().astype(bool), mo), (kind, i)
+            assert np.array_equal(out["dets"][i, :int(out["counts"][i])].cpu().numpy(), orc.mask_to_dets(mo))
+            if kind == "ca":
+                assert np.allclose(out["noise"][i].cpu().numpy(), noise, rtol=1e-12, atol=0)
+    sig = rng.exponential(1.0, (1, 1, 50000)).astype(np.float32)
+    sig[0, 0, 777] = 80.0
+    out = plain.cfar(torch.from_numpy(sig).cuda(), cfar_params("os", 16, 4, rho=0.75, alpha=6.0), one_d=True, want_mask=True)
+    _, _, mo = orc.cfar_1d(sig[0, 0].astype(np.float64), "os", 16, 4, rho=0.75, alpha=6.0)
+    assert np.array_equal(out["mask"][0, 0].cpu().numpy().astype(bool), mo) and mo[777]
+
+
 def test_error_paths(torch_cuda):
     torch = torch_cuda
     from mmwave_radar_processing_b200 import _native as nat
