@@ -86,18 +86,24 @@ __global__ void __launch_bounds__(C::NT, 1) rd_reg_kernel(const __grid_constant_
         }
     } else {
         // ===== phase B: range =====
-        const int col = (warp - C::NA) * 32 + lane;
+        const int wb = warp - C::NA;
+        const int cls = wb / C::NB1;                                  // output class k_BF of this warp (warp uniform)
+        const int ca = C::BF == 4 ? cls >> 1 : (C::BF == 2 ? cls : 0), odd = C::BF == 4 ? cls & 1 : 0;
+        const float sigma = ca ? -1.0f : 1.0f;
+        const int col = (wb - cls * C::NB1) * 32 + lane;
         const bool active = col < C::COLS_B;
         const int colc = active ? col : C::COLS_B - 1;
         const int g = colc / C::L, d = colc - g * C::L;
+        const long long half = (long long)ca * (C::S / 2) * C::L;    // a*S/2 rows of the output
         unsigned j = 0;
         for (unsigned item = blockIdx.x; item < n_items; item += gridDim.x, ++j) {
             const unsigned tb = j % C::NTILE, tround = j / C::NTILE;
             const unsigned frame = item / IPF, grp = item - frame * IPF;
             const int ant = (int)grp * C::G + g;
-            cf v[C::S];
+            cf v[C::SH];
             mb::wait(tile_full + tb, tround & 1);
-            rd_reg_range_load<C>(tiles + (size_t)tb * C::TILE, g, d, v);
+            if (odd) rd_reg_range_load<C, 1>(tiles + (size_t)tb * C::TILE, g, d, sigma, v);
+            else rd_reg_range_load<C, 0>(tiles + (size_t)tb * C::TILE, g, d, sigma, v);
             mb::arrive(tile_empty + tb);
             const size_t o = ((size_t)frame * C::CR + ant) * (C::S * C::L) + d;
             cf* out = (a.rd_out && active) ? a.rd_out + o : nullptr;
@@ -106,7 +112,8 @@ __global__ void __launch_bounds__(C::NT, 1) rd_reg_kernel(const __grid_constant_
                 if (a.mag_antenna < 0) mag = a.mag_out + o;
                 else if (a.mag_antenna == ant) mag = a.mag_out + (size_t)frame * (C::S * C::L) + d;
             }
-            rd_reg_range_store<C>(v, out, mag);
+            if (odd) rd_reg_range_store<C, 1>(v, out ? out + half : nullptr, out ? out - half : nullptr, mag ? mag + half : nullptr, mag ? mag - half : nullptr);
+            else rd_reg_range_store<C, 0>(v, out ? out + half : nullptr, out ? out - half : nullptr, mag ? mag + half : nullptr, mag ? mag - half : nullptr);
         }
     }
 }
@@ -157,13 +164,15 @@ int launch_range_doppler_reg(radar_ctx* ctx, const void* adc, int n_frames, int 
     if (reinterpret_cast<uintptr_t>(adc) % 16 != 0) return 1;
     const int CR = ctx->shape.chirps_per_loop * R;
     const int variant = ctx->rd_reg;
-#define RB_REG(var, s, l, cr, g, df, nstage, ntile)                                                           \
+#define RB_REG(var, s, l, cr, g, df, nstage, ntile, bf)                                                       \
     if (variant == var && S == s && L == l && CR == cr && R % g == 0)                                         \
-        return launch_reg<RdRegShape<s, l, cr, g, df, nstage, ntile>>(ctx, adc, n_frames, window_flags, rd_out, mag_out, mag_antenna, st);
-    // RB_REG(variant (RADAR_B200_RD_REG; 1 is the default), S, L, CR, G, DF, ring stages, tile buffers)
-    RB_REG(1, 63, 70, 12, 2, 1, 3, 1)      // 6843 ODS: 0.547 ms per 4096 frames (0.75 of measured HBM), 166 registers, 10 warps
-    RB_REG(2, 63, 70, 12, 2, 2, 3, 1)      //   split column: 14 warps are allocated as 16 -> 128 registers, phase B spills: 0.886
-    RB_REG(3, 63, 70, 12, 2, 2, 2, 2)      //   the same with two tile buffers: 0.976
+        return launch_reg<RdRegShape<s, l, cr, g, df, nstage, ntile, bf>>(ctx, adc, n_frames, window_flags, rd_out, mag_out, mag_antenna, st);
+    // RB_REG(variant (RADAR_B200_RD_REG; 1 is the default), S, L, CR, G, DF, ring stages, tile buffers, BF)
+    RB_REG(1, 63, 70, 12, 2, 1, 3, 1, 1)      // 6843 ODS: 0.547 ms per 4096 frames (0.75 of measured HBM), 166 registers, 10 warps
+    RB_REG(2, 63, 70, 12, 2, 2, 3, 1, 1)      //   split column: 14 warps are allocated as 16 -> 128 registers, phase B spills: 0.886
+    RB_REG(3, 63, 70, 12, 2, 2, 2, 2, 1)      //   the same with two tile buffers: 0.976
+    RB_REG(1, 100, 30, 8, 2, 1, 3, 1, 4)     // 1843_RadVel: 30-point Doppler per thread, 100-point range split 4 x 25
+    RB_REG(2, 100, 30, 8, 2, 1, 2, 2, 4)
 #undef RB_REG
     return 1;
 }

@@ -32,20 +32,66 @@ template <> struct Dft<70> : DftPfa<7, 10> {};
 template <> struct Dft<40> : DftPfa<5, 8> {};
 template <> struct Dft<35> : DftPfa<5, 7> {};
 template <> struct Dft<45> : DftPfa<5, 9> {};
+// 25 = 5 x 5 by Cooley-Tukey in registers: n = 5*n1 + n2, k = k1 + 5*k2, twiddles W25^(n2*k1) as literals
+template <> struct Dft<25> {
+    RB_HD static void run(cf* v) {
+        cf a[5][5];
+#pragma unroll
+        for (int n2 = 0; n2 < 5; ++n2) {
+#pragma unroll
+            for (int n1 = 0; n1 < 5; ++n1) a[n2][n1] = v[5 * n1 + n2];
+            Dft<5>::run(a[n2]);
+        }
+        a[1][1] = cmul(a[1][1], cmake(0.96858316112863107605f, -0.24868988716485479484f));   // W25^1
+        a[1][2] = cmul(a[1][2], cmake(0.87630668004386358394f, -0.48175367410171532345f));   // W25^2
+        a[1][3] = cmul(a[1][3], cmake(0.72896862742141155245f, -0.68454710592868861507f));   // W25^3
+        a[1][4] = cmul(a[1][4], cmake(0.53582679497899654564f, -0.84432792550201507531f));   // W25^4
+        a[2][1] = cmul(a[2][1], cmake(0.87630668004386358394f, -0.48175367410171532345f));   // W25^2
+        a[2][2] = cmul(a[2][2], cmake(0.53582679497899654564f, -0.84432792550201507531f));   // W25^4
+        a[2][3] = cmul(a[2][3], cmake(0.06279051952931352654f, -0.99802672842827155897f));   // W25^6
+        a[2][4] = cmul(a[2][4], cmake(-0.42577929156507271502f, -0.90482705246601946580f));   // W25^8
+        a[3][1] = cmul(a[3][1], cmake(0.72896862742141155245f, -0.68454710592868861507f));   // W25^3
+        a[3][2] = cmul(a[3][2], cmake(0.06279051952931352654f, -0.99802672842827155897f));   // W25^6
+        a[3][3] = cmul(a[3][3], cmake(-0.63742398974868974548f, -0.77051324277578925326f));   // W25^9
+        a[3][4] = cmul(a[3][4], cmake(-0.99211470131447776488f, -0.12533323356430453588f));   // W25^12
+        a[4][1] = cmul(a[4][1], cmake(0.53582679497899654564f, -0.84432792550201507531f));   // W25^4
+        a[4][2] = cmul(a[4][2], cmake(-0.42577929156507271502f, -0.90482705246601946580f));   // W25^8
+        a[4][3] = cmul(a[4][3], cmake(-0.99211470131447776488f, -0.12533323356430453588f));   // W25^12
+        a[4][4] = cmul(a[4][4], cmake(-0.63742398974868952344f, 0.77051324277578936428f));   // W25^16
+#pragma unroll
+        for (int k1 = 0; k1 < 5; ++k1) {
+            cf y[5] = {a[0][k1], a[1][k1], a[2][k1], a[3][k1], a[4][k1]};
+            Dft<5>::run(y);
+#pragma unroll
+            for (int k2 = 0; k2 < 5; ++k2) v[k1 + 5 * k2] = y[k2];
+        }
+    }
+};
+template <> struct Dft<50> : DftPfa<2, 25> {};
 
 // DF = 2: the Doppler column is split over two threads by the prime-factor map L = 2 * (L/2), L/2 odd: thread h transforms
 // the L/2 inputs l = (h*L/2 + 2m) mod L and X[k] = Y0[k mod L/2] + (-1)^k Y1[k mod L/2] is formed by phase B as it loads
 // (twice the A warps with half the registers and half the straight-line code each; the code of all roles then fits the
 // 32 KB instruction cache level, which the undivided version overflowed: 44 % of its phase-A cycles were no-instruction stalls).
-template <int S_, int L_, int CR_, int G_, int DF_ = 1, int NSTAGE_ = 3, int NTILE_ = 1>
+// BF = 2 or 4: the range column is split over BF threads by the prime-factor map S = BF * (S/BF), S/BF odd: thread class k_BF
+// reads all S tile values, folds them with the trivial radix-BF butterfly of ITS output class into S/BF values, transforms
+// those and stores the bins k = k_BF (mod BF) - no twiddles, BF times the B warps with 1/BF of the registers (S = 100 does
+// not fit one thread's registers at all).  The class is a = k_BF >> 1 (run time: a sign and a base pointer) and, for BF = 4,
+// ODD = k_BF & 1 (two copies of the code).
+template <int S_, int L_, int CR_, int G_, int DF_ = 1, int NSTAGE_ = 3, int NTILE_ = 1, int BF_ = 1>
 struct RdRegShape {
-    static constexpr int S = S_, L = L_, CR = CR_, G = G_, DF = DF_, NTILE = NTILE_;
+    static constexpr int S = S_, L = L_, CR = CR_, G = G_, DF = DF_, NTILE = NTILE_, BF = BF_;
+    static constexpr int SH = S / BF;                        // points per phase-B thread
+    static constexpr int E_SH = BF * pfa_inv(BF % (SH > 1 ? SH : 2), SH > 1 ? SH : 2);     // 1 (mod SH), 0 (mod BF)
+    static constexpr int E_BF = BF == 1 ? 0 : SH * pfa_inv(SH % (BF > 1 ? BF : 2), BF > 1 ? BF : 2);   // 1 (mod BF), 0 (mod SH)
+    static_assert(BF == 1 || ((BF == 2 || BF == 4) && SH % 2 == 1 && SH * BF == S), "the range split needs coprime factors");
     static constexpr int LH = L / DF;                        // points per phase-A thread
     static constexpr int HP = (LH + 1) / 2 * 2;              // tile offset between the halves (16-byte aligned)
     static constexpr int ROW = CR * S;                       // words between consecutive loops of one TX slot
     static constexpr int COLS_A = G * S, COLS_B = G * L;
     static constexpr int NA1 = (COLS_A + 31) / 32;           // phase-A warps per residue class
-    static constexpr int NA = NA1 * DF, NB = (COLS_B + 31) / 32;             // warps per role
+    static constexpr int NB1 = (COLS_B + 31) / 32;           // phase-B warps per output class
+    static constexpr int NA = NA1 * DF, NB = NB1 * BF;       // warps per role
     static constexpr int NT = 32 * (NA + NB + 1);            // + one TMA warp
     // raw ring: one stage = L rows of the item's G*S words, fetched from the 16-byte aligned address below the first word
     static constexpr int ROW_COPY = ((G * S * 4 + 12) + 15) / 16 * 16;    // bytes per bulk copy (covers any 4-byte start shift)
@@ -136,33 +182,58 @@ RB_HD void rd_reg_store_row(const cf (&v)[C::LH], cf* row, int h) {
     }
 }
 
-// ---- phase B: range transform of column (antenna g, Doppler position d) -----------------------------------------------
+// ---- phase B: range transform of column (antenna g, Doppler position d), output class (a, ODD) ------------------------------
 // DF == 2: position d holds frequency bin k = (d + L - L/2) mod L = Y0[k mod LH] + (-1)^k Y1[k mod LH]
 template <class C>
-RB_HD void rd_reg_range_load(const cf* tile, int g, int d, cf (&v)[C::S]) {
-    if (C::DF == 1) {
-        const cf* p = tile + (size_t)g * C::S * C::P + d;
+struct RdRegColumn {                      // one tile column as phase B sees it: value(s) applies the Doppler combine
+    const cf* p;
+    float sign;
+    RB_HD RdRegColumn(const cf* tile, int g, int d) {
+        if (C::DF == 1) { p = tile + (size_t)g * C::S * C::P + d; sign = 1.0f; }
+        else {
+            const int k = (d + C::L - C::L / 2) % C::L;
+            sign = (k & 1) ? -1.0f : 1.0f;
+            p = tile + (size_t)g * C::S * C::P + k % C::LH;
+        }
+    }
+    RB_HD cf value(int s) const { return C::DF == 1 ? p[s * C::P] : cfma(sign, p[s * C::P + C::HP], p[s * C::P]); }
+};
+// sigma = +1 for a = 0, -1 for a = 1.  Input m of class k_BF: sum_q x[(SH*q + BF*m) mod S] * W_BF^(q*k_BF)
+template <class C, int ODD>
+RB_HD void rd_reg_range_load(const cf* tile, int g, int d, float sigma, cf (&v)[C::SH]) {
+    const RdRegColumn<C> col(tile, g, d);
 #pragma unroll
-        for (int s = 0; s < C::S; ++s) v[s] = p[s * C::P];
-    } else {
-        const int k = (d + C::L - C::L / 2) % C::L;
-        const float sign = (k & 1) ? -1.0f : 1.0f;
-        const cf* p = tile + (size_t)g * C::S * C::P + k % C::LH;
-#pragma unroll
-        for (int s = 0; s < C::S; ++s) v[s] = cfma(sign, p[s * C::P + C::HP], p[s * C::P]);
+    for (int m = 0; m < C::SH; ++m) {
+        if (C::BF == 1) v[m] = col.value(m);
+        else if (C::BF == 2) v[m] = cfma(sigma, col.value((C::SH + 2 * m) % C::S), col.value((2 * m) % C::S));
+        else {
+            const cf x0 = col.value((4 * m) % C::S), x1 = col.value((C::SH + 4 * m) % C::S);
+            const cf x2 = col.value((2 * C::SH + 4 * m) % C::S), x3 = col.value((3 * C::SH + 4 * m) % C::S);
+            // k_4 = 0, 2: (x0 + x2) +- (x1 + x3);  k_4 = 1, 3: (x0 - x2) -+ i (x1 - x3)
+            if (ODD == 0) v[m] = cfma(sigma, cadd(x1, x3), cadd(x0, x2));
+            else v[m] = cfma(sigma, csub_mi(x1, x3), csub(x0, x2));
+        }
     }
 }
-// out: &rd_out[frame][v0 + g][0][d] (or null), mag: &mag_out[..][0][d] (or null)
-template <class C>
-RB_HD void rd_reg_range_store(cf (&v)[C::S], cf* out, float* mag) {
-    Dft<C::S>::run(v);
-    if (out) {
+// Output kh of the class is bin k = (a*S/2 + ODD*E_BF + E_SH*kh) mod S: r = (ODD*E_BF + E_SH*kh) mod S is a compile-time
+// constant and the a*S/2 term with its wrap is folded into two base pointers (lo = base + a*S/2 rows for r < S/2, hi = base
+// - a*S/2 rows for r >= S/2; a = 0: both are the base).  out_*: &rd_out[frame][ant][0][d] +- a*(S/2)*L (or null); mag likewise.
+template <class C, int ODD>
+RB_HD void rd_reg_range_store(cf (&v)[C::SH], cf* out_lo, cf* out_hi, float* mag_lo, float* mag_hi) {
+    Dft<C::SH>::run(v);
+    if (out_lo) {
 #pragma unroll
-        for (int k = 0; k < C::S; ++k) out[k * C::L] = v[k];
+        for (int kh = 0; kh < C::SH; ++kh) {
+            const int r = (ODD * C::E_BF + C::E_SH * kh) % C::S;
+            (C::BF > 1 && r >= C::S / 2 ? out_hi : out_lo)[r * C::L] = v[kh];
+        }
     }
-    if (mag) {
+    if (mag_lo) {
 #pragma unroll
-        for (int k = 0; k < C::S; ++k) mag[k * C::L] = rd_reg_sqrt(v[k].x * v[k].x + v[k].y * v[k].y);
+        for (int kh = 0; kh < C::SH; ++kh) {
+            const int r = (ODD * C::E_BF + C::E_SH * kh) % C::S;
+            (C::BF > 1 && r >= C::S / 2 ? mag_hi : mag_lo)[r * C::L] = rd_reg_sqrt(v[kh].x * v[kh].x + v[kh].y * v[kh].y);
+        }
     }
 }
 

@@ -46,12 +46,22 @@ static double check(int n_frames) {
                 rd_reg_doppler_finish<C>(a.winS[col % S], v);
                 rd_reg_store_row<C>(v, tile.data() + (size_t)col * C::P, h);
             }
-        for (int col = 0; col < C::COLS_B; ++col) {
-            const int g = col / L, d = col % L, ant = grp * C::G + g;
-            cf v[S];
-            rd_reg_range_load<C>(tile.data(), g, d, v);
-            rd_reg_range_store<C>(v, rd.data() + (((size_t)frame * V + ant) * S) * L + d, ant == 0 ? mag.data() + (size_t)frame * S * L + d : nullptr);
-        }
+        for (int cls = 0; cls < C::BF; ++cls)
+            for (int col = 0; col < C::COLS_B; ++col) {
+                const int g = col / L, d = col % L, ant = grp * C::G + g;
+                const int ca = C::BF == 4 ? cls >> 1 : (C::BF == 2 ? cls : 0), odd = C::BF == 4 ? cls & 1 : 0;
+                const long long half = (long long)ca * (S / 2) * L;
+                cf* out = rd.data() + (((size_t)frame * V + ant) * S) * L + d;
+                float* mg = ant == 0 ? mag.data() + (size_t)frame * S * L + d : nullptr;
+                cf v[C::SH];
+                if (odd) {
+                    rd_reg_range_load<C, 1>(tile.data(), g, d, ca ? -1.0f : 1.0f, v);
+                    rd_reg_range_store<C, 1>(v, out + half, out - half, mg ? mg + half : nullptr, mg ? mg - half : nullptr);
+                } else {
+                    rd_reg_range_load<C, 0>(tile.data(), g, d, ca ? -1.0f : 1.0f, v);
+                    rd_reg_range_store<C, 0>(v, out + half, out - half, mg ? mg + half : nullptr, mg ? mg - half : nullptr);
+                }
+            }
     }
     // direct fp64 transform of (frame 0 .. n_frames-1, a few antennas)
     double worst = 0.0;
@@ -94,6 +104,7 @@ int main() {
     double worst = 0.0, r;
     r = check<RdRegShape<63, 70, 12, 2, 1, 3, 1>>(2); printf("63x70 G=2 DF=1: rel_l2 = %.3e\n", r); worst = fmax(worst, r);
     r = check<RdRegShape<63, 70, 12, 2, 2, 3, 1>>(2); printf("63x70 G=2 DF=2: rel_l2 = %.3e\n", r); worst = fmax(worst, r);
+    r = check<RdRegShape<100, 30, 8, 2, 1, 3, 1, 4>>(2); printf("100x30 G=2 BF=4: rel_l2 = %.3e\n", r); worst = fmax(worst, r);
     printf("worst rel_l2 = %.3e\n", worst);
     return worst < 2e-6 ? 0 : 1;
 }
