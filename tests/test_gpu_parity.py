@@ -10,7 +10,7 @@ import os
 import numpy as np
 import pytest
 
-from conftest import (CFAR1D_SETS, CFAR2D_SETS, GOLDEN_CASES, GROUND_VEL, SEQ_PARAMS, ant_sets, frame_iq, golden,
+from conftest import (CFAR1D_SETS, CFAR2D_SETS, GOLDEN_CASES, GOLDEN_DIR, GROUND_VEL, SEQ_PARAMS, ant_sets, frame_iq, golden,
                       load_cfg, rel_l2)
 
 pytestmark = pytest.mark.gpu
@@ -262,6 +262,29 @@ def test_range_angle(torch_cuda, name, seed):
         assert rel_l2(eng.range_angle(dev, 0, sets["ra"], a)[0].cpu().numpy(), g[f"ra_{a}_sub"]) < RD_TOL
         assert rel_l2(eng.range_angle(dev, 2, None, a)[0].cpu().numpy(), g[f"ra_{a}_all_c2"]) < RD_TOL
     assert rel_l2(eng.range_angle(dev, 1, sets["ra"], 64, windowing=False)[0].cpu().numpy(), g["ra_64_nowin"]) < RD_TOL
+
+
+@pytest.mark.parametrize("name", ["RadarHD", "RadCloud"])
+def test_range_angle_1024_bins(torch_cuda, name):
+    """BASELINE.json configs[2] (RadarHD / RadCloud high-resolution heat maps, 2 MB fp32 per RadarHD frame): 1024 angle bins
+    against the reference's RangeAngleProcessor goldens - stored rows and the row sums of all rows to 1e-4, argmax of every clear stored row."""
+    torch = torch_cuda
+    cm = load_cfg(name)
+    g = np.load(os.path.join(GOLDEN_DIR, f"ra1024_{name}.npz"))
+    eng = _engine(cm)
+    seeds = (0, 1) if name == "RadarHD" else (0,)
+    iq = torch.from_numpy(np.stack([frame_iq(cm, s) for s in seeds])).cuda()
+    for tag, chirp, ants in (("all", 0, None), ("sub_c1", 1, [0, 1, 3])):
+        ra = eng.range_angle(iq, chirp, ants, 1024).cpu().numpy().astype(np.float64)
+        for i, seed in enumerate(seeds):
+            key = f"s{seed}_{tag}"
+            assert tuple(g[key + "_shape"]) == ra[i].shape
+            assert rel_l2(ra[i][::8], g[key + "_rows"]) < RD_TOL
+            assert rel_l2(ra[i].sum(axis=1), g[key + "_rowsum"]) < RD_TOL           # pins the rows that are not stored
+            rows = g[key + "_rows"].astype(np.float64)
+            top2 = np.partition(rows, -2, axis=1)[:, -2:]
+            clear = (top2[:, 1] - top2[:, 0]) > 1e-4 * top2[:, 1]
+            assert np.array_equal(ra[i][::8].argmax(axis=1)[clear], g[key + "_argmax"][::8][clear])
 
 
 @pytest.mark.parametrize("name", ["RadSAR_1843_official", "6843_RadVel_ods_20Hz"])

@@ -104,6 +104,28 @@ def test_range_angle(name, seed):
     assert rel_l2(orc.range_angle(cube, 64, 1, sets["ra"], perform_windowing=False), g["ra_64_nowin"]) < 1e-13
 
 
+RA_HIRES = {"RadarHD": (0, 1), "RadCloud": (0,)}
+
+
+@pytest.mark.parametrize("name", sorted(RA_HIRES))
+def test_range_angle_1024_bins(name):
+    """BASELINE.json configs[2]: zero-padded range-azimuth maps with 1024 angle bins against the reference's
+    RangeAngleProcessor (tests/golden/make_golden_ra_hires.py): stored rows, fp64 row sums and argmax of every row."""
+    cm = load_cfg(name)
+    g = np.load(os.path.join(GOLDEN_DIR, f"ra1024_{name}.npz"))
+    for seed in RA_HIRES[name]:
+        cube = orc.virtual_array(orc.iq_to_cube(frame_iq(cm, seed)), cm.num_rx_antennas, cm.chirp_cfgs_per_loop, cm.frameCfg_loops)
+        for tag, chirp, ants in (("all", 0, ()), ("sub_c1", 1, (0, 1, 3))):
+            ra = orc.range_angle(cube, 1024, chirp, ants)
+            key = f"s{seed}_{tag}"
+            assert tuple(g[key + "_shape"]) == ra.shape
+            assert rel_l2(ra[::8], g[key + "_rows"]) < 1e-6            # rows are stored as float32
+            assert np.allclose(ra.sum(axis=1), g[key + "_rowsum"], rtol=1e-12)
+            top2 = np.partition(ra, -2, axis=1)[:, -2:]
+            clear = (top2[:, 1] - top2[:, 0]) > 1e-9 * top2[:, 1]        # a single live antenna gives a flat row: no argmax to pin
+            assert np.array_equal(ra.argmax(axis=1)[clear], g[key + "_argmax"][clear])
+
+
 @pytest.mark.parametrize("name", ["RadSAR_1843_official", "6843_RadVel_ods_20Hz"])
 def test_dbs(name):
     cm = load_cfg(name)
