@@ -155,6 +155,7 @@ int radar_ctx_create(const radar_shape* shape, int device, radar_ctx** out_ctx) 
     { const char* sv = std::getenv("RADAR_B200_STREAM_VARIANT"); ctx->stream_variant = sv ? std::atoi(sv) : 0; }
     { const char* sv = std::getenv("RADAR_B200_RA_FC"); ctx->ra_fc = sv ? std::atoi(sv) : 0; }
     { const char* sv = std::getenv("RADAR_B200_PC"); ctx->pc_mode = sv ? std::atoi(sv) : 0; }
+    { const char* sv = std::getenv("RADAR_B200_CFAR_BOX"); ctx->cfar_box = sv ? std::atoi(sv) : 1; }
     { const char* sv = std::getenv("RADAR_B200_CFAR_TILE"); ctx->cfar_tile = sv ? std::atoi(sv) : 0; }
     { const char* sv = std::getenv("RADAR_B200_CFAR_LADDER"); ctx->cfar_ladder = sv ? std::atoi(sv) : 1; }
     { const char* sv = std::getenv("RADAR_B200_CFAR_PH1"); ctx->cfar_ph1 = sv ? std::atoi(sv) : -1; }

@@ -43,6 +43,7 @@ struct CfarArgs {
                           // across valid rows, read consecutive banks (>= cols)
     FastDiv div_cols, div_vd, div_wd;
     int ph1_extra;        // OS counting path: full rows counted before the first decision, beyond the minimum that can reject
+    int ca_box;           // CA: separable sliding box sums (ca_box_cells) instead of one window walk per cell
     int ladder;           // OS mask-only path: 1 = level-ladder screen (os_ladder_cells) before the exact count
     int seg_d, seg_r;     // ladder: cells per sliding segment along Doppler / range
     int nseg_d, nseg_r;   // ladder: segments per row / per column
@@ -428,6 +429,73 @@ __device__ __forceinline__ void os_ladder_cells(const CfarArgs& a, const float* 
     }
 }
 
+
+// ---- CA-CFAR by separable sliding box sums in fp64 ---------------------------------------------------------------------
+// (reference: detectors/ca_cfar.py:85-155 - mean of the training cells = (window sum - guard-block sum) / N.)
+// Pass 1: H[r][d] = sum of the window's columns d-cd .. d+cd of row r, one thread per (row, Doppler segment), sliding.
+// Pass 2: one thread per (Doppler bin, range segment): W = sum of H over the window's rows, G = sum of the guard block
+// (its row sums formed on the fly from 2*gd+1 map cells), both sliding.  Every add is an error-free TwoSum with the
+// round-off carried along, so a strong cell that leaves the window takes its rounding error with it: the sums are the
+// correctly rounded window sums whatever the dynamic range (sums of <= 255 floats are exact in double anyway while the
+// window spans < 2^21).  ~45 instructions per cell instead of 3 per window cell (153 cells for the 4,4 / 2,2 detector).
+struct DD { double s, c; };
+__device__ __forceinline__ void dd_add(DD& a, double b) {
+    const double t = a.s + b, bb = t - a.s;
+    a.c += (a.s - (t - bb)) + (b - bb);
+    a.s = t;
+}
+__device__ __forceinline__ void ca_box_cells(const CfarArgs& a, const float* map, uint8_t* mask, double* hsum, double* noise_dst,
+                                              int npitch, const uint8_t* rsel) {
+    const int cr = a.tr + a.gr, cd = a.td + a.gd;
+    const int nvr = a.rows - 2 * cr, nvd = a.cols - 2 * cd;
+    {
+        const int nseg = a.nseg_d;
+        for (int t = threadIdx.x; t < a.rows * nseg; t += blockDim.x) {
+            const int r = (int)a.div_nseg_d.div((uint32_t)t), sg = t - r * nseg;
+            const int d0 = cd + sg * a.seg_d, d1 = min(d0 + a.seg_d, a.cols - cd);
+            const float* mr = map + r * a.pitch;
+            double* out = hsum + r * a.cols;
+            DD h{0.0, 0.0};
+            for (int x = d0 - cd; x <= d0 + cd; ++x) dd_add(h, (double)mr[x]);
+            out[d0] = h.s + h.c;
+            for (int d = d0 + 1; d < d1; ++d) {
+                dd_add(h, (double)mr[d + cd]);
+                dd_add(h, -(double)mr[d - cd - 1]);
+                out[d] = h.s + h.c;
+            }
+        }
+    }
+    __syncthreads();
+    const int nseg = a.nseg_r;
+    for (int t = threadIdx.x; t < nseg * nvd; t += blockDim.x) {
+        const int sg = (int)a.div_vd.div((uint32_t)t), vd = t - sg * nvd;
+        const int d = vd + cd;
+        const int r0 = cr + sg * a.seg_r, r1 = min(r0 + a.seg_r, a.rows - cr);
+        auto guard_row = [&](int y) {                    // sum of the guard block's cells of map row y (exact: <= 7 floats)
+            const float* p = map + y * a.pitch + d - a.gd;
+            double g = 0.0;
+            for (int x = 0; x <= 2 * a.gd; ++x) g += (double)p[x];
+            return g;
+        };
+        DD w{0.0, 0.0}, g{0.0, 0.0};
+        for (int y = r0 - cr; y <= r0 + cr; ++y) dd_add(w, hsum[y * a.cols + d]);
+        for (int y = r0 - a.gr; y <= r0 + a.gr; ++y) dd_add(g, guard_row(y));
+        for (int r = r0; r < r1; ++r) {
+            if (r > r0) {
+                dd_add(w, hsum[(r + cr) * a.cols + d]);
+                dd_add(w, -hsum[(r - cr - 1) * a.cols + d]);
+                dd_add(g, guard_row(r + a.gr));
+                dd_add(g, -guard_row(r - a.gr - 1));
+            }
+            if (rsel && !rsel[r]) continue;
+            // the reference divides the sum by N (ca_cfar.py:139-141: sum(...)/num_train_cells); same operation order here
+            const double noise = ((w.s - g.s) + (w.c - g.c)) / (double)a.n_train;
+            mask[r * a.cols + d] = ((double)map[r * a.pitch + d] > a.alpha * noise) ? 1 : 0;
+            if (noise_dst) noise_dst[r * npitch + d] = noise;
+        }
+    }
+}
+
 __device__ __forceinline__ void os_count_dispatch(const CfarArgs& a, const float* map, uint8_t* mask, int* wc, float* wt, int* wn) {
     // Doppler-axis (train, guard) of the reference's detector settings (tests/verify_processors.py:121-143,
     // gui_configs/processor_params.yaml:41-88)
@@ -447,7 +515,7 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
     uint8_t* mask = ar.take<uint8_t>(n_cells + 32);
     const int n_work_max = max(a.rows - 2 * (a.tr + a.gr), 0) * max(a.cols - 2 * (a.td + a.gd), 0);   // cells under test
     int* work_cell = ar.take<int>(n_work_max);           // OS counting path: undecided cells after phase 1
-    float* work_t = ar.take<float>(a.ladder ? n_cells : n_work_max);   // ladder: the packed sliding sums, one word per cell
+    float* work_t = ar.take<float>(a.ladder ? n_cells : (a.ca_box ? 2 * n_cells : n_work_max));   // ladder: packed sliding sums (a word per cell); CA: row sums (a double per cell)
     __shared__ int work_n;
     __shared__ float ladder_lvl[9];
     __shared__ uint64_t load_bar;
@@ -542,6 +610,8 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
             if (wcells <= 32 * 8) os_cells<8>(la, map, mask, noise_dst, npitch);
             else if (wcells <= 32 * 16) os_cells<16>(la, map, mask, noise_dst, npitch);
             else os_cells<32>(la, map, mask, noise_dst, npitch);
+        } else if (a.kind == RADAR_CFAR_CA && a.ca_box) {
+            ca_box_cells(a, map, mask, reinterpret_cast<double*>(work_t), noise_dst, npitch, rsel);
         } else {
             const int n_cut = nvr * nvd;
             for (int c = threadIdx.x; c < n_cut; c += blockDim.x) {
@@ -744,11 +814,22 @@ static size_t configure_shape(radar_ctx* ctx, const radar_cfar_params& p, bool m
         a->seg_r = (nvr + per_r - 1) / per_r;
         a->nseg_r = (nvr + a->seg_r - 1) / a->seg_r;
     }
+    // CA: separable box sums (RADAR_B200_CFAR_BOX=0: one window walk per cell, kept for comparison)
+    a->ca_box = (p.kind == RADAR_CFAR_CA && ctx->cfar_box && nvr > 0 && nvd > 0) ? 1 : 0;
+    if (a->ca_box) {
+        const int per_d = kCfarThreads / rows > 0 ? kCfarThreads / rows : 1;
+        a->seg_d = (nvd + per_d - 1) / per_d;
+        a->nseg_d = (nvd + a->seg_d - 1) / a->seg_d;
+        a->div_nseg_d = make_fastdiv((uint32_t)a->nseg_d);
+        const int per_r = kCfarThreads / nvd > 0 ? kCfarThreads / nvd : 1;
+        a->seg_r = (nvr + per_r - 1) / per_r;
+        a->nseg_r = (nvr + a->seg_r - 1) / a->seg_r;
+    }
     a->pitch = cols;
     if (nvd > 0 && !a->ladder) while ((a->pitch - nvd) % 32 != 0) ++a->pitch;
     const size_t n_work_max = (size_t)(nvr > 0 ? nvr : 0) * (size_t)(nvd > 0 ? nvd : 0);
     return arena_bytes((size_t)rows * a->pitch + kMapSpare, 4) + arena_bytes(n_cells + 32, 1) + arena_bytes(n_work_max, 4) +
-           arena_bytes(a->ladder ? n_cells : n_work_max, 4);
+           arena_bytes(a->ladder ? n_cells : (a->ca_box ? 2 * n_cells : n_work_max), 4);
 }
 
 static int launch_cfar(radar_ctx* ctx, const float* maps, int n_maps, int rows, int cols, const radar_cfar_params& p,

@@ -49,6 +49,7 @@ struct radar_ctx {
     double* point_mirrors[16] = {nullptr};       // radar_ctx_set_point_mirrors: extra destinations of every packed point row
     int n_point_mirrors = 0, point_mirror_cap = 0;
     int cfar_ph1 = -1;                            // RADAR_B200_CFAR_PH1: extra full rows of the OS-CFAR first counting phase (-1 = default)
+    int cfar_box = 1;                             // RADAR_B200_CFAR_BOX=0: CA-CFAR by one window walk per cell (comparison)
     int cfar_tile = 0;                            // RADAR_B200_CFAR_TILE=n: force n x n tiles in the CFAR kernel (tests of the large-map path)
     int cfar_ladder = 1;                          // RADAR_B200_CFAR_LADDER=0: OS-CFAR without the level-ladder screen (tests / comparison)
     int pc_mode = 0;                              // RADAR_B200_PC=1: warp-per-detection point-cloud kernel only (tests / comparison)
