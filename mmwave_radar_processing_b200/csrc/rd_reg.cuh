@@ -121,6 +121,22 @@ struct RdRegParams {
     float winS[C::S];
 };
 
+// int16 pair -> complex float on the conversion unit (two I2F.S16, the second with the .H1 selector): half the issue slots
+// of the LOP3/PRMT/LOP3/FADD2 form of iq_word and nothing on the FMA / ALU pipes, which phase A keeps busy; the conversion
+// unit is otherwise idle in this kernel (70 words per item and thread = 140 quarter-rate instructions per A warp and item)
+RB_HD cf iq_word_cvt(uint32_t w) {
+#ifdef __CUDA_ARCH__
+    short lo, hi;
+    asm("mov.b32 {%0,%1}, %2;" : "=h"(lo), "=h"(hi) : "r"(w));
+    float a, b;
+    asm("cvt.rn.f32.s16 %0, %1;" : "=f"(a) : "h"(lo));
+    asm("cvt.rn.f32.s16 %0, %1;" : "=f"(b) : "h"(hi));
+    return cmake(a, b);
+#else
+    return cmake((float)(short)(w & 0xffffu), (float)(short)(w >> 16));
+#endif
+}
+
 // sqrt to 1 ulp in one MUFU (the IEEE sqrtf costs a Newton step and a guarded slow path per cell, 20 KB of code here)
 RB_HD float rd_reg_sqrt(float x) {
 #ifdef __CUDA_ARCH__
@@ -146,7 +162,8 @@ RB_HD void rd_reg_doppler_load(const RdRegParams<C>& a, const uint32_t* raw, int
         // class 1 wraps when DF*m + LH >= L; class 0 never does (h = 0 makes lo and hi + L rows the same address)
         const bool wraps = C::DF * m + C::LH >= C::L;
         const uint32_t w = wraps ? (h ? hi : lo)[C::DF * m * C::RAW_PITCH_W] : lo[C::DF * m * C::RAW_PITCH_W];
-        const cf x = iq_word(w);
+        // the conversion unit serves one A warp per scheduler well (6843: 0.547 -> 0.519 ms); with two they queue (1843: 0.257 -> 0.262)
+        const cf x = C::NA <= 4 ? iq_word_cvt(w) : iq_word(w);
 #ifdef __CUDA_ARCH__
         pk64 r;
         asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk(x)), "l"(pk(cmake(win[m].x, win[m].y))));
