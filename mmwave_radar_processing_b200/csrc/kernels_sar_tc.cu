@@ -197,7 +197,12 @@ struct SarTcArgs {
     const double* dirs;   // [3][G]
     int npad, n_chunks, seg_chunks, G, S, SP, NB;
     int g_begin, g_end;
-    cf* beams;            // [S][g_end - g_begin]
+    cf* beams;            // [S][g_end - g_begin]; split-K: one such array per accumulation segment
+    // split-K over gridDim.y: CTA row y owns the accumulation segments [y*segs_per_split, (y+1)*segs_per_split).  With
+    // ksplit > 1 every segment is drained into ITS OWN array and sar_range_fft_kernel adds the arrays in segment order - the
+    // same fp32 additions in the same order as the in-place accumulation of ksplit == 1, so the image does not depend on
+    // how the aperture is cut over CTAs (slices of the grid, which pick another ksplit, stay bit-identical to the full grid).
+    int ksplit, segs_per_split;
 };
 
 // MT accumulator tiles (128 directions each) per CTA, TPR threads per direction row (they split the elements of a chunk and
@@ -241,6 +246,10 @@ __global__ void __launch_bounds__(128 * MT * TPR + 64, 1) sar_tc_kernel(const __
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_slot;
     const int width = a.g_end - a.g_begin;
+    // this CTA row's share of the aperture: whole accumulation segments
+    const int seg0 = blockIdx.y * a.segs_per_split;
+    const int c0 = seg0 * a.seg_chunks;
+    const int n_local = min(a.n_chunks, (seg0 + a.segs_per_split) * a.seg_chunks) - c0;
 
     if (warp == kGenWarps) {
         // ===== MMA issuer =====
@@ -248,9 +257,9 @@ __global__ void __launch_bounds__(128 * MT * TPR + 64, 1) sar_tc_kernel(const __
             // M = 128, N = NB, fp32 accumulate, TF32 x TF32, both operands K-major
             const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(a.NB >> 3) << 17) | ((128u >> 4) << 24);
             int n_seg = 0;
-            for (int c = 0; c < a.n_chunks; ++c) {
+            for (int c = 0; c < n_local; ++c) {
                 const int s = c & 1, c_seg = c % a.seg_chunks;
-                const bool seg_end = (c_seg == a.seg_chunks - 1) || (c == a.n_chunks - 1);
+                const bool seg_end = (c_seg == a.seg_chunks - 1) || (c == n_local - 1);
                 float* st = stage0 + s * stage_floats;
                 mbar_wait(&full[s], (c >> 1) & 1);
                 mbar_wait(&bfull[s], (c >> 1) & 1);
@@ -277,13 +286,13 @@ __global__ void __launch_bounds__(128 * MT * TPR + 64, 1) sar_tc_kernel(const __
         // ===== B loader: one bulk copy (hi and lo, canonical layout) per chunk =====
         if (lane == 0) {
             const uint32_t bytes = 2u * (uint32_t)b_floats * 4u;
-            for (int c = 0; c < a.n_chunks; ++c) {
+            for (int c = 0; c < n_local; ++c) {
                 const int s = c & 1;
                 if (c >= 2) mbar_wait(&empty[s], ((c >> 1) - 1) & 1);
                 const uint32_t bar = smem_u32(&bfull[s]);
                 asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
                 asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                             ::"r"(smem_u32(stage0 + s * stage_floats + MT * 2 * kTcATile)), "l"(a.bblk + (size_t)c * 2 * b_floats),
+                             ::"r"(smem_u32(stage0 + s * stage_floats + MT * 2 * kTcATile)), "l"(a.bblk + (size_t)(c0 + c) * 2 * b_floats),
                                "r"(bytes), "r"(bar) : "memory");
             }
         }
@@ -299,13 +308,14 @@ __global__ void __launch_bounds__(128 * MT * TPR + 64, 1) sar_tc_kernel(const __
         const float dh[3] = {(float)dx, (float)dy, (float)dz};
         const float dl[3] = {(float)(dx - (double)dh[0]), (float)(dy - (double)dh[1]), (float)(dz - (double)dh[2])};
         int n_drained = 0;
-        for (int c = 0; c < a.n_chunks; ++c) {
-            const int s = c & 1, c_seg = c % a.seg_chunks;
-            const bool seg_end = (c_seg == a.seg_chunks - 1) || (c == a.n_chunks - 1);
+        for (int cl = 0; cl < n_local; ++cl) {
+            const int c = c0 + cl;                                 // chunk of the aperture; cl counts this CTA's stages
+            const int s = cl & 1, c_seg = cl % a.seg_chunks;
+            const bool seg_end = (c_seg == a.seg_chunks - 1) || (cl == n_local - 1);
             float* st = stage0 + s * stage_floats;
             float* a_hi = st + mt * kTcATile;
             float* a_lo = st + MT * kTcATile + mt * kTcATile;
-            if (c >= 2) mbar_wait(&empty[s], ((c >> 1) - 1) & 1);            // the MMAs of chunk c-2 have finished reading this stage
+            if (cl >= 2) mbar_wait(&empty[s], ((cl >> 1) - 1) & 1);          // the MMAs of stage cl-2 have finished reading this stage
             const double* px = a.posl + (size_t)c * kTcElems;
             const float* pf = a.posf + (size_t)c * kTcElems;
             constexpr int W = kTcElems / TPR;                      // elements of a chunk this thread generates
@@ -415,9 +425,10 @@ __global__ void __launch_bounds__(128 * MT * TPR + 64, 1) sar_tc_kernel(const __
                     tmem_ld16(taddr + a.SP + s0, im);
                     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                     if (g_out < width) {
-                        cf* dst = a.beams + (size_t)s0 * width + g_out;
+                        // ksplit > 1: this segment's own array, plain stores; ksplit == 1: accumulate in place
+                        cf* dst = a.beams + (a.ksplit > 1 ? (size_t)(seg0 + n_drained) * a.S * width : (size_t)0) + (size_t)s0 * width + g_out;
                         cf old[16];
-                        if (n_drained > 0) {                               // all loads in flight before the first store
+                        if (n_drained > 0 && a.ksplit == 1) {              // all loads in flight before the first store
 #pragma unroll
                             for (int i = 0; i < 16; ++i)
                                 old[i] = (s0 + i < a.S) ? __ldcg(dst + (size_t)i * width) : cmake(0.f, 0.f);
@@ -445,7 +456,8 @@ __global__ void __launch_bounds__(128 * MT * TPR + 64, 1) sar_tc_kernel(const __
 
 // ---- Hann + range FFT of every beam -----------------------------------------------------------------------------
 struct SarFftArgs {
-    const cf* beams;      // [S][width]
+    const cf* beams;      // [n_part][S][width]: per-segment arrays (split-K) or one accumulated array
+    int n_part;
     int S, width;
     const float* winS; const cf* twS; const uint16_t* posS;
     cf* out;              // [S][width]
@@ -469,7 +481,15 @@ __global__ void __launch_bounds__(256) sar_range_fft_kernel(const __grid_constan
     const int cells = S * kTcFftDirs;
     for (int i = threadIdx.x; i < cells; i += blockDim.x) {
         const int s = i / kTcFftDirs, gl = i - s * kTcFftDirs;
-        const cf v = (g0 + gl < a.width) ? a.beams[(size_t)s * a.width + g0 + gl] : cmake(0.f, 0.f);
+        cf v = cmake(0.f, 0.f);
+        if (g0 + gl < a.width) {
+            const cf* src = a.beams + (size_t)s * a.width + g0 + gl;
+            v = src[0];
+            for (int k = 1; k < a.n_part; ++k) {               // segment order, the additions of the in-place accumulation
+                const cf u = src[(size_t)k * a.S * a.width];
+                v = cmake(u.x + v.x, u.y + v.y);
+            }
+        }
         tile[s * Gp + gl] = cscale(v, win[s]);
     }
     __syncthreads();
@@ -487,10 +507,38 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
     if (NB > 256 || (NB & 15) != 0) return 1;                   // tcgen05.mma with M = 128 takes N in 16..256, multiples of 16
     const int width = g_end - g_begin;
     const int n_chunks = (N + kTcElems - 1) / kTcElems, npad = n_chunks * kTcElems;
+    // segment length: measured bias 1.3e-8 * sqrt(N * len) relative; keep it near 1e-5
+    int seg_chunks = (int)(6.0e5 / (double)N) / kTcElems;
+    seg_chunks = seg_chunks < 4 ? 4 : (seg_chunks > n_chunks ? n_chunks : seg_chunks);
+    if (ctx->sar_seg_chunks > 0) seg_chunks = ctx->sar_seg_chunks;
+    const int n_seg = (n_chunks + seg_chunks - 1) / seg_chunks;
+    auto smem_for = [&](int tiles) {
+        const size_t stage_floats = (size_t)tiles * 2 * kTcATile + 2 * (size_t)NB * kTcKC;
+        return 2 * stage_floats * sizeof(float) + 8 * sizeof(uint64_t) + 16;
+    };
+    // two accumulator tiles per CTA (a B chunk serves 256 directions) once every SM has work anyway and the stages fit
+    int mt = (width > 128 * ctx->sm_count && smem_for(2) <= (size_t)ctx->max_smem_optin) ? 2 : 1;
+    if (ctx->sar_mode == 2) mt = 1;
+    if (ctx->sar_mode == 3 && smem_for(2) <= (size_t)ctx->max_smem_optin) mt = 2;
+    const size_t smem = smem_for(mt);
+    if (smem > (size_t)ctx->max_smem_optin) return 1;
+    const int per_cta = 128 * mt;
+    const unsigned grid = (unsigned)((width + per_cta - 1) / per_cta);
+    // split-K: every CTA walks its share of the aperture one chunk at a time (~1.2 us per chunk, whatever the number of
+    // directions), so a grid that leaves SMs empty - a voxel slice of a multi-GPU run - is cut along the aperture too, in
+    // whole accumulation segments (see SarTcArgs: the image does not depend on the cut).  RADAR_B200_SAR_KSPLIT forces it.
+    int want_split = (int)(ctx->sm_count / (grid > 0 ? grid : 1));
+    if (ctx->sar_ksplit > 0) want_split = ctx->sar_ksplit;
+    if (want_split > n_seg) want_split = n_seg;
+    if (want_split < 1) want_split = 1;
+    const int segs_per_split = (n_seg + want_split - 1) / want_split;
+    const int ksplit = (n_seg + segs_per_split - 1) / segs_per_split;
+    const int n_part = ksplit > 1 ? n_seg : 1;
+
     const size_t bblk_bytes = (size_t)n_chunks * 2 * NB * kTcKC * sizeof(float);
     const size_t posl_bytes = (size_t)3 * npad * sizeof(double);
     const size_t posf_bytes = (size_t)6 * npad * sizeof(float);
-    const size_t beams_bytes = (size_t)S * width * sizeof(cf);
+    const size_t beams_bytes = (size_t)n_part * S * width * sizeof(cf);
     const size_t step_bytes = (size_t)6 * n_chunks * sizeof(float), lin_bytes = (size_t)n_chunks;
     auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
     if (int rc = ensure_scratch(ctx, up(bblk_bytes) + up(posl_bytes) + up(posf_bytes) + up(beams_bytes) + up(step_bytes) + up(lin_bytes))) return rc;
@@ -506,29 +554,14 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
     sar_tc_prep_kernel<<<n_chunks, 256, 0, st>>>(p);
     RB_CUDA_OK(ctx, cudaGetLastError());
 
-    // segment length: measured bias 1.3e-8 * sqrt(N * len) relative; keep it near 1e-5
-    int seg_chunks = (int)(6.0e5 / (double)N) / kTcElems;
-    seg_chunks = seg_chunks < 4 ? 4 : (seg_chunks > n_chunks ? n_chunks : seg_chunks);
-    if (ctx->sar_seg_chunks > 0) seg_chunks = ctx->sar_seg_chunks;
-    SarTcArgs a{bblk, posl, posf, stepf, (ctx->sar_dbg & 32) ? nullptr : lin, dirs, npad, n_chunks, seg_chunks, G, S, SP, NB, g_begin, g_end, beams};
-    auto smem_for = [&](int tiles) {
-        const size_t stage_floats = (size_t)tiles * 2 * kTcATile + 2 * (size_t)NB * kTcKC;
-        return 2 * stage_floats * sizeof(float) + 8 * sizeof(uint64_t) + 16;
-    };
-    // two accumulator tiles per CTA (a B chunk serves 256 directions) once every SM has work anyway and the stages fit
-    int mt = (width > 128 * ctx->sm_count && smem_for(2) <= (size_t)ctx->max_smem_optin) ? 2 : 1;
-    if (ctx->sar_mode == 2) mt = 1;
-    if (ctx->sar_mode == 3 && smem_for(2) <= (size_t)ctx->max_smem_optin) mt = 2;
-    const size_t smem = smem_for(mt);
-    if (smem > (size_t)ctx->max_smem_optin) return 1;
-    const int per_cta = 128 * mt;
-    const unsigned grid = (unsigned)((width + per_cta - 1) / per_cta);
+    SarTcArgs a{bblk, posl, posf, stepf, (ctx->sar_dbg & 32) ? nullptr : lin, dirs, npad, n_chunks, seg_chunks, G, S, SP, NB, g_begin, g_end, beams,
+                ksplit, segs_per_split};
     const int tpr = ctx->sar_tpr > 0 ? ctx->sar_tpr : (mt == 2 ? 1 : 2);      // measured: 0.443 / 0.450 ms (2 tiles), 0.550 / 0.503 ms (1 tile)
     const int unr = ctx->sar_dbg & 15, cs = !(ctx->sar_dbg & 16);      // RADAR_B200_SAR_DBG: unroll of the element loop (0 = default), +16 = sincospif
 #define RB_SAR_TC_LAUNCH(MT_, TPR_, UNR_, CS_)                                                                               \
     do {                                                                                                                     \
         RB_CUDA_OK(ctx, cudaFuncSetAttribute(sar_tc_kernel<MT_, TPR_, UNR_, CS_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-        sar_tc_kernel<MT_, TPR_, UNR_, CS_><<<grid, 128 * MT_ * TPR_ + 64, smem, st>>>(a);                                   \
+        sar_tc_kernel<MT_, TPR_, UNR_, CS_><<<dim3(grid, (unsigned)ksplit), 128 * MT_ * TPR_ + 64, smem, st>>>(a);                                   \
     } while (0)
 #define RB_SAR_TC_VARIANTS(MT_, TPR_)                                                                                        \
     do {                                                                                                                     \
@@ -543,7 +576,7 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
 #undef RB_SAR_TC_LAUNCH
     RB_CUDA_OK(ctx, cudaGetLastError());
 
-    SarFftArgs f{beams, S, width, ctx->fftS.hann, ctx->fftS.tw, ctx->fftS.pos, out, ctx->fftS.plan, make_fastdiv(kTcFftDirs)};
+    SarFftArgs f{beams, n_part, S, width, ctx->fftS.hann, ctx->fftS.tw, ctx->fftS.pos, out, ctx->fftS.plan, make_fastdiv(kTcFftDirs)};
     const size_t fsmem = arena_bytes((size_t)S * (kTcFftDirs | 1), sizeof(cf)) + arena_bytes(S, sizeof(cf)) + arena_bytes(S, 4) + arena_bytes(S, 2);
     RB_CUDA_OK(ctx, cudaFuncSetAttribute(sar_range_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
     sar_range_fft_kernel<<<(unsigned)((width + kTcFftDirs - 1) / kTcFftDirs), 256, fsmem, st>>>(f);

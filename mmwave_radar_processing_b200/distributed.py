@@ -124,21 +124,29 @@ def sar_image_sharded(compute_slice: Callable[[torch.Tensor, torch.Tensor, torch
     tile = compute_slice(aperture, positions, dirs, lo, hi)
     if not gather or w == 1:
         return tile, (lo, hi)
+    # Tiles travel as they are, [S][width] row-major into slot `rank` of a [world][S][widest] buffer (no transposes; ragged
+    # shards are padded on the right), then ONE strided copy lays the slots side by side as the [S][G] image.
     s = tile.shape[0]
     widest = shard_range(g, 0, w)[1]
-    pad = torch.zeros((widest, s), dtype=tile.dtype, device=tile.device)
-    pad[:hi - lo] = tile.transpose(0, 1)
-    allt = torch.empty((w, widest, s), dtype=tile.dtype, device=tile.device)
+    if hi - lo == widest and tile.is_contiguous():
+        mine = tile
+    else:
+        mine = torch.zeros((s, widest), dtype=tile.dtype, device=tile.device)
+        mine[:, :hi - lo] = tile
+    allt = torch.empty((w, s, widest), dtype=tile.dtype, device=tile.device)
     # complex tensors travel as their real view (NCCL / gloo have no complex all-gather)
     if tile.is_complex():
-        dist.all_gather_into_tensor(torch.view_as_real(allt).view(-1), torch.view_as_real(pad).reshape(-1))
+        dist.all_gather_into_tensor(torch.view_as_real(allt).view(-1), torch.view_as_real(mine).reshape(-1))
     else:
-        dist.all_gather_into_tensor(allt.view(-1), pad.view(-1))
-    cols = []
-    for r in range(w):
-        rlo, rhi = shard_range(g, r, w)
-        cols.append(allt[r, :rhi - rlo])
-    return torch.cat(cols, dim=0).transpose(0, 1).contiguous(), (lo, hi)
+        dist.all_gather_into_tensor(allt.view(-1), mine.reshape(-1))
+    if g == w * widest:
+        image = allt.permute(1, 0, 2).reshape(s, g)            # one copy: [S][world][width] -> [S][G]
+    else:
+        image = torch.empty((s, g), dtype=tile.dtype, device=tile.device)
+        for r in range(w):
+            rlo, rhi = shard_range(g, r, w)
+            image[:, rlo:rhi] = allt[r, :, :rhi - rlo]
+    return image, (lo, hi)
 
 
 class PeerPointExchange:

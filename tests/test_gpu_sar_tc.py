@@ -124,3 +124,28 @@ def test_equispaced_chunks_step_the_phase(torch_cuda, s, frames, per_frame, g):
     assert rel_l2(step2, general) < 5e-6, rel_l2(step2, general)
     np.testing.assert_array_equal(step2, step3)
     assert not np.array_equal(step2, general)                # the stepping path really ran
+
+
+def test_split_k_does_not_change_a_bit(torch_cuda):
+    """The aperture cut over CTA rows (split-K, chosen from the grid size so that voxel slices of a multi-GPU run fill the
+    SMs): every accumulation segment is drained into its own array and summed in segment order, so any cut - and the
+    in-place accumulation of ksplit = 1 - gives the same image bit for bit; a slice equals the full grid's columns."""
+    torch = torch_cuda
+    from mmwave_radar_processing_b200.engine import RadarEngine
+    s, n, g = 90, 2000, 700
+    x, pos, dirs, lam = sar_case(s, n, g, seed=11)
+    xs, ps, ds = torch.from_numpy(x).cuda(), torch.from_numpy(pos).cuda(), torch.from_numpy(dirs).cuda()
+    outs = {}
+    for ks in (1, 2, 3, 7, 0):
+        os.environ["RADAR_B200_SAR_KSPLIT"] = str(ks)
+        try:
+            eng = RadarEngine(1, s, 1, 1)
+        finally:
+            del os.environ["RADAR_B200_SAR_KSPLIT"]
+        outs[ks] = eng.sar_image(xs, ps, ds, lam).cpu().numpy()
+        if ks == 0:
+            part = eng.sar_image(xs, ps, ds, lam, 100, 333).cpu().numpy()
+            np.testing.assert_array_equal(part, outs[0][:, 100:333])
+    for ks in (2, 3, 7, 0):
+        np.testing.assert_array_equal(outs[ks], outs[1])
+    assert rel_l2(outs[1][:, :64], sar_direct(x, pos, dirs, lam, np.arange(64))) < TOL
