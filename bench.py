@@ -266,7 +266,7 @@ def workload_config(cm, wl, frames_per_gpu, global_frames, n_gpus, exchange="cop
             "l2_policy": "per-step working set (int16 in + complex RD out) exceeds the 126 MB L2; no explicit flush"}
 
 
-def stage_rooflines(cm, wl, F, stage_ms, ms_per_step, points, peak):
+def stage_rooflines(cm, wl, F, stage_ms, ms_per_step, points, peak, rd_kernel="rd_reg_kernel"):
     """Algorithmic bytes per frame (DESIGN.md section 4 / SURVEY.md section 8d) and achieved fraction of the HBM peak for
     every stage kernel of one step."""
     R, S, cpl, L = cm.num_rx_antennas, cm.get_num_adc_samples(0), cm.chirp_cfgs_per_loop, cm.frameCfg_loops
@@ -279,7 +279,7 @@ def stage_rooflines(cm, wl, F, stage_ms, ms_per_step, points, peak):
         "cfar": 4 * S * L + 8 * ppf + 4,
         "point_cloud": (8 * (len(az) + len(el)) + 8 + 32) * ppf,
     }
-    names = {"range_doppler": "rd_stream_kernel", "range_angle": "range_angle_kernel", "cfar": "cfar_kernel",
+    names = {"range_doppler": rd_kernel, "range_angle": "range_angle_kernel", "cfar": "cfar_kernel",
              "point_cloud": "point_cloud_thread_kernel"}
     out = []
     for st, ms in stage_ms.items():
@@ -336,7 +336,7 @@ def extra_single_gpu_lines(torch, dev, peak):
         steps = 50
         ms_total, stage_ms, out = time_stage_loop(torch, pipe, iq_dev, steps, 5)
         pts = int(out["offsets"][F].item())
-        kernels, bytes_pf, step_bytes = stage_rooflines(cm, wl, F, stage_ms, ms_total / steps, pts, peak)
+        kernels, bytes_pf, step_bytes = stage_rooflines(cm, wl, F, stage_ms, ms_total / steps, pts, peak, pipe.engine.last_rd_kernel())
         if det_name == "ca_cfar_2d":
             extras.append({"workload": f"configs/{cfg_name}.cfg", "detector": "ca_cfar_2d num_train=(4,4) num_guard=(2,2) pfa=1e-5",
                            "frames_per_step": F, "cfar_ms_per_launch": stage_ms["cfar"],
@@ -346,7 +346,7 @@ def extra_single_gpu_lines(torch, dev, peak):
             extras.append({"workload": f"configs/{cfg_name}.cfg batched synthetic int16 ADC cubes", "frames_per_step": F,
                            "steps": steps, "value": F * steps / (ms_total * 1e-3), "unit": "frames/s",
                            "ms_per_step": ms_total / steps, "stage_ms_per_step": stage_ms,
-                           "roofline": {"kernel": "rd_stream_kernel", "frac": kernels[0]["frac"],
+                           "roofline": {"kernel": kernels[0]["kernel"], "frac": kernels[0]["frac"],
                                         "achieved": kernels[0]["achieved_gbs"], "peak": peak, "unit": "GB/s",
                                         "algorithmic_bytes_per_frame": bytes_pf["range_doppler"], "kernels": kernels,
                                         "step_hbm_frac": step_bytes * F / (ms_total / steps * 1e-3) / 1e9 / peak},
@@ -717,10 +717,11 @@ def main():
         ms_per_step = ms_total / a.steps
         value = F_global * a.steps / (ms_total * 1e-3)
         peak, peak_src = hbm_peak()
-        kernels, bytes_pf, step_bytes = stage_rooflines(cm, a.workload, F, stage_ms, ms_per_step, total_points, peak)
+        rd_kernel = pipe.engine.last_rd_kernel()
+        kernels, bytes_pf, step_bytes = stage_rooflines(cm, a.workload, F, stage_ms, ms_per_step, total_points, peak, rd_kernel)
         rd_ms = stage_ms["range_doppler"]
         achieved = bytes_pf["range_doppler"] * F / (rd_ms * 1e-3) / 1e9
-        traffic, traffic_src = ncu_traffic("rd_stream_kernel", a.workload)
+        traffic, traffic_src = ncu_traffic(rd_kernel, a.workload)
         e2e_value = world * Fe * e2e_steps / (e2e_ms * 1e-3)
         h2d_gbs = world * h2d * e2e_steps / (h2d_ms * 1e-3) / 1e9
         line = {
@@ -728,7 +729,7 @@ def main():
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
             "dtype": "f32", "data": f"synthetic ({min(N_UNIQUE, F)} distinct seeded frames per rank tiled to the rank's block)",
             "config": workload_config(cm, a.workload, F, F_global, world, a.exchange),
-            "roofline": {"kernel": "rd_stream_kernel", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "roofline": {"kernel": rd_kernel, "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": (traffic * F if traffic else None), "traffic_source": traffic_src,
                          "peak_source": peak_src, "algorithmic_bytes_per_frame": bytes_pf["range_doppler"],
                          "kernel_ms_per_launch": rd_ms, "kernels": kernels,

@@ -87,6 +87,9 @@ int radar_ctx_create(const radar_shape* shape, int device, radar_ctx** out_ctx);
 int radar_ctx_destroy(radar_ctx* ctx);
 /* message of the last failed call on ctx (ctx == NULL: last failure of radar_ctx_create in this thread) */
 const char* radar_last_error(const radar_ctx* ctx);
+/* name of the kernel the last radar_range_doppler call on ctx launched ("rd_reg_kernel", "rd_stream_kernel", "rd_spec_kernel",
+ * "rd_fused_kernel"; "" before the first call) - for benchmark lines and tests that must know which path ran */
+const char* radar_last_rd_kernel(const radar_ctx* ctx);
 
 /* Bin axes looked up by radar_point_cloud (host pointers, copied).  They must be produced with the
  * reference's numpy expressions (processors/range_doppler_resp.py:33-47, point_cloud_generator.py:89-105)

@@ -42,6 +42,7 @@ SIGNATURES = {
     "radar_ctx_create": (_I, [C.POINTER(RadarShape), _I, C.POINTER(_P)]),
     "radar_ctx_destroy": (_I, [_P]),
     "radar_last_error": (C.c_char_p, [_P]),
+    "radar_last_rd_kernel": (C.c_char_p, [_P]),
     "radar_ctx_set_axes": (_I, [_P, C.POINTER(C.c_double), _I, C.POINTER(C.c_double), _I]),
     "radar_ctx_set_angle_bins": (_I, [_P, C.POINTER(C.c_double), _I]),
     "radar_range_doppler": (_I, [_P, _P, _I, _I, _P, _I, _I, _P, _P, _I, _P]),

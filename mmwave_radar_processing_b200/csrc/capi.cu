@@ -126,6 +126,7 @@ extern "C" {
 int radar_abi_version(void) { return RADAR_B200_ABI_VERSION; }
 
 const char* radar_last_error(const radar_ctx* ctx) { return ctx ? ctx->err : g_create_error; }
+const char* radar_last_rd_kernel(const radar_ctx* ctx) { return ctx ? ctx->last_rd_kernel : ""; }
 
 double radar_cfar_ca_alpha(int n_train_cells, double pfa) {
     return (double)n_train_cells * (std::pow(pfa, -1.0 / (double)n_train_cells) - 1.0);

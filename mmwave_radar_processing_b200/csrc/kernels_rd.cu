@@ -207,6 +207,7 @@ int launch_range_doppler(radar_ctx* ctx, const void* adc, int in_kind, int n_fra
     const long long grid = (long long)n_frames * a.n_out_ant;
     if (grid > 0x7fffffffLL) return set_error(ctx, RADAR_E_INVALID, "too many frames in one call");
     rd_fused_kernel<<<(unsigned)grid, kRdThreads, smem, st>>>(a);
+    ctx->last_rd_kernel = "rd_fused_kernel";
     RB_CUDA_OK(ctx, cudaGetLastError());
     return RADAR_OK;
 }

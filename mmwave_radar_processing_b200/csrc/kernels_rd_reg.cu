@@ -153,6 +153,7 @@ static int launch_reg(radar_ctx* ctx, const void* adc, int n_frames, int window_
     unsigned grid = (unsigned)ctx->sm_count;
     if (grid > a.n_items) grid = a.n_items;
     rd_reg_kernel<C><<<grid, C::NT, smem, st>>>(a);
+    ctx->last_rd_kernel = "rd_reg_kernel";
     RB_CUDA_OK(ctx, cudaGetLastError());
     return RADAR_OK;
 }

@@ -207,6 +207,7 @@ static int launch_spec(radar_ctx* ctx, const RdSpecArgs& a, int n_frames, cudaSt
     const long long grid = (long long)n_frames * a.n_out_ant;
     if (grid > 0x7fffffffLL) return set_error(ctx, RADAR_E_INVALID, "too many frames in one call");
     rd_spec_kernel<C><<<(unsigned)grid, C::NT, smem, st>>>(a);
+    ctx->last_rd_kernel = "rd_spec_kernel";
     RB_CUDA_OK(ctx, cudaGetLastError());
     return RADAR_OK;
 }

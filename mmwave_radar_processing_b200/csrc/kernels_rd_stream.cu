@@ -146,6 +146,7 @@ static int launch_stream(radar_ctx* ctx, const void* adc, int n_frames, int wind
     long long grid = (long long)ctx->sm_count * resident;
     if (grid > a.n_items) grid = a.n_items;
     rd_stream_kernel<C><<<(unsigned)grid, C::NT, smem, st>>>(a);
+    ctx->last_rd_kernel = "rd_stream_kernel";
     RB_CUDA_OK(ctx, cudaGetLastError());
     return RADAR_OK;
 }

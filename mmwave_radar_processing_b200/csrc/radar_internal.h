@@ -57,6 +57,7 @@ struct radar_ctx {
     int ra_fc = 0;                                // RADAR_B200_RA_FC: frames per pass of the range-angle kernel (0 = cost model)
     int rd_reg = 1;                               // RADAR_B200_RD_REG=0: skip the register-resident range-Doppler kernel (tests / comparison)
     int stream_variant = 0;                       // RADAR_B200_STREAM_VARIANT: tuning candidate of the streaming kernel
+    const char* last_rd_kernel = "";              // name of the range-Doppler kernel the last radar_range_doppler call launched
     char err[512] = {0};
 };
 

@@ -125,6 +125,10 @@ class RadarEngine:
                   self.ctx)
 
     # ------------------------------------------------------------------ kernels
+    def last_rd_kernel(self) -> str:
+        """Name of the kernel the last range_doppler call launched."""
+        return (self.lib.radar_last_rd_kernel(self.ctx) or b"").decode()
+
     def range_doppler(self, adc: torch.Tensor, ant_list=None, window_flags: int = 3, want_rd: bool = True,
                       mag_antenna: Optional[int] = None, rd_out=None, mag_out=None):
         """-> (rd complex64 [F, n_ant, S, L] or None, mag float32 [F,S,L] / [F,n_ant,S,L] or None)."""
