@@ -285,6 +285,7 @@ struct RaArgs {
     const cf* twS; const uint16_t* posS; const cf* twA;
     float* out;
     long long n_frames; int frames_per_pass;
+    int fft4;             // ra_angle_stage_fft4 (2/4/8 antennas, power-of-two bins, A/N >= 4, 16-byte aligned output)
     FftPlan planS; FastDiv divS, divN, divW;
 };
 
@@ -384,10 +385,53 @@ __device__ __forceinline__ void ra_angle_stage_fft(const cf* tile, int Np, const
     }
 }
 
+// Four neighbouring residues per lane (A/NC >= 4): the NC - 1 twiddles of a residue come from a transposed table
+// twT[j-1][r] = W_A^(j r) (neighbouring lanes read neighbouring entries: no bank conflicts, 128-bit loads), the four
+// butterflies share the row loads and the index arithmetic, and the four bins r .. r+3 of every q leave as ONE 128-bit store.
+// ncu on the one-residue form at A = 1024 (profiles/r3e): issue-bound, 26 thread-instructions per output cell, 26 % of them
+// address arithmetic, a third of the shared-memory wavefronts bank conflicts of the stride-j twiddle reads.
+template <int NC>
+__device__ __forceinline__ void ra_angle_stage_fft4(const cf* tile, int Np, const uint16_t* pos, const cf* twT, int S, int A,
+                                                    float* dst) {
+    const int M = A / NC, M4 = M >> 2, total = S * M4;
+    const int m_shift = 31 - __clz(M4);
+    for (int t = threadIdx.x; t < total; t += blockDim.x) {
+        const int k = t >> m_shift, r = (t & (M4 - 1)) << 2;
+        const cf* row = tile + pos[k] * Np;
+        cf v[4][NC];
+        const cf x0 = row[0];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) v[i][0] = x0;
+#pragma unroll
+        for (int j = 1; j < NC; ++j) {
+            const cf x = row[j];
+            const float4 wa = *reinterpret_cast<const float4*>(twT + (j - 1) * M + r);
+            const float4 wb = *reinterpret_cast<const float4*>(twT + (j - 1) * M + r + 2);
+            v[0][j] = cmul(x, cmake(wa.x, wa.y));
+            v[1][j] = cmul(x, cmake(wa.z, wa.w));
+            v[2][j] = cmul(x, cmake(wb.x, wb.y));
+            v[3][j] = cmul(x, cmake(wb.z, wb.w));
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) Dft<NC>::run(v[i]);
+        float* out = dst + k * A;
+#pragma unroll
+        for (int q = 0; q < NC; ++q) {
+            float4 m;
+            m.x = sqrt_fast(v[0][q].x * v[0][q].x + v[0][q].y * v[0][q].y);
+            m.y = sqrt_fast(v[1][q].x * v[1][q].x + v[1][q].y * v[1][q].y);
+            m.z = sqrt_fast(v[2][q].x * v[2][q].x + v[2][q].y * v[2][q].y);
+            m.w = sqrt_fast(v[3][q].x * v[3][q].x + v[3][q].y * v[3][q].y);
+            *reinterpret_cast<float4*>(out + ((r + M * q + A / 2) & (A - 1))) = m;
+        }
+    }
+}
+
 template <int NC>
 __device__ __forceinline__ void ra_angle_stage_any(const cf* tile, int Np, const uint16_t* pos, const cf* twA, int S, int A,
-                                                   float* dst, int n_rt = 0) {
+                                                   float* dst, int n_rt = 0, const cf* twT = nullptr) {
     if constexpr (NC == 2 || NC == 4 || NC == 8) {
+        if (twT) { ra_angle_stage_fft4<NC>(tile, Np, pos, twT, S, A, dst); return; }
         if (A >= 32 && (A & (A - 1)) == 0) { ra_angle_stage_fft<NC>(tile, Np, pos, twA, S, A, dst); return; }
     }
     if (A == 64) ra_angle_stage<NC, 2>(tile, Np, pos, twA, S, A, dst, n_rt);
@@ -407,8 +451,16 @@ __global__ void __launch_bounds__(kRdThreads) range_angle_kernel(const __grid_co
     cf* twA = ar.take<cf>(A);
     float* win = ar.take<float>(S);
     uint16_t* pos = ar.take<uint16_t>(S);
+    cf* twT = a.fft4 ? ar.take<cf>((N - 1) * (A / N)) : nullptr;         // transposed twiddles of ra_angle_stage_fft4
     load_table(tw, a.twS, S);
     load_table(twA, a.twA, A);
+    if (twT) {
+        const int M = A / N;
+        for (int i = threadIdx.x; i < (N - 1) * M; i += blockDim.x) {
+            const int j = i / M + 1, r = i - (j - 1) * M;
+            twT[i] = a.twA[(j * r) & (A - 1)];
+        }
+    }
     load_table(win, a.winS, S);
     load_table(pos, a.posS, S);
     for (int i = threadIdx.x; i < S * P; i += blockDim.x) tile[i] = cmake(0.f, 0.f);
@@ -430,10 +482,10 @@ __global__ void __launch_bounds__(kRdThreads) range_angle_kernel(const __grid_co
             const cf* t = tile + f * N;
             switch (N) {
                 case 1: ra_angle_stage_any<1>(t, P, pos, twA, S, A, dst); break;
-                case 2: ra_angle_stage_any<2>(t, P, pos, twA, S, A, dst); break;
+                case 2: ra_angle_stage_any<2>(t, P, pos, twA, S, A, dst, 0, twT); break;
                 case 3: ra_angle_stage_any<3>(t, P, pos, twA, S, A, dst); break;
-                case 4: ra_angle_stage_any<4>(t, P, pos, twA, S, A, dst); break;
-                case 8: ra_angle_stage_any<8>(t, P, pos, twA, S, A, dst); break;
+                case 4: ra_angle_stage_any<4>(t, P, pos, twA, S, A, dst, 0, twT); break;
+                case 8: ra_angle_stage_any<8>(t, P, pos, twA, S, A, dst, 0, twT); break;
                 case 12: ra_angle_stage_any<12>(t, P, pos, twA, S, A, dst); break;
                 default: ra_angle_stage_any<0>(t, P, pos, twA, S, A, dst, N); break;
             }
@@ -473,9 +525,13 @@ int launch_range_angle(radar_ctx* ctx, const void* adc, int in_kind, int n_frame
     int fc_max = 32 / N; if (fc_max < 1) fc_max = 1; if (fc_max > 8) fc_max = 8;
     while (fc_max > 1 && (size_t)S * ((fc_max * N) | 1) * sizeof(cf) > 64 * 1024) --fc_max;
     if (fc_max > n_frames) fc_max = n_frames;
+    const bool pow2 = (num_angle_bins & (num_angle_bins - 1)) == 0;
+    a.fft4 = ((N == 2 || N == 4 || N == 8) && pow2 && num_angle_bins / N >= 4 && num_angle_bins <= 2048 && ctx->ra_fft4 &&
+              reinterpret_cast<uintptr_t>(out) % 16 == 0) ? 1 : 0;
     auto smem_for = [&](int fc) {
         return arena_bytes((size_t)S * ((fc * N) | 1), sizeof(cf)) + arena_bytes(S, sizeof(cf)) +
-               arena_bytes(num_angle_bins, sizeof(cf)) + arena_bytes(S, 4) + arena_bytes(S, 2);
+               arena_bytes(num_angle_bins, sizeof(cf)) + arena_bytes(S, 4) + arena_bytes(S, 2) +
+               (a.fft4 ? arena_bytes((size_t)(N - 1) * (num_angle_bins / N), sizeof(cf)) : 0);
     };
     if (int rc = opt_in_smem(ctx, range_angle_kernel, smem_for(fc_max), "range-angle tile")) return rc;
     int fc = fc_max;

@@ -54,6 +54,7 @@ struct radar_ctx {
     int cfar_tile = 0;                            // RADAR_B200_CFAR_TILE=n: force n x n tiles in the CFAR kernel (tests of the large-map path)
     int cfar_ladder = 1;                          // RADAR_B200_CFAR_LADDER=0: OS-CFAR without the level-ladder screen (tests / comparison)
     int pc_mode = 0;                              // RADAR_B200_PC=1: warp-per-detection point-cloud kernel only (tests / comparison)
+    int ra_fft4 = 1;                              // RADAR_B200_RA_FFT4=0: one residue per lane in the range-angle stage (comparison)
     int ra_fc = 0;                                // RADAR_B200_RA_FC: frames per pass of the range-angle kernel (0 = cost model)
     int rd_reg = 1;                               // RADAR_B200_RD_REG=0: skip the register-resident range-Doppler kernel (tests / comparison)
     int stream_variant = 0;                       // RADAR_B200_STREAM_VARIANT: tuning candidate of the streaming kernel
