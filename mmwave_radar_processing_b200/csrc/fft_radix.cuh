@@ -308,4 +308,101 @@ template <> struct Dft<16> {
     }
 };
 
+// 64 = 8 x 8 by Cooley-Tukey in registers: n = 8*n1 + n2, k = k1 + 8*k2, twiddles W64^(n2*k1) as literals
+template <> struct Dft<64> {
+    RB_HD static void run(cf* v) {
+        cf a[8][8];
+#pragma unroll
+        for (int n2 = 0; n2 < 8; ++n2) {
+#pragma unroll
+            for (int n1 = 0; n1 < 8; ++n1) a[n2][n1] = v[8 * n1 + n2];
+            Dft<8>::run(a[n2]);
+        }
+        a[1][1] = cmul(a[1][1], cmake(0.99518472667219692873f, -0.09801714032956060363f));   // W64^1
+        a[1][2] = cmul(a[1][2], cmake(0.98078528040323043058f, -0.19509032201612824808f));   // W64^2
+        a[1][3] = cmul(a[1][3], cmake(0.95694033573220882438f, -0.29028467725446233105f));   // W64^3
+        a[1][4] = cmul(a[1][4], cmake(0.92387953251128673848f, -0.38268343236508978178f));   // W64^4
+        a[1][5] = cmul(a[1][5], cmake(0.88192126434835504956f, -0.47139673682599764204f));   // W64^5
+        a[1][6] = cmul(a[1][6], cmake(0.83146961230254523567f, -0.55557023301960217765f));   // W64^6
+        a[1][7] = cmul(a[1][7], cmake(0.77301045336273699338f, -0.63439328416364548779f));   // W64^7
+        a[2][1] = cmul(a[2][1], cmake(0.98078528040323043058f, -0.19509032201612824808f));   // W64^2
+        a[2][2] = cmul(a[2][2], cmake(0.92387953251128673848f, -0.38268343236508978178f));   // W64^4
+        a[2][3] = cmul(a[2][3], cmake(0.83146961230254523567f, -0.55557023301960217765f));   // W64^6
+        a[2][4] = cmul(a[2][4], cmake(0.70710678118654757274f, -0.70710678118654746172f));   // W64^8
+        a[2][5] = cmul(a[2][5], cmake(0.55557023301960228867f, -0.83146961230254523567f));   // W64^10
+        a[2][6] = cmul(a[2][6], cmake(0.38268343236508983729f, -0.92387953251128673848f));   // W64^12
+        a[2][7] = cmul(a[2][7], cmake(0.19509032201612833135f, -0.98078528040323043058f));   // W64^14
+        a[3][1] = cmul(a[3][1], cmake(0.95694033573220882438f, -0.29028467725446233105f));   // W64^3
+        a[3][2] = cmul(a[3][2], cmake(0.83146961230254523567f, -0.55557023301960217765f));   // W64^6
+        a[3][3] = cmul(a[3][3], cmake(0.63439328416364548779f, -0.77301045336273699338f));   // W64^9
+        a[3][4] = cmul(a[3][4], cmake(0.38268343236508983729f, -0.92387953251128673848f));   // W64^12
+        a[3][5] = cmul(a[3][5], cmake(0.09801714032956077016f, -0.99518472667219681771f));   // W64^15
+        a[3][6] = cmul(a[3][6], cmake(-0.19509032201612819257f, -0.98078528040323043058f));   // W64^18
+        a[3][7] = cmul(a[3][7], cmake(-0.47139673682599769755f, -0.88192126434835504956f));   // W64^21
+        a[4][1] = cmul(a[4][1], cmake(0.92387953251128673848f, -0.38268343236508978178f));   // W64^4
+        a[4][2] = cmul(a[4][2], cmake(0.70710678118654757274f, -0.70710678118654746172f));   // W64^8
+        a[4][3] = cmul(a[4][3], cmake(0.38268343236508983729f, -0.92387953251128673848f));   // W64^12
+        a[4][4] = cmul_mi(a[4][4]);
+        a[4][5] = cmul(a[4][5], cmake(-0.38268343236508972627f, -0.92387953251128673848f));   // W64^20
+        a[4][6] = cmul(a[4][6], cmake(-0.70710678118654746172f, -0.70710678118654757274f));   // W64^24
+        a[4][7] = cmul(a[4][7], cmake(-0.92387953251128673848f, -0.38268343236508989280f));   // W64^28
+        a[5][1] = cmul(a[5][1], cmake(0.88192126434835504956f, -0.47139673682599764204f));   // W64^5
+        a[5][2] = cmul(a[5][2], cmake(0.55557023301960228867f, -0.83146961230254523567f));   // W64^10
+        a[5][3] = cmul(a[5][3], cmake(0.09801714032956077016f, -0.99518472667219681771f));   // W64^15
+        a[5][4] = cmul(a[5][4], cmake(-0.38268343236508972627f, -0.92387953251128673848f));   // W64^20
+        a[5][5] = cmul(a[5][5], cmake(-0.77301045336273699338f, -0.63439328416364548779f));   // W64^25
+        a[5][6] = cmul(a[5][6], cmake(-0.98078528040323043058f, -0.19509032201612860891f));   // W64^30
+        a[5][7] = cmul(a[5][7], cmake(-0.95694033573220893540f, 0.29028467725446210901f));   // W64^35
+        a[6][1] = cmul(a[6][1], cmake(0.83146961230254523567f, -0.55557023301960217765f));   // W64^6
+        a[6][2] = cmul(a[6][2], cmake(0.38268343236508983729f, -0.92387953251128673848f));   // W64^12
+        a[6][3] = cmul(a[6][3], cmake(-0.19509032201612819257f, -0.98078528040323043058f));   // W64^18
+        a[6][4] = cmul(a[6][4], cmake(-0.70710678118654746172f, -0.70710678118654757274f));   // W64^24
+        a[6][5] = cmul(a[6][5], cmake(-0.98078528040323043058f, -0.19509032201612860891f));   // W64^30
+        a[6][6] = cmul(a[6][6], cmake(-0.92387953251128684951f, 0.38268343236508967076f));   // W64^36
+        a[6][7] = cmul(a[6][7], cmake(-0.55557023301960217765f, 0.83146961230254523567f));   // W64^42
+        a[7][1] = cmul(a[7][1], cmake(0.77301045336273699338f, -0.63439328416364548779f));   // W64^7
+        a[7][2] = cmul(a[7][2], cmake(0.19509032201612833135f, -0.98078528040323043058f));   // W64^14
+        a[7][3] = cmul(a[7][3], cmake(-0.47139673682599769755f, -0.88192126434835504956f));   // W64^21
+        a[7][4] = cmul(a[7][4], cmake(-0.92387953251128673848f, -0.38268343236508989280f));   // W64^28
+        a[7][5] = cmul(a[7][5], cmake(-0.95694033573220893540f, 0.29028467725446210901f));   // W64^35
+        a[7][6] = cmul(a[7][6], cmake(-0.55557023301960217765f, 0.83146961230254523567f));   // W64^42
+        a[7][7] = cmul(a[7][7], cmake(0.09801714032956009015f, 0.99518472667219692873f));   // W64^49
+#pragma unroll
+        for (int k1 = 0; k1 < 8; ++k1) {
+            cf y[8] = {a[0][k1], a[1][k1], a[2][k1], a[3][k1], a[4][k1], a[5][k1], a[6][k1], a[7][k1]};
+            Dft<8>::run(y);
+#pragma unroll
+            for (int k2 = 0; k2 < 8; ++k2) v[k1 + 8 * k2] = y[k2];
+        }
+    }
+};
+
+// 32 = 2 x 16: decimation in time over two register-resident 16-point transforms, twiddles W32^k as literals
+template <> struct Dft<32> {
+    RB_HD static void run(cf* v) {
+        cf e[16], o[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i) { e[i] = v[2 * i]; o[i] = v[2 * i + 1]; }
+        Dft<16>::run(e);
+        Dft<16>::run(o);
+        o[1] = cmul(o[1], cmake(0.98078528040323043058f, -0.19509032201612824808f));
+        o[2] = cmul(o[2], cmake(0.92387953251128673848f, -0.38268343236508978178f));
+        o[3] = cmul(o[3], cmake(0.83146961230254523567f, -0.55557023301960217765f));
+        o[4] = cmul(o[4], cmake(0.70710678118654757274f, -0.70710678118654746172f));
+        o[5] = cmul(o[5], cmake(0.55557023301960228867f, -0.83146961230254523567f));
+        o[6] = cmul(o[6], cmake(0.38268343236508983729f, -0.92387953251128673848f));
+        o[7] = cmul(o[7], cmake(0.19509032201612833135f, -0.98078528040323043058f));
+        o[8] = cmul_mi(o[8]);
+        o[9] = cmul(o[9], cmake(-0.19509032201612819257f, -0.98078528040323043058f));
+        o[10] = cmul(o[10], cmake(-0.38268343236508972627f, -0.92387953251128673848f));
+        o[11] = cmul(o[11], cmake(-0.55557023301960195560f, -0.83146961230254545772f));
+        o[12] = cmul(o[12], cmake(-0.70710678118654746172f, -0.70710678118654757274f));
+        o[13] = cmul(o[13], cmake(-0.83146961230254534669f, -0.55557023301960217765f));
+        o[14] = cmul(o[14], cmake(-0.92387953251128673848f, -0.38268343236508989280f));
+        o[15] = cmul(o[15], cmake(-0.98078528040323043058f, -0.19509032201612860891f));
+#pragma unroll
+        for (int k = 0; k < 16; ++k) { v[k] = cadd(e[k], o[k]); v[k + 16] = csub(e[k], o[k]); }
+    }
+};
+
 }  // namespace rb

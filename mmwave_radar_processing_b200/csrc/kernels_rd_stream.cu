@@ -110,7 +110,7 @@ static int launch_stream(radar_ctx* ctx, const void* adc, int n_frames, int wind
                          int mag_antenna, cudaStream_t st) {
     constexpr size_t smem = C::smem_bytes();
     static_assert(smem <= 227 * 1024, "tiles exceed shared memory");
-    static_assert(sizeof(RdStreamParams<C>) <= 4000, "parameter block too large");
+    static_assert(sizeof(RdStreamParams<C>) <= 30000, "parameter block too large (CUDA 12.1+: 32 764 bytes)");
     RdStreamParams<C> a;
     a.iq = reinterpret_cast<const uint32_t*>(adc);
     a.rd_out = rd_out; a.mag_out = mag_out; a.mag_antenna = mag_antenna;

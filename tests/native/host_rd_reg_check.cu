@@ -105,6 +105,7 @@ int main() {
     r = check<RdRegShape<63, 70, 12, 2, 1, 3, 1>>(2); printf("63x70 G=2 DF=1: rel_l2 = %.3e\n", r); worst = fmax(worst, r);
     r = check<RdRegShape<63, 70, 12, 2, 2, 3, 1>>(2); printf("63x70 G=2 DF=2: rel_l2 = %.3e\n", r); worst = fmax(worst, r);
     r = check<RdRegShape<100, 30, 8, 2, 1, 3, 1, 4>>(2); printf("100x30 G=2 BF=4: rel_l2 = %.3e\n", r); worst = fmax(worst, r);
+    r = check<RdRegShape<64, 40, 4, 2, 1, 3, 1, 1>>(2); printf("64x40 G=2: rel_l2 = %.3e\n", r); worst = fmax(worst, r);
     printf("worst rel_l2 = %.3e\n", worst);
     return worst < 2e-6 ? 0 : 1;
 }
