@@ -1,20 +1,26 @@
-// CFAR family + ordered detection compaction: one CTA per map, the map resident in shared memory.
+// CFAR family + ordered detection compaction: one CTA per map (or per tile of a map that exceeds one CTA's shared memory),
+// the map resident in shared memory (one bulk copy of the TMA engine when the layout is unpadded).
 //
 // Reference arithmetic reproduced (paths relative to mmwave_radar_processing/ in the reference):
 //   detectors/base.py:38-65, :208-230 (strict x > threshold, np.where order),
 //   detectors/ca_cfar.py:11-155, detectors/os_cfar.py:11-195, detectors/go_so_cfar.py:11-123.
 //
-// * CA / GO / SO: one thread per cell under test, training sums accumulated in fp64.
-// * OS, mask only (the streaming path): one thread per cell under test counts the training cells below a per-cell bound
-//   and stops as soon as the decision is fixed (see os_count_cells).
+// * CA: separable sliding box sums in fp64 with error-free accumulation (ca_box_cells); GO / SO (1-D) and CA with
+//   RADAR_B200_CFAR_BOX=0: one thread per cell under test, training sums accumulated in fp64.
+// * OS, mask only (the streaming path): a ladder of four levels around the expected order statistic - the window counts at
+//   the levels are carried as packed bytes by sliding sums and decide all but a fraction of a percent of the cells; the rest
+//   get an exact count (os_ladder_cells).  Detector settings the packed fields cannot hold, row_select, or
+//   RADAR_B200_CFAR_LADDER=0: one thread per cell under test counts the training cells below a per-cell bound and stops as
+//   soon as the decision is fixed (os_count_cells).
 // * OS with noise estimates requested: one warp per cell under test; every lane keeps its share of the training window in registers
 //   and the exact k-th order statistic is built bit by bit (MSB->LSB) from warp-wide counts
 //   (__reduce_add_sync), which is an exact selection on order-preserving integer keys of the fp32 values.
 //   Maps with a negative cell (detect() accepts signed data; the counting paths assume magnitudes) always take this path.
 // * decision in fp64: (double)x > alpha*(double)noise - the same expression the host layer uses to publish
 //   `thresholds`.
-// * compaction: warp ballots + popcounts, an exclusive scan over the warps' totals, then an ordered
-//   scatter - row-major (range, Doppler) like np.where, one global counter write per map.
+// * compaction: every thread owns a contiguous run of cells (popcounts of whole mask words, shuffle scan, warp totals through
+//   shared memory), then an ordered scatter - row-major (range, Doppler) like np.where, one global counter write per map.
+//   Tiled maps: the tiles write a full-size mask and cfar_compact_kernel does the same per map.
 #include <cmath>
 #include "radar_internal.h"
 #include "rd_core.cuh"
