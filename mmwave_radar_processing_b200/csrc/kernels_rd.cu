@@ -574,7 +574,11 @@ struct DbsArgs {
     FastDiv divOut;
 };
 
-__global__ void __launch_bounds__(kRdThreads) dbs_kernel(const __grid_constant__ DbsArgs a) {
+// 1024 threads: one CTA per frame holds a whole antenna tile (149 KB for 90 x 100) so only one CTA fits an SM; ncu on the
+// 256-thread launch showed it latency-bound at 8 warps per SM (issue 23 %, long scoreboard 3.9 of 8 stall cycles).
+// 256 / 512 / 768 / 1024 threads: 1.92 / 1.18 / 0.98 / 0.89 ms per 1024 frames of RadSAR_1843_official.
+constexpr int kDbsThreads = 1024;
+__global__ void __launch_bounds__(kDbsThreads) dbs_kernel(const __grid_constant__ DbsArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int S = a.rd.adc.S, L = a.rd.adc.L, Lp = odd_pitch(L);
     RdSmem sm = rd_carve(smem_raw, S, L);
@@ -655,7 +659,7 @@ int launch_dbs(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, const
         a.acc_global = reinterpret_cast<cf*>(ctx->scratch);
     }
     if (int rc = opt_in_smem(ctx, dbs_kernel, smem, "DBS tile")) return rc;
-    dbs_kernel<<<(unsigned)n_frames, kRdThreads, smem, st>>>(a);
+    dbs_kernel<<<(unsigned)n_frames, kDbsThreads, smem, st>>>(a);
     RB_CUDA_OK(ctx, cudaGetLastError());
     return RADAR_OK;
 }

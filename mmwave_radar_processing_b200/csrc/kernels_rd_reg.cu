@@ -170,7 +170,8 @@ int launch_range_doppler_reg(radar_ctx* ctx, const void* adc, int n_frames, int 
         return launch_reg<RdRegShape<s, l, cr, g, df, nstage, ntile, bf>>(ctx, adc, n_frames, window_flags, rd_out, mag_out, mag_antenna, st);
     // RB_REG(variant (RADAR_B200_RD_REG; 1 is the default), S, L, CR, G, DF, ring stages, tile buffers, BF)
     RB_REG(1, 63, 70, 12, 2, 1, 3, 1, 1)      // 6843 ODS: 0.547 ms per 4096 frames (0.75 of measured HBM), 166 registers, 10 warps
-    RB_REG(4, 63, 70, 12, 2, 1, 2, 2, 1)      //   two tile buffers, two ring stages
+    RB_REG(4, 63, 70, 12, 2, 1, 2, 2, 1)      //   two tile buffers, two ring stages: 0.530
+    RB_REG(5, 63, 70, 12, 2, 1, 4, 1, 1)      //   four ring stages
     RB_REG(2, 63, 70, 12, 2, 2, 3, 1, 1)      //   split column: 14 warps are allocated as 16 -> 128 registers, phase B spills: 0.886
     RB_REG(3, 63, 70, 12, 2, 2, 2, 2, 1)      //   the same with two tile buffers: 0.976
     RB_REG(1, 100, 30, 8, 2, 1, 3, 1, 4)     // 1843_RadVel: 30-point Doppler per thread, 100-point range split 4 x 25
