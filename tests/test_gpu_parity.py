@@ -11,7 +11,7 @@ import numpy as np
 import pytest
 
 from conftest import (CFAR1D_SETS, CFAR2D_SETS, GOLDEN_CASES, GOLDEN_DIR, GROUND_VEL, SEQ_PARAMS, ant_sets, frame_iq, golden,
-                      load_cfg, rel_l2)
+                      load_cfg, rel_l2, REPO)
 
 pytestmark = pytest.mark.gpu
 
@@ -645,3 +645,37 @@ def test_frame_file_to_point_clouds(torch_cuda, tmp_path):
                           az_antenna_idxs=(0, 1, 2, 3), el_antenna_idxs=(), max_dets=64)
     with pytest.raises(ValueError):
         ingest.process_file(pipe2, path)
+
+
+def test_nvtx_ranges_do_not_change_results(torch_cuda):
+    """RADAR_B200_NVTX=1 (read at import) wraps the pipeline stages in NVTX ranges: a fresh interpreter runs a small batch
+    with the ranges on and prints the point total, which must equal the in-process run."""
+    import subprocess
+    import sys
+    torch = torch_cuda
+    from mmwave_radar_processing_b200.pipeline import DetectorSpec, FramePipeline
+    from mmwave_radar_processing_b200.synthetic import synth_batch_for_cfg
+    cm = load_cfg("6843_RadVel_ods_20Hz", "ods")
+    pipe = FramePipeline(cm, detector=DetectorSpec(kind="os", num_train=(8, 4), num_guard=(2, 1), rho=0.75, alpha=3.5),
+                         az_antenna_idxs=(0, 3, 4, 7), el_antenna_idxs=(9, 8, 5, 4), max_dets=256)
+    out = pipe.run(torch.from_numpy(synth_batch_for_cfg(cm, range(6))).cuda())
+    want = int(out["offsets"][6])
+    code = (
+        "import sys; sys.path.insert(0, %r); sys.path.insert(0, %r)\n"
+        "import torch\n"
+        "from conftest import load_cfg\n"
+        "from mmwave_radar_processing_b200 import pipeline\n"
+        "from mmwave_radar_processing_b200.synthetic import synth_batch_for_cfg\n"
+        "assert pipeline._NVTX\n"
+        "cm = load_cfg('6843_RadVel_ods_20Hz', 'ods')\n"
+        "p = pipeline.FramePipeline(cm, detector=pipeline.DetectorSpec(kind='os', num_train=(8, 4), num_guard=(2, 1), rho=0.75, alpha=3.5),\n"
+        "                           az_antenna_idxs=(0, 3, 4, 7), el_antenna_idxs=(9, 8, 5, 4), max_dets=256, with_range_angle=True)\n"
+        "marks = []\n"
+        "o = p.run(torch.from_numpy(synth_batch_for_cfg(cm, range(6))).cuda(), marks.append)\n"
+        "print('TOTAL', int(o['offsets'][6]), ','.join(marks))\n"
+    ) % (REPO, os.path.join(REPO, "tests"))
+    env = dict(os.environ, RADAR_B200_NVTX="1")
+    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=240)
+    assert res.returncode == 0, res.stderr[-2000:]
+    line = [l for l in res.stdout.splitlines() if l.startswith("TOTAL")][0].split()
+    assert int(line[1]) == want and line[2] == "range_doppler,range_angle,cfar,point_cloud"
