@@ -102,8 +102,8 @@ __global__ void __launch_bounds__(C::NT, 1) rd_reg_kernel(const __grid_constant_
             const int ant = (int)grp * C::G + g;
             cf v[C::SH];
             mb::wait(tile_full + tb, tround & 1);
-            if (odd) rd_reg_range_load<C, 1>(tiles + (size_t)tb * C::TILE, g, d, sigma, v);
-            else rd_reg_range_load<C, 0>(tiles + (size_t)tb * C::TILE, g, d, sigma, v);
+            if (odd) rd_reg_range_load<C, 1>(a, tiles + (size_t)tb * C::TILE, g, d, sigma, v);
+            else rd_reg_range_load<C, 0>(a, tiles + (size_t)tb * C::TILE, g, d, sigma, v);
             mb::arrive(tile_empty + tb);
             const size_t o = ((size_t)frame * C::CR + ant) * (C::S * C::L) + d;
             cf* out = (a.rd_out && active) ? a.rd_out + o : nullptr;
@@ -141,8 +141,13 @@ static int launch_reg(radar_ctx* ctx, const void* adc, int n_frames, int window_
     host_hann_f(C::L, window_flags & RADAR_WIN_DOPPLER, wl);
     for (int h = 0; h < C::DF; ++h)
         for (int m = 0; m < C::LH; ++m) {
-            const float w = wl[(h * C::LH + C::DF * m) % C::L];
+            const float w = wl[rd_reg_doppler_input<C>(h, m)];
             a.winL[h * C::LH + m] = make_float2(w, w);
+        }
+    if (C::TW)
+        for (int k = 0; k < C::L; ++k) {
+            const double ang = -2.0 * M_PI * (double)k / (double)C::L;
+            a.twL[k] = cmake((float)std::cos(ang), (float)std::sin(ang));
         }
     host_hann_f(C::S, window_flags & RADAR_WIN_RANGE, a.winS);
     static bool configured[64] = {false};
@@ -177,6 +182,7 @@ int launch_range_doppler_reg(radar_ctx* ctx, const void* adc, int n_frames, int 
     RB_REG(1, 100, 30, 8, 2, 1, 3, 1, 4)     // 1843_RadVel: 30-point Doppler per thread, 100-point range split 4 x 25
     RB_REG(2, 100, 30, 8, 2, 1, 2, 2, 4)
     RB_REG(1, 64, 40, 4, 2, 1, 3, 1, 1)      // RadCloud: 40-point Doppler, 64-point range (8 x 8) per thread
+    RB_REG(1, 90, 100, 8, 1, 2, 3, 1, 2)     // RadSAR_1843_official: Doppler in even / odd halves of 50 folded with the column's twiddle, range 2 x 45
 #undef RB_REG
     return 1;
 }

@@ -86,6 +86,10 @@ struct RdRegShape {
     static constexpr int E_BF = BF == 1 ? 0 : SH * pfa_inv(SH % (BF > 1 ? BF : 2), BF > 1 ? BF : 2);   // 1 (mod BF), 0 (mod SH)
     static_assert(BF == 1 || ((BF == 2 || BF == 4) && SH % 2 == 1 && SH * BF == S), "the range split needs coprime factors");
     static constexpr int LH = L / DF;                        // points per phase-A thread
+    // DF = 2 with an even half (L = 100): no coprime split exists, so the halves are the even / odd samples (plain decimation
+    // in time) and phase B folds them with the column's own twiddle: X[k] = E[k mod LH] + W_L^k O[k mod LH] (a per-thread
+    // constant: four FMAs per value instead of one packed FMA)
+    static constexpr bool TW = DF == 2 && LH % 2 == 0;
     static constexpr int HP = (LH + 1) / 2 * 2;              // tile offset between the halves (16-byte aligned)
     static constexpr int ROW = CR * S;                       // words between consecutive loops of one TX slot
     static constexpr int COLS_A = G * S, COLS_B = G * L;
@@ -104,7 +108,7 @@ struct RdRegShape {
     static constexpr int P = PMIN % 4 == 2 ? PMIN : PMIN + 2;
     static constexpr int TILE = COLS_A * P;                  // complex elements
     static_assert(L % 2 == 0, "phase A pairs neighbouring Doppler bins into 128-bit stores");
-    static_assert(DF == 1 || (DF == 2 && LH % 2 == 1), "the split needs coprime factors 2 and L/2");
+    static_assert(DF == 1 || DF == 2, "Doppler column: whole or in two halves");
     static constexpr size_t smem_bytes() {
         return (size_t)NTILE * TILE * sizeof(cf) + (size_t)NSTAGE * RAW_STAGE_W * 4 + 16 * sizeof(unsigned long long);
     }
@@ -117,9 +121,13 @@ struct RdRegParams {
     float* mag_out;            // see radar_range_doppler
     unsigned n_items;          // frames * items_per_frame
     int mag_antenna;
-    float2 winL[C::L];         // (w, w) pairs, [h][m] = Doppler window of input l = (h*LH + DF*m) mod L: one LDC.64 per packed multiply
+    float2 winL[C::L];         // (w, w) pairs, [h][m] = Doppler window of input m of class h (see rd_reg_doppler_input): one LDC.64 per packed multiply
     float winS[C::S];
+    cf twL[C::TW ? C::L : 1];  // W_L^k (twiddle mode of the Doppler split only)
 };
+// input index of sample m of residue class h
+template <class C>
+RB_HD constexpr int rd_reg_doppler_input(int h, int m) { return C::TW ? C::DF * m + h : (h * C::LH + C::DF * m) % C::L; }
 
 // int16 pair -> complex float on the conversion unit (two I2F.S16, the second with the .H1 selector): half the issue slots
 // of the LOP3/PRMT/LOP3/FADD2 form of iq_word and nothing on the FMA / ALU pipes, which phase A keeps busy; the conversion
@@ -154,13 +162,14 @@ RB_HD float rd_reg_sqrt(float x) {
 // every row offset a compile-time immediate for both classes (one copy of the code serves both).
 template <class C>
 RB_HD void rd_reg_doppler_load(const RdRegParams<C>& a, const uint32_t* raw, int col_shift, int h, cf (&v)[C::LH]) {
-    const uint32_t* lo = raw + col_shift + h * (C::LH * C::RAW_PITCH_W);
+    // twiddle mode: class h starts at row h and never wraps
+    const uint32_t* lo = raw + col_shift + h * ((C::TW ? 1 : C::LH) * C::RAW_PITCH_W);
     const uint32_t* hi = lo - C::L * C::RAW_PITCH_W;
     const float2* win = a.winL + h * C::LH;
 #pragma unroll
     for (int m = 0; m < C::LH; ++m) {
         // class 1 wraps when DF*m + LH >= L; class 0 never does (h = 0 makes lo and hi + L rows the same address)
-        const bool wraps = C::DF * m + C::LH >= C::L;
+        const bool wraps = !C::TW && C::DF * m + C::LH >= C::L;
         const uint32_t w = wraps ? (h ? hi : lo)[C::DF * m * C::RAW_PITCH_W] : lo[C::DF * m * C::RAW_PITCH_W];
         // the conversion unit serves one A warp per scheduler well (6843: 0.547 -> 0.519 ms); with two they queue (1843: 0.257 -> 0.262)
         const cf x = C::NA <= 4 ? iq_word_cvt(w) : iq_word(w);
@@ -205,20 +214,28 @@ template <class C>
 struct RdRegColumn {                      // one tile column as phase B sees it: value(s) applies the Doppler combine
     const cf* p;
     float sign;
-    RB_HD RdRegColumn(const cf* tile, int g, int d) {
-        if (C::DF == 1) { p = tile + (size_t)g * C::S * C::P + d; sign = 1.0f; }
+    cf w;
+    RB_HD RdRegColumn(const cf* tile, int g, int d, const cf* twL) {
+        sign = 1.0f; w = cmake(1.0f, 0.0f);
+        if (C::DF == 1) p = tile + (size_t)g * C::S * C::P + d;
         else {
             const int k = (d + C::L - C::L / 2) % C::L;
             sign = (k & 1) ? -1.0f : 1.0f;
+            if (C::TW) w = twL[k];
             p = tile + (size_t)g * C::S * C::P + k % C::LH;
         }
     }
-    RB_HD cf value(int s) const { return C::DF == 1 ? p[s * C::P] : cfma(sign, p[s * C::P + C::HP], p[s * C::P]); }
+    RB_HD cf value(int s) const {
+        if (C::DF == 1) return p[s * C::P];
+        const cf e = p[s * C::P], o = p[s * C::P + C::HP];
+        if (C::TW) return cmake(fmaf(w.x, o.x, fmaf(-w.y, o.y, e.x)), fmaf(w.x, o.y, fmaf(w.y, o.x, e.y)));
+        return cfma(sign, o, e);
+    }
 };
 // sigma = +1 for a = 0, -1 for a = 1.  Input m of class k_BF: sum_q x[(SH*q + BF*m) mod S] * W_BF^(q*k_BF)
 template <class C, int ODD>
-RB_HD void rd_reg_range_load(const cf* tile, int g, int d, float sigma, cf (&v)[C::SH]) {
-    const RdRegColumn<C> col(tile, g, d);
+RB_HD void rd_reg_range_load(const RdRegParams<C>& a, const cf* tile, int g, int d, float sigma, cf (&v)[C::SH]) {
+    const RdRegColumn<C> col(tile, g, d, a.twL);
 #pragma unroll
     for (int m = 0; m < C::SH; ++m) {
         if (C::BF == 1) v[m] = col.value(m);

@@ -27,7 +27,8 @@ static double check(int n_frames) {
     for (int k = 0; k < L; ++k) wl[k] = 0.5 - 0.5 * cos(2.0 * M_PI * k / (L - 1));
     for (int k = 0; k < S; ++k) ws[k] = 0.5 - 0.5 * cos(2.0 * M_PI * k / (S - 1));
     for (int h = 0; h < C::DF; ++h)
-        for (int m = 0; m < C::LH; ++m) { const float w = (float)wl[(h * C::LH + C::DF * m) % L]; a.winL[h * C::LH + m] = make_float2(w, w); }
+        for (int m = 0; m < C::LH; ++m) { const float w = (float)wl[rd_reg_doppler_input<C>(h, m)]; a.winL[h * C::LH + m] = make_float2(w, w); }
+    if (C::TW) for (int k = 0; k < L; ++k) a.twL[k] = cmake((float)cos(-2.0 * M_PI * k / L), (float)sin(-2.0 * M_PI * k / L));
     for (int k = 0; k < S; ++k) a.winS[k] = (float)ws[k];
     std::vector<cf> rd((size_t)n_frames * V * S * L);
     std::vector<float> mag((size_t)n_frames * S * L, -1.0f);
@@ -55,10 +56,10 @@ static double check(int n_frames) {
                 float* mg = ant == 0 ? mag.data() + (size_t)frame * S * L + d : nullptr;
                 cf v[C::SH];
                 if (odd) {
-                    rd_reg_range_load<C, 1>(tile.data(), g, d, ca ? -1.0f : 1.0f, v);
+                    rd_reg_range_load<C, 1>(a, tile.data(), g, d, ca ? -1.0f : 1.0f, v);
                     rd_reg_range_store<C, 1>(v, out + half, out - half, mg ? mg + half : nullptr, mg ? mg - half : nullptr);
                 } else {
-                    rd_reg_range_load<C, 0>(tile.data(), g, d, ca ? -1.0f : 1.0f, v);
+                    rd_reg_range_load<C, 0>(a, tile.data(), g, d, ca ? -1.0f : 1.0f, v);
                     rd_reg_range_store<C, 0>(v, out + half, out - half, mg ? mg + half : nullptr, mg ? mg - half : nullptr);
                 }
             }
@@ -106,6 +107,7 @@ int main() {
     r = check<RdRegShape<63, 70, 12, 2, 2, 3, 1>>(2); printf("63x70 G=2 DF=2: rel_l2 = %.3e\n", r); worst = fmax(worst, r);
     r = check<RdRegShape<100, 30, 8, 2, 1, 3, 1, 4>>(2); printf("100x30 G=2 BF=4: rel_l2 = %.3e\n", r); worst = fmax(worst, r);
     r = check<RdRegShape<64, 40, 4, 2, 1, 3, 1, 1>>(2); printf("64x40 G=2: rel_l2 = %.3e\n", r); worst = fmax(worst, r);
+    r = check<RdRegShape<90, 100, 8, 1, 2, 3, 1, 2>>(2); printf("90x100 G=1 DF=2 (twiddle) BF=2: rel_l2 = %.3e\n", r); worst = fmax(worst, r);
     printf("worst rel_l2 = %.3e\n", worst);
     return worst < 2e-6 ? 0 : 1;
 }
