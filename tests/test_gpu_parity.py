@@ -679,3 +679,48 @@ def test_nvtx_ranges_do_not_change_results(torch_cuda):
     assert res.returncode == 0, res.stderr[-2000:]
     line = [l for l in res.stdout.splitlines() if l.startswith("TOTAL")][0].split()
     assert int(line[1]) == want and line[2] == "range_doppler,range_angle,cfar,point_cloud"
+
+
+@pytest.mark.parametrize("name,geom", [("6843_RadVel_ods_20Hz", "ods"), ("1843_RadVel", "standard"), ("RadCloud", "standard"),
+                                       ("RadSAR_1843_official", "standard")])
+def test_register_resident_kernel_options_against_previous_kernels(torch_cuda, name, geom):
+    """Every option of radar_range_doppler through rd_reg_kernel (all four instantiated shapes: whole / split Doppler and
+    range columns, twiddle mode) against the previous kernels (RADAR_B200_RD_REG=0) and the oracle: window flags, magnitude
+    of one / every antenna, magnitude only, batches of 1 / 3 / 301 frames (fewer and more items than CTAs), and a cube that
+    is not 16-byte aligned (the bulk copies need the alignment: the call must fall back, not fail)."""
+    torch = torch_cuda
+    from oracle import radar_oracle as orc
+    cm = load_cfg(name, geom)
+    new = _engine_with_env(cm, "RADAR_B200_RD_REG", 1)
+    old = _engine_with_env(cm, "RADAR_B200_RD_REG", 0)
+    from mmwave_radar_processing_b200.synthetic import synth_batch_for_cfg
+    iq_all = synth_batch_for_cfg(cm, range(7))
+    big = torch.from_numpy(np.tile(iq_all, (43, 1, 1, 1, 1))).cuda()             # 301 frames
+    for f in (1, 3, 301):
+        x = big[:f]
+        for flags in (3, 0, 1, 2):
+            a, am = new.range_doppler(x, window_flags=flags, mag_antenna=0)
+            assert new.last_rd_kernel() == "rd_reg_kernel"
+            b, bm = old.range_doppler(x, window_flags=flags, mag_antenna=0)
+            assert old.last_rd_kernel() != "rd_reg_kernel"
+            assert rel_l2(a.cpu().numpy(), b.cpu().numpy()) < 1e-6 and rel_l2(am.cpu().numpy(), bm.cpu().numpy()) < 1e-6
+            if f > 1 and flags != 3:
+                continue
+            _, all_mag = new.range_doppler(x, window_flags=flags, want_rd=False, mag_antenna=-1)
+            assert rel_l2(all_mag.cpu().numpy(), a.abs().cpu().numpy()) < 1e-6
+            last = new.V - 1
+            _, one = new.range_doppler(x, window_flags=flags, want_rd=False, mag_antenna=last)
+            assert torch.equal(one, all_mag[:, last])
+    # frames repeat with period 7: identical inputs give identical outputs wherever they sit in the batch
+    a, _ = new.range_doppler(big, mag_antenna=0)
+    assert torch.equal(a[:7], a[294:301]) and torch.equal(a[7:14], a[140:147])
+    cube = orc.virtual_array(orc.iq_to_cube(iq_all[2]), cm.num_rx_antennas, cm.chirp_cfgs_per_loop, cm.frameCfg_loops)
+    assert rel_l2(a[2].cpu().numpy(), orc.range_doppler(cube)) < RD_TOL
+    # misaligned cube (8 bytes off a 16-byte boundary)
+    flat = torch.empty(big[:3].numel() + 8, dtype=torch.int16, device="cuda")
+    off = flat[4:4 + big[:3].numel()].view(big[:3].shape)
+    off.copy_(big[:3])
+    assert off.data_ptr() % 16 == 8
+    c, _ = new.range_doppler(off, mag_antenna=0)
+    assert new.last_rd_kernel() != "rd_reg_kernel"
+    assert rel_l2(c.cpu().numpy(), a[:3].cpu().numpy()) < 1e-6
