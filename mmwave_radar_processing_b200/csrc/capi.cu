@@ -152,6 +152,7 @@ int radar_ctx_create(const radar_shape* shape, int device, radar_ctx** out_ctx) 
     { const char* tp = std::getenv("RADAR_B200_SAR_TPR"); ctx->sar_tpr = tp ? std::atoi(tp) : 0; }
     { const char* sg = std::getenv("RADAR_B200_SAR_SEG"); ctx->sar_seg_chunks = sg ? std::atoi(sg) : 0; }
     { const char* r4 = std::getenv("RADAR_B200_RA_FFT4"); ctx->ra_fft4 = r4 ? std::atoi(r4) : 1; }
+    { const char* pa = std::getenv("RADAR_B200_SAR_PARTS"); ctx->sar_parts = pa ? std::atoi(pa) : 0; }
     { const char* ks = std::getenv("RADAR_B200_SAR_KSPLIT"); ctx->sar_ksplit = ks ? std::atoi(ks) : 0; }
     { const char* sm = std::getenv("RADAR_B200_SAR"); ctx->sar_mode = sm ? std::atoi(sm) : 0; }
     { const char* sv = std::getenv("RADAR_B200_RD_REG"); ctx->rd_reg = sv ? std::atoi(sv) : 1; }

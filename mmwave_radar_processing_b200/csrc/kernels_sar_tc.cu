@@ -203,6 +203,7 @@ struct SarTcArgs {
     // same fp32 additions in the same order as the in-place accumulation of ksplit == 1, so the image does not depend on
     // how the aperture is cut over CTAs (slices of the grid, which pick another ksplit, stay bit-identical to the full grid).
     int ksplit, segs_per_split;
+    int parts;            // 1: one array per segment (always with ksplit > 1; RADAR_B200_SAR_PARTS=1 forces it for ksplit == 1)
 };
 
 // MT accumulator tiles (128 directions each) per CTA, TPR threads per direction row (they split the elements of a chunk and
@@ -426,9 +427,9 @@ __global__ void __launch_bounds__(128 * MT * TPR + 64, 1) sar_tc_kernel(const __
                     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                     if (g_out < width) {
                         // ksplit > 1: this segment's own array, plain stores; ksplit == 1: accumulate in place
-                        cf* dst = a.beams + (a.ksplit > 1 ? (size_t)(seg0 + n_drained) * a.S * width : (size_t)0) + (size_t)s0 * width + g_out;
+                        cf* dst = a.beams + (a.parts ? (size_t)(seg0 + n_drained) * a.S * width : (size_t)0) + (size_t)s0 * width + g_out;
                         cf old[16];
-                        if (n_drained > 0 && a.ksplit == 1) {              // all loads in flight before the first store
+                        if (n_drained > 0 && !a.parts) {              // all loads in flight before the first store
 #pragma unroll
                             for (int i = 0; i < 16; ++i)
                                 old[i] = (s0 + i < a.S) ? __ldcg(dst + (size_t)i * width) : cmake(0.f, 0.f);
@@ -533,7 +534,7 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
     if (want_split < 1) want_split = 1;
     const int segs_per_split = (n_seg + want_split - 1) / want_split;
     const int ksplit = (n_seg + segs_per_split - 1) / segs_per_split;
-    const int n_part = ksplit > 1 ? n_seg : 1;
+    const int n_part = (ksplit > 1 || ctx->sar_parts) ? n_seg : 1;
 
     const size_t bblk_bytes = (size_t)n_chunks * 2 * NB * kTcKC * sizeof(float);
     const size_t posl_bytes = (size_t)3 * npad * sizeof(double);
@@ -555,7 +556,7 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
     RB_CUDA_OK(ctx, cudaGetLastError());
 
     SarTcArgs a{bblk, posl, posf, stepf, (ctx->sar_dbg & 32) ? nullptr : lin, dirs, npad, n_chunks, seg_chunks, G, S, SP, NB, g_begin, g_end, beams,
-                ksplit, segs_per_split};
+                ksplit, segs_per_split, n_part > 1 ? 1 : 0};
     const int tpr = ctx->sar_tpr > 0 ? ctx->sar_tpr : (mt == 2 ? 1 : 2);      // measured: 0.443 / 0.450 ms (2 tiles), 0.550 / 0.503 ms (1 tile)
     const int unr = ctx->sar_dbg & 15, cs = !(ctx->sar_dbg & 16);      // RADAR_B200_SAR_DBG: unroll of the element loop (0 = default), +16 = sincospif
 #define RB_SAR_TC_LAUNCH(MT_, TPR_, UNR_, CS_)                                                                               \

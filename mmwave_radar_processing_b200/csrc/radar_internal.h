@@ -45,6 +45,7 @@ struct radar_ctx {
     int sar_mode = 0;                             // RADAR_B200_SAR: 0 auto (tcgen05 when the shape fits), 1 FP32-pipe kernel, 2/3 tcgen05 with 1/2 tiles per CTA
     int sar_dbg = 0;                              // RADAR_B200_SAR_DBG: timing experiments of the tensor-core SAR kernel (results invalid)
     int sar_tpr = 0;                              // RADAR_B200_SAR_TPR: threads per direction row of the tensor-core SAR kernel (0 = default)
+    int sar_parts = 0;                            // RADAR_B200_SAR_PARTS=1: per-segment arrays (plain stores) even without a split
     int sar_ksplit = 0;                           // RADAR_B200_SAR_KSPLIT: CTA rows the aperture is cut into (0 = fill the SMs)
     int sar_seg_chunks = 0;                       // RADAR_B200_SAR_SEG: chunks (16 elements) per accumulation segment, 0 = automatic
     double* point_mirrors[16] = {nullptr};       // radar_ctx_set_point_mirrors: extra destinations of every packed point row
