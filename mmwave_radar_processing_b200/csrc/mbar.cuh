@@ -27,7 +27,7 @@ __device__ __forceinline__ void wait(uint64_t* bar, uint32_t parity) {
     do {
         asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                      : "=r"(ok) : "r"(addr), "r"(parity), "r"(20000u) : "memory");
-        if (!ok && ++spins > (1u << 24)) __trap();       // a lost arrive must not hang the device
+        if (!ok && ++spins > (1u << 27)) __trap();       // a lost arrive must not hang the device (tens of seconds of polling)
     } while (!ok);
 }
 // global -> shared bulk copy (16-byte aligned addresses and size), completion counted in bytes on `bar`
