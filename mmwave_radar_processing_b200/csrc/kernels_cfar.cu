@@ -269,33 +269,39 @@ __device__ __forceinline__ void os_ladder_cells(const CfarArgs& a, const float* 
     const int wr = 2 * cr + 1, wd = 2 * cd + 1;
     const int nvr = a.rows - 2 * cr, nvd = a.cols - 2 * cd;
     const int n_cells = a.rows * a.cols;
-    // -- levels: median of 64 samples on a regular grid (rank by counting, ties by index), times lvl_mul
-    if (warp == 0) {
-        const int stride = n_cells / 64;
-        const int i0 = lane * stride + stride / 2, i1 = (lane + 32) * stride + stride / 2;
-        const int y0 = (int)a.div_cols.div((uint32_t)i0), y1 = (int)a.div_cols.div((uint32_t)i1);
-        const float v0 = map[y0 * a.pitch + (i0 - y0 * a.cols)], v1 = map[y1 * a.pitch + (i1 - y1 * a.cols)];
-        int r0 = 0, r1 = 0;
-        for (int src = 0; src < 32; ++src) {
-            const float s0 = __shfl_sync(0xffffffffu, v0, src), s1 = __shfl_sync(0xffffffffu, v1, src);
-            r0 += (s0 < v0 || (s0 == v0 && src < lane)) + (s1 < v0);
-            r1 += (s0 < v1 || s0 == v1) + (s1 < v1 || (s1 == v1 && src < lane));
+    // -- levels: median of 64 samples on a regular grid (rank by counting, ties by index: four threads per sample, 16
+    //    comparisons each), times lvl_mul
+    {
+        float* samp = reinterpret_cast<float*>(lad);        // the sliding-sum words are written later
+        if (threadIdx.x < 64) {
+            const int stride = n_cells / 64;
+            samp[threadIdx.x] = map[threadIdx.x * stride + stride / 2];       // ladder path: the map is unpadded
         }
-        if (lane == 0) lvl[8] = 0.0f;
-        __syncwarp();
-        if (r0 == 31) lvl[8] = v0;
-        if (r1 == 31) lvl[8] = v1;
-        __syncwarp();
-        if (lane < 4) {
-            float l = lvl[8] * a.lvl_mul[lane];
+        if (threadIdx.x == 0) lvl[8] = 0.0f;
+        __syncthreads();
+        const int i = threadIdx.x >> 2, part = threadIdx.x & 3;
+        const float v = samp[i];
+        int rank = 0;
+#pragma unroll
+        for (int jj = 0; jj < 16; ++jj) {
+            const int jx = part * 16 + jj;
+            const float sj = samp[jx];
+            rank += (sj < v || (sj == v && jx < i)) ? 1 : 0;
+        }
+        rank += __shfl_xor_sync(0xffffffffu, rank, 1);
+        rank += __shfl_xor_sync(0xffffffffu, rank, 2);
+        if (part == 0 && rank == 31) lvl[8] = v;
+        __syncthreads();
+        if (threadIdx.x < 4) {
+            float l = lvl[8] * a.lvl_mul[threadIdx.x];
             // a negative or NaN median (maps are magnitudes, but detect() takes anything): the level moves to +inf, where it
             // is never a lower level and, with every finite cell below it, never rules a detection out
             if (!(l >= 0.0f)) l = __int_as_float(0x7f800000);
             const double th = a.alpha * (double)l;           // x > th  <=>  alpha*l < x  (l is a lower level for this cell)
             float f = (float)th;                             // largest float <= th: x > th <=> x > f for float x
             if ((double)f > th) f = __uint_as_float(__float_as_uint(f) - 1u);
-            lvl[lane] = l;
-            lvl[4 + lane] = f;
+            lvl[threadIdx.x] = l;
+            lvl[4 + threadIdx.x] = f;
         }
     }
     __syncthreads();
@@ -542,8 +548,6 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
     const float* src = a.maps + m * map_cells + (long long)R0 * src_pitch + C0;
     double* noise_dst = a.noise_out ? a.noise_out + m * map_cells + (long long)R0 * npitch + C0 : nullptr;
     const uint8_t* rsel = a.row_select ? a.row_select + m * map_rows + R0 : nullptr;
-    CfarArgs la = a;
-    la.row_select = rsel;
     // map -> shared memory.  Unpadded layout (ladder path): ONE bulk copy of the TMA engine from the 16-byte aligned address
     // below the map (the copy may run a few bytes into the next map, so the last map of the batch takes the plain loop when
     // its end is not aligned); otherwise batches of independent loads (one load latency per batch, not per cell).
@@ -610,9 +614,13 @@ __global__ void __launch_bounds__(kCfarThreads, 4) cfar_kernel(const __grid_cons
             else if (a.tr == 5 && a.gr == 3 && a.td == 5 && a.gd == 2) os_ladder_cells<5, 3, 5, 2>(a, map, mask, lad, work_cell, &work_n, ladder_lvl);
             else os_ladder_cells<0, 0, 0, 0>(a, map, mask, lad, work_cell, &work_n, ladder_lvl);
         } else if (counting) {
+            CfarArgs la = a;                                   // per-map row_select (a local copy only on the paths that read it)
+            la.row_select = rsel;
             os_count_dispatch(la, map, mask, work_cell, work_t, &work_n);
         } else if (a.kind == RADAR_CFAR_OS) {
             const int wcells = (2 * cr + 1) * (2 * cd + 1);
+            CfarArgs la = a;
+            la.row_select = rsel;
             if (wcells <= 32 * 8) os_cells<8>(la, map, mask, noise_dst, npitch);
             else if (wcells <= 32 * 16) os_cells<16>(la, map, mask, noise_dst, npitch);
             else os_cells<32>(la, map, mask, noise_dst, npitch);
