@@ -18,7 +18,9 @@ pass of the hot path over the whole stream; with N > 1 the stream is cut into N 
 call (``FramePipeline.run_host``): pinned host int16 frames in, host point clouds out, copies inside the timed region.
 ``roofline`` is for the dominant kernel (the fused range-Doppler kernel) and lists every stage kernel under ``kernels``;
 ``cpu_baseline`` is the numpy oracle port timed on this box's host cores (rank 0, N=1 only).  ``extra`` (N=1) carries
-the second single-GPU workload (configs/1843_RadVel.cfg, BASELINE.json configs[1]) and the CA-CFAR-2D detector timing.
+the second single-GPU workload (configs/1843_RadVel.cfg, BASELINE.json configs[1]), the CA-CFAR-2D detector timing, the
+other BASELINE shapes (RadCloud, RadSAR_1843_official, RadarHD) through the same pipeline and the high-resolution
+range-azimuth maps of configs[2] (RadarHD, 256 / 1024 angle bins).
 ``--impl reference`` times the CPU path on all host cores and prints the same line shape.
 ``--workload sar``: the voxel-sharded synthetic-array image (BASELINE.json configs[3]), images/s + tensor-pipe roofline.
 """
@@ -325,15 +327,18 @@ def extra_single_gpu_lines(torch, dev, peak):
     from mmwave_radar_processing_b200.synthetic import synth_batch_for_cfg
     extras = []
     for wl, det_name, det in (("1843_RadVel", "os_cfar_2d", DETECTOR), ("1843_RadVel", "ca_cfar_2d", DETECTOR_CA),
-                              (DEFAULT_WORKLOAD, "ca_cfar_2d", DETECTOR_CA)):
+                              (DEFAULT_WORKLOAD, "ca_cfar_2d", DETECTOR_CA),
+                              # the other BASELINE shapes (configs[2], configs[3]) through the same pipeline
+                              ("RadCloud", "os_cfar_2d", DETECTOR), ("RadSAR_1843_official", "os_cfar_2d", DETECTOR),
+                              ("RadarHD", "os_cfar_2d", DETECTOR)):
         cfg_name, geom, az, el, ra_ants = WORKLOADS[wl]
         cm = load_cfg(cfg_name, geom)
-        F = 4096
+        F = 4096 if wl in ("1843_RadVel", DEFAULT_WORKLOAD, "RadCloud") else 2048
         pipe = FramePipeline(cm, detector=DetectorSpec(**det), az_antenna_idxs=az, el_antenna_idxs=el, max_dets=MAX_DETS,
                              with_range_angle=True, ra_antennas=ra_ants, device=dev)
         uniq = synth_batch_for_cfg(cm, range(N_UNIQUE))
         iq_dev = torch.from_numpy(np.concatenate([uniq] * (F // N_UNIQUE))).to(dev)
-        steps = 50
+        steps = 50 if wl in ("1843_RadVel", DEFAULT_WORKLOAD) else 20
         ms_total, stage_ms, out = time_stage_loop(torch, pipe, iq_dev, steps, 5)
         pts = int(out["offsets"][F].item())
         kernels, bytes_pf, step_bytes = stage_rooflines(cm, wl, F, stage_ms, ms_total / steps, pts, peak, pipe.engine.last_rd_kernel())
@@ -353,6 +358,30 @@ def extra_single_gpu_lines(torch, dev, peak):
                            "points_per_step": pts})
         del pipe, iq_dev, out
         torch.cuda.empty_cache()
+    # BASELINE.json configs[2]: high-resolution range-azimuth maps (RadarHD, all 8 antennas)
+    from mmwave_radar_processing_b200.engine import RadarEngine
+    cm = load_cfg("RadarHD", "standard")
+    eng = RadarEngine(cm.num_rx_antennas, cm.get_num_adc_samples(0), cm.chirp_cfgs_per_loop, cm.frameCfg_loops, device=dev)
+    F = 2048
+    iq_dev = torch.from_numpy(np.concatenate([synth_batch_for_cfg(cm, range(64))] * (F // 64))).to(dev)
+    for bins in (256, 1024):
+        out = torch.empty((F, eng.S, bins), dtype=torch.float32, device=dev)
+        for _ in range(5):
+            eng.range_angle(iq_dev, 0, None, bins, out=out)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(20):
+            eng.range_angle(iq_dev, 0, None, bins, out=out)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 20
+        alg = 4 * eng.R * eng.S * eng.cpl + 4 * eng.S * bins
+        extras.append({"workload": f"configs/RadarHD.cfg range-azimuth map, {bins} angle bins, {eng.V} antennas", "kernel": "range_angle_kernel",
+                       "frames_per_step": F, "ms_per_launch": ms, "value": F / ms * 1e3, "unit": "frames/s",
+                       "algorithmic_bytes_per_frame": alg, "frac_of_hbm": alg * F / ms / 1e6 / peak})
+        del out
+    del iq_dev
+    torch.cuda.empty_cache()
     return extras
 
 
