@@ -291,6 +291,23 @@ int radar_doppler_azimuth(radar_ctx* ctx, const void* cube, int n_frames, int n_
 int radar_chirp_zoom(radar_ctx* ctx, const void* range_cube, int n_frames, int n_ant, int k_begin, int k_end,
                      const double* turns, int n_out, void* zoom_out, void* stream);
 
+/* radar_chirp_zoom without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments, same kernels and same results as radar_chirp_zoom, but the per-call twiddle table [num_loops][n_out]
+ * lives in a file-scope device array of the library (512 KiB, held by every GPU that loads the library until exit)
+ * instead of the context's cudaMalloc'ed scratch; the call makes no cudaMalloc / cudaFree and calls no allocating
+ * library routine.
+ *   limit  : num_loops * n_out <= radar_chirp_zoom_static_capacity() (= 65536 twiddles); larger requests return
+ *            RADAR_E_UNSUPPORTED with a message naming the limit - use radar_chirp_zoom for those
+ *   set-up : the first call on a device looks the array's device address up (cudaGetSymbolAddress, once per device);
+ *            a call with n_frames == 0 does only that, e.g. before a graph capture starts
+ *   sharing: all calls on a device (any ctx) share the array; every call rewrites the entries it reads before reading
+ *            them (nothing of the previous call survives into the result), so calls ordered on one stream are safe;
+ *            calls that overlap on the GPU (different streams without a dependency) RACE on it. */
+int radar_chirp_zoom_static(radar_ctx* ctx, const void* range_cube, int n_frames, int n_ant, int k_begin, int k_end,
+                            const double* turns, int n_out, void* zoom_out, void* stream);
+int radar_chirp_zoom_static_capacity(void);
+
 /* Column-wise reduction over the selected rows of every map: MicroDopplerProcessor.process takes np.max of |RD|
  * over the range rows inside target_ranges (processors/micro_doppler_resp.py:104-108).
  *   maps float [n_maps][rows][cols]; row_select device uint8[rows] or NULL (all rows); op RADAR_REDUCE_*;

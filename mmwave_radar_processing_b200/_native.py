@@ -63,6 +63,8 @@ SIGNATURES = {
     "radar_ctx_set_point_mirrors": (_I, [_P, _P, _I, _I]),
     "radar_doppler_azimuth": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _I, _I, _P, _P]),
     "radar_chirp_zoom": (_I, [_P, _P, _I, _I, _I, _I, _P, _I, _P, _P]),
+    "radar_chirp_zoom_static": (_I, [_P, _P, _I, _I, _I, _I, _P, _I, _P, _P]),
+    "radar_chirp_zoom_static_capacity": (_I, []),
     "radar_row_reduce": (_I, [_P, _P, _I, _I, _I, _P, _I, _P, _P]),
     "radar_ego_velocity": (_I, [_P, _P, _P, _I, _I, _P, _P, _I, _I, _I, C.c_double, C.c_double, _P, _P, _P, _P, _P]),
 }

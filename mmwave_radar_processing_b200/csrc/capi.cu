@@ -350,6 +350,16 @@ int radar_chirp_zoom(radar_ctx* ctx, const void* range_cube, int n_frames, int n
                              reinterpret_cast<cf*>(zoom_out), (cudaStream_t)stream);
 }
 
+int radar_chirp_zoom_static(radar_ctx* ctx, const void* range_cube, int n_frames, int n_ant, int k_begin, int k_end, const double* turns,
+                            int n_out, void* zoom_out, void* stream) {
+    RB_ENTER(ctx);
+    if (n_frames > 0 && (!range_cube || !turns || !zoom_out)) return set_error(ctx, RADAR_E_INVALID, "null pointer");
+    return launch_chirp_zoom_static(ctx, reinterpret_cast<const cf*>(range_cube), n_frames, n_ant, k_begin, k_end, turns, n_out,
+                                    reinterpret_cast<cf*>(zoom_out), (cudaStream_t)stream);
+}
+
+int radar_chirp_zoom_static_capacity(void) { return chirp_zoom_static_capacity(); }
+
 int radar_row_reduce(radar_ctx* ctx, const float* maps, int n_maps, int rows, int cols, const uint8_t* row_select, int op, float* out,
                      void* stream) {
     RB_ENTER(ctx);

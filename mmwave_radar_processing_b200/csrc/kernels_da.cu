@@ -14,6 +14,7 @@
 // Doppler-shifted range-Doppler cube that radar_range_doppler already produces, so the kernel starts from that cube.
 // The inner dimension (antennas, 4..12) is far too short for a tensor-core GEMM in a precision that keeps 1e-4
 // (TF32 does not); the zero-padded angle DFT is Horner's rule on the FP32 pipe with the antenna samples in registers.
+#include <mutex>
 #include "radar_internal.h"
 #include "rd_core.cuh"
 
@@ -155,6 +156,73 @@ int launch_chirp_zoom(radar_ctx* ctx, const cf* range_cube, int n_frames, int n_
     CzArgs a{range_cube, S, L, k_begin, k_end, n_out, tw, out};
     const long long grid = (long long)n_frames * n_ant;
     if (grid > 0x7fffffffLL) return set_error(ctx, RADAR_E_INVALID, "too many frames in one call");
+    chirp_zoom_kernel<<<(unsigned)grid, kDaThreads, 0, st>>>(a);
+    RB_CUDA_OK(ctx, cudaGetLastError());
+    return RADAR_OK;
+}
+
+// ---- zoom Doppler transform without any allocation (radar_chirp_zoom_static) ------------------------------------------
+// Same two kernels as launch_chirp_zoom, but the per-call twiddle table lives in a file-scope device array instead of the
+// context's cudaMalloc'ed scratch, so the call allocates nothing (CUDA graph capture, serving loops, harnesses that forbid
+// cudaMalloc).  Every GPU that loads the library holds the array (kZoomStaticEntries * 8 bytes = 512 KiB) until exit.
+// All calls on a device share it: the entries [0, L*n_out) are rewritten by zoom_twiddle_static_kernel at the start of every
+// call (nothing has to start at zero, nothing of the previous call is read), and two calls that overlap on the GPU
+// (different streams, no dependency) race on it.
+constexpr int kZoomStaticEntries = 1 << 16;            // twiddles: num_loops * n_out <= 65536
+constexpr int kZoomStaticDevices = 64;
+static __device__ __align__(256) cf g_zoom_tw_static[kZoomStaticEntries];
+// In host code `g_zoom_tw_static` is only a handle; the device address is looked up once per device, with that device
+// current, and cached here.
+static cf* g_zoom_tw_addr[kZoomStaticDevices] = {nullptr};
+static std::mutex g_zoom_tw_mutex;
+
+// device code may name the array directly: the table builder does, the transform kernel takes the looked-up address
+__global__ void zoom_twiddle_static_kernel(const double* __restrict__ turns, int L, int J) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= L * J) return;
+    const int l = i / J, j = i - l * J;
+    double ph = (double)l * turns[j];
+    ph -= rint(ph);
+    double s, c;
+    sincospi(-2.0 * ph, &s, &c);
+    g_zoom_tw_static[i] = cmake((float)c, (float)s);
+}
+
+static int zoom_static_table(radar_ctx* ctx, cf** out) {
+    int dev = -1;
+    RB_CUDA_OK(ctx, cudaGetDevice(&dev));
+    if (dev != ctx->device) return set_error(ctx, RADAR_E_INVALID, "device %d is current, the context lives on %d", dev, ctx->device);
+    if (dev < 0 || dev >= kZoomStaticDevices) return set_error(ctx, RADAR_E_UNSUPPORTED, "device index %d beyond %d", dev, kZoomStaticDevices - 1);
+    std::lock_guard<std::mutex> lock(g_zoom_tw_mutex);
+    if (!g_zoom_tw_addr[dev]) {
+        cf* p = nullptr;
+        RB_CUDA_OK(ctx, cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_zoom_tw_static));
+        if (!p) return set_error(ctx, RADAR_E_CUDA, "cudaGetSymbolAddress returned a null address");
+        g_zoom_tw_addr[dev] = p;
+    }
+    *out = g_zoom_tw_addr[dev];
+    return RADAR_OK;
+}
+
+int chirp_zoom_static_capacity() { return kZoomStaticEntries; }
+
+int launch_chirp_zoom_static(radar_ctx* ctx, const cf* range_cube, int n_frames, int n_ant, int k_begin, int k_end,
+                             const double* turns, int n_out, cf* out, cudaStream_t st) {
+    const int S = ctx->shape.num_samples, L = ctx->shape.num_loops;
+    if (n_ant <= 0 || n_out <= 0) return set_error(ctx, RADAR_E_INVALID, "empty antenna list or frequency list");
+    if (k_begin < 0 || k_end > S || k_begin > k_end) return set_error(ctx, RADAR_E_INVALID, "range rows [%d, %d) outside [0, %d)", k_begin, k_end, S);
+    if ((long long)L * n_out > kZoomStaticEntries)
+        return set_error(ctx, RADAR_E_UNSUPPORTED, "radar_chirp_zoom_static: num_loops * n_out = %d * %d exceeds the static twiddle table (%d entries); use radar_chirp_zoom",
+                         L, n_out, kZoomStaticEntries);
+    cf* tw = nullptr;
+    if (int rc = zoom_static_table(ctx, &tw)) return rc;          // set-up: also what a call with n_frames == 0 does
+    if (n_frames <= 0 || k_begin == k_end) return RADAR_OK;
+    const long long grid = (long long)n_frames * n_ant;
+    if (grid > 0x7fffffffLL) return set_error(ctx, RADAR_E_INVALID, "too many frames in one call");
+    const int n_tw = L * n_out;
+    zoom_twiddle_static_kernel<<<(n_tw + 255) / 256, 256, 0, st>>>(turns, L, n_out);
+    RB_CUDA_OK(ctx, cudaGetLastError());
+    CzArgs a{range_cube, S, L, k_begin, k_end, n_out, tw, out};
     chirp_zoom_kernel<<<(unsigned)grid, kDaThreads, 0, st>>>(a);
     RB_CUDA_OK(ctx, cudaGetLastError());
     return RADAR_OK;

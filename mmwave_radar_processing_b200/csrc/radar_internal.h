@@ -118,6 +118,9 @@ int launch_doppler_azimuth(radar_ctx* ctx, const cf* cube, int n_frames, int n_a
                            cudaStream_t st);
 int launch_chirp_zoom(radar_ctx* ctx, const cf* range_cube, int n_frames, int n_ant, int k_begin, int k_end,
                       const double* turns, int n_out, cf* out, cudaStream_t st);
+int launch_chirp_zoom_static(radar_ctx* ctx, const cf* range_cube, int n_frames, int n_ant, int k_begin, int k_end,
+                             const double* turns, int n_out, cf* out, cudaStream_t st);
+int chirp_zoom_static_capacity();
 int launch_row_reduce(radar_ctx* ctx, const float* maps, int n_maps, int rows, int cols, const uint8_t* row_select,
                       int op, float* out, cudaStream_t st);
 int launch_ego_velocity(radar_ctx* ctx, const double* points, const int32_t* offsets, int n_frames, int dims,

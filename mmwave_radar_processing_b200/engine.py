@@ -319,6 +319,25 @@ class RadarEngine:
                                             nat.ptr(tt), tt.numel(), nat.ptr(out), _stream_ptr()), self.ctx)
         return out
 
+    def chirp_zoom_static(self, range_cube: torch.Tensor, turns: torch.Tensor, out: torch.Tensor, k_begin: int = 0,
+                          k_end: Optional[int] = None) -> torch.Tensor:
+        """``chirp_zoom`` through ``radar_chirp_zoom_static``: the twiddle table lives in a static device array of the
+        library (L * J <= 65536), so neither the library nor this method allocates - the caller passes ``turns`` (float64
+        device tensor [J]) and ``out`` (complex64 [F, n_ant, k_end-k_begin, J]).  No counterpart in the reference; calls
+        that overlap on the GPU race on the shared table."""
+        if range_cube.dtype != torch.complex64 or range_cube.dim() != 4 or tuple(range_cube.shape[2:]) != (self.S, self.L) \
+                or not range_cube.is_contiguous():
+            raise ValueError("range_cube must be a contiguous complex64 [F, n_ant, S, L] tensor")
+        f, n_ant = range_cube.shape[:2]
+        k_end = self.S if k_end is None else k_end
+        if turns.dtype != torch.float64 or turns.dim() != 1 or not turns.is_cuda or not turns.is_contiguous():
+            raise ValueError("turns must be a contiguous float64 device tensor [J]")
+        if out.dtype != torch.complex64 or tuple(out.shape) != (f, n_ant, k_end - k_begin, turns.numel()) or not out.is_contiguous():
+            raise ValueError("out must be a contiguous complex64 [F, n_ant, k_end-k_begin, J] tensor")
+        nat.check(self.lib.radar_chirp_zoom_static(self.ctx, nat.ptr(range_cube), f, n_ant, int(k_begin), int(k_end),
+                                                   nat.ptr(turns), turns.numel(), nat.ptr(out), _stream_ptr()), self.ctx)
+        return out
+
     def row_reduce(self, maps: torch.Tensor, row_select=None, op: str = "max") -> torch.Tensor:
         """maps float32 [n, rows, cols] -> float32 [n, cols]: max / mean over the selected rows."""
         if maps.dtype != torch.float32 or maps.dim() != 3 or not maps.is_contiguous():
