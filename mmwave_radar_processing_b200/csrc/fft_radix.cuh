@@ -275,6 +275,12 @@ template <> struct Dft<14> : DftPfa<7, 2> {};
 template <> struct Dft<15> : DftPfa<5, 3> {};
 template <> struct Dft<20> : DftPfa<5, 4> {};
 template <> struct Dft<30> : DftPfa<5, 6> {};
+// whole range / Doppler axes of the register-resident kernels (rd_reg.cuh, sar_range_fft_reg_kernel)
+template <> struct Dft<63> : DftPfa<7, 9> {};
+template <> struct Dft<70> : DftPfa<7, 10> {};
+template <> struct Dft<40> : DftPfa<5, 8> {};
+template <> struct Dft<35> : DftPfa<5, 7> {};
+template <> struct Dft<45> : DftPfa<5, 9> {};
 
 template <> struct Dft<16> {
     RB_HD static void run(cf* v) {

@@ -1,4 +1,4 @@
-// K5a on the 5th-generation tensor cores: the synthetic-array beamformer as a split-precision TF32 GEMM (tcgen05 + TMEM).
+// K5a on the 5th-generation tensor cores: the synthetic-array beamformer as a split-precision FP16 GEMM (tcgen05 + TMEM).
 //
 // Reference arithmetic (processors/simple_synthetic_array_beamformer_processor_multiFrame.py:499-585):
 //   out[:, g] = FFT_S( hanning(S) * sum_n hamming(N)[n] * x[s, n] * exp(+2 pi i (d_g . p_n) / lambda) )
@@ -11,11 +11,16 @@
 //   (d.p)/lambda reaches 1e2..1e4 turns, so it is reduced modulo 1 in fp64 before the fp32 sincospi - and writes it
 //   straight into shared memory in the UMMA canonical K-major layout (no swizzle: 8-row x 16-byte core matrices).
 // * B is prepared once per call (sar_tc_prep_kernel) in global memory in exactly that layout, chunk by chunk, so a CTA
-//   moves a chunk (hi and lo, 48 KB for S = 90) with ONE bulk copy of the TMA engine (cp.async.bulk, completion counted
+//   moves a chunk (hi and lo, 48 KB for S = 90, 32 aperture elements) with ONE bulk copy of the TMA engine (cp.async.bulk, completion counted
 //   on an mbarrier) - no thread touches it.
-// * TF32 keeps 11 significant bits, far from the 1e-4 bar, so both operands are split  v = hi + lo  (hi = v rounded to
-//   TF32, lo = v - hi exactly) and three MMAs accumulate  hi.hi + hi.lo + lo.hi  in the fp32 TMEM accumulator: relative
-//   error ~2^-21 per product.  The dropped lo.lo term is ~2^-22.
+// * One 16-bit operand keeps 11 significant bits, far from the 1e-4 bar, so both operands are split  v = hi + lo  (hi = v
+//   rounded to FP16, lo = v - hi rounded to FP16) and three MMAs accumulate  hi.hi + hi.lo + lo.hi  in the fp32 TMEM
+//   accumulator: relative error ~2^-21 per product, the dropped lo.lo term is ~2^-22.  FP16 rather than TF32 because
+//   kind::f16 runs at twice the TF32 rate (K = 16 per instruction instead of 8) for the same 11 + 11 bits.  FP16's narrow
+//   exponent is handled by exact power-of-two scales: the steering coefficients (|w| <= 1) are scaled by 2^13, the aperture
+//   samples by the power of two that brings the largest |x| just below 2^15 (sar_tc_max_kernel finds it), so hi and lo
+//   of everything that matters are normal numbers; the range-FFT kernel multiplies the beams by the inverse power of two
+//   (exact), so the scales leave no trace in the result.
 // * One thread issues tcgen05.mma; tcgen05.commit arrives on an mbarrier per shared-memory stage, so generating chunk
 //   c+1 overlaps the MMAs of chunk c (two stages).  The accumulators (128 lanes x Nb columns per tile, MT tiles per CTA so
 //   a B chunk is reused for 128 MT directions) stay in TMEM for the whole K loop and are read once with tcgen05.ld.
@@ -23,18 +28,70 @@
 //   TMEM and summed in ordinary fp32 (see the drain in sar_tc_kernel).
 // * The beams go to a scratch array [S][width] (coalesced: lanes = directions); sar_range_fft_kernel applies Hann and the
 //   range FFT per direction with the shared-memory FFT of the range-Doppler family.
+#include <cuda_fp16.h>
 #include "radar_internal.h"
 #include "rd_core.cuh"
+#include "fft_radix.cuh"
 
 namespace rb {
 
-constexpr int kTcKC = 32;                 // real k-values per chunk (= 16 aperture elements); 4 MMA k-steps of 8
-constexpr int kTcElems = kTcKC / 2;
-constexpr int kTcATile = 128 * kTcKC;     // floats of one A tile (128 rows)
+constexpr int kTcKC = 64;                 // real k-values (halves) per chunk row = 128 bytes; 4 MMA k-steps of 16
+constexpr int kTcElems = kTcKC / 2;       // aperture elements per chunk: one 32-bit word (Re, Im as two halves) each
+constexpr int kTcATile = 128 * kTcElems;  // 32-bit words of one A tile (128 rows)
+constexpr int kTcLin = 16;                // elements of one "equispaced" unit (two per chunk)
 constexpr int kTcFftDirs = 32;
+constexpr float kTcAScale = 8192.0f;      // 2^13: steering coefficients as FP16 hi + lo without subnormals
 
-__host__ __device__ inline int tc_canon(int row, int k) {   // float index inside a K-major no-swizzle tile, kTcKC wide
-    return ((row >> 3) * (kTcKC / 4) + (k >> 2)) * 32 + (row & 7) * 4 + (k & 3);
+// word index of element n (0..31) of row `row` inside a K-major no-swizzle tile: core matrices of 8 rows x 16 bytes
+__host__ __device__ inline int tc_canon(int row, int n) {
+    return ((row >> 3) * (kTcElems / 4) + (n >> 2)) * 32 + (row & 7) * 4 + (n & 3);
+}
+
+// FP16 hi / lo words of the complex value (re, im): low half = re (k = 2n), high half = im (k = 2n + 1)
+__device__ __forceinline__ void split_h2(float re, float im, uint32_t* hi, uint32_t* lo) {
+    const __half2 h = __floats2half2_rn(re, im);
+    const float2 hf = __half22float2(h);
+    const __half2 l = __floats2half2_rn(re - hf.x, im - hf.y);
+    *hi = *reinterpret_cast<const uint32_t*>(&h);
+    *lo = *reinterpret_cast<const uint32_t*>(&l);
+}
+
+// Power-of-two scale of the aperture samples from the largest |x| of the call: max * scale in [2^14, 2^15).
+__device__ __forceinline__ int sar_scale_exp(float mx) {
+    if (!(mx > 0.0f) || mx > 3.0e38f) return 0;             // empty / all-zero / non-finite input: no scaling
+    int e;
+    frexpf(mx, &e);                                          // mx = m 2^e, m in [1/2, 1)
+    e = e < -100 ? -100 : (e > 100 ? 100 : e);
+    return 15 - e;
+}
+
+// One thread per aperture element n (coalesced rows of the [S][N] cube), blockIdx.y cuts the range rows: the Hamming weight
+// of n is formed once per thread (fp64 cospi) and stored as a float for sar_tc_prep_kernel, the largest |x hamming| of
+// the call goes to max_bits.
+constexpr int kTcMaxThreads = 128;
+__global__ void __launch_bounds__(kTcMaxThreads) sar_tc_max_kernel(const cf* __restrict__ aperture, int S, int N, float* __restrict__ hamf,
+                                                                   uint32_t* __restrict__ max_bits) {
+    __shared__ float red[kTcMaxThreads / 32];
+    const int n = blockIdx.x * kTcMaxThreads + threadIdx.x;
+    float m = 0.0f;
+    if (n < N) {
+        const float ham = (float)(N > 1 ? 0.54 - 0.46 * cospi(2.0 * (double)n / (double)(N - 1)) : 1.0);
+        if (blockIdx.y == 0) hamf[n] = ham;
+        const int rows = (S + gridDim.y - 1) / gridDim.y;
+        const int s0 = blockIdx.y * rows, s1 = min(S, s0 + rows);
+#pragma unroll 4
+        for (int r = s0; r < s1; ++r) {
+            const cf x = cscale(__ldg(aperture + (size_t)r * N + n), ham);
+            m = fmaxf(m, fmaxf(fabsf(x.x), fabsf(x.y)));     // fmaxf drops NaNs: they reach the image through the MMAs
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < kTcMaxThreads / 32; ++w) m = fmaxf(m, red[w]);
+        atomicMax(max_bits, __float_as_uint(m));             // non-negative floats order like their bit patterns
+    }
 }
 
 // ---- operand preparation -----------------------------------------------------------------------------------------
@@ -43,18 +100,14 @@ struct SarPrepArgs {
     int S, N, SP, NB, n_chunks;
     const double* pos;    // [3][N]
     double inv_lambda;
-    float* bblk;          // [n_chunks][2][NB * kTcKC]
+    uint32_t* bblk;       // [n_chunks][2][NB * kTcElems] words (hi block, lo block)
     double* posl;         // [3][n_chunks * kTcElems]  positions / lambda, zero padded
     float* posf;          // [6][n_chunks * kTcElems]  the same as float pairs: rows 2a = hi, 2a+1 = lo of axis a
-    float* stepf;         // [6][n_chunks]  per-axis element spacing / lambda (float hi / lo pairs) of an equispaced chunk
-    uint8_t* lin;         // [n_chunks]     1 = the chunk is an arithmetic progression to 1e-9 wavelengths (and has no padding)
+    float* stepf;         // [6][n_units]  per-axis element spacing / lambda (float hi / lo pairs) of an equispaced unit
+    uint8_t* lin;         // [n_units]     1 = the unit (kTcLin elements) is an arithmetic progression to 1e-9 wavelengths (no padding)
+    const uint32_t* max_bits;   // largest |x hamming| of the call (float bits), from sar_tc_max_kernel
+    const float* hamf;    // [N] np.hamming(N) as floats, from sar_tc_max_kernel
 };
-
-__device__ __forceinline__ float tf32_round(float v) {
-    uint32_t r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
-    return __uint_as_float(r);
-}
 
 __global__ void __launch_bounds__(256) sar_tc_prep_kernel(const __grid_constant__ SarPrepArgs a) {
     const int c = blockIdx.x;
@@ -67,43 +120,44 @@ __global__ void __launch_bounds__(256) sar_tc_prep_kernel(const __grid_constant_
         a.posf[(size_t)(2 * axis) * npad + n] = vh;
         a.posf[(size_t)(2 * axis + 1) * npad + n] = (float)(v - (double)vh);
     }
-    if (threadIdx.x == 0) {
-        // equispaced chunk (constant platform velocity inside a frame): the generators may then step the phase by a constant
-        bool lin = (c + 1) * kTcElems <= a.N;
+    constexpr int kUnits = kTcElems / kTcLin;
+    const int n_units = a.n_chunks * kUnits;
+    if (threadIdx.x < kUnits) {
+        // equispaced unit (constant platform velocity inside a frame): the generators may then step the phase by a constant
+        const int u = c * kUnits + threadIdx.x;
+        bool lin = (u + 1) * kTcLin <= a.N;
         double step[3] = {0.0, 0.0, 0.0};
         if (lin) {
             for (int axis = 0; axis < 3; ++axis) {
-                const double* v = a.pos + (size_t)axis * a.N + (size_t)c * kTcElems;
+                const double* v = a.pos + (size_t)axis * a.N + (size_t)u * kTcLin;
                 const double v0 = v[0] * a.inv_lambda;
-                step[axis] = (v[kTcElems - 1] * a.inv_lambda - v0) / (double)(kTcElems - 1);
-                for (int e = 1; e < kTcElems; ++e)
+                step[axis] = (v[kTcLin - 1] * a.inv_lambda - v0) / (double)(kTcLin - 1);
+                for (int e = 1; e < kTcLin; ++e)
                     lin = lin && fabs(v[e] * a.inv_lambda - (v0 + (double)e * step[axis])) <= 1e-9;
             }
         }
-        a.lin[c] = lin ? 1 : 0;
+        a.lin[u] = lin ? 1 : 0;
         for (int axis = 0; axis < 3; ++axis) {
             const float sh = (float)step[axis];
-            a.stepf[(size_t)(2 * axis) * a.n_chunks + c] = sh;
-            a.stepf[(size_t)(2 * axis + 1) * a.n_chunks + c] = (float)(step[axis] - (double)sh);
+            a.stepf[(size_t)(2 * axis) * n_units + u] = sh;
+            a.stepf[(size_t)(2 * axis + 1) * n_units + u] = (float)(step[axis] - (double)sh);
         }
     }
-    float* hi = a.bblk + (size_t)c * 2 * a.NB * kTcKC;
-    float* lo = hi + a.NB * kTcKC;
+    const float bscale = ldexpf(1.0f, sar_scale_exp(__uint_as_float(__ldg(a.max_bits))));
+    uint32_t* hi = a.bblk + (size_t)c * 2 * a.NB * kTcElems;
+    uint32_t* lo = hi + a.NB * kTcElems;
     for (int i = threadIdx.x; i < a.NB * kTcElems; i += blockDim.x) {
         const int col = i / kTcElems, nl = i - col * kTcElems;      // consecutive threads: consecutive n (coalesced reads)
         const int n = c * kTcElems + nl;
         const int s = col >= a.SP ? col - a.SP : col;
         cf x = cmake(0.f, 0.f);
         if (s < a.S && n < a.N) {
-            const double ham = a.N > 1 ? 0.54 - 0.46 * cospi(2.0 * (double)n / (double)(a.N - 1)) : 1.0;
-            x = cscale(__ldg(a.aperture + (size_t)s * a.N + n), (float)ham);
+            x = cscale(__ldg(a.aperture + (size_t)s * a.N + n), __ldg(a.hamf + n));
         }
         const float v0 = col >= a.SP ? x.y : x.x;       // multiplies Re W
         const float v1 = col >= a.SP ? x.x : -x.y;      // multiplies Im W
-        const float h0 = tf32_round(v0), h1 = tf32_round(v1);
-        const int idx = tc_canon(col, 2 * nl);
-        hi[idx] = h0; hi[idx + 1] = h1;
-        lo[idx] = v0 - h0; lo[idx + 1] = v1 - h1;
+        const int idx = tc_canon(col, nl);
+        split_h2(v0 * bscale, v1 * bscale, hi + idx, lo + idx);
     }
 }
 
@@ -123,13 +177,13 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
     } while (!ok);
 }
 // K-major, no swizzle: core matrices of 8 rows x 16 bytes; LBO = 128 B between the two 16-byte K chunks of one MMA,
-// SBO = kTcKC/4 * 128 B between 8-row groups; descriptor version 1 (sm_100).
+// SBO = (row bytes / 16) * 128 B between 8-row groups; descriptor version 1 (sm_100).
 __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
-    return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)(128 >> 4) << 16) | ((uint64_t)((kTcKC / 4) * 128 >> 4) << 32) |
+    return (uint64_t)((saddr >> 4) & 0x3FFF) | ((uint64_t)(128 >> 4) << 16) | ((uint64_t)((kTcElems / 4) * 128 >> 4) << 32) |
            (1ull << 46);
 }
-__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
                  ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
@@ -189,11 +243,11 @@ __device__ __forceinline__ void sincos_turns(float t, float* sn, float* cs) {
 
 // ---- the GEMM ---------------------------------------------------------------------------------------------------
 struct SarTcArgs {
-    const float* bblk;    // prepared B chunks
+    const uint32_t* bblk; // prepared B chunks (FP16 pairs)
     const double* posl;   // [3][npad] positions / lambda
     const float* posf;    // [6][npad] hi / lo float pairs of the same
-    const float* stepf;   // [6][n_chunks] element spacing / lambda of the equispaced chunks, float hi / lo pairs
-    const uint8_t* lin;   // [n_chunks] chunk is equispaced (null: never use the stepping path)
+    const float* stepf;   // [6][n_units] element spacing / lambda of the equispaced units, float hi / lo pairs
+    const uint8_t* lin;   // [n_units] unit of kTcLin elements is equispaced (null: never use the stepping path)
     const double* dirs;   // [3][G]
     int npad, n_chunks, seg_chunks, G, S, SP, NB;
     int g_begin, g_end;
@@ -204,6 +258,7 @@ struct SarTcArgs {
     // how the aperture is cut over CTAs (slices of the grid, which pick another ksplit, stay bit-identical to the full grid).
     int ksplit, segs_per_split;
     int parts;            // 1: one array per segment (always with ksplit > 1; RADAR_B200_SAR_PARTS=1 forces it for ksplit == 1)
+    int skip_drain_stores;   // RADAR_B200_SAR_DBG & 64: timing experiment, the drains read TMEM but do not touch `beams` (image invalid)
 };
 
 // MT accumulator tiles (128 directions each) per CTA, TPR threads per direction row (they split the elements of a chunk and
@@ -224,10 +279,10 @@ __global__ void __launch_bounds__(128 * MT * TPR + 64, 1) sar_tc_kernel(const __
     extern __shared__ __align__(128) unsigned char smem_raw[];
     constexpr int kGenThreads = 128 * MT * TPR, kGenWarps = kGenThreads / 32;
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int b_floats = a.NB * kTcKC;                         // one of B_hi / B_lo
-    const int stage_floats = MT * 2 * kTcATile + 2 * b_floats;
-    float* stage0 = reinterpret_cast<float*>(smem_raw);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(stage0 + 2 * stage_floats);
+    const int b_words = a.NB * kTcElems;                       // one of B_hi / B_lo
+    const int stage_words = MT * 2 * kTcATile + 2 * b_words;
+    uint32_t* stage0 = reinterpret_cast<uint32_t*>(smem_raw);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(stage0 + 2 * stage_words);
     uint64_t *empty = bars, *full = bars + 2, *bfull = bars + 4, *done = bars + 6, *drained = bars + 7;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
 
@@ -255,28 +310,28 @@ __global__ void __launch_bounds__(128 * MT * TPR + 64, 1) sar_tc_kernel(const __
     if (warp == kGenWarps) {
         // ===== MMA issuer =====
         if (lane == 0) {
-            // M = 128, N = NB, fp32 accumulate, TF32 x TF32, both operands K-major
-            const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(a.NB >> 3) << 17) | ((128u >> 4) << 24);
+            // M = 128, N = NB, fp32 accumulate, FP16 x FP16, both operands K-major
+            const uint32_t idesc = (1u << 4) | ((uint32_t)(a.NB >> 3) << 17) | ((128u >> 4) << 24);
             int n_seg = 0;
             for (int c = 0; c < n_local; ++c) {
                 const int s = c & 1, c_seg = c % a.seg_chunks;
                 const bool seg_end = (c_seg == a.seg_chunks - 1) || (c == n_local - 1);
-                float* st = stage0 + s * stage_floats;
+                uint32_t* st = stage0 + s * stage_words;
                 mbar_wait(&full[s], (c >> 1) & 1);
                 mbar_wait(&bfull[s], (c >> 1) & 1);
                 if (c_seg == 0 && c > 0) mbar_wait(drained, (n_seg - 1) & 1);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t b_hi = smem_u32(st + MT * 2 * kTcATile), b_lo = b_hi + b_floats * 4;
+                const uint32_t b_hi = smem_u32(st + MT * 2 * kTcATile), b_lo = b_hi + b_words * 4;
 #pragma unroll
                 for (int m = 0; m < MT; ++m) {
                     const uint32_t ah = smem_u32(st + m * kTcATile), al = smem_u32(st + MT * kTcATile + m * kTcATile);
                     const uint32_t d = tmem_base + m * 256;
 #pragma unroll
-                    for (int j = 0; j < kTcKC / 8; ++j) {                  // 8 k-values = two 16-byte chunks = 256 B further on
+                    for (int j = 0; j < kTcKC / 16; ++j) {                 // 16 k-values = two 16-byte chunks = 256 B further on
                         const uint32_t off = j * 256;
-                        umma_tf32(d, umma_desc(al + off), umma_desc(b_hi + off), idesc, (c_seg | j) != 0);
-                        umma_tf32(d, umma_desc(ah + off), umma_desc(b_lo + off), idesc, 1);
-                        umma_tf32(d, umma_desc(ah + off), umma_desc(b_hi + off), idesc, 1);
+                        umma_f16(d, umma_desc(al + off), umma_desc(b_hi + off), idesc, (c_seg | j) != 0);
+                        umma_f16(d, umma_desc(ah + off), umma_desc(b_lo + off), idesc, 1);
+                        umma_f16(d, umma_desc(ah + off), umma_desc(b_hi + off), idesc, 1);
                     }
                 }
                 umma_commit(&empty[s]);
@@ -285,17 +340,29 @@ __global__ void __launch_bounds__(128 * MT * TPR + 64, 1) sar_tc_kernel(const __
         }
     } else if (warp == kGenWarps + 1) {
         // ===== B loader: one bulk copy (hi and lo, canonical layout) per chunk =====
-        if (lane == 0) {
-            const uint32_t bytes = 2u * (uint32_t)b_floats * 4u;
-            for (int c = 0; c < n_local; ++c) {
-                const int s = c & 1;
-                if (c >= 2) mbar_wait(&empty[s], ((c >> 1) - 1) & 1);
+        // Lanes 8..20 pull the NEXT chunk's geometry (positions, steps, flags: what every generator thread is about to
+        // load, the same addresses for the whole CTA) into L1 one chunk ahead of the generators.
+        const int n_units = a.n_chunks * (kTcElems / kTcLin);
+        const int row6 = (lane - 8) % 6, which = lane < 8 ? -1 : (lane - 8) / 6;
+        const uint32_t bytes = 2u * (uint32_t)b_words * 4u;
+        for (int c = 0; c < n_local; ++c) {
+            const int s = c & 1;
+            if (c >= 2) mbar_wait(&empty[s], ((c >> 1) - 1) & 1);               // warp uniform
+            if (lane == 0) {
                 const uint32_t bar = smem_u32(&bfull[s]);
                 asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
                 asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                             ::"r"(smem_u32(stage0 + s * stage_floats + MT * 2 * kTcATile)), "l"(a.bblk + (size_t)(c0 + c) * 2 * b_floats),
+                             ::"r"(smem_u32(stage0 + s * stage_words + MT * 2 * kTcATile)), "l"(a.bblk + (size_t)(c0 + c) * 2 * b_words),
                                "r"(bytes), "r"(bar) : "memory");
+            } else if (which >= 0 && c + 1 < n_local) {
+                const int cc = c0 + c + 1;
+                const void* ptr = nullptr;
+                if (which == 0) ptr = a.posf + (size_t)row6 * a.npad + (size_t)cc * kTcElems;        // 128 bytes = one line
+                else if (which == 1) ptr = a.stepf + (size_t)row6 * n_units + (size_t)cc * (kTcElems / kTcLin);
+                else if (lane == 20 && a.lin) ptr = a.lin + (size_t)cc * (kTcElems / kTcLin);
+                if (ptr) asm volatile("prefetch.global.L1 [%0];" ::"l"(ptr));
             }
+            __syncwarp();
         }
     } else {
         // ===== generators =====
@@ -308,106 +375,104 @@ __global__ void __launch_bounds__(128 * MT * TPR + 64, 1) sar_tc_kernel(const __
         // float pairs of the direction for the fp32 phase (CS): d = dh + dl to 2^-48
         const float dh[3] = {(float)dx, (float)dy, (float)dz};
         const float dl[3] = {(float)(dx - (double)dh[0]), (float)(dy - (double)dh[1]), (float)(dz - (double)dh[2])};
+        constexpr int W = kTcElems / TPR;                          // elements of a chunk this thread generates
+        static_assert(W % kTcLin == 0, "a thread generates whole units of kTcLin elements");
+        const int n_units = a.n_chunks * (kTcElems / kTcLin);
+        const int row_word = ((row >> 3) * (kTcElems / 4)) * 32 + (row & 7) * 4;     // word of element 0 of this row
         int n_drained = 0;
         for (int cl = 0; cl < n_local; ++cl) {
             const int c = c0 + cl;                                 // chunk of the aperture; cl counts this CTA's stages
             const int s = cl & 1, c_seg = cl % a.seg_chunks;
             const bool seg_end = (c_seg == a.seg_chunks - 1) || (cl == n_local - 1);
-            float* st = stage0 + s * stage_floats;
-            float* a_hi = st + mt * kTcATile;
-            float* a_lo = st + MT * kTcATile + mt * kTcATile;
+            uint32_t* st = stage0 + s * stage_words;
+            uint32_t* a_hi = st + mt * kTcATile + row_word;
+            uint32_t* a_lo = st + MT * kTcATile + mt * kTcATile + row_word;
             if (cl >= 2) mbar_wait(&empty[s], ((cl >> 1) - 1) & 1);          // the MMAs of stage cl-2 have finished reading this stage
             const double* px = a.posl + (size_t)c * kTcElems;
             const float* pf = a.posf + (size_t)c * kTcElems;
-            constexpr int W = kTcElems / TPR;                      // elements of a chunk this thread generates
-            if (CS && a.lin && a.lin[c]) {
-                // Equispaced chunk: phase(e) = t0 + e * delta.  Per group of 8 elements: the group's first phase and delta as
-                // float pairs (phase_pair, once per group / chunk instead of once per element), exp(2 pi i delta 2^k) by
-                // sincos_turns of the exactly doubled and re-reduced pair (no squaring error), and every coefficient is the
-                // group's first one times at most three of those powers: ~12 instructions per element instead of ~46.  The
-                // arithmetic of an element does not depend on TPR (bit-identical tilings).
-                float sh[3], sl[3];
 #pragma unroll
-                for (int ax = 0; ax < 3; ++ax) {
-                    sh[ax] = __ldg(a.stepf + (size_t)(2 * ax) * a.n_chunks + c);
-                    sl[ax] = __ldg(a.stepf + (size_t)(2 * ax + 1) * a.n_chunks + c);
-                }
-                float uh, ul, ur[3], ui[3];
-                phase_pair(dh, dl, sh, sl, &uh, &ul);
-#pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    sincos_turns(uh + ul, &ui[k], &ur[k]);
-                    uh *= 2.0f; ul *= 2.0f;
-                    uh -= (uh + 12582912.0f) - 12582912.0f;
-                }
-#pragma unroll
-                for (int grp = 0; grp < W / 8; ++grp) {
-                    const int nl0 = part * W + grp * 8;
-                    float ph[3], pl[3], t0h, t0l, wr[8], wi[8];
+            for (int ul = 0; ul < W / kTcLin; ++ul) {
+                const int nl0 = part * W + ul * kTcLin;            // first element (inside the chunk) of this unit
+                const int unit = (c * kTcElems + nl0) / kTcLin;
+                float wr[kTcLin], wi[kTcLin];                      // the coefficients, already scaled by 2^13
+                if (CS && a.lin && a.lin[unit]) {
+                    // Equispaced unit: phase(e) = t0 + e * delta.  The unit's first phase and delta as float pairs
+                    // (phase_pair, once per unit instead of once per element), exp(2 pi i delta 2^k) by sincos_turns of the
+                    // exactly doubled and re-reduced pair (no squaring error), and every coefficient is the first one times
+                    // at most four of those powers: ~10 instructions per element instead of ~46.  The five sincos chains
+                    // are independent (instruction-level parallelism for the two warps a scheduler holds).  The
+                    // arithmetic of an element does not depend on TPR (bit-identical tilings).
+                    float sh[3], sl[3], ph[3], pl[3];
 #pragma unroll
                     for (int ax = 0; ax < 3; ++ax) {
+                        sh[ax] = __ldg(a.stepf + (size_t)(2 * ax) * n_units + unit);
+                        sl[ax] = __ldg(a.stepf + (size_t)(2 * ax + 1) * n_units + unit);
                         ph[ax] = __ldg(pf + (size_t)(2 * ax) * a.npad + nl0);
                         pl[ax] = __ldg(pf + (size_t)(2 * ax + 1) * a.npad + nl0);
                     }
+                    float uh, ul2, t0h, t0l, ur[4], ui[4];
+                    phase_pair(dh, dl, sh, sl, &uh, &ul2);
                     phase_pair(dh, dl, ph, pl, &t0h, &t0l);
-                    sincos_turns(t0h + t0l, &wi[0], &wr[0]);
 #pragma unroll
-                    for (int k = 0; k < 3; ++k) {
+                    for (int k = 0; k < 4; ++k) {
+                        sincos_turns(uh + ul2, &ui[k], &ur[k]);
+                        uh *= 2.0f; ul2 *= 2.0f;
+                        uh -= (uh + 12582912.0f) - 12582912.0f;
+                    }
+                    sincos_turns(t0h + t0l, &wi[0], &wr[0]);
+                    wr[0] *= kTcAScale; wi[0] *= kTcAScale;       // exact; every product below inherits the scale
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
 #pragma unroll
                         for (int e = 0; e < (1 << k); ++e) {
                             wr[(1 << k) + e] = fmaf(wr[e], ur[k], -wi[e] * ui[k]);
                             wi[(1 << k) + e] = fmaf(wr[e], ui[k], wi[e] * ur[k]);
                         }
                     }
-#pragma unroll
-                    for (int nq = 0; nq < 8; nq += 2) {
-                        const int nl = nl0 + nq;
-                        float4 h, l;
-                        h.x = tf32_round(wr[nq]); h.y = tf32_round(wi[nq]); h.z = tf32_round(wr[nq + 1]); h.w = tf32_round(wi[nq + 1]);
-                        l.x = wr[nq] - h.x; l.y = wi[nq] - h.y; l.z = wr[nq + 1] - h.z; l.w = wi[nq + 1] - h.w;
-                        const int idx = ((row >> 3) * (kTcKC / 4) + (nl >> 1)) * 32 + (row & 7) * 4;
-                        *reinterpret_cast<float4*>(a_hi + idx) = h;
-                        *reinterpret_cast<float4*>(a_lo + idx) = l;
-                    }
-                }
-            } else
+                } else {
 #pragma unroll UNR
-            for (int nq = 0; nq < kTcElems / TPR; nq += 2) {
-                const int nl = part * (kTcElems / TPR) + nq;
-                float w[4];
+                    for (int e = 0; e < kTcLin; ++e) {
+                        const int nl = nl0 + e;
+                        float sn, cs;
+                        if (CS) {
+                            // Phase (d.p)/lambda modulo 1 WITHOUT the fp64 pipe (ncu: a third of all stall samples were
+                            // math-pipe throttle on DFMA / DMUL).  d = dh + dl, p = ph + pl as float pairs; dh*ph is split
+                            // exactly into a rounded product and its FMA remainder; the rounded product (up to 1e4 turns)
+                            // loses its integer part exactly (x - rint(x) is exact below 2^22, rint by the magic-number
+                            // add); what is left are terms below one turn, summed in fp32: ~1e-7 turns of error.
+                            float acc = 0.0f, small = 0.0f;
 #pragma unroll
-                for (int e = 0; e < 2; ++e) {
-                    if (CS) {
-                        // Phase (d.p)/lambda modulo 1 WITHOUT the fp64 pipe (ncu: a third of all stall samples were
-                        // math-pipe throttle on DFMA / DMUL).  d = dh + dl, p = ph + pl as float pairs; dh*ph is split
-                        // exactly into a rounded product and its FMA remainder; the rounded product (up to 1e4 turns) loses
-                        // its integer part exactly (x - rint(x) is exact below 2^22, rint by the magic-number add);
-                        // what is left are terms below one turn, summed in fp32: ~1e-7 turns of error.
-                        float acc = 0.0f, small = 0.0f;
-#pragma unroll
-                        for (int ax = 0; ax < 3; ++ax) {
-                            const float ph = __ldg(pf + (size_t)(2 * ax) * a.npad + nl + e), pl = __ldg(pf + (size_t)(2 * ax + 1) * a.npad + nl + e);
-                            const float hi = dh[ax] * ph;
-                            const float lo = fmaf(dh[ax], ph, -hi);
-                            const float ri = (hi + 12582912.0f) - 12582912.0f;
-                            acc += hi - ri;
-                            small += fmaf(dh[ax], pl, fmaf(dl[ax], ph, lo));
+                            for (int ax = 0; ax < 3; ++ax) {
+                                const float ph = __ldg(pf + (size_t)(2 * ax) * a.npad + nl), pl = __ldg(pf + (size_t)(2 * ax + 1) * a.npad + nl);
+                                const float hi = dh[ax] * ph;
+                                const float lo = fmaf(dh[ax], ph, -hi);
+                                const float ri = (hi + 12582912.0f) - 12582912.0f;
+                                acc += hi - ri;
+                                small += fmaf(dh[ax], pl, fmaf(dl[ax], ph, lo));
+                            }
+                            float t = acc + small;
+                            t -= (t + 12582912.0f) - 12582912.0f;
+                            sincos_turns(t, &sn, &cs);
+                        } else {
+                            const double turns = fma(dx, __ldg(px + nl), fma(dy, __ldg(px + a.npad + nl), dz * __ldg(px + 2 * (size_t)a.npad + nl)));
+                            const float frac = (float)(turns - rint(turns));
+                            sincospif(2.0f * frac, &sn, &cs);
                         }
-                        float t = acc + small;
-                        t -= (t + 12582912.0f) - 12582912.0f;
-                        sincos_turns(t, &w[2 * e + 1], &w[2 * e]);
-                    } else {
-                        const double turns = fma(dx, __ldg(px + nl + e), fma(dy, __ldg(px + a.npad + nl + e), dz * __ldg(px + 2 * (size_t)a.npad + nl + e)));
-                        const float frac = (float)(turns - rint(turns));
-                        sincospif(2.0f * frac, &w[2 * e + 1], &w[2 * e]);
+                        wr[e] = cs * kTcAScale; wi[e] = sn * kTcAScale;
                     }
                 }
-                float4 h, l;
-                h.x = tf32_round(w[0]); h.y = tf32_round(w[1]); h.z = tf32_round(w[2]); h.w = tf32_round(w[3]);
-                l.x = w[0] - h.x; l.y = w[1] - h.y; l.z = w[2] - h.z; l.w = w[3] - h.w;
-                const int idx = ((row >> 3) * (kTcKC / 4) + (nl >> 1)) * 32 + (row & 7) * 4;
-                *reinterpret_cast<float4*>(a_hi + idx) = h;
-                *reinterpret_cast<float4*>(a_lo + idx) = l;
+                // FP16 hi / lo words of the coefficients: 16-byte core-matrix rows of four elements
+#pragma unroll
+                for (int q = 0; q < kTcLin; q += 4) {
+                    uint4 h, l;
+                    split_h2(wr[q], wi[q], &h.x, &l.x);
+                    split_h2(wr[q + 1], wi[q + 1], &h.y, &l.y);
+                    split_h2(wr[q + 2], wi[q + 2], &h.z, &l.z);
+                    split_h2(wr[q + 3], wi[q + 3], &h.w, &l.w);
+                    const int idx = ((nl0 + q) >> 2) * 32;
+                    *reinterpret_cast<uint4*>(a_hi + idx) = h;
+                    *reinterpret_cast<uint4*>(a_lo + idx) = l;
+                }
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the tensor core
             __syncwarp();
@@ -425,7 +490,7 @@ __global__ void __launch_bounds__(128 * MT * TPR + 64, 1) sar_tc_kernel(const __
                     tmem_ld16(taddr + s0, re);
                     tmem_ld16(taddr + a.SP + s0, im);
                     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                    if (g_out < width) {
+                    if (g_out < width && !a.skip_drain_stores) {
                         // ksplit > 1: this segment's own array, plain stores; ksplit == 1: accumulate in place
                         cf* dst = a.beams + (a.parts ? (size_t)(seg0 + n_drained) * a.S * width : (size_t)0) + (size_t)s0 * width + g_out;
                         cf old[16];
@@ -464,6 +529,7 @@ struct SarFftArgs {
     cf* out;              // [S][width]
     FftPlan planS;
     FastDiv divDirs;
+    const uint32_t* max_bits;   // the operand scales of the GEMM are undone here (exact powers of two)
 };
 
 __global__ void __launch_bounds__(256) sar_range_fft_kernel(const __grid_constant__ SarFftArgs a) {
@@ -478,6 +544,7 @@ __global__ void __launch_bounds__(256) sar_range_fft_kernel(const __grid_constan
     load_table(win, a.winS, S);
     load_table(pos, a.posS, S);
     __syncthreads();
+    const float descale = ldexpf(1.0f, -13 - sar_scale_exp(__uint_as_float(__ldg(a.max_bits))));
     const int g0 = blockIdx.x * kTcFftDirs;
     const int cells = S * kTcFftDirs;
     for (int i = threadIdx.x; i < cells; i += blockDim.x) {
@@ -491,13 +558,56 @@ __global__ void __launch_bounds__(256) sar_range_fft_kernel(const __grid_constan
                 v = cmake(u.x + v.x, u.y + v.y);
             }
         }
-        tile[s * Gp + gl] = cscale(v, win[s]);
+        tile[s * Gp + gl] = cscale(cscale(v, descale), win[s]);
     }
     __syncthreads();
     fft_axis(tile, Gp, 1, kTcFftDirs, a.divDirs, a.planS, tw);
     for (int i = threadIdx.x; i < cells; i += blockDim.x) {
         const int k = i / kTcFftDirs, gl = i - k * kTcFftDirs;
         if (g0 + gl < a.width) a.out[(size_t)k * a.width + g0 + gl] = tile[pos[k] * Gp + gl];
+    }
+}
+
+// The same for S = 2 * H with H odd and a register transform Dft<H> (S = 90: the RadSAR cfgs): no shared-memory tile at
+// all.  Lanes are directions (every load and store is a coalesced row segment of [S][width]); the two halves of a
+// CTA are the two output classes k = k1 (mod 2) of the prime-factor split 2 x H:
+//   X[(H k1 + (H + 1) k2) mod S] = sum_n2 ( v[2 n2 mod S] + (-1)^k1 v[(H + 2 n2) mod S] ) W_H^(n2 k2)
+// so a thread forms H sums / differences and runs one H-point transform in registers.
+constexpr int kTcFftRegDirs = 64;
+template <int H>
+__global__ void __launch_bounds__(2 * kTcFftRegDirs) sar_range_fft_reg_kernel(const __grid_constant__ SarFftArgs a) {
+    constexpr int S = 2 * H;
+    __shared__ float win[S];
+    for (int i = threadIdx.x; i < S; i += blockDim.x) win[i] = a.winS[i];
+    __syncthreads();
+    const float descale = ldexpf(1.0f, -13 - sar_scale_exp(__uint_as_float(__ldg(a.max_bits))));
+    const int k1 = threadIdx.x / kTcFftRegDirs;                           // warp uniform
+    const int g = blockIdx.x * kTcFftRegDirs + (threadIdx.x - k1 * kTcFftRegDirs);
+    if (g >= a.width) return;
+    const float sigma = k1 ? -1.0f : 1.0f;
+    const cf* src = a.beams + g;
+    const size_t part_stride = (size_t)S * a.width;
+    cf y[H];
+#pragma unroll
+    for (int n2 = 0; n2 < H; ++n2) {
+        const int s0 = (2 * n2) % S, s1 = (H + 2 * n2) % S;
+        cf v0 = __ldcg(src + (size_t)s0 * a.width), v1 = __ldcg(src + (size_t)s1 * a.width);
+        for (int k = 1; k < a.n_part; ++k) {                              // segment order, the additions of the in-place accumulation
+            const cf u0 = __ldcg(src + (size_t)k * part_stride + (size_t)s0 * a.width);
+            const cf u1 = __ldcg(src + (size_t)k * part_stride + (size_t)s1 * a.width);
+            v0 = cmake(u0.x + v0.x, u0.y + v0.y);
+            v1 = cmake(u1.x + v1.x, u1.y + v1.y);
+        }
+        v0 = cscale(cscale(v0, descale), win[s0]);
+        v1 = cscale(cscale(v1, descale), win[s1]);
+        y[n2] = cmake(fmaf(sigma, v1.x, v0.x), fmaf(sigma, v1.y, v0.y));
+    }
+    Dft<H>::run(y);
+    cf* dst = a.out + g;
+#pragma unroll
+    for (int k2 = 0; k2 < H; ++k2) {
+        const int k = (H * k1 + (H + 1) * k2) % S;
+        dst[(size_t)k * a.width] = y[k2];
     }
 }
 
@@ -508,14 +618,15 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
     if (NB > 256 || (NB & 15) != 0) return 1;                   // tcgen05.mma with M = 128 takes N in 16..256, multiples of 16
     const int width = g_end - g_begin;
     const int n_chunks = (N + kTcElems - 1) / kTcElems, npad = n_chunks * kTcElems;
-    // segment length: measured bias 1.3e-8 * sqrt(N * len) relative; keep it near 1e-5
-    int seg_chunks = (int)(6.0e5 / (double)N) / kTcElems;
-    seg_chunks = seg_chunks < 4 ? 4 : (seg_chunks > n_chunks ? n_chunks : seg_chunks);
+    // segment length: the truncation bias grows linearly with it (measured on S = 90, N = 2000 against fp64: 2.1e-6 relative
+    // at 288 elements, 3.5e-6 at 512, 6.9e-6 at 1024, 1.3e-5 undivided; tools/sar_seg_error.py); keep it near 4e-6
+    int seg_chunks = (int)(1.05e6 / (double)N) / kTcElems;
+    seg_chunks = seg_chunks < 2 ? 2 : (seg_chunks > n_chunks ? n_chunks : seg_chunks);
     if (ctx->sar_seg_chunks > 0) seg_chunks = ctx->sar_seg_chunks;
     const int n_seg = (n_chunks + seg_chunks - 1) / seg_chunks;
     auto smem_for = [&](int tiles) {
-        const size_t stage_floats = (size_t)tiles * 2 * kTcATile + 2 * (size_t)NB * kTcKC;
-        return 2 * stage_floats * sizeof(float) + 8 * sizeof(uint64_t) + 16;
+        const size_t stage_words = (size_t)tiles * 2 * kTcATile + 2 * (size_t)NB * kTcElems;
+        return 2 * stage_words * sizeof(uint32_t) + 8 * sizeof(uint64_t) + 16;
     };
     // two accumulator tiles per CTA (a B chunk serves 256 directions) once every SM has work anyway and the stages fit
     int mt = (width > 128 * ctx->sm_count && smem_for(2) <= (size_t)ctx->max_smem_optin) ? 2 : 1;
@@ -536,27 +647,38 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
     const int ksplit = (n_seg + segs_per_split - 1) / segs_per_split;
     const int n_part = (ksplit > 1 || ctx->sar_parts) ? n_seg : 1;
 
-    const size_t bblk_bytes = (size_t)n_chunks * 2 * NB * kTcKC * sizeof(float);
+    const size_t bblk_bytes = (size_t)n_chunks * 2 * NB * kTcElems * sizeof(uint32_t);
+    const int n_units = n_chunks * (kTcElems / kTcLin);
     const size_t posl_bytes = (size_t)3 * npad * sizeof(double);
     const size_t posf_bytes = (size_t)6 * npad * sizeof(float);
     const size_t beams_bytes = (size_t)n_part * S * width * sizeof(cf);
-    const size_t step_bytes = (size_t)6 * n_chunks * sizeof(float), lin_bytes = (size_t)n_chunks;
+    const size_t step_bytes = (size_t)6 * n_units * sizeof(float), lin_bytes = (size_t)n_units;
     auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
-    if (int rc = ensure_scratch(ctx, up(bblk_bytes) + up(posl_bytes) + up(posf_bytes) + up(beams_bytes) + up(step_bytes) + up(lin_bytes))) return rc;
+    const size_t ham_bytes = (size_t)N * sizeof(float);
+    if (int rc = ensure_scratch(ctx, up(bblk_bytes) + up(posl_bytes) + up(posf_bytes) + up(beams_bytes) + up(step_bytes) + up(lin_bytes) + 256 + up(ham_bytes))) return rc;
     unsigned char* base = reinterpret_cast<unsigned char*>(ctx->scratch);
-    float* bblk = reinterpret_cast<float*>(base);
+    uint32_t* bblk = reinterpret_cast<uint32_t*>(base);
     double* posl = reinterpret_cast<double*>(base + up(bblk_bytes));
     float* posf = reinterpret_cast<float*>(base + up(bblk_bytes) + up(posl_bytes));
     cf* beams = reinterpret_cast<cf*>(base + up(bblk_bytes) + up(posl_bytes) + up(posf_bytes));
     float* stepf = reinterpret_cast<float*>(base + up(bblk_bytes) + up(posl_bytes) + up(posf_bytes) + up(beams_bytes));
     uint8_t* lin = reinterpret_cast<uint8_t*>(stepf) + up(step_bytes);
+    uint32_t* max_bits = reinterpret_cast<uint32_t*>(lin + up(lin_bytes));
+    float* hamf = reinterpret_cast<float*>(lin + up(lin_bytes) + 256);
 
-    SarPrepArgs p{aperture, S, N, SP, NB, n_chunks, positions, 1.0 / lambda_m, bblk, posl, posf, stepf, lin};
+    // largest |x hamming| of the call -> power-of-two scale of the FP16 B operand
+    RB_CUDA_OK(ctx, cudaMemsetAsync(max_bits, 0, sizeof(uint32_t), st));
+    {
+        const int slices = S >= 64 ? 8 : (S >= 8 ? 4 : 1);
+        sar_tc_max_kernel<<<dim3((unsigned)((N + kTcMaxThreads - 1) / kTcMaxThreads), (unsigned)slices), kTcMaxThreads, 0, st>>>(aperture, S, N, hamf, max_bits);
+        RB_CUDA_OK(ctx, cudaGetLastError());
+    }
+    SarPrepArgs p{aperture, S, N, SP, NB, n_chunks, positions, 1.0 / lambda_m, bblk, posl, posf, stepf, lin, max_bits, hamf};
     sar_tc_prep_kernel<<<n_chunks, 256, 0, st>>>(p);
     RB_CUDA_OK(ctx, cudaGetLastError());
 
     SarTcArgs a{bblk, posl, posf, stepf, (ctx->sar_dbg & 32) ? nullptr : lin, dirs, npad, n_chunks, seg_chunks, G, S, SP, NB, g_begin, g_end, beams,
-                ksplit, segs_per_split, n_part > 1 ? 1 : 0};
+                ksplit, segs_per_split, n_part > 1 ? 1 : 0, (ctx->sar_dbg & 64) ? 1 : 0};
     const int tpr = ctx->sar_tpr > 0 ? ctx->sar_tpr : (mt == 2 ? 1 : 2);      // measured: 0.443 / 0.450 ms (2 tiles), 0.550 / 0.503 ms (1 tile)
     const int unr = ctx->sar_dbg & 15, cs = !(ctx->sar_dbg & 16);      // RADAR_B200_SAR_DBG: unroll of the element loop (0 = default), +16 = sincospif
 #define RB_SAR_TC_LAUNCH(MT_, TPR_, UNR_, CS_)                                                                               \
@@ -566,8 +688,8 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
     } while (0)
 #define RB_SAR_TC_VARIANTS(MT_, TPR_)                                                                                        \
     do {                                                                                                                     \
-        if (cs) { if (unr == 1) RB_SAR_TC_LAUNCH(MT_, TPR_, 1, true); else if (unr == 2) RB_SAR_TC_LAUNCH(MT_, TPR_, 2, true); else RB_SAR_TC_LAUNCH(MT_, TPR_, 8, true); } \
-        else { if (unr == 1) RB_SAR_TC_LAUNCH(MT_, TPR_, 1, false); else if (unr == 2) RB_SAR_TC_LAUNCH(MT_, TPR_, 2, false); else RB_SAR_TC_LAUNCH(MT_, TPR_, 8, false); } \
+        if (cs) { if (unr == 1) RB_SAR_TC_LAUNCH(MT_, TPR_, 1, true); else if (unr == 2) RB_SAR_TC_LAUNCH(MT_, TPR_, 2, true); else RB_SAR_TC_LAUNCH(MT_, TPR_, 16, true); } \
+        else { if (unr == 1) RB_SAR_TC_LAUNCH(MT_, TPR_, 1, false); else if (unr == 2) RB_SAR_TC_LAUNCH(MT_, TPR_, 2, false); else RB_SAR_TC_LAUNCH(MT_, TPR_, 16, false); } \
     } while (0)
     if (mt == 2 && tpr == 2) RB_SAR_TC_VARIANTS(2, 2);
     else if (mt == 2) RB_SAR_TC_VARIANTS(2, 1);
@@ -577,7 +699,12 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
 #undef RB_SAR_TC_LAUNCH
     RB_CUDA_OK(ctx, cudaGetLastError());
 
-    SarFftArgs f{beams, n_part, S, width, ctx->fftS.hann, ctx->fftS.tw, ctx->fftS.pos, out, ctx->fftS.plan, make_fastdiv(kTcFftDirs)};
+    SarFftArgs f{beams, n_part, S, width, ctx->fftS.hann, ctx->fftS.tw, ctx->fftS.pos, out, ctx->fftS.plan, make_fastdiv(kTcFftDirs), max_bits};
+    if (S == 90 && !(ctx->sar_dbg & 128)) {            // RADAR_B200_SAR_DBG & 128: the shared-memory transform for every S (comparison)
+        sar_range_fft_reg_kernel<45><<<(unsigned)((width + kTcFftRegDirs - 1) / kTcFftRegDirs), 2 * kTcFftRegDirs, 0, st>>>(f);
+        RB_CUDA_OK(ctx, cudaGetLastError());
+        return RADAR_OK;
+    }
     const size_t fsmem = arena_bytes((size_t)S * (kTcFftDirs | 1), sizeof(cf)) + arena_bytes(S, sizeof(cf)) + arena_bytes(S, 4) + arena_bytes(S, 2);
     RB_CUDA_OK(ctx, cudaFuncSetAttribute(sar_range_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
     sar_range_fft_kernel<<<(unsigned)((width + kTcFftDirs - 1) / kTcFftDirs), 256, fsmem, st>>>(f);

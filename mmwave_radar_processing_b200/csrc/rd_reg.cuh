@@ -27,11 +27,7 @@
 namespace rb {
 
 // ---- whole-length transforms in registers -------------------------------------------------------------------------
-template <> struct Dft<63> : DftPfa<7, 9> {};
-template <> struct Dft<70> : DftPfa<7, 10> {};
-template <> struct Dft<40> : DftPfa<5, 8> {};
-template <> struct Dft<35> : DftPfa<5, 7> {};
-template <> struct Dft<45> : DftPfa<5, 9> {};
+// (the prime-factor lengths 35, 40, 45, 63, 70 live in fft_radix.cuh)
 // 25 = 5 x 5 by Cooley-Tukey in registers: n = 5*n1 + n2, k = k1 + 5*k2, twiddles W25^(n2*k1) as literals
 template <> struct Dft<25> {
     RB_HD static void run(cf* v) {

@@ -1,8 +1,8 @@
 #!/usr/bin/env python
 """Timing of radar_sar_image on the throughput grid of SURVEY.md section 8d (S = 90, N = 2000, G = 32768) for the
-FP32-pipe kernel and the tcgen05 split-TF32 path.  One JSON line per mode: ms per image, useful complex-GEMM TFLOP/s
-(8 S N G flop) and, for the tensor-core path, executed TF32 TFLOP/s (3 MMAs per product, padded tile) against the dense
-bf16 peak of MEASURED_PEAKS.json (TF32 peaks at half of it).  CUDA events on the launching stream, warm-up first."""
+FP32-pipe kernel and the tcgen05 split-FP16 path.  One JSON line per mode: ms per image, useful complex-GEMM TFLOP/s
+(8 S N G flop) and, for the tensor-core path, executed FP16 TFLOP/s (3 MMAs per product, padded tile) against the dense
+bf16 / fp16 peak of MEASURED_PEAKS.json.  CUDA events on the launching stream, warm-up first."""
 import json
 import os
 import sys
@@ -31,8 +31,12 @@ def main():
         pass
     bf16_peak = float(peaks.get("bf16_tflops", peaks.get("tensor_bf16_tflops", 0.0)) or 0.0)
     ref = None
-    for mode, label in ((1, "fp32_pipe"), (2, "tcgen05_tf32x3_1tile"), (3, "tcgen05_tf32x3_2tiles"), (0, "auto")):
+    for mode, dbg, tpr, label in ((1, 0, 0, "fp32_pipe"), (2, 0, 0, "tcgen05_f16x3_1tile"), (3, 0, 0, "tcgen05_f16x3_2tiles"),
+                                  (3, 0, 2, "tcgen05_f16x3_2tiles_tpr2"), (2, 0, 1, "tcgen05_f16x3_1tile_tpr1"), (0, 0, 0, "auto"),
+                                  (0, 64, 0, "auto_no_drain_stores_INVALID"), (0, 32, 0, "auto_general_phase_path")):
         os.environ["RADAR_B200_SAR"] = str(mode)
+        os.environ["RADAR_B200_SAR_DBG"] = str(dbg)
+        os.environ["RADAR_B200_SAR_TPR"] = str(tpr)
         eng = RadarEngine(1, s, 1, 1)
         out = torch.empty((s, g), dtype=torch.complex64, device="cuda")
         for _ in range(3):
@@ -53,9 +57,9 @@ def main():
                 "rel_l2_vs_fp32_pipe": float((torch.linalg.norm(out - ref) / torch.linalg.norm(ref)).item())}
         if mode != 1:
             executed = 3 * 2.0 * 192 * (2 * 2000) * g        # three MMAs, N padded to 192 columns, K = 2 N real
-            line["executed_tf32_tflops"] = executed / (ms * 1e-3) / 1e12
+            line["executed_f16_tflops"] = executed / (ms * 1e-3) / 1e12
             if bf16_peak:
-                line["frac_of_measured_bf16_peak"] = line["executed_tf32_tflops"] / bf16_peak
+                line["frac_of_measured_bf16_peak"] = line["executed_f16_tflops"] / bf16_peak
                 line["measured_bf16_peak_tflops"] = bf16_peak
         print(json.dumps(line), flush=True)
 
