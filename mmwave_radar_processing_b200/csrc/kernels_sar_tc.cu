@@ -104,56 +104,78 @@ struct SarPrepArgs {
     double* posl;         // [3][n_chunks * kTcElems]  positions / lambda, zero padded
     float* posf;          // [6][n_chunks * kTcElems]  the same as float pairs: rows 2a = hi, 2a+1 = lo of axis a
     float* stepf;         // [6][n_units]  per-axis element spacing / lambda (float hi / lo pairs) of an equispaced unit
-    uint8_t* lin;         // [n_units]     1 = the unit (kTcLin elements) is an arithmetic progression to 1e-9 wavelengths (no padding)
+    uint8_t* lin;         // [n_units]     1 = the unit (kTcLin elements) is an arithmetic progression to 1e-9 wavelengths (no padding), 2 = and continues the unit one chunk earlier
     const uint32_t* max_bits;   // largest |x hamming| of the call (float bits), from sar_tc_max_kernel
     const float* hamf;    // [N] np.hamming(N) as floats, from sar_tc_max_kernel
 };
 
+// Block (c, y): chunk c of the aperture, quarter y of the B columns; the y = 0 blocks also write the chunk's geometry.
+constexpr int kTcPrepSplit = 4;
 __global__ void __launch_bounds__(256) sar_tc_prep_kernel(const __grid_constant__ SarPrepArgs a) {
     const int c = blockIdx.x;
     const int npad = a.n_chunks * kTcElems;
-    for (int i = threadIdx.x; i < 3 * kTcElems; i += blockDim.x) {
-        const int axis = i / kTcElems, n = c * kTcElems + (i - axis * kTcElems);
-        const double v = n < a.N ? a.pos[(size_t)axis * a.N + n] * a.inv_lambda : 0.0;
-        a.posl[(size_t)axis * npad + n] = v;
-        const float vh = (float)v;
-        a.posf[(size_t)(2 * axis) * npad + n] = vh;
-        a.posf[(size_t)(2 * axis + 1) * npad + n] = (float)(v - (double)vh);
-    }
     constexpr int kUnits = kTcElems / kTcLin;
     const int n_units = a.n_chunks * kUnits;
-    if (threadIdx.x < kUnits) {
-        // equispaced unit (constant platform velocity inside a frame): the generators may then step the phase by a constant
-        const int u = c * kUnits + threadIdx.x;
-        bool lin = (u + 1) * kTcLin <= a.N;
-        double step[3] = {0.0, 0.0, 0.0};
-        if (lin) {
-            for (int axis = 0; axis < 3; ++axis) {
-                const double* v = a.pos + (size_t)axis * a.N + (size_t)u * kTcLin;
-                const double v0 = v[0] * a.inv_lambda;
-                step[axis] = (v[kTcLin - 1] * a.inv_lambda - v0) / (double)(kTcLin - 1);
-                for (int e = 1; e < kTcLin; ++e)
-                    lin = lin && fabs(v[e] * a.inv_lambda - (v0 + (double)e * step[axis])) <= 1e-9;
-            }
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (blockIdx.y == 0) {
+        for (int i = threadIdx.x; i < 3 * kTcElems; i += blockDim.x) {
+            const int axis = i / kTcElems, n = c * kTcElems + (i - axis * kTcElems);
+            const double v = n < a.N ? a.pos[(size_t)axis * a.N + n] * a.inv_lambda : 0.0;
+            a.posl[(size_t)axis * npad + n] = v;
+            const float vh = (float)v;
+            a.posf[(size_t)(2 * axis) * npad + n] = vh;
+            a.posf[(size_t)(2 * axis + 1) * npad + n] = (float)(v - (double)vh);
         }
-        a.lin[u] = lin ? 1 : 0;
-        for (int axis = 0; axis < 3; ++axis) {
-            const float sh = (float)step[axis];
-            a.stepf[(size_t)(2 * axis) * n_units + u] = sh;
-            a.stepf[(size_t)(2 * axis + 1) * n_units + u] = (float)(step[axis] - (double)sh);
+        if (warp < kUnits) {
+            // One warp per unit u of kTcLin elements, one lane per element.  Flag 1: the unit lies inside the aperture and is
+            // an arithmetic progression to 1e-9 wavelengths (constant platform velocity inside a frame): the generators may
+            // then step the phase by a constant.  Flag 2: it also continues the progression of the unit one chunk earlier
+            // (same step, kTcElems elements further on), so its coefficients are the earlier unit's times
+            // exp(2 pi i kTcElems delta).
+            const int u = c * kUnits + warp;
+            const bool inside = (u + 1) * kTcLin <= a.N, has_prev = u >= kUnits;
+            double step[3] = {0.0, 0.0, 0.0};
+            bool ok = inside, okp = inside && has_prev, okc = inside && has_prev;
+            if (inside) {
+                const int e = lane & (kTcLin - 1);
+#pragma unroll
+                for (int axis = 0; axis < 3; ++axis) {
+                    const double* v = a.pos + (size_t)axis * a.N + (size_t)u * kTcLin;
+                    const double v0 = v[0] * a.inv_lambda;
+                    step[axis] = (v[kTcLin - 1] * a.inv_lambda - v0) / (double)(kTcLin - 1);
+                    ok = ok && fabs(v[e] * a.inv_lambda - (v0 + (double)e * step[axis])) <= 1e-9;
+                    if (has_prev) {
+                        const double* w = v - kTcElems;
+                        const double w0 = w[0] * a.inv_lambda;
+                        const double prev = (w[kTcLin - 1] * a.inv_lambda - w0) / (double)(kTcLin - 1);
+                        okp = okp && fabs(w[e] * a.inv_lambda - (w0 + (double)e * prev)) <= 1e-9;
+                        okc = okc && fabs((v[e] - w[e]) * a.inv_lambda - (double)kTcElems * prev) <= 1e-9;
+                    }
+                }
+            }
+            const bool lin = __all_sync(0xffffffffu, ok);
+            const bool cont = lin && __all_sync(0xffffffffu, okp) && __all_sync(0xffffffffu, okc);
+            if (lane == 0) {
+                a.lin[u] = lin ? (cont ? 2 : 1) : 0;
+                for (int axis = 0; axis < 3; ++axis) {
+                    const float sh = (float)step[axis];
+                    a.stepf[(size_t)(2 * axis) * n_units + u] = sh;
+                    a.stepf[(size_t)(2 * axis + 1) * n_units + u] = (float)(step[axis] - (double)sh);
+                }
+            }
         }
     }
     const float bscale = ldexpf(1.0f, sar_scale_exp(__uint_as_float(__ldg(a.max_bits))));
     uint32_t* hi = a.bblk + (size_t)c * 2 * a.NB * kTcElems;
     uint32_t* lo = hi + a.NB * kTcElems;
-    for (int i = threadIdx.x; i < a.NB * kTcElems; i += blockDim.x) {
+    const int cols = (a.NB + kTcPrepSplit - 1) / kTcPrepSplit;
+    const int col0 = blockIdx.y * cols, col1 = min(a.NB, col0 + cols);
+    for (int i = col0 * kTcElems + threadIdx.x; i < col1 * kTcElems; i += blockDim.x) {
         const int col = i / kTcElems, nl = i - col * kTcElems;      // consecutive threads: consecutive n (coalesced reads)
         const int n = c * kTcElems + nl;
         const int s = col >= a.SP ? col - a.SP : col;
         cf x = cmake(0.f, 0.f);
-        if (s < a.S && n < a.N) {
-            x = cscale(__ldg(a.aperture + (size_t)s * a.N + n), __ldg(a.hamf + n));
-        }
+        if (s < a.S && n < a.N) x = cscale(__ldg(a.aperture + (size_t)s * a.N + n), __ldg(a.hamf + n));
         const float v0 = col >= a.SP ? x.y : x.x;       // multiplies Re W
         const float v1 = col >= a.SP ? x.x : -x.y;      // multiplies Im W
         const int idx = tc_canon(col, nl);
@@ -380,6 +402,22 @@ __global__ void __launch_bounds__(128 * MT * TPR + 64, 1) sar_tc_kernel(const __
         const int n_units = a.n_chunks * (kTcElems / kTcLin);
         const int row_word = ((row >> 3) * (kTcElems / 4)) * 32 + (row & 7) * 4;     // word of element 0 of this row
         int n_drained = 0;
+        // Equispaced units: phase(e) = t0 + e * delta.  Per unit the thread keeps the first coefficient w0 = exp(2 pi i t0)
+        // (scaled by 2^13) and the powers exp(2 pi i delta 2^k), k = 0..3 and 5, in registers from one chunk to the next.
+        // A unit that continues the progression of the unit one chunk earlier (flag 2) only multiplies w0 by the k = 5
+        // power (32 elements further on) - no phase, no sincos.  The chain restarts from the phases (flag 1 path) at the
+        // start of every accumulation segment and then every 8 chunks, so at most 7 such multiplies (~1e-7 each) stack
+        // up, the same ones whatever the tiling or the split of the aperture over CTAs.  The 16 coefficients of the unit
+        // are w0 times at most four of the powers (a ladder of 15 complex multiplies): ~7 instructions per element
+        // instead of ~46 for the general path.
+        constexpr int U = W / kTcLin;
+        float w0r[U], w0i[U], pwr[U][5], pwi[U][5];
+#pragma unroll
+        for (int i = 0; i < U; ++i) {
+            w0r[i] = 0.0f; w0i[i] = 0.0f;
+#pragma unroll
+            for (int k = 0; k < 5; ++k) { pwr[i][k] = 1.0f; pwi[i][k] = 0.0f; }
+        }
         for (int cl = 0; cl < n_local; ++cl) {
             const int c = c0 + cl;                                 // chunk of the aperture; cl counts this CTA's stages
             const int s = cl & 1, c_seg = cl % a.seg_chunks;
@@ -391,42 +429,46 @@ __global__ void __launch_bounds__(128 * MT * TPR + 64, 1) sar_tc_kernel(const __
             const double* px = a.posl + (size_t)c * kTcElems;
             const float* pf = a.posf + (size_t)c * kTcElems;
 #pragma unroll
-            for (int ul = 0; ul < W / kTcLin; ++ul) {
+            for (int ul = 0; ul < U; ++ul) {
                 const int nl0 = part * W + ul * kTcLin;            // first element (inside the chunk) of this unit
                 const int unit = (c * kTcElems + nl0) / kTcLin;
-                float wr[kTcLin], wi[kTcLin];                      // the coefficients, already scaled by 2^13
-                if (CS && a.lin && a.lin[unit]) {
-                    // Equispaced unit: phase(e) = t0 + e * delta.  The unit's first phase and delta as float pairs
-                    // (phase_pair, once per unit instead of once per element), exp(2 pi i delta 2^k) by sincos_turns of the
-                    // exactly doubled and re-reduced pair (no squaring error), and every coefficient is the first one times
-                    // at most four of those powers: ~10 instructions per element instead of ~46.  The five sincos chains
-                    // are independent (instruction-level parallelism for the two warps a scheduler holds).  The
-                    // arithmetic of an element does not depend on TPR (bit-identical tilings).
-                    float sh[3], sl[3], ph[3], pl[3];
+                float wr[kTcLin], wi[kTcLin];                      // the coefficients, scaled by 2^13
+                const int flag = (CS && a.lin) ? a.lin[unit] : 0;
+                if (flag) {
+                    if (flag == 2 && (c_seg & 7) != 0) {
+                        const float xr = w0r[ul], xi = w0i[ul];
+                        w0r[ul] = fmaf(xr, pwr[ul][4], -xi * pwi[ul][4]);
+                        w0i[ul] = fmaf(xr, pwi[ul][4], xi * pwr[ul][4]);
+                    } else {
+                        // the unit's first phase and delta as float pairs (phase_pair), exp(2 pi i delta 2^k) by sincos_turns
+                        // of the exactly doubled and re-reduced pair (no squaring error); the six sincos chains are independent
+                        float sh[3], sl[3], ph[3], pl[3];
 #pragma unroll
-                    for (int ax = 0; ax < 3; ++ax) {
-                        sh[ax] = __ldg(a.stepf + (size_t)(2 * ax) * n_units + unit);
-                        sl[ax] = __ldg(a.stepf + (size_t)(2 * ax + 1) * n_units + unit);
-                        ph[ax] = __ldg(pf + (size_t)(2 * ax) * a.npad + nl0);
-                        pl[ax] = __ldg(pf + (size_t)(2 * ax + 1) * a.npad + nl0);
-                    }
-                    float uh, ul2, t0h, t0l, ur[4], ui[4];
-                    phase_pair(dh, dl, sh, sl, &uh, &ul2);
-                    phase_pair(dh, dl, ph, pl, &t0h, &t0l);
+                        for (int ax = 0; ax < 3; ++ax) {
+                            sh[ax] = __ldg(a.stepf + (size_t)(2 * ax) * n_units + unit);
+                            sl[ax] = __ldg(a.stepf + (size_t)(2 * ax + 1) * n_units + unit);
+                            ph[ax] = __ldg(pf + (size_t)(2 * ax) * a.npad + nl0);
+                            pl[ax] = __ldg(pf + (size_t)(2 * ax + 1) * a.npad + nl0);
+                        }
+                        float uh, ul2, t0h, t0l;
+                        phase_pair(dh, dl, sh, sl, &uh, &ul2);
+                        phase_pair(dh, dl, ph, pl, &t0h, &t0l);
 #pragma unroll
-                    for (int k = 0; k < 4; ++k) {
-                        sincos_turns(uh + ul2, &ui[k], &ur[k]);
-                        uh *= 2.0f; ul2 *= 2.0f;
-                        uh -= (uh + 12582912.0f) - 12582912.0f;
+                        for (int k = 0; k < 6; ++k) {
+                            if (k != 4) sincos_turns(uh + ul2, &pwi[ul][k < 4 ? k : 4], &pwr[ul][k < 4 ? k : 4]);
+                            uh *= 2.0f; ul2 *= 2.0f;
+                            uh -= (uh + 12582912.0f) - 12582912.0f;
+                        }
+                        sincos_turns(t0h + t0l, &w0i[ul], &w0r[ul]);
+                        w0r[ul] *= kTcAScale; w0i[ul] *= kTcAScale;      // exact; every product inherits the scale
                     }
-                    sincos_turns(t0h + t0l, &wi[0], &wr[0]);
-                    wr[0] *= kTcAScale; wi[0] *= kTcAScale;       // exact; every product below inherits the scale
+                    wr[0] = w0r[ul]; wi[0] = w0i[ul];
 #pragma unroll
                     for (int k = 0; k < 4; ++k) {
 #pragma unroll
                         for (int e = 0; e < (1 << k); ++e) {
-                            wr[(1 << k) + e] = fmaf(wr[e], ur[k], -wi[e] * ui[k]);
-                            wi[(1 << k) + e] = fmaf(wr[e], ui[k], wi[e] * ur[k]);
+                            wr[(1 << k) + e] = fmaf(wr[e], pwr[ul][k], -wi[e] * pwi[ul][k]);
+                            wi[(1 << k) + e] = fmaf(wr[e], pwi[ul][k], wi[e] * pwr[ul][k]);
                         }
                     }
                 } else {
@@ -491,21 +533,22 @@ __global__ void __launch_bounds__(128 * MT * TPR + 64, 1) sar_tc_kernel(const __
                     tmem_ld16(taddr + a.SP + s0, im);
                     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                     if (g_out < width && !a.skip_drain_stores) {
-                        // ksplit > 1: this segment's own array, plain stores; ksplit == 1: accumulate in place
+                        // ksplit > 1: this segment's own array, plain stores; ksplit == 1: accumulate in place - the first
+                        // segment stores, the later ones add with fire-and-forget reductions (red.global.add, round to
+                        // nearest in the L2): nothing is loaded, and the additions to one address come from this one
+                        // thread in program order, so the sum is the same sequence of fp32 adds as the per-segment arrays.
                         cf* dst = a.beams + (a.parts ? (size_t)(seg0 + n_drained) * a.S * width : (size_t)0) + (size_t)s0 * width + g_out;
-                        cf old[16];
-                        if (n_drained > 0 && !a.parts) {              // all loads in flight before the first store
+                        if (n_drained > 0 && !a.parts) {
 #pragma unroll
                             for (int i = 0; i < 16; ++i)
-                                old[i] = (s0 + i < a.S) ? __ldcg(dst + (size_t)i * width) : cmake(0.f, 0.f);
+                                if (s0 + i < a.S)
+                                    asm volatile("red.global.add.v2.f32 [%0], {%1, %2};" ::"l"(dst + (size_t)i * width), "f"(__uint_as_float(re[i])),
+                                                 "f"(__uint_as_float(im[i])) : "memory");
                         } else {
 #pragma unroll
-                            for (int i = 0; i < 16; ++i) old[i] = cmake(0.f, 0.f);
+                            for (int i = 0; i < 16; ++i)
+                                if (s0 + i < a.S) __stcg(dst + (size_t)i * width, cmake(__uint_as_float(re[i]), __uint_as_float(im[i])));
                         }
-#pragma unroll
-                        for (int i = 0; i < 16; ++i)
-                            if (s0 + i < a.S)
-                                __stcg(dst + (size_t)i * width, cmake(__uint_as_float(re[i]) + old[i].x, __uint_as_float(im[i]) + old[i].y));
                     }
                 }
                 ++n_drained;
@@ -569,10 +612,11 @@ __global__ void __launch_bounds__(256) sar_range_fft_kernel(const __grid_constan
 }
 
 // The same for S = 2 * H with H odd and a register transform Dft<H> (S = 90: the RadSAR cfgs): no shared-memory tile at
-// all.  Lanes are directions (every load and store is a coalesced row segment of [S][width]); the two halves of a
-// CTA are the two output classes k = k1 (mod 2) of the prime-factor split 2 x H:
+// all.  Lanes are directions (every load and store is a coalesced row segment of [S][width]); lanes l and l ^ 16 work on
+// the same direction and are the two output classes k = k1 (mod 2) of the prime-factor split 2 x H:
 //   X[(H k1 + (H + 1) k2) mod S] = sum_n2 ( v[2 n2 mod S] + (-1)^k1 v[(H + 2 n2) mod S] ) W_H^(n2 k2)
-// so a thread forms H sums / differences and runs one H-point transform in registers.
+// Lane k1 loads the H samples v[(H k1 + 2 n2) mod S] (every sample is read once), gets the partner's by shuffle, forms
+// the H sums / differences and runs one H-point transform in registers.
 constexpr int kTcFftRegDirs = 64;
 template <int H>
 __global__ void __launch_bounds__(2 * kTcFftRegDirs) sar_range_fft_reg_kernel(const __grid_constant__ SarFftArgs a) {
@@ -581,28 +625,27 @@ __global__ void __launch_bounds__(2 * kTcFftRegDirs) sar_range_fft_reg_kernel(co
     for (int i = threadIdx.x; i < S; i += blockDim.x) win[i] = a.winS[i];
     __syncthreads();
     const float descale = ldexpf(1.0f, -13 - sar_scale_exp(__uint_as_float(__ldg(a.max_bits))));
-    const int k1 = threadIdx.x / kTcFftRegDirs;                           // warp uniform
-    const int g = blockIdx.x * kTcFftRegDirs + (threadIdx.x - k1 * kTcFftRegDirs);
-    if (g >= a.width) return;
-    const float sigma = k1 ? -1.0f : 1.0f;
+    const int lane = threadIdx.x & 31, k1 = lane >> 4;
+    const int g_raw = blockIdx.x * kTcFftRegDirs + (threadIdx.x >> 5) * 16 + (lane & 15);
+    const int g = min(g_raw, a.width - 1);                                // surplus lanes repeat the last direction, no store
     const cf* src = a.beams + g;
     const size_t part_stride = (size_t)S * a.width;
     cf y[H];
 #pragma unroll
     for (int n2 = 0; n2 < H; ++n2) {
-        const int s0 = (2 * n2) % S, s1 = (H + 2 * n2) % S;
-        cf v0 = __ldcg(src + (size_t)s0 * a.width), v1 = __ldcg(src + (size_t)s1 * a.width);
-        for (int k = 1; k < a.n_part; ++k) {                              // segment order, the additions of the in-place accumulation
-            const cf u0 = __ldcg(src + (size_t)k * part_stride + (size_t)s0 * a.width);
-            const cf u1 = __ldcg(src + (size_t)k * part_stride + (size_t)s1 * a.width);
-            v0 = cmake(u0.x + v0.x, u0.y + v0.y);
-            v1 = cmake(u1.x + v1.x, u1.y + v1.y);
-        }
-        v0 = cscale(cscale(v0, descale), win[s0]);
-        v1 = cscale(cscale(v1, descale), win[s1]);
-        y[n2] = cmake(fmaf(sigma, v1.x, v0.x), fmaf(sigma, v1.y, v0.y));
+        const int s_mine = k1 ? (H + 2 * n2) % S : (2 * n2) % S;
+        cf v = __ldcg(src + (size_t)s_mine * a.width);
+        if (a.n_part > 1)
+            for (int k = 1; k < a.n_part; ++k) {                          // segment order, the additions of the in-place accumulation
+                const cf u = __ldcg(src + (size_t)k * part_stride + (size_t)s_mine * a.width);
+                v = cmake(u.x + v.x, u.y + v.y);
+            }
+        v = cscale(cscale(v, descale), win[s_mine]);
+        const cf o = cmake(__shfl_xor_sync(0xffffffffu, v.x, 16), __shfl_xor_sync(0xffffffffu, v.y, 16));
+        y[n2] = k1 ? cmake(o.x - v.x, o.y - v.y) : cmake(v.x + o.x, v.y + o.y);
     }
     Dft<H>::run(y);
+    if (g_raw >= a.width) return;
     cf* dst = a.out + g;
 #pragma unroll
     for (int k2 = 0; k2 < H; ++k2) {
@@ -674,7 +717,7 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
         RB_CUDA_OK(ctx, cudaGetLastError());
     }
     SarPrepArgs p{aperture, S, N, SP, NB, n_chunks, positions, 1.0 / lambda_m, bblk, posl, posf, stepf, lin, max_bits, hamf};
-    sar_tc_prep_kernel<<<n_chunks, 256, 0, st>>>(p);
+    sar_tc_prep_kernel<<<dim3((unsigned)n_chunks, kTcPrepSplit), 256, 0, st>>>(p);
     RB_CUDA_OK(ctx, cudaGetLastError());
 
     SarTcArgs a{bblk, posl, posf, stepf, (ctx->sar_dbg & 32) ? nullptr : lin, dirs, npad, n_chunks, seg_chunks, G, S, SP, NB, g_begin, g_end, beams,
