@@ -280,6 +280,7 @@ struct SarTcArgs {
     // how the aperture is cut over CTAs (slices of the grid, which pick another ksplit, stay bit-identical to the full grid).
     int ksplit, segs_per_split;
     int parts;            // 1: one array per segment (always with ksplit > 1; RADAR_B200_SAR_PARTS=1 forces it for ksplit == 1)
+    size_t part_stride;   // cells between two per-segment arrays (S of the whole call x width; S here is one column tile of it)
     int skip_drain_stores;   // RADAR_B200_SAR_DBG & 64: timing experiment, the drains read TMEM but do not touch `beams` (image invalid)
 };
 
@@ -537,7 +538,7 @@ __global__ void __launch_bounds__(128 * MT * TPR + 64, 1) sar_tc_kernel(const __
                         // segment stores, the later ones add with fire-and-forget reductions (red.global.add, round to
                         // nearest in the L2): nothing is loaded, and the additions to one address come from this one
                         // thread in program order, so the sum is the same sequence of fp32 adds as the per-segment arrays.
-                        cf* dst = a.beams + (a.parts ? (size_t)(seg0 + n_drained) * a.S * width : (size_t)0) + (size_t)s0 * width + g_out;
+                        cf* dst = a.beams + (a.parts ? (size_t)(seg0 + n_drained) * a.part_stride : (size_t)0) + (size_t)s0 * width + g_out;
                         if (n_drained > 0 && !a.parts) {
 #pragma unroll
                             for (int i = 0; i < 16; ++i)
@@ -657,8 +658,14 @@ __global__ void __launch_bounds__(2 * kTcFftRegDirs) sar_range_fft_reg_kernel(co
 // 1 = shape not handled here (caller falls back to the FP32-pipe kernel), 0 = launched, < 0 = error
 int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const double* positions, const double* dirs,
                         int G, double lambda_m, int g_begin, int g_end, cf* out, cudaStream_t st) {
-    const int SP = (S + 7) & ~7, NB = 2 * SP;
-    if (NB > 256 || (NB & 15) != 0) return 1;                   // tcgen05.mma with M = 128 takes N in 16..256, multiples of 16
+    // tcgen05.mma with M = 128 takes N in 16..256 (multiples of 16) and N = 2 * samples here, so more than 128 range samples
+    // are cut into column tiles of 96 samples (192 columns: two accumulator tiles of 128 directions still fit the shared
+    // memory stages and TMEM, as for S = 90); every tile is one pass of prep + GEMM over the whole aperture into its rows
+    // of the beams, the range FFT then runs once over all S.
+    const int ST = S <= 128 ? S : 96;
+    const int n_tiles = (S + ST - 1) / ST;
+    const int SP = (ST + 7) & ~7, NB = 2 * SP;                  // the widest tile: sizes the stages and the B blocks
+    if (NB > 256 || (NB & 15) != 0) return 1;
     const int width = g_end - g_begin;
     const int n_chunks = (N + kTcElems - 1) / kTcElems, npad = n_chunks * kTcElems;
     // segment length: the truncation bias grows linearly with it (measured on S = 90, N = 2000 against fp64: 2.1e-6 relative
@@ -716,12 +723,16 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
         sar_tc_max_kernel<<<dim3((unsigned)((N + kTcMaxThreads - 1) / kTcMaxThreads), (unsigned)slices), kTcMaxThreads, 0, st>>>(aperture, S, N, hamf, max_bits);
         RB_CUDA_OK(ctx, cudaGetLastError());
     }
-    SarPrepArgs p{aperture, S, N, SP, NB, n_chunks, positions, 1.0 / lambda_m, bblk, posl, posf, stepf, lin, max_bits, hamf};
+    const size_t fsmem = arena_bytes((size_t)S * (kTcFftDirs | 1), sizeof(cf)) + arena_bytes(S, sizeof(cf)) + arena_bytes(S, 4) + arena_bytes(S, 2);
+    if (fsmem > (size_t)ctx->max_smem_optin) return 1;          // the range FFT of the beams keeps S x 33 cells in shared memory
+    for (int t = 0; t < n_tiles; ++t) {
+    const int s_base = t * ST, S_t = (S - s_base < ST) ? S - s_base : ST, SP_t = (S_t + 7) & ~7, NB_t = 2 * SP_t;
+    SarPrepArgs p{aperture + (size_t)s_base * N, S_t, N, SP_t, NB_t, n_chunks, positions, 1.0 / lambda_m, bblk, posl, posf, stepf, lin, max_bits, hamf};
     sar_tc_prep_kernel<<<dim3((unsigned)n_chunks, kTcPrepSplit), 256, 0, st>>>(p);
     RB_CUDA_OK(ctx, cudaGetLastError());
 
-    SarTcArgs a{bblk, posl, posf, stepf, (ctx->sar_dbg & 32) ? nullptr : lin, dirs, npad, n_chunks, seg_chunks, G, S, SP, NB, g_begin, g_end, beams,
-                ksplit, segs_per_split, n_part > 1 ? 1 : 0, (ctx->sar_dbg & 64) ? 1 : 0};
+    SarTcArgs a{bblk, posl, posf, stepf, (ctx->sar_dbg & 32) ? nullptr : lin, dirs, npad, n_chunks, seg_chunks, G, S_t, SP_t, NB_t, g_begin, g_end,
+                beams + (size_t)s_base * width, ksplit, segs_per_split, n_part > 1 ? 1 : 0, (size_t)S * width, (ctx->sar_dbg & 64) ? 1 : 0};
     const int tpr = ctx->sar_tpr > 0 ? ctx->sar_tpr : (mt == 2 ? 1 : 2);      // measured: 0.443 / 0.450 ms (2 tiles), 0.550 / 0.503 ms (1 tile)
     const int unr = ctx->sar_dbg & 15, cs = !(ctx->sar_dbg & 16);      // RADAR_B200_SAR_DBG: unroll of the element loop (0 = default), +16 = sincospif
 #define RB_SAR_TC_LAUNCH(MT_, TPR_, UNR_, CS_)                                                                               \
@@ -741,6 +752,7 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
 #undef RB_SAR_TC_VARIANTS
 #undef RB_SAR_TC_LAUNCH
     RB_CUDA_OK(ctx, cudaGetLastError());
+    }
 
     SarFftArgs f{beams, n_part, S, width, ctx->fftS.hann, ctx->fftS.tw, ctx->fftS.pos, out, ctx->fftS.plan, make_fastdiv(kTcFftDirs), max_bits};
     if (S == 90 && !(ctx->sar_dbg & 128)) {            // RADAR_B200_SAR_DBG & 128: the shared-memory transform for every S (comparison)
@@ -748,7 +760,6 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
         RB_CUDA_OK(ctx, cudaGetLastError());
         return RADAR_OK;
     }
-    const size_t fsmem = arena_bytes((size_t)S * (kTcFftDirs | 1), sizeof(cf)) + arena_bytes(S, sizeof(cf)) + arena_bytes(S, 4) + arena_bytes(S, 2);
     RB_CUDA_OK(ctx, cudaFuncSetAttribute(sar_range_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsmem));
     sar_range_fft_kernel<<<(unsigned)((width + kTcFftDirs - 1) / kTcFftDirs), 256, fsmem, st>>>(f);
     RB_CUDA_OK(ctx, cudaGetLastError());

@@ -77,14 +77,35 @@ def test_tensor_core_path_matches_fp64_and_fp32_kernel(torch_cuda, s, n, g):
     np.testing.assert_array_equal(part, outs[2][:, lo:hi])
 
 
-def test_fallback_shape_and_throughput_grid(torch_cuda):
-    """S = 200 does not fit one MMA (N = 2 S > 256): the FP32-pipe kernel serves it.  The throughput grid of SURVEY.md
-    section 8d (S = 90, N = 2000, G = 32768) is checked on a sample of directions."""
+@pytest.mark.parametrize("s,n,g", [(200, 64, 40), (130, 100, 150), (512, 300, 300)])
+def test_more_than_128_range_samples_stay_on_the_tensor_cores(torch_cuda, s, n, g):
+    """2 S > 256 does not fit one MMA: the samples are cut into column tiles of 96 (one pass of prep + GEMM each, one range
+    FFT over all S).  Against fp64 and the FP32-pipe kernel; a voxel slice and a forced aperture split stay bit-identical."""
     torch = torch_cuda
-    x, pos, dirs, lam = sar_case(200, 64, 40, seed=5)
-    eng = engine_with_mode(0, 200)
-    out = eng.sar_image(torch.from_numpy(x).cuda(), torch.from_numpy(pos).cuda(), torch.from_numpy(dirs).cuda(), lam)
-    assert rel_l2(out.cpu().numpy(), sar_direct(x, pos, dirs, lam, np.arange(40))) < TOL
+    from mmwave_radar_processing_b200.engine import RadarEngine
+    x, pos, dirs, lam = sar_case(s, n, g, seed=s + n)
+    want = sar_direct(x, pos, dirs, lam, np.arange(g))
+    xs, ps, ds = torch.from_numpy(x).cuda(), torch.from_numpy(pos).cuda(), torch.from_numpy(dirs).cuda()
+    tc = engine_with_mode(0, s).sar_image(xs, ps, ds, lam).cpu().numpy()
+    fp32 = engine_with_mode(1, s).sar_image(xs, ps, ds, lam).cpu().numpy()
+    assert rel_l2(tc, want) < TOL, rel_l2(tc, want)
+    assert rel_l2(fp32, want) < TOL
+    assert rel_l2(tc, fp32) < 1e-5
+    assert not np.array_equal(tc, fp32)                      # the tensor-core path really ran
+    lo, hi = g // 3, g - 5
+    part = engine_with_mode(0, s).sar_image(xs, ps, ds, lam, lo, hi).cpu().numpy()
+    np.testing.assert_array_equal(part, tc[:, lo:hi])
+    os.environ["RADAR_B200_SAR_KSPLIT"] = "2"
+    try:
+        eng = RadarEngine(1, s, 1, 1)
+    finally:
+        del os.environ["RADAR_B200_SAR_KSPLIT"]
+    np.testing.assert_array_equal(eng.sar_image(xs, ps, ds, lam).cpu().numpy(), tc)
+
+
+def test_throughput_grid(torch_cuda):
+    """The throughput grid of SURVEY.md section 8d (S = 90, N = 2000, G = 32768) is checked on a sample of directions."""
+    torch = torch_cuda
     x, pos, dirs, lam = sar_case(90, 2000, 32768, seed=6)
     eng = engine_with_mode(0, 90)
     out = eng.sar_image(torch.from_numpy(x).cuda(), torch.from_numpy(pos).cuda(), torch.from_numpy(dirs).cuda(), lam)

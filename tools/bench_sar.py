@@ -63,6 +63,33 @@ def main():
                 line["measured_bf16_peak_tflops"] = bf16_peak
         print(json.dumps(line), flush=True)
 
+    # more than 128 range samples (RadarHD: S = 512): column tiles of 96 samples on the tensor cores against the FP32-pipe kernel
+    s2, g2 = 512, 8192
+    x2 = (rng.integers(-2000, 2000, (s2, n)) + 1j * rng.integers(-2000, 2000, (s2, n))).astype(np.complex64)
+    x2s, d2s = torch.from_numpy(x2).cuda(), ds[:, :g2].contiguous()
+    os.environ["RADAR_B200_SAR_DBG"] = "0"
+    os.environ["RADAR_B200_SAR_TPR"] = "0"
+    ref2 = None
+    for mode, label, reps in ((1, "fp32_pipe_S512", 3), (0, "tcgen05_f16x3_S512_column_tiles", 10)):
+        os.environ["RADAR_B200_SAR"] = str(mode)
+        eng = RadarEngine(1, s2, 1, 1)
+        out = torch.empty((s2, g2), dtype=torch.complex64, device="cuda")
+        for _ in range(2):
+            eng.sar_image(x2s, ps, d2s, 0.0039, out=out)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            eng.sar_image(x2s, ps, d2s, 0.0039, out=out)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        if ref2 is None:
+            ref2 = out.clone()
+        print(json.dumps({"kernel": label, "S": s2, "N": n, "G": g2, "ms_per_image": ms,
+                          "useful_tflops": 8.0 * s2 * n * g2 / (ms * 1e-3) / 1e12,
+                          "rel_l2_vs_fp32_pipe": float((torch.linalg.norm(out - ref2) / torch.linalg.norm(ref2)).item())}), flush=True)
+
 
 if __name__ == "__main__":
     main()
