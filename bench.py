@@ -416,7 +416,18 @@ def run_sar(a):
         ps = torch.empty((3, n), dtype=torch.float64, device=dev)
     ds = torch.from_numpy(dirs).to(dev)
 
+    # N > 1: the exchange is fused into the kernels (distributed.PeerImageExchange: the range-FFT kernel stores its tile
+    # into every rank's image over NVLink peer memory, the kernels read rank 0's aperture from its symmetric region);
+    # RADAR_B200_SAR_EXCHANGE=nccl keeps the collectives (broadcast + all-gather) for comparison.
+    fused = world > 1 and os.environ.get("RADAR_B200_SAR_EXCHANGE", "peer") != "nccl"
+    ex = rdist.PeerImageExchange(eng, s, n, g, depth=2, src=0) if fused else None
+    step_no = [0]
+
     def step():
+        if ex is not None:
+            k = step_no[0]
+            step_no[0] += 1
+            return ex.run(k, ds, lam, xs if rank == 0 else None, ps if rank == 0 else None)
         # broadcast of the aperture cube + geometry from rank 0, this rank's direction slice, all-gather of the tiles
         img, _ = rdist.sar_image_sharded(lambda ap, po, di, lo, hi: eng.sar_image(ap, po, di, lam, lo, hi),
                                          xs, ps, ds, src=0, gather=True)
@@ -425,6 +436,27 @@ def run_sar(a):
     for _ in range(max(3, a.warmup)):
         img = step()
     torch.cuda.synchronize()
+    graphed = False
+    if ex is not None and os.environ.get("RADAR_B200_SAR_GRAPH", "1") != "0":
+        # one image is ten short launches per rank: replay them as a CUDA graph per image slot so the host does not set the pace
+        ok = torch.ones(1, device=dev)
+        try:
+            replay = ex.capture(ds, lam, xs if rank == 0 else None, ps if rank == 0 else None)
+        except Exception as exc:  # noqa: BLE001 - capture is an optimisation; the eager path below is the same work
+            replay = None
+            ok.zero_()
+            print(f"[bench] rank {rank}: graph capture failed ({exc}); eager launches", file=sys.stderr)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        if float(ok.item()) > 0:
+            graphed = True
+
+            def step():  # noqa: F811
+                k = step_no[0]
+                step_no[0] += 1
+                return replay(k)
+            for _ in range(3):
+                img = step()
+            torch.cuda.synchronize()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     if sampler:
         sampler.start()
@@ -441,11 +473,14 @@ def run_sar(a):
     if world > 1:
         dist.barrier()
     ms_total = e0.elapsed_time(e1)
-    # kernel-only time of this rank's slice (no collectives)
+    # kernel-only time of this rank's slice (no collectives, no mirrors)
+    if ex is not None:
+        ex.disarm()
     lo, hi = rdist.shard_range(g, rank, world)
+    kx, kp = ex.inputs() if ex is not None else (xs, ps)      # the fused variant: this rank's pulled copy of rank 0's cube
     k0.record()
     for _ in range(a.steps):
-        eng.sar_image(xs, ps, ds, lam, lo, hi)
+        eng.sar_image(kx, kp, ds, lam, lo, hi)
     k1.record()
     torch.cuda.synchronize()
     k_ms = k0.elapsed_time(k1) / a.steps
@@ -488,8 +523,12 @@ def run_sar(a):
                 "data": "synthetic aperture cube (seeded integers), linear platform track",
                 "config": {"workload": "configs/RadSAR_1843_official.cfg multi-frame synthetic array: S=90 range bins, N=2000 "
                                        "aperture elements, G=512x64 directions", "S": s, "N": n, "G": g,
-                           "parallelism": f"voxel-sharded x{world}: NCCL broadcast of aperture cube + geometry, "
-                                          "radar_sar_image(g_begin, g_end) per rank, NCCL all-gather of the image tiles",
+                           "parallelism": (f"voxel-sharded x{world}: radar_sar_image(g_begin, g_end) per rank reads rank 0's aperture cube + "
+                                           "geometry over NVLink peer memory and its range-FFT kernel stores the tile into every rank's "
+                                           "image (symmetric memory, radar_ctx_set_image_mirrors); two device barriers per image, no collective"
+                                           if fused else
+                                           f"voxel-sharded x{world}: NCCL broadcast of aperture cube + geometry, "
+                                           "radar_sar_image(g_begin, g_end) per rank, NCCL all-gather of the image tiles"),
                            "l2_policy": "operands (1.4 MB) are L2-resident by design; output tiles are written once"},
                 "roofline": {"kernel": "sar_tc_kernel", "bound": "tensor", "achieved": executed,
                              "peak": bf16 if bf16 else None, "unit": "TFLOP/s",
@@ -501,7 +540,7 @@ def run_sar(a):
                         "h2d_bytes_per_step": int(x.nbytes + pos.nbytes), "d2h_bytes_per_step": int(s * g * 8),
                         "ms_per_step": e2e_ms / e2e_steps, "steps": e2e_steps,
                         "api": "distributed.sar_image_sharded over RadarEngine.sar_image (pinned host aperture in, host image out)"},
-                "gpu_launches": a.steps * 4, "clocks": clocks}
+                "gpu_launches": a.steps * 4, "cuda_graph": graphed, "clocks": clocks}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

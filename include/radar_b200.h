@@ -234,6 +234,16 @@ int radar_sar_image(radar_ctx* ctx, const void* aperture, int num_samples, int n
                     const double* positions, const double* dirs, int n_dirs, double lambda_m,
                     int g_begin, int g_end, void* out, void* stream);
 
+/* Multi-GPU exchange fused into the beamformer (the voxel-sharded image).  After this call every cell
+ * out[k][j] that radar_sar_image writes (k = range bin, j = direction - g_begin) is also stored at
+ * mirrors[i] + k * row_stride + col_offset + j (complex64 cells): mirrors are device pointers the kernel can store to - the
+ * full [S][G] images of the other ranks (NVLink / NVSwitch peer memory, e.g. torch symmetric memory) and this rank's own -
+ * with row_stride = G and col_offset = this rank's g_begin, so the all-gather of the image tiles happens inside the
+ * range-FFT kernel, cell by cell, already in the final layout: no collective kernel, no staging copy, no transpose.
+ * h_mirrors: host array of n_mirrors (<= 16) device pointers (8-byte aligned); n_mirrors = 0 switches it off.  Completion
+ * across ranks is the caller's barrier.  No counterpart in the reference (single process). */
+int radar_ctx_set_image_mirrors(radar_ctx* ctx, const uint64_t* h_mirrors, int n_mirrors, int64_t row_stride, int64_t col_offset);
+
 /* ---- SAR self-calibration of the synthetic-array geometry ---------------------- *
  * SyntheticArrayBeamformerProcessor.perform_array_calibration
  * (processors/simple_synthetic_array_beamformer_processor_multiFrame.py:673-816): range FFT of the windowed

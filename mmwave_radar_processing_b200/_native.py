@@ -61,6 +61,7 @@ SIGNATURES = {
     "radar_polar_to_cart": (_I, [_P, _P, _I, _I, _I, _P, _P, _P, _I, C.c_double, C.c_double, _I, C.c_double, C.c_double, _I, _I,
                                  _P, _P, _P]),
     "radar_ctx_set_point_mirrors": (_I, [_P, _P, _I, _I]),
+    "radar_ctx_set_image_mirrors": (_I, [_P, _P, _I, C.c_int64, C.c_int64]),
     "radar_doppler_azimuth": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _I, _I, _P, _P]),
     "radar_chirp_zoom": (_I, [_P, _P, _I, _I, _I, _I, _P, _I, _P, _P]),
     "radar_chirp_zoom_static": (_I, [_P, _P, _I, _I, _I, _I, _P, _I, _P, _P]),

@@ -229,6 +229,20 @@ int radar_ctx_set_point_mirrors(radar_ctx* ctx, const uint64_t* h_mirrors, int n
     return RADAR_OK;
 }
 
+int radar_ctx_set_image_mirrors(radar_ctx* ctx, const uint64_t* h_mirrors, int n_mirrors, int64_t row_stride, int64_t col_offset) {
+    RB_ENTER(ctx);
+    if (n_mirrors < 0 || n_mirrors > 16) return set_error(ctx, RADAR_E_INVALID, "n_mirrors %d outside 0..16", n_mirrors);
+    if (n_mirrors > 0 && (!h_mirrors || row_stride <= 0 || col_offset < 0)) return set_error(ctx, RADAR_E_INVALID, "mirrors need pointers, a positive row stride and a non-negative column offset");
+    for (int i = 0; i < n_mirrors; ++i) {
+        if (!h_mirrors[i] || (h_mirrors[i] & 7u)) return set_error(ctx, RADAR_E_INVALID, "mirror %d is null or not 8-byte aligned", i);
+        ctx->image_mirrors[i] = reinterpret_cast<cf*>(h_mirrors[i]);
+    }
+    ctx->n_image_mirrors = n_mirrors;
+    ctx->image_row_stride = n_mirrors > 0 ? row_stride : 0;
+    ctx->image_col0 = n_mirrors > 0 ? col_offset : 0;
+    return RADAR_OK;
+}
+
 int radar_range_doppler(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, const int32_t* ant_list, int n_ant,
                         int window_flags, void* rd_out, float* mag_out, int mag_antenna, void* stream) {
     RB_ENTER(ctx);

@@ -135,6 +135,11 @@ int launch_sar_image(radar_ctx* ctx, const cf* aperture, int num_samples, int n_
     const int grid = (g_end - g_begin + kSarDirs - 1) / kSarDirs;
     sar_kernel<<<grid, kSarThreads, smem, st>>>(a);
     RB_CUDA_OK(ctx, cudaGetLastError());
+    // radar_ctx_set_image_mirrors on this (comparison / fallback) path: strided copies of the finished tile
+    const size_t row_bytes = (size_t)(g_end - g_begin) * sizeof(cf);
+    for (int m = 0; m < ctx->n_image_mirrors; ++m)
+        RB_CUDA_OK(ctx, cudaMemcpy2DAsync(ctx->image_mirrors[m] + ctx->image_col0, (size_t)ctx->image_row_stride * sizeof(cf), out, row_bytes,
+                                          row_bytes, (size_t)S, cudaMemcpyDeviceToDevice, st));
     return RADAR_OK;
 }
 

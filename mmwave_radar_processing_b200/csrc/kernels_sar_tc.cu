@@ -574,6 +574,11 @@ struct SarFftArgs {
     FftPlan planS;
     FastDiv divDirs;
     const uint32_t* max_bits;   // the operand scales of the GEMM are undone here (exact powers of two)
+    // radar_ctx_set_image_mirrors: every cell is also stored at mirrors[i][k * mstride + mcol0 + column] - the full images of
+    // all ranks over NVLink peer memory (the all-gather of the tiles, done by the stores of this kernel)
+    cf* mirrors[16];
+    int n_mirrors;
+    long long mstride, mcol0;
 };
 
 __global__ void __launch_bounds__(256) sar_range_fft_kernel(const __grid_constant__ SarFftArgs a) {
@@ -608,7 +613,11 @@ __global__ void __launch_bounds__(256) sar_range_fft_kernel(const __grid_constan
     fft_axis(tile, Gp, 1, kTcFftDirs, a.divDirs, a.planS, tw);
     for (int i = threadIdx.x; i < cells; i += blockDim.x) {
         const int k = i / kTcFftDirs, gl = i - k * kTcFftDirs;
-        if (g0 + gl < a.width) a.out[(size_t)k * a.width + g0 + gl] = tile[pos[k] * Gp + gl];
+        if (g0 + gl < a.width) {
+            const cf v = tile[pos[k] * Gp + gl];
+            a.out[(size_t)k * a.width + g0 + gl] = v;
+            for (int m = 0; m < a.n_mirrors; ++m) a.mirrors[m][(size_t)k * a.mstride + a.mcol0 + g0 + gl] = v;
+        }
     }
 }
 
@@ -652,6 +661,14 @@ __global__ void __launch_bounds__(2 * kTcFftRegDirs) sar_range_fft_reg_kernel(co
     for (int k2 = 0; k2 < H; ++k2) {
         const int k = (H * k1 + (H + 1) * k2) % S;
         dst[(size_t)k * a.width] = y[k2];
+    }
+    for (int m = 0; m < a.n_mirrors; ++m) {
+        cf* md = a.mirrors[m] + a.mcol0 + g;
+#pragma unroll
+        for (int k2 = 0; k2 < H; ++k2) {
+            const int k = (H * k1 + (H + 1) * k2) % S;
+            md[(size_t)k * a.mstride] = y[k2];
+        }
     }
 }
 
@@ -754,7 +771,8 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
     RB_CUDA_OK(ctx, cudaGetLastError());
     }
 
-    SarFftArgs f{beams, n_part, S, width, ctx->fftS.hann, ctx->fftS.tw, ctx->fftS.pos, out, ctx->fftS.plan, make_fastdiv(kTcFftDirs), max_bits};
+    SarFftArgs f{beams, n_part, S, width, ctx->fftS.hann, ctx->fftS.tw, ctx->fftS.pos, out, ctx->fftS.plan, make_fastdiv(kTcFftDirs), max_bits, {nullptr}, ctx->n_image_mirrors, ctx->image_row_stride, ctx->image_col0};
+    for (int m = 0; m < ctx->n_image_mirrors; ++m) f.mirrors[m] = ctx->image_mirrors[m];
     if (S == 90 && !(ctx->sar_dbg & 128)) {            // RADAR_B200_SAR_DBG & 128: the shared-memory transform for every S (comparison)
         sar_range_fft_reg_kernel<45><<<(unsigned)((width + kTcFftRegDirs - 1) / kTcFftRegDirs), 2 * kTcFftRegDirs, 0, st>>>(f);
         RB_CUDA_OK(ctx, cudaGetLastError());

@@ -50,6 +50,9 @@ struct radar_ctx {
     int sar_seg_chunks = 0;                       // RADAR_B200_SAR_SEG: chunks (16 elements) per accumulation segment, 0 = automatic
     double* point_mirrors[16] = {nullptr};       // radar_ctx_set_point_mirrors: extra destinations of every packed point row
     int n_point_mirrors = 0, point_mirror_cap = 0;
+    rb::cf* image_mirrors[16] = {nullptr};       // radar_ctx_set_image_mirrors: extra destinations of every cell radar_sar_image writes
+    int n_image_mirrors = 0;
+    long long image_row_stride = 0, image_col0 = 0;
     int cfar_ph1 = -1;                            // RADAR_B200_CFAR_PH1: extra full rows of the OS-CFAR first counting phase (-1 = default)
     int cfar_box = 1;                             // RADAR_B200_CFAR_BOX=0: CA-CFAR by one window walk per cell (comparison)
     int cfar_tile = 0;                            // RADAR_B200_CFAR_TILE=n: force n x n tiles in the CFAR kernel (tests of the large-map path)

@@ -216,3 +216,108 @@ class PeerPointExchange:
         cnt = s[:, self.cnt_off:self.tot_off].view(torch.int32)
         tot = s[:, self.tot_off:self.tot_off + 4].view(torch.int32).view(self.world)
         return pts, cnt, tot
+
+
+class PeerImageExchange:
+    """The voxel-sharded synthetic-array image over NVLink peer memory, without a collective: one symmetric allocation
+    holds the aperture cube + geometry of the feeding rank and ``depth`` full [S][G] images on every rank.
+
+        ex.put_inputs(aperture, positions)      # rank ``src`` only: into its symmetric region; then every rank:
+        ex.inputs_ready()                       # cross-rank barrier on the current stream
+        ap, po = ex.inputs()                    # this rank's copy, pulled from rank src's region by one peer copy each (1.5 MB)
+        ex.arm(k)                               # radar_sar_image also stores its cells into image k of EVERY rank, at this rank's columns
+        engine.sar_image(ap, po, dirs, lam, lo, hi, out=ex.tile)
+        ex.finish(k)                            # cross-rank barrier: all tiles of image k have landed everywhere
+        img = ex.image(k)                       # [S][G] complex64 view of this rank's image k
+
+    The all-gather of the tiles is the store stream of the range-FFT kernel (``radar_ctx_set_image_mirrors``), the
+    broadcast is a pull by the copy engines (kernels that load the cube straight from the peer run 1.5x longer: the small
+    preparation kernels are latency chains); ``finish(k)`` also fences the inputs (rank src may overwrite them afterwards) and
+    the reader must be done with image k before ``arm`` of step k + depth."""
+
+    def __init__(self, engine, num_samples: int, n_elems: int, n_dirs: int, depth: int = 2, src: int = 0):
+        import torch.distributed._symmetric_memory as symm
+        self.engine, self.s, self.n, self.g, self.depth, self.src = engine, int(num_samples), int(n_elems), int(n_dirs), int(depth), int(src)
+        self.world, self.rank = world_size(), dist.get_rank()
+        up = lambda v: (v + 255) // 256 * 256                                  # noqa: E731
+        self.ap_bytes, self.pos_bytes, self.img_bytes = self.s * self.n * 8, 3 * self.n * 8, self.s * self.g * 8
+        self.pos_off = up(self.ap_bytes)
+        self.img_off = self.pos_off + up(self.pos_bytes)
+        self.img_slot = up(self.img_bytes)
+        dev = engine.device
+        self.buf = symm.empty((self.img_off + self.depth * self.img_slot,), dtype=torch.uint8, device=dev)
+        self.buf.zero_()
+        self.hdl = symm.rendezvous(self.buf, dist.group.WORLD)
+        self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        self.src_buf = self.hdl.get_buffer(self.src, self.buf.shape, torch.uint8)
+        self.lo, self.hi = shard_range(self.g, self.rank, self.world)
+        self.tile = torch.empty((self.s, self.hi - self.lo), dtype=torch.complex64, device=dev)
+        self.ap_local = torch.zeros((self.s, self.n), dtype=torch.complex64, device=dev)
+        self.pos_local = torch.zeros((3, self.n), dtype=torch.float64, device=dev)
+        torch.cuda.synchronize(dev)
+        self.hdl.barrier(channel=0)
+
+    def put_inputs(self, aperture: torch.Tensor, positions: torch.Tensor):
+        if self.rank != self.src:
+            return
+        self.buf[:self.ap_bytes].view(torch.complex64).view(self.s, self.n).copy_(aperture, non_blocking=True)
+        self.buf[self.pos_off:self.pos_off + self.pos_bytes].view(torch.float64).view(3, self.n).copy_(positions, non_blocking=True)
+
+    def inputs_ready(self):
+        self.hdl.barrier(channel=1)
+
+    def inputs(self):
+        """After ``inputs_ready``: pull rank src's aperture cube + geometry into this rank's memory (rank src uses its own
+        region in place) -> (aperture [S, N] c64, positions [3, N] f64)."""
+        b = self.src_buf if self.rank != self.src else self.buf
+        ap = b[:self.ap_bytes].view(torch.complex64).view(self.s, self.n)
+        po = b[self.pos_off:self.pos_off + self.pos_bytes].view(torch.float64).view(3, self.n)
+        if self.rank == self.src:
+            return ap, po
+        self.ap_local.copy_(ap, non_blocking=True)
+        self.pos_local.copy_(po, non_blocking=True)
+        return self.ap_local, self.pos_local
+
+    def arm(self, k: int):
+        off = self.img_off + (k % self.depth) * self.img_slot
+        self.engine.set_image_mirrors([p + off for p in self.ptrs], self.g, self.lo)
+
+    def disarm(self):
+        self.engine.set_image_mirrors([], 0, 0)
+
+    def finish(self, k: int):
+        self.hdl.barrier(channel=2 + (k % self.depth))
+
+    def image(self, k: int) -> torch.Tensor:
+        off = self.img_off + (k % self.depth) * self.img_slot
+        return self.buf[off:off + self.img_bytes].view(torch.complex64).view(self.s, self.g)
+
+    def run(self, k: int, dirs: torch.Tensor, lambda_m: float, aperture: Optional[torch.Tensor] = None,
+            positions: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """One image: rank ``src`` passes the aperture cube + geometry, the others None."""
+        if aperture is not None:
+            self.put_inputs(aperture, positions)
+        self.inputs_ready()
+        ap, po = self.inputs()
+        self.arm(k)
+        self.engine.sar_image(ap, po, dirs, lambda_m, self.lo, self.hi, out=self.tile)
+        self.finish(k)
+        return self.image(k)
+
+    def capture(self, dirs: torch.Tensor, lambda_m: float, aperture: Optional[torch.Tensor] = None,
+                positions: Optional[torch.Tensor] = None):
+        """CUDA graphs of ``run`` for the ``depth`` image slots (one image is ten short launches: at these sizes the host
+        would otherwise set the pace).  Call after a few eager ``run`` calls (scratch sized, symmetric memory warm) with the
+        tensors that will hold the inputs of every later image; returns ``replay(k) -> image k``.  Every rank must capture
+        and replay in step."""
+        graphs = []
+        for k in range(self.depth):
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr):
+                self.run(k, dirs, lambda_m, aperture, positions)
+            graphs.append(gr)
+
+        def replay(k: int) -> torch.Tensor:
+            graphs[k % self.depth].replay()
+            return self.image(k)
+        return replay

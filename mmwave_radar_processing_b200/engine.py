@@ -124,6 +124,13 @@ class RadarEngine:
         nat.check(self.lib.radar_ctx_set_point_mirrors(self.ctx, C.cast(arr, C.c_void_p), len(pointers), int(cap_rows)),
                   self.ctx)
 
+    def set_image_mirrors(self, pointers, row_stride: int = 0, col_offset: int = 0):
+        """Device pointers (ints) of [S][row_stride] complex64 images every cell ``sar_image`` writes is also stored to, at
+        column ``col_offset`` + (direction - g_begin) (peer-mapped full images of all ranks); [] switches off."""
+        arr = (C.c_uint64 * max(1, len(pointers)))(*[int(p) for p in pointers])
+        nat.check(self.lib.radar_ctx_set_image_mirrors(self.ctx, C.cast(arr, C.c_void_p), len(pointers), int(row_stride),
+                                                       int(col_offset)), self.ctx)
+
     # ------------------------------------------------------------------ kernels
     def last_rd_kernel(self) -> str:
         """Name of the kernel the last range_doppler call launched."""

@@ -1,6 +1,7 @@
 """Run under torchrun on >= 2 GPUs (tests/test_gpu_multi.py launches it): the voxel-sharded synthetic-array image
 (NCCL broadcast of the aperture cube + geometry from rank 0, radar_sar_image(g_begin, g_end) per rank, NCCL all-gather of
-the tiles) must equal the image one GPU computes alone, on every rank.
+the tiles) must equal the image one GPU computes alone, on every rank - and so must the collective-free variant
+(distributed.PeerImageExchange: the range-FFT kernel stores its tile into every rank's image over NVLink peer memory).
 Reference arithmetic: processors/simple_synthetic_array_beamformer_processor_multiFrame.py:543-585."""
 import os
 import sys
@@ -45,6 +46,25 @@ def main():
         # slices and the full grid tile the directions differently; the kernel's tilings agree to rounding of the segment sums
         assert err < 2e-6, (rank, s, n, g, err)
         assert torch.equal(img[:, lo:hi], eng.sar_image(xs, ps, ds, lam, lo, hi)), (rank, "own tile differs")
+        dist.barrier()
+        # the same image without a collective: the range-FFT kernel stores every cell into the full image of every rank
+        # (radar_ctx_set_image_mirrors over symmetric memory), the kernels read rank 0's aperture over NVLink
+        ex = rdist.PeerImageExchange(eng, s, n, g, depth=2, src=0)
+        for k in range(3):                                  # k = 2 reuses slot 0
+            scale = float(k + 1)
+            fused = ex.run(k, ds, lam, xs * scale if rank == 0 else None, ps if rank == 0 else None)
+            torch.cuda.synchronize()
+            assert fused.shape == (s, g)
+            want = img * scale                              # power-of-two / small-integer scale of the input: exact for k = 0, 1
+            if k < 2:
+                assert torch.equal(fused, want), (rank, s, n, g, k, "fused exchange differs from the NCCL all-gather")
+            else:
+                e3 = float((fused - want).abs().max() / want.abs().max())
+                assert e3 < 2e-6, (rank, k, e3)
+            dist.barrier()
+        ex.disarm()
+        after = eng.sar_image(xs, ps, ds, lam, lo, hi)      # mirrors off again: a plain call
+        assert torch.equal(after, img[:, lo:hi])
         dist.barrier()
     if rank == 0:
         print("SAR_SHARDED_OK world", world)
