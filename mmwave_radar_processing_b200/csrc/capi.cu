@@ -162,6 +162,8 @@ int radar_ctx_create(const radar_shape* shape, int device, radar_ctx** out_ctx) 
     { const char* sv = std::getenv("RADAR_B200_CFAR_BOX"); ctx->cfar_box = sv ? std::atoi(sv) : 1; }
     { const char* sv = std::getenv("RADAR_B200_CFAR_TILE"); ctx->cfar_tile = sv ? std::atoi(sv) : 0; }
     { const char* sv = std::getenv("RADAR_B200_CFAR_LADDER"); ctx->cfar_ladder = sv ? std::atoi(sv) : 1; }
+    { const char* sv = std::getenv("RADAR_B200_DBS"); ctx->dbs_mode = sv ? std::atoi(sv) : 0; }
+    { const char* sv = std::getenv("RADAR_B200_DBS_CHUNK"); ctx->dbs_chunk = sv ? std::atoi(sv) : 0; }
     { const char* sv = std::getenv("RADAR_B200_CFAR_PH1"); ctx->cfar_ph1 = sv ? std::atoi(sv) : -1; }
     { const char* g = std::getenv("RADAR_B200_GENERIC"); ctx->force_generic = (g && g[0] == '1') ? 1 : ((g && g[0] == '2') ? 2 : 0); }
     DeviceGuard guard(device);

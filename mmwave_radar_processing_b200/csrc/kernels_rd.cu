@@ -624,6 +624,98 @@ __global__ void __launch_bounds__(kDbsThreads) dbs_kernel(const __grid_constant_
     }
 }
 
+// K5b on top of the register-resident range-Doppler kernel: for the raw int16 layout and the shapes rd_reg_kernel serves,
+// the windowed range-Doppler cube of a block of frames is written to scratch by that kernel (0.6-0.8 of the HBM roofline
+// instead of the shared-memory FFT of dbs_kernel, one CTA per SM) and dbs_combine_kernel forms
+//   out[f][k][i] = | sum_j hann_N[j] RD[f][v_j][k][vel_bin[i]] W_A^(j * (ang_bin[i] - A/2)) |
+// from it, block of frames by block of frames.
+struct DbsCombineArgs {
+    const cf* cube;      // [frames][V][S][L]
+    int V, S, L, N, A, n_out;
+    const int32_t* ant_list; const float* ant_weight;
+    const int32_t* vel_bin; const int32_t* ang_bin;
+    const cf* twA;
+    float* out;          // [frames][S][n_out]
+    FastDiv divOut;
+};
+
+constexpr int kDbsCombineThreads = 256;
+constexpr int kDbsCombineMaxAnt = 16;
+__global__ void __launch_bounds__(kDbsCombineThreads) dbs_combine_kernel(const __grid_constant__ DbsCombineArgs a) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    cf* wtab = reinterpret_cast<cf*>(smem_raw);                        // [N][n_out]: antenna weight x steering coefficient
+    int* col = reinterpret_cast<int*>(wtab + (size_t)a.N * a.n_out);   // [n_out]: Doppler column of output angle i
+    __shared__ long long ant_off[kDbsCombineMaxAnt];
+    for (int i = threadIdx.x; i < a.n_out; i += blockDim.x) col[i] = a.vel_bin[i];
+    for (int j = threadIdx.x; j < a.N; j += blockDim.x)
+        ant_off[j] = (long long)(a.ant_list ? a.ant_list[j] : j) * a.S * a.L;
+    for (int e = threadIdx.x; e < a.N * a.n_out; e += blockDim.x) {
+        const int j = e / a.n_out, i = e - j * a.n_out;
+        int f = a.ang_bin[i] - a.A / 2;
+        if (f < 0) f += a.A;
+        const cf w = a.twA[(int)(((long long)j * f) % a.A)];
+        const float wt = a.ant_weight ? a.ant_weight[j] : 1.0f;
+        wtab[e] = cmake(w.x * wt, w.y * wt);
+    }
+    __syncthreads();
+    const long long frame = blockIdx.x;
+    const cf* src = a.cube + frame * (long long)a.V * a.S * a.L;
+    float* dst = a.out + frame * (long long)a.S * a.n_out;
+    const int total = a.S * a.n_out;
+    for (int idx = threadIdx.x + blockIdx.y * blockDim.x; idx < total; idx += blockDim.x * gridDim.y) {
+        const int k = (int)a.divOut.div((uint32_t)idx);
+        const int i = idx - k * a.n_out;
+        const cf* p = src + (size_t)k * a.L + col[i];
+        cf c = cmake(0.f, 0.f);
+        for (int j = 0; j < a.N; ++j) {
+            const cf x = __ldcg(p + ant_off[j]);
+            const cf w = wtab[j * a.n_out + i];
+            c.x = fmaf(x.x, w.x, fmaf(-x.y, w.y, c.x));
+            c.y = fmaf(x.x, w.y, fmaf(x.y, w.x, c.y));
+        }
+        dst[idx] = sqrtf(c.x * c.x + c.y * c.y);
+    }
+}
+
+// 0 = done, 1 = not applicable (caller runs dbs_kernel), < 0 = error
+static int launch_dbs_two_pass(radar_ctx* ctx, const void* adc, int n_frames, const int32_t* ant_list, int N, int num_angle_bins,
+                               const int32_t* vel_bin, const int32_t* ang_bin, int n_out, const cf* twA, const float* hannN, float* out,
+                               cudaStream_t st) {
+    if (!ctx->rd_reg || ctx->dbs_mode == 1 || N > kDbsCombineMaxAnt) return 1;
+    if (reinterpret_cast<uintptr_t>(adc) & 15u) return 1;
+    const int S = ctx->shape.num_samples, L = ctx->shape.num_loops, V = ctx->V;
+    const size_t frame_cells = (size_t)V * S * L;
+    const size_t frame_in_bytes = (size_t)ctx->C * ctx->shape.num_rx * S * 4;
+    if (frame_in_bytes & 15u) return 1;
+    // frames per block: as many as 1 GiB of scratch holds.  Measured on RadSAR_1843_official, 1024 frames: blocks of 64 / 113
+    // (L2-sized) / 256 / 1024 frames take 0.591 / 0.474 / 0.362 / 0.305 ms - the launches and the tail of the persistent
+    // range-Doppler kernel cost more than the cube's trip through HBM.  RADAR_B200_DBS_CHUNK overrides.
+    long long chunk = ctx->dbs_chunk > 0 ? ctx->dbs_chunk : (long long)((1ull << 30) / (frame_cells * sizeof(cf)));
+    if (chunk < 16) chunk = 16;
+    if (chunk > n_frames) chunk = n_frames;
+    const size_t smem = ((size_t)N * n_out * sizeof(cf) + (size_t)n_out * sizeof(int) + 15) & ~(size_t)15;
+    if (smem > 96 * 1024) return 1;
+    const char* keep = ctx->last_rd_kernel;
+    for (long long f0 = 0; f0 < n_frames; f0 += chunk) {
+        const int nf = (int)((n_frames - f0 < chunk) ? n_frames - f0 : chunk);
+        if (f0 == 0) {
+            if (int rc = ensure_scratch(ctx, (size_t)chunk * frame_cells * sizeof(cf))) return rc;
+        }
+        cf* cube = reinterpret_cast<cf*>(ctx->scratch);
+        const int rc = launch_range_doppler_reg(ctx, reinterpret_cast<const unsigned char*>(adc) + (size_t)f0 * frame_in_bytes, nf,
+                                                RADAR_WIN_RANGE | RADAR_WIN_DOPPLER, cube, nullptr, 0, st);
+        ctx->last_rd_kernel = keep;                         // radar_last_rd_kernel reports radar_range_doppler calls only
+        if (rc != 0) return f0 == 0 ? rc : set_error(ctx, RADAR_E_CUDA, "range-Doppler kernel refused a later block of frames");
+        DbsCombineArgs c{cube, V, S, L, N, num_angle_bins, n_out, ant_list, hannN, vel_bin, ang_bin, twA,
+                         out + (size_t)f0 * S * n_out, make_fastdiv((uint32_t)n_out)};
+        RB_CUDA_OK(ctx, cudaFuncSetAttribute(dbs_combine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        const int ysplit = (S * n_out + 8 * kDbsCombineThreads - 1) / (8 * kDbsCombineThreads);
+        dbs_combine_kernel<<<dim3((unsigned)nf, (unsigned)(ysplit < 1 ? 1 : ysplit)), kDbsCombineThreads, smem, st>>>(c);
+        RB_CUDA_OK(ctx, cudaGetLastError());
+    }
+    return 0;
+}
+
 int launch_dbs(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, const int32_t* ant_list, int n_ant,
                int num_angle_bins, const int32_t* vel_bin, const int32_t* ang_bin, int n_out, float* out,
                cudaStream_t st) {
@@ -637,6 +729,10 @@ int launch_dbs(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, const
     if (int rc = get_angle_tables(ctx, num_angle_bins, &at)) return rc;
     float* hannN = nullptr;
     if (int rc = get_hann(ctx, N, &hannN)) return rc;           // Hann over the SUBSET's length (ref :176-177)
+    if (in_kind == RADAR_IN_IQ16) {
+        const int rc = launch_dbs_two_pass(ctx, adc, n_frames, ant_list, N, num_angle_bins, vel_bin, ang_bin, n_out, at.tw, hannN, out, st);
+        if (rc <= 0) return rc;
+    }
     DbsArgs a;
     a.rd.adc = make_view(ctx, adc, in_kind);
     a.rd.n_out_ant = N; a.rd.ant_list = ant_list; a.rd.ant_weight = hannN;

@@ -60,6 +60,8 @@ struct radar_ctx {
     int pc_mode = 0;                              // RADAR_B200_PC=1: warp-per-detection point-cloud kernel only (tests / comparison)
     int ra_fft4 = 1;                              // RADAR_B200_RA_FFT4=0: one residue per lane in the range-angle stage (comparison)
     int ra_fc = 0;                                // RADAR_B200_RA_FC: frames per pass of the range-angle kernel (0 = cost model)
+    int dbs_mode = 0;                             // RADAR_B200_DBS=1: one-kernel DBS (dbs_kernel) only (tests / comparison)
+    int dbs_chunk = 0;                            // RADAR_B200_DBS_CHUNK: frames per block of the two-pass DBS (0 = L2-sized)
     int rd_reg = 1;                               // RADAR_B200_RD_REG=0: skip the register-resident range-Doppler kernel (tests / comparison)
     int stream_variant = 0;                       // RADAR_B200_STREAM_VARIANT: tuning candidate of the streaming kernel
     const char* last_rd_kernel = "";              // name of the range-Doppler kernel the last radar_range_doppler call launched

@@ -39,7 +39,7 @@ def main():
         torch.cuda.synchronize()
         return e0.elapsed_time(e1) / a.steps
 
-    for name in ("RadarHD", "RadCloud"):
+    for name in (() if os.environ.get("BENCH_DBS_ONLY") else ("RadarHD", "RadCloud")):
         cm = load_cfg(name, "standard")
         eng = RadarEngine(cm.num_rx_antennas, cm.get_num_adc_samples(0), cm.chirp_cfgs_per_loop, cm.frameCfg_loops)
         iq = torch.from_numpy(np.tile(synth_batch_for_cfg(cm, range(64)), (a.frames // 64, 1, 1, 1, 1))).cuda()
@@ -62,13 +62,21 @@ def main():
     vbin, abin = orc.dbs_bin_selection(coarse, fine, vb, np.array([0.5, 0.1, 0.0]))
     f = iq.shape[0]
     out = torch.empty((f, eng.S, 100), dtype=torch.float32, device="cuda")
-    ms = timed(lambda: eng.dbs(iq, vbin.tolist(), abin.tolist(), ant_list=None, num_angle_bins=64, out=out))
     alg = 4 * eng.R * eng.S * eng.C + 4 * eng.S * 100           # whole int16 cube in, one fp32 map out
     flops = 8.0 * eng.S * eng.V * eng.L * 100                   # GEMM form of the restricted 3-D DFT
-    print(json.dumps({"kernel": "dbs_kernel", "workload": "configs/RadSAR_1843_official.cfg Doppler beam sharpening, 100 output bins, velocity (0.5, 0.1, 0)",
-                      "frames": f, "ms_per_launch": ms, "frames_per_s": f / ms * 1e3, "algorithmic_bytes_per_frame": alg,
-                      "achieved_gbs": alg * f / ms / 1e6, "peak_gbs": peak, "frac": alg * f / ms / 1e6 / peak,
-                      "useful_tflops": flops * f / ms / 1e9}))
+    shape = (cm.num_rx_antennas, cm.get_num_adc_samples(0), cm.chirp_cfgs_per_loop, cm.frameCfg_loops)
+    for mode, chunk, label in (("1", "0", "dbs_kernel (one kernel, shared-memory FFT)"), ("0", "0", "rd_reg_kernel + dbs_combine_kernel, default blocks (1 GiB of scratch)"),
+                               ("0", "64", "rd_reg_kernel + dbs_combine_kernel, blocks of 64 frames"), ("0", "113", "rd_reg_kernel + dbs_combine_kernel, blocks of 113 frames (L2-sized)"),
+                               ("0", "256", "rd_reg_kernel + dbs_combine_kernel, blocks of 256 frames"),
+                               ("0", "1024", "rd_reg_kernel + dbs_combine_kernel, one block")):
+        os.environ["RADAR_B200_DBS"] = mode
+        os.environ["RADAR_B200_DBS_CHUNK"] = chunk
+        eng = RadarEngine(*shape)
+        ms = timed(lambda: eng.dbs(iq, vbin.tolist(), abin.tolist(), ant_list=None, num_angle_bins=64, out=out))
+        print(json.dumps({"kernel": label, "workload": "configs/RadSAR_1843_official.cfg Doppler beam sharpening, 100 output bins, velocity (0.5, 0.1, 0)",
+                          "frames": f, "ms_per_launch": ms, "frames_per_s": f / ms * 1e3, "algorithmic_bytes_per_frame": alg,
+                          "achieved_gbs": alg * f / ms / 1e6, "peak_gbs": peak, "frac": alg * f / ms / 1e6 / peak,
+                          "useful_tflops": flops * f / ms / 1e9}), flush=True)
 
 
 if __name__ == "__main__":
