@@ -683,6 +683,10 @@ static int launch_dbs_two_pass(radar_ctx* ctx, const void* adc, int n_frames, co
                                cudaStream_t st) {
     if (!ctx->rd_reg || ctx->dbs_mode == 1 || N > kDbsCombineMaxAnt) return 1;
     if (reinterpret_cast<uintptr_t>(adc) & 15u) return 1;
+    if (ctx->dbs_mode != 2) {               // RADAR_B200_DBS=2: keep the cube round trip (comparison)
+        const int rc = launch_dbs_reg(ctx, adc, n_frames, ant_list, N, num_angle_bins, vel_bin, ang_bin, n_out, twA, hannN, out, st);
+        if (rc <= 0) return rc;
+    }
     const int S = ctx->shape.num_samples, L = ctx->shape.num_loops, V = ctx->V;
     const size_t frame_cells = (size_t)V * S * L;
     const size_t frame_in_bytes = (size_t)ctx->C * ctx->shape.num_rx * S * 4;

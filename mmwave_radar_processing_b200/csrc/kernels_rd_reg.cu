@@ -118,6 +118,201 @@ __global__ void __launch_bounds__(C::NT, 1) rd_reg_kernel(const __grid_constant_
     }
 }
 
+// ---- Doppler beam sharpening without the range-Doppler cube ---------------------------------------------------------
+//   out[f][k][i] = | sum_j w_j RD[f][v_j][k][vel_bin[i]] W_A^(j (ang_bin[i] - A/2)) |     (processors/range_angle_resp_dbs_enhanced.py:137-304)
+// The range transform is linear, so the antennas are combined BEFORE it: Z[s][i] = sum_j w_ji Y_j[s][vel_bin[i]] with Y_j the
+// windowed, Doppler-transformed samples phase A leaves in the tile, and one range transform per output angle (n_out of
+// them) replaces one per antenna and Doppler column (CR * L).  The same three roles as rd_reg_kernel; a CTA owns whole frames
+// (frame = blockIdx.x, += gridDim.x) and walks their antenna groups in order, so Z (S x n_out complex values) stays in its
+// shared memory.  Phase B, per item: every thread adds its cells of Z (lanes along the output angles: neighbouring angles read
+// the same or neighbouring tile columns, Z is contiguous; the first antenna of the subset stores, so nothing is zeroed); after the last antenna of the
+// frame, between two barriers of the phase-B warps, one thread per (output angle, output class) transforms its column of Z in
+// registers and writes the magnitudes.
+template <class C, int ODD>
+__device__ __forceinline__ void rd_reg_dbs_range(const cf* zcol, int n_out, int ca, float* out_col) {
+    cf v[C::SH];
+    rd_reg_range_load_plain<C, ODD>(zcol, n_out, ca ? -1.0f : 1.0f, v);
+    Dft<C::SH>::run(v);
+    const int half_rows = ca * (C::S / 2);
+#pragma unroll
+    for (int kh = 0; kh < C::SH; ++kh) {
+        const int r = (ODD * C::E_BF + C::E_SH * kh) % C::S;
+        const int k = (C::BF > 1 && r >= C::S / 2) ? r - half_rows : r + half_rows;
+        out_col[(size_t)k * n_out] = sqrtf(v[kh].x * v[kh].x + v[kh].y * v[kh].y);
+    }
+}
+
+constexpr int kDbsSlots = 4;             // output angles per lane: n_out <= 128
+template <class C>
+__global__ void __launch_bounds__(C::NT, 1) rd_reg_dbs_kernel(const __grid_constant__ RdRegParams<C> a, const __grid_constant__ RdRegDbs b) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    cf* tiles = reinterpret_cast<cf*>(smem_raw);
+    uint32_t* ring = reinterpret_cast<uint32_t*>(smem_raw + (size_t)C::NTILE * C::TILE * sizeof(cf));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_raw + (size_t)C::NTILE * C::TILE * sizeof(cf) + (size_t)C::NSTAGE * C::RAW_STAGE_W * 4);
+    uint64_t* raw_full = bars;
+    uint64_t* raw_empty = bars + C::NSTAGE;
+    uint64_t* tile_full = bars + 2 * C::NSTAGE;
+    uint64_t* tile_empty = tile_full + C::NTILE;
+    cf* Z = reinterpret_cast<cf*>(smem_raw + C::smem_bytes());                    // [S][n_out] beamformed samples of the frame
+    cf* wtab = Z + (size_t)C::S * b.n_out;                                          // [N][n_out]: antenna weight x steering coefficient
+    int* colL = reinterpret_cast<int*>(wtab + (size_t)b.N * b.n_out);              // [n_out] Doppler column of output angle i
+    int* jsub = colL + b.n_out;                                                     // [CR] index in the subset or -1; then first / last antenna
+    constexpr unsigned IPF = C::CR / C::G;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    if (tid == 0) {
+        for (int s = 0; s < C::NSTAGE; ++s) {
+            mb::init(raw_full + s, 1);
+            mb::init(raw_empty + s, C::NA * 32);
+        }
+        for (int t = 0; t < C::NTILE; ++t) {
+            mb::init(tile_full + t, C::NA * 32);
+            mb::init(tile_empty + t, C::NB * 32);
+        }
+        mb::fence_init();
+    }
+    // tables of the call
+    for (int v = tid; v < C::CR; v += C::NT) jsub[v] = -1;
+    for (int i = tid; i < b.n_out; i += C::NT) {
+        const int d = b.vel_bin[i];
+        colL[i] = d < 0 ? 0 : (d >= C::L ? C::L - 1 : d);
+    }
+    for (int e = tid; e < b.N * b.n_out; e += C::NT) {
+        const int j = e / b.n_out, i = e - j * b.n_out;
+        int f = b.ang_bin[i] - b.A / 2;
+        if (f < 0) f += b.A;
+        const cf w = b.twA[(int)(((long long)j * f) % b.A)];
+        const float wt = b.ant_weight ? b.ant_weight[j] : 1.0f;
+        wtab[e] = cmake(w.x * wt, w.y * wt);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int lo = C::CR, hi = -1;
+        for (int j = 0; j < b.N; ++j) {
+            const int v = b.ant_list ? b.ant_list[j] : j;
+            jsub[v] = j;
+            lo = v < lo ? v : lo;
+            hi = v > hi ? v : hi;
+        }
+        jsub[C::CR] = lo; jsub[C::CR + 1] = hi;
+    }
+    __syncthreads();
+    const unsigned n_frames = b.n_frames;
+
+    if (warp == C::NA + C::NB) {
+        // ===== TMA warp =====
+        if (lane == 0) {
+            unsigned j = 0;
+            for (unsigned frame = blockIdx.x; frame < n_frames; frame += gridDim.x)
+                for (unsigned grp = 0; grp < IPF; ++grp, ++j) {
+                    const unsigned st = j % C::NSTAGE, round = j / C::NSTAGE;
+                    mb::wait(raw_empty + st, (round & 1) ^ 1);
+                    const unsigned off = grp * (C::G * C::S * 4);
+                    const unsigned a0 = off & ~15u;
+                    const unsigned bytes = ((off - a0) + C::G * C::S * 4 + 15u) & ~15u;
+                    mb::arrive_expect_tx(raw_full + st, bytes * C::L);
+                    const unsigned char* src = reinterpret_cast<const unsigned char*>(a.iq) + (size_t)frame * ((size_t)C::ROW * C::L * 4) + a0;
+                    uint32_t* dst = ring + st * C::RAW_STAGE_W;
+#pragma unroll 5
+                    for (int l = 0; l < C::L; ++l)
+                        mb::bulk_g2s(dst + l * C::RAW_PITCH_W, src + (size_t)l * (C::ROW * 4), bytes, raw_full + st);
+                }
+        }
+    } else if (warp < C::NA) {
+        // ===== phase A: Doppler (as in rd_reg_kernel) =====
+        const int h = C::DF == 1 ? 0 : warp / C::NA1;
+        const int col = (warp - h * C::NA1) * 32 + lane;
+        const bool active = col < C::COLS_A;
+        const int colc = active ? col : C::COLS_A - 1;
+        const float ws = a.winS[colc % C::S];
+        unsigned j = 0;
+        for (unsigned frame = blockIdx.x; frame < n_frames; frame += gridDim.x)
+            for (unsigned grp = 0; grp < IPF; ++grp, ++j) {
+                const unsigned st = j % C::NSTAGE, round = j / C::NSTAGE;
+                const unsigned tb = j % C::NTILE, tround = j / C::NTILE;
+                const int shift = (int)((grp * (C::G * C::S * 4)) & 15u) >> 2;
+                cf v[C::LH];
+                mb::wait(raw_full + st, round & 1);
+                rd_reg_doppler_load<C>(a, ring + st * C::RAW_STAGE_W, shift + colc, h, v);
+                mb::arrive(raw_empty + st);
+                rd_reg_doppler_finish<C>(ws, v);
+                mb::wait(tile_empty + tb, (tround & 1) ^ 1);
+                if (active) rd_reg_store_row<C>(v, tiles + (size_t)tb * C::TILE + (size_t)col * C::P, h);
+                mb::arrive(tile_full + tb);
+            }
+    } else {
+        // ===== phase B: beamform per output angle, range transform after the frame's last antenna =====
+        // warp w takes the samples s = w, w + NB, ...; its lanes take the output angles i = lane + 32 q: per angle the tile
+        // position, the Doppler combine (see RdRegColumn) and the steering coefficient sit in registers, the kDbsSlots cells
+        // of a sample are independent (instruction-level parallelism for the shared-memory read-modify-writes)
+        constexpr int nB = C::NB * 32;
+        const int tB = tid - C::NA * 32, wB = tB >> 5;
+        const int n_out = b.n_out;
+        const int ant_first = jsub[C::CR], ant_last = jsub[C::CR + 1];
+        int pos[kDbsSlots];
+        cf cw[kDbsSlots];
+#pragma unroll
+        for (int q = 0; q < kDbsSlots; ++q) {
+            const int i = lane + 32 * q;
+            const int d = i < n_out ? colL[i] : 0;
+            pos[q] = d; cw[q] = cmake(1.0f, 0.0f);
+            if (C::DF == 2) {
+                const int k = (d + C::L - C::L / 2) % C::L;
+                pos[q] = k % C::LH;
+                cw[q] = C::TW ? a.twL[k] : cmake((k & 1) ? -1.0f : 1.0f, 0.0f);
+            }
+        }
+        unsigned j = 0;
+        for (unsigned frame = blockIdx.x; frame < n_frames; frame += gridDim.x)
+            for (unsigned grp = 0; grp < IPF; ++grp, ++j) {
+                const unsigned tb = j % C::NTILE, tround = j / C::NTILE;
+                const cf* tile = tiles + (size_t)tb * C::TILE;
+                mb::wait(tile_full + tb, tround & 1);
+#pragma unroll
+                for (int g = 0; g < C::G; ++g) {
+                    const int ant = (int)grp * C::G + g;
+                    const int js = jsub[ant];
+                    if (js < 0) continue;                                   // uniform over the CTA
+                    const bool first = ant == ant_first;
+                    cf w[kDbsSlots];
+#pragma unroll
+                    for (int q = 0; q < kDbsSlots; ++q) w[q] = lane + 32 * q < n_out ? wtab[(size_t)js * n_out + lane + 32 * q] : cmake(0.f, 0.f);
+                    for (int s = wB; s < C::S; s += C::NB) {
+                        const cf* row = tile + ((size_t)g * C::S + s) * C::P;
+                        cf* zrow = Z + (size_t)s * n_out + lane;
+#pragma unroll
+                        for (int q = 0; q < kDbsSlots; ++q) {
+                            if (lane + 32 * q < n_out) {
+                                cf x = row[pos[q]];
+                                if (C::DF == 2) {                           // the Doppler combine of RdRegColumn::value
+                                    const cf o = row[pos[q] + C::HP];
+                                    if (C::TW) x = cmake(fmaf(cw[q].x, o.x, fmaf(-cw[q].y, o.y, x.x)), fmaf(cw[q].x, o.y, fmaf(cw[q].y, o.x, x.y)));
+                                    else x = cfma(cw[q].x, o, x);
+                                }
+                                cf c = first ? cmake(0.f, 0.f) : zrow[32 * q];
+                                c.x = fmaf(x.x, w[q].x, fmaf(-x.y, w[q].y, c.x));
+                                c.y = fmaf(x.x, w[q].y, fmaf(x.y, w[q].x, c.y));
+                                zrow[32 * q] = c;
+                            }
+                        }
+                    }
+                }
+                mb::arrive(tile_empty + tb);
+                if ((int)grp == ant_last / C::G) {
+                    asm volatile("bar.sync 1, %0;" ::"n"(nB) : "memory");          // every cell of the frame is complete
+                    float* out_frame = b.out + (size_t)frame * C::S * n_out;
+                    for (int t = tB; t < n_out * C::BF; t += nB) {
+                        const int cls = t / n_out, i = t - cls * n_out;
+                        const int ca = C::BF == 4 ? cls >> 1 : (C::BF == 2 ? cls : 0), odd = C::BF == 4 ? cls & 1 : 0;
+                        if (odd) rd_reg_dbs_range<C, 1>(Z + i, n_out, ca, out_frame + i);
+                        else rd_reg_dbs_range<C, 0>(Z + i, n_out, ca, out_frame + i);
+                    }
+                    asm volatile("bar.sync 1, %0;" ::"n"(nB) : "memory");          // Z may be overwritten by the next frame
+                }
+            }
+    }
+}
+
 static void host_hann_f(int n, bool on, float* w) {
     for (int k = 0; k < n; ++k)
         w[k] = (on && n > 1) ? (float)(0.5 - 0.5 * std::cos(2.0 * M_PI * (double)k / (double)(n - 1))) : 1.0f;
@@ -161,6 +356,60 @@ static int launch_reg(radar_ctx* ctx, const void* adc, int n_frames, int window_
     ctx->last_rd_kernel = "rd_reg_kernel";
     RB_CUDA_OK(ctx, cudaGetLastError());
     return RADAR_OK;
+}
+
+template <class C>
+static int launch_reg_dbs(radar_ctx* ctx, const void* adc, int n_frames, const RdRegDbs& b0, cudaStream_t st) {
+    static_assert(sizeof(RdRegParams<C>) + sizeof(RdRegDbs) <= 4000, "parameter block too large");
+    static_assert((C::ROW * 4) % 16 == 0, "chirp rows must keep the 16-byte alignment of the bulk copies");
+    static_assert(C::CR % C::G == 0, "antenna groups must tile the virtual array");
+    const size_t extra = ((size_t)C::S * b0.n_out + (size_t)b0.N * b0.n_out) * sizeof(cf) + ((size_t)b0.n_out + C::CR + 2) * sizeof(int);
+    const size_t smem = C::smem_bytes() + ((extra + 15) & ~(size_t)15);
+    if (smem > (size_t)ctx->max_smem_optin || b0.n_out > 32 * kDbsSlots) return 1;
+    RdRegParams<C> a;
+    a.iq = reinterpret_cast<const uint32_t*>(adc);
+    a.rd_out = nullptr; a.mag_out = nullptr; a.mag_antenna = 0; a.n_items = 0;
+    float wl[C::L];
+    host_hann_f(C::L, true, wl);
+    for (int h = 0; h < C::DF; ++h)
+        for (int m = 0; m < C::LH; ++m) {
+            const float w = wl[rd_reg_doppler_input<C>(h, m)];
+            a.winL[h * C::LH + m] = make_float2(w, w);
+        }
+    if (C::TW)
+        for (int k = 0; k < C::L; ++k) {
+            const double ang = -2.0 * M_PI * (double)k / (double)C::L;
+            a.twL[k] = cmake((float)std::cos(ang), (float)std::sin(ang));
+        }
+    host_hann_f(C::S, true, a.winS);
+    RdRegDbs b = b0;
+    b.n_frames = (unsigned)n_frames;
+    RB_CUDA_OK(ctx, cudaFuncSetAttribute(rd_reg_dbs_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    unsigned grid = (unsigned)ctx->sm_count;
+    if (grid > (unsigned)n_frames) grid = (unsigned)n_frames;
+    rd_reg_dbs_kernel<C><<<grid, C::NT, smem, st>>>(a, b);
+    RB_CUDA_OK(ctx, cudaGetLastError());
+    return RADAR_OK;
+}
+
+// Doppler beam sharpening fused into the register-resident kernel: RADAR_OK when launched, 1 when the shape has no
+// instantiation or the accumulator does not fit beside the tile and the ring (caller falls back).
+int launch_dbs_reg(radar_ctx* ctx, const void* adc, int n_frames, const int32_t* ant_list, int N, int num_angle_bins,
+                   const int32_t* vel_bin, const int32_t* ang_bin, int n_out, const cf* twA, const float* ant_weight, float* out,
+                   cudaStream_t st) {
+    const int S = ctx->shape.num_samples, L = ctx->shape.num_loops, R = ctx->shape.num_rx;
+    if (reinterpret_cast<uintptr_t>(adc) % 16 != 0) return 1;
+    const int CR = ctx->shape.chirps_per_loop * R;
+    RdRegDbs b{vel_bin, ang_bin, ant_list, ant_weight, twA, out, n_out, N, num_angle_bins, 0u};
+#define RB_REG_DBS(s, l, cr, g, df, nstage, ntile, bf)                                                        \
+    if (S == s && L == l && CR == cr && R % g == 0)                                                           \
+        return launch_reg_dbs<RdRegShape<s, l, cr, g, df, nstage, ntile, bf>>(ctx, adc, n_frames, b, st);
+    // two ring stages: the accumulator needs the room (ring depth 2 / 3 / 4 measured equal on the range-Doppler kernel)
+    RB_REG_DBS(90, 100, 8, 1, 2, 2, 1, 2)
+    RB_REG_DBS(63, 70, 12, 2, 1, 2, 1, 1)
+    RB_REG_DBS(100, 30, 8, 2, 1, 2, 1, 4)
+#undef RB_REG_DBS
+    return 1;
 }
 
 // Returns RADAR_OK when the register-resident kernel was launched, 1 when the shape has no instantiation (caller falls back).

@@ -60,7 +60,7 @@ struct radar_ctx {
     int pc_mode = 0;                              // RADAR_B200_PC=1: warp-per-detection point-cloud kernel only (tests / comparison)
     int ra_fft4 = 1;                              // RADAR_B200_RA_FFT4=0: one residue per lane in the range-angle stage (comparison)
     int ra_fc = 0;                                // RADAR_B200_RA_FC: frames per pass of the range-angle kernel (0 = cost model)
-    int dbs_mode = 0;                             // RADAR_B200_DBS=1: one-kernel DBS (dbs_kernel) only (tests / comparison)
+    int dbs_mode = 0;                             // RADAR_B200_DBS=1: one-kernel DBS (dbs_kernel) only, =2: two passes over the range-Doppler cube (tests / comparison)
     int dbs_chunk = 0;                            // RADAR_B200_DBS_CHUNK: frames per block of the two-pass DBS (0 = L2-sized)
     int rd_reg = 1;                               // RADAR_B200_RD_REG=0: skip the register-resident range-Doppler kernel (tests / comparison)
     int stream_variant = 0;                       // RADAR_B200_STREAM_VARIANT: tuning candidate of the streaming kernel
@@ -93,6 +93,9 @@ int launch_range_doppler_stream(radar_ctx* ctx, const void* adc, int n_frames, i
                                 float* mag_out, int mag_antenna, cudaStream_t st);
 int launch_range_doppler_reg(radar_ctx* ctx, const void* adc, int n_frames, int window_flags, cf* rd_out,
                              float* mag_out, int mag_antenna, cudaStream_t st);
+int launch_dbs_reg(radar_ctx* ctx, const void* adc, int n_frames, const int32_t* ant_list, int N, int num_angle_bins,
+                   const int32_t* vel_bin, const int32_t* ang_bin, int n_out, const cf* twA, const float* ant_weight, float* out,
+                   cudaStream_t st);
 int launch_range_profile(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx,
                          float* profile_out, cudaStream_t st);
 int launch_range_zoom(radar_ctx* ctx, const void* adc, int in_kind, int n_frames, int loop_idx, const double* start_m,

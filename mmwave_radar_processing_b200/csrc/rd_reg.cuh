@@ -125,6 +125,19 @@ struct RdRegParams {
 template <class C>
 RB_HD constexpr int rd_reg_doppler_input(int h, int m) { return C::TW ? C::DF * m + h : (h * C::LH + C::DF * m) % C::L; }
 
+// Doppler beam sharpening on top of the same phases (kernels_rd_reg.cu: rd_reg_dbs_kernel): phase B beamforms the Doppler
+// transformed samples of the frame's antennas per output angle in shared memory and runs one range transform per angle.
+struct RdRegDbs {
+    const int32_t* vel_bin;     // [n_out] Doppler column (shifted axis) of output angle i
+    const int32_t* ang_bin;     // [n_out] coarse angle bin of output angle i
+    const int32_t* ant_list;    // [N] virtual antennas of the subset, ascending, or null (all CR antennas)
+    const float* ant_weight;    // [N] or null
+    const cf* twA;              // [A] W_A^j
+    float* out;                 // [frames][S][n_out]
+    int n_out, N, A;
+    unsigned n_frames;
+};
+
 // int16 pair -> complex float on the conversion unit (two I2F.S16, the second with the .H1 selector): half the issue slots
 // of the LOP3/PRMT/LOP3/FADD2 form of iq_word and nothing on the FMA / ALU pipes, which phase A keeps busy; the conversion
 // unit is otherwise idle in this kernel (70 words per item and thread = 140 quarter-rate instructions per A warp and item)
@@ -240,6 +253,21 @@ RB_HD void rd_reg_range_load(const RdRegParams<C>& a, const cf* tile, int g, int
             const cf x0 = col.value((4 * m) % C::S), x1 = col.value((C::SH + 4 * m) % C::S);
             const cf x2 = col.value((2 * C::SH + 4 * m) % C::S), x3 = col.value((3 * C::SH + 4 * m) % C::S);
             // k_4 = 0, 2: (x0 + x2) +- (x1 + x3);  k_4 = 1, 3: (x0 - x2) -+ i (x1 - x3)
+            if (ODD == 0) v[m] = cfma(sigma, cadd(x1, x3), cadd(x0, x2));
+            else v[m] = cfma(sigma, csub_mi(x1, x3), csub(x0, x2));
+        }
+    }
+}
+// the same input combination for a plain column p[s * pitch] (rd_reg_dbs_kernel: the beamformed samples of one output angle)
+template <class C, int ODD>
+RB_HD void rd_reg_range_load_plain(const cf* p, int pitch, float sigma, cf (&v)[C::SH]) {
+#pragma unroll
+    for (int m = 0; m < C::SH; ++m) {
+        if (C::BF == 1) v[m] = p[m * pitch];
+        else if (C::BF == 2) v[m] = cfma(sigma, p[((C::SH + 2 * m) % C::S) * pitch], p[((2 * m) % C::S) * pitch]);
+        else {
+            const cf x0 = p[((4 * m) % C::S) * pitch], x1 = p[((C::SH + 4 * m) % C::S) * pitch];
+            const cf x2 = p[((2 * C::SH + 4 * m) % C::S) * pitch], x3 = p[((3 * C::SH + 4 * m) % C::S) * pitch];
             if (ODD == 0) v[m] = cfma(sigma, cadd(x1, x3), cadd(x0, x2));
             else v[m] = cfma(sigma, csub_mi(x1, x3), csub(x0, x2));
         }

@@ -307,36 +307,42 @@ def test_dbs(torch_cuda, name):
 
 
 @pytest.mark.parametrize("name", ["RadSAR_1843_official", "6843_RadVel_ods_20Hz", "1843_RadVel"])
-def test_dbs_two_pass_equals_one_kernel(torch_cuda, name, monkeypatch):
-    """Raw int16 batches of the shapes rd_reg_kernel serves take the two-pass path (range-Doppler cube of a block of frames in
-    scratch + dbs_combine_kernel); RADAR_B200_DBS=1 keeps the one-kernel dbs_kernel.  Blocks of 16 frames with a ragged last
-    one, antenna subset and all antennas."""
+def test_dbs_fused_and_two_pass_equal_one_kernel(torch_cuda, name, monkeypatch):
+    """Raw int16 batches of the shapes rd_reg_kernel serves: by default the sharpening runs inside the register-resident
+    kernel (rd_reg_dbs_kernel: phase B accumulates the steered range transforms of a frame's antennas in shared memory);
+    RADAR_B200_DBS=2 takes the two-pass path (range-Doppler cube of a block of frames in scratch + dbs_combine_kernel),
+    RADAR_B200_DBS=1 the one-kernel dbs_kernel.  Blocks of 16 frames with a ragged last one, antenna subset and all
+    antennas, more frames than SMs so CTAs walk several frames."""
     torch = torch_cuda
     from oracle import radar_oracle as orc
     from mmwave_radar_processing_b200.engine import RadarEngine
     from mmwave_radar_processing_b200.synthetic import synth_batch_for_cfg
     cm = load_cfg(name)
-    iq = torch.from_numpy(synth_batch_for_cfg(cm, range(40))).cuda()
+    iq = torch.from_numpy(np.tile(synth_batch_for_cfg(cm, range(40)), (5, 1, 1, 1, 1))[:173]).cuda()
     _, vb = orc.rd_axes(cm.vel_max_m_s, cm.vel_res_m_s, cm.range_max_m, cm.range_res_m)
     _, coarse = orc.angle_axis(64)
     fine = np.linspace(coarse[0], coarse[-1], 100)
     vbin, abin = orc.dbs_bin_selection(coarse, fine, vb, np.array([0.5, 0.1, 0.0]))
     shape = (cm.num_rx_antennas, cm.get_num_adc_samples(0), cm.chirp_cfgs_per_loop, cm.frameCfg_loops)
     outs = {}
-    for mode, chunk in (("1", "0"), ("0", "16"), ("0", "0")):
+    for mode, chunk in (("1", "0"), ("2", "16"), ("2", "0"), ("0", "0")):
         monkeypatch.setenv("RADAR_B200_DBS", mode)
         monkeypatch.setenv("RADAR_B200_DBS_CHUNK", chunk)
         eng = RadarEngine(*shape)
         sub = [0, 1, 2, 3] if eng.V < 8 else [0, 3, 4, 7]
         outs[(mode, chunk)] = (eng.dbs(iq, vbin.tolist(), abin.tolist(), ant_list=sub, num_angle_bins=64).cpu().numpy(),
-                               eng.dbs(iq, vbin.tolist(), abin.tolist(), ant_list=None, num_angle_bins=64).cpu().numpy())
+                               eng.dbs(iq, vbin.tolist(), abin.tolist(), ant_list=None, num_angle_bins=64).cpu().numpy(),
+                               eng.dbs(iq, vbin.tolist(), abin.tolist(), ant_list=[sub[1]], num_angle_bins=64).cpu().numpy())
     ref = outs[("1", "0")]
-    for key in (("0", "16"), ("0", "0")):
+    for key in (("2", "16"), ("2", "0"), ("0", "0")):
         for got, want in zip(outs[key], ref):
             assert got.shape == want.shape
+            assert np.isfinite(got).all()
             assert rel_l2(got, want) < 1e-5, (key, rel_l2(got, want))
-    np.testing.assert_array_equal(outs[("0", "16")][0], outs[("0", "0")][0])       # the block size does not change a bit
-    assert not np.array_equal(outs[("0", "0")][1], ref[1])                         # the two-pass path really ran
+    np.testing.assert_array_equal(outs[("2", "16")][0], outs[("2", "0")][0])       # the block size does not change a bit
+    assert not np.array_equal(outs[("2", "0")][1], ref[1])                         # the two-pass path really ran
+    assert not np.array_equal(outs[("0", "0")][1], outs[("2", "0")][1])            # and so did the fused one
+    np.testing.assert_array_equal(outs[("0", "0")][1][:40], outs[("0", "0")][1][40:80])   # the tiled frames repeat: so must the maps
 
 
 def test_sar(torch_cuda):

@@ -65,10 +65,11 @@ def main():
     alg = 4 * eng.R * eng.S * eng.C + 4 * eng.S * 100           # whole int16 cube in, one fp32 map out
     flops = 8.0 * eng.S * eng.V * eng.L * 100                   # GEMM form of the restricted 3-D DFT
     shape = (cm.num_rx_antennas, cm.get_num_adc_samples(0), cm.chirp_cfgs_per_loop, cm.frameCfg_loops)
-    for mode, chunk, label in (("1", "0", "dbs_kernel (one kernel, shared-memory FFT)"), ("0", "0", "rd_reg_kernel + dbs_combine_kernel, default blocks (1 GiB of scratch)"),
-                               ("0", "64", "rd_reg_kernel + dbs_combine_kernel, blocks of 64 frames"), ("0", "113", "rd_reg_kernel + dbs_combine_kernel, blocks of 113 frames (L2-sized)"),
-                               ("0", "256", "rd_reg_kernel + dbs_combine_kernel, blocks of 256 frames"),
-                               ("0", "1024", "rd_reg_kernel + dbs_combine_kernel, one block")):
+    for mode, chunk, label in (("1", "0", "dbs_kernel (one kernel, shared-memory FFT)"), ("0", "0", "rd_reg_dbs_kernel (sharpening inside the register-resident range-Doppler kernel)"),
+                               ("2", "0", "rd_reg_kernel + dbs_combine_kernel, default blocks (1 GiB of scratch)"),
+                               ("2", "64", "rd_reg_kernel + dbs_combine_kernel, blocks of 64 frames"), ("2", "113", "rd_reg_kernel + dbs_combine_kernel, blocks of 113 frames (L2-sized)"),
+                               ("2", "256", "rd_reg_kernel + dbs_combine_kernel, blocks of 256 frames"),
+                               ("2", "1024", "rd_reg_kernel + dbs_combine_kernel, one block")):
         os.environ["RADAR_B200_DBS"] = mode
         os.environ["RADAR_B200_DBS_CHUNK"] = chunk
         eng = RadarEngine(*shape)
