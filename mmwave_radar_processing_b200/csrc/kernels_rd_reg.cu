@@ -154,9 +154,9 @@ __global__ void __launch_bounds__(C::NT, 1) rd_reg_dbs_kernel(const __grid_const
     uint64_t* tile_full = bars + 2 * C::NSTAGE;
     uint64_t* tile_empty = tile_full + C::NTILE;
     cf* Z = reinterpret_cast<cf*>(smem_raw + C::smem_bytes());                    // [S][n_out] beamformed samples of the frame
-    cf* wtab = Z + (size_t)C::S * b.n_out;                                          // [N][n_out]: antenna weight x steering coefficient
-    int* colL = reinterpret_cast<int*>(wtab + (size_t)b.N * b.n_out);              // [n_out] Doppler column of output angle i
-    int* jsub = colL + b.n_out;                                                     // [CR] index in the subset or -1; then first / last antenna
+    cf* wtab = Z + (size_t)C::S * b.n_out;                                          // [CR][n_out]: antenna weight x steering coefficient of a virtual antenna
+    int* colL = reinterpret_cast<int*>(wtab + (size_t)C::CR * b.n_out);            // [n_out] Doppler column of output angle i
+    int* jsub = colL + b.n_out;                                                     // [CR] antenna is in the subset; then first / last antenna
     constexpr unsigned IPF = C::CR / C::G;
     const int tid = threadIdx.x, lane = tid & 31;
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
@@ -177,20 +177,28 @@ __global__ void __launch_bounds__(C::NT, 1) rd_reg_dbs_kernel(const __grid_const
         const int d = b.vel_bin[i];
         colL[i] = d < 0 ? 0 : (d >= C::L ? C::L - 1 : d);
     }
-    for (int e = tid; e < b.N * b.n_out; e += C::NT) {
-        const int j = e / b.n_out, i = e - j * b.n_out;
+    // the coefficient of virtual antenna v for output angle i: position j of v in the subset sets the steering phase; a
+    // list that names an antenna twice (or out of order) gets the sum of its positions' coefficients - the same image
+    for (int e = tid; e < C::CR * b.n_out; e += C::NT) {
+        const int v = e / b.n_out, i = e - v * b.n_out;
         int f = b.ang_bin[i] - b.A / 2;
         if (f < 0) f += b.A;
-        const cf w = b.twA[(int)(((long long)j * f) % b.A)];
-        const float wt = b.ant_weight ? b.ant_weight[j] : 1.0f;
-        wtab[e] = cmake(w.x * wt, w.y * wt);
+        cf acc = cmake(0.f, 0.f);
+        for (int j = 0; j < b.N; ++j) {
+            if ((b.ant_list ? b.ant_list[j] : j) != v) continue;
+            const cf w = b.twA[(int)(((long long)j * f) % b.A)];
+            const float wt = b.ant_weight ? b.ant_weight[j] : 1.0f;
+            acc.x += w.x * wt; acc.y += w.y * wt;
+        }
+        wtab[e] = acc;
     }
     __syncthreads();
     if (tid == 0) {
         int lo = C::CR, hi = -1;
         for (int j = 0; j < b.N; ++j) {
             const int v = b.ant_list ? b.ant_list[j] : j;
-            jsub[v] = j;
+            if (v < 0 || v >= C::CR) continue;
+            jsub[v] = 1;
             lo = v < lo ? v : lo;
             hi = v > hi ? v : hi;
         }
@@ -276,7 +284,7 @@ __global__ void __launch_bounds__(C::NT, 1) rd_reg_dbs_kernel(const __grid_const
                     const bool first = ant == ant_first;
                     cf w[kDbsSlots];
 #pragma unroll
-                    for (int q = 0; q < kDbsSlots; ++q) w[q] = lane + 32 * q < n_out ? wtab[(size_t)js * n_out + lane + 32 * q] : cmake(0.f, 0.f);
+                    for (int q = 0; q < kDbsSlots; ++q) w[q] = lane + 32 * q < n_out ? wtab[(size_t)ant * n_out + lane + 32 * q] : cmake(0.f, 0.f);
                     for (int s = wB; s < C::S; s += C::NB) {
                         const cf* row = tile + ((size_t)g * C::S + s) * C::P;
                         cf* zrow = Z + (size_t)s * n_out + lane;
@@ -363,7 +371,7 @@ static int launch_reg_dbs(radar_ctx* ctx, const void* adc, int n_frames, const R
     static_assert(sizeof(RdRegParams<C>) + sizeof(RdRegDbs) <= 4000, "parameter block too large");
     static_assert((C::ROW * 4) % 16 == 0, "chirp rows must keep the 16-byte alignment of the bulk copies");
     static_assert(C::CR % C::G == 0, "antenna groups must tile the virtual array");
-    const size_t extra = ((size_t)C::S * b0.n_out + (size_t)b0.N * b0.n_out) * sizeof(cf) + ((size_t)b0.n_out + C::CR + 2) * sizeof(int);
+    const size_t extra = ((size_t)C::S * b0.n_out + (size_t)C::CR * b0.n_out) * sizeof(cf) + ((size_t)b0.n_out + C::CR + 2) * sizeof(int);
     const size_t smem = C::smem_bytes() + ((extra + 15) & ~(size_t)15);
     if (smem > (size_t)ctx->max_smem_optin || b0.n_out > 32 * kDbsSlots) return 1;
     RdRegParams<C> a;

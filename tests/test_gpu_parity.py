@@ -332,7 +332,9 @@ def test_dbs_fused_and_two_pass_equal_one_kernel(torch_cuda, name, monkeypatch):
         sub = [0, 1, 2, 3] if eng.V < 8 else [0, 3, 4, 7]
         outs[(mode, chunk)] = (eng.dbs(iq, vbin.tolist(), abin.tolist(), ant_list=sub, num_angle_bins=64).cpu().numpy(),
                                eng.dbs(iq, vbin.tolist(), abin.tolist(), ant_list=None, num_angle_bins=64).cpu().numpy(),
-                               eng.dbs(iq, vbin.tolist(), abin.tolist(), ant_list=[sub[1]], num_angle_bins=64).cpu().numpy())
+                               eng.dbs(iq, vbin.tolist(), abin.tolist(), ant_list=[sub[1]], num_angle_bins=64).cpu().numpy(),
+                               # out of order and one antenna named twice: its two positions' steering coefficients add up
+                               eng.dbs(iq[:7], vbin.tolist(), abin.tolist(), ant_list=[sub[2], sub[0], sub[2]], num_angle_bins=64).cpu().numpy())
     ref = outs[("1", "0")]
     for key in (("2", "16"), ("2", "0"), ("0", "0")):
         for got, want in zip(outs[key], ref):
