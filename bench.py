@@ -321,7 +321,8 @@ def time_stage_loop(torch, pipe, iq_dev, steps, warmup):
 
 def extra_single_gpu_lines(torch, dev, peak):
     """N=1 extras: (a) configs/1843_RadVel.cfg, 4096 frames per step (BASELINE.json configs[1]; round-1 headline, kept for
-    continuity); (b) the CA-CFAR-2D detector of tests/verify_processors.py:156-191 on both shapes."""
+    continuity); (b) the CA-CFAR-2D detector of tests/verify_processors.py:156-191 on both shapes; (c) the other BASELINE
+    shapes through the pipeline, the high-resolution range-azimuth maps, Doppler beam sharpening and the synthetic-array image."""
     import numpy as np
     from mmwave_radar_processing_b200.pipeline import DetectorSpec, FramePipeline
     from mmwave_radar_processing_b200.synthetic import synth_batch_for_cfg
@@ -381,6 +382,60 @@ def extra_single_gpu_lines(torch, dev, peak):
                        "algorithmic_bytes_per_frame": alg, "frac_of_hbm": alg * F / ms / 1e6 / peak})
         del out
     del iq_dev
+    torch.cuda.empty_cache()
+    # Doppler beam sharpening (K5b) on RadSAR_1843_official: the reference-facing class picks the bins (fp64 argmins on the
+    # host), radar_dbs does the rest
+    from mmwave_radar_processing_b200.processors.range_angle_resp_dbs_enhanced import RangeAngleProcessorDBSEnhanced
+    cm = load_cfg("RadSAR_1843_official", "standard")
+    proc = RangeAngleProcessorDBSEnhanced(cm, num_angle_bins_dbs_enhanced_response=100)
+    vbin, abin = proc.select_bins(np.array([0.5, 0.1, 0.0]))
+    eng = RadarEngine(cm.num_rx_antennas, cm.get_num_adc_samples(0), cm.chirp_cfgs_per_loop, cm.frameCfg_loops, device=dev)
+    F = 1024
+    iq_dev = torch.from_numpy(np.concatenate([synth_batch_for_cfg(cm, range(32))] * (F // 32))).to(dev)
+    out = torch.empty((F, eng.S, len(vbin)), dtype=torch.float32, device=dev)
+    vl, al = [int(v) for v in vbin], [int(v) for v in abin]
+    for _ in range(5):
+        eng.dbs(iq_dev, vl, al, ant_list=None, num_angle_bins=int(proc.num_angle_bins), out=out)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(20):
+        eng.dbs(iq_dev, vl, al, ant_list=None, num_angle_bins=int(proc.num_angle_bins), out=out)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 20
+    alg = 4 * eng.R * eng.S * eng.C + 4 * eng.S * len(vl)
+    extras.append({"workload": f"configs/RadSAR_1843_official.cfg Doppler beam sharpening, {len(vl)} output angles, velocity (0.5, 0.1, 0), all {eng.V} antennas",
+                   "kernel": "rd_reg_dbs_kernel", "frames_per_step": F, "ms_per_launch": ms, "value": F / ms * 1e3, "unit": "frames/s",
+                   "algorithmic_bytes_per_frame": alg, "frac_of_hbm": alg * F / ms / 1e6 / peak})
+    del iq_dev, out
+    torch.cuda.empty_cache()
+    # the synthetic-array image (K5a), BASELINE.json configs[3] shape: the whole line is `bench.py --workload sar`
+    s_, n_, g_ = 90, 2000, 512 * 64
+    rng = np.random.default_rng(0)
+    x = (rng.integers(-2000, 2000, (s_, n_)) + 1j * rng.integers(-2000, 2000, (s_, n_))).astype(np.complex64)
+    t = np.arange(n_) * 1e-4
+    pos = np.stack([0.01 * t, 0.5 * t, np.zeros(n_)])
+    az = np.repeat(np.linspace(-1.0, 1.0, 512), 64)
+    el = np.tile(np.linspace(-0.3, 0.3, 64), 512)
+    dirs = np.stack([np.cos(az) * np.cos(el), np.sin(az) * np.cos(el), np.sin(el)])
+    eng = RadarEngine(1, s_, 1, 1, device=dev)
+    xs, ps, ds = torch.from_numpy(x).to(dev), torch.from_numpy(pos).to(dev), torch.from_numpy(dirs).to(dev)
+    img = torch.empty((s_, g_), dtype=torch.complex64, device=dev)
+    for _ in range(5):
+        eng.sar_image(xs, ps, ds, 0.0039, out=img)
+    e0.record()
+    for _ in range(20):
+        eng.sar_image(xs, ps, ds, 0.0039, out=img)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 20
+    bf16 = float(measured_peaks().get("bf16_tflops", 0.0) or 0.0)
+    executed = 3 * 2.0 * 192 * (2 * n_) * g_ / (ms * 1e-3) / 1e12
+    extras.append({"workload": "configs/RadSAR_1843_official.cfg synthetic-array image: S=90 range bins, N=2000 aperture elements, G=512x64 directions",
+                   "kernel": "sar_tc_kernel (+ max / prep / range FFT)", "ms_per_image": ms, "value": 1e3 / ms, "unit": "images/s",
+                   "useful_tflops": 8.0 * s_ * n_ * g_ / (ms * 1e-3) / 1e12, "executed_f16_tflops": executed,
+                   "frac_of_measured_bf16_peak": executed / bf16 if bf16 else None})
+    del xs, ps, ds, img
     torch.cuda.empty_cache()
     return extras
 
