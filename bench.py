@@ -475,7 +475,10 @@ def run_sar(a):
     # into every rank's image over NVLink peer memory, the kernels read rank 0's aperture from its symmetric region);
     # RADAR_B200_SAR_EXCHANGE=nccl keeps the collectives (broadcast + all-gather) for comparison.
     fused = world > 1 and os.environ.get("RADAR_B200_SAR_EXCHANGE", "peer") != "nccl"
-    ex = rdist.PeerImageExchange(eng, s, n, g, depth=2, src=0) if fused else None
+    # RADAR_B200_SAR_PIPELINE=0: one image at a time; default: the two image slots run on their own streams and contexts, so the
+    # peer stores and barriers of image k overlap the GEMM of image k + 1
+    pipelined = fused and os.environ.get("RADAR_B200_SAR_PIPELINE", "1") != "0"
+    ex = rdist.PeerImageExchange(eng, s, n, g, depth=2, src=0, pipelined=pipelined) if fused else None
     step_no = [0]
 
     def step():
@@ -523,6 +526,9 @@ def run_sar(a):
     e0.record()
     for _ in range(a.steps):
         img = step()
+    if ex is not None:
+        for kk in range(max(0, step_no[0] - 2), step_no[0]):     # pipelined: the last images are still on their own streams
+            ex.wait(kk)
     e1.record()
     torch.cuda.synchronize()
     if world > 1:
@@ -532,7 +538,7 @@ def run_sar(a):
     if ex is not None:
         ex.disarm()
     lo, hi = rdist.shard_range(g, rank, world)
-    kx, kp = ex.inputs() if ex is not None else (xs, ps)      # the fused variant: this rank's pulled copy of rank 0's cube
+    kx, kp = ex.inputs(0) if ex is not None else (xs, ps)     # the fused variant: this rank's pulled copy of rank 0's cube
     k0.record()
     for _ in range(a.steps):
         eng.sar_image(kx, kp, ds, lam, lo, hi)
@@ -555,7 +561,10 @@ def run_sar(a):
         if rank == 0:
             xs.copy_(xh, non_blocking=True)
             ps.copy_(ph, non_blocking=True)
-        ih.copy_(step(), non_blocking=True)
+        img = step()
+        if ex is not None:
+            ex.wait(step_no[0] - 1)                              # the image's stream -> the stream of the read-back
+        ih.copy_(img, non_blocking=True)
     e1.record()
     torch.cuda.synchronize()
     e2e_ms = e0.elapsed_time(e1)
@@ -581,6 +590,7 @@ def run_sar(a):
                            "parallelism": (f"voxel-sharded x{world}: radar_sar_image(g_begin, g_end) per rank reads rank 0's aperture cube + "
                                            "geometry over NVLink peer memory and its range-FFT kernel stores the tile into every rank's "
                                            "image (symmetric memory, radar_ctx_set_image_mirrors); two device barriers per image, no collective"
+                                           + ("; two images in flight (one stream + one context per image slot)" if pipelined else "")
                                            if fused else
                                            f"voxel-sharded x{world}: NCCL broadcast of aperture cube + geometry, "
                                            "radar_sar_image(g_begin, g_end) per rank, NCCL all-gather of the image tiles"),

@@ -220,104 +220,154 @@ class PeerPointExchange:
 
 class PeerImageExchange:
     """The voxel-sharded synthetic-array image over NVLink peer memory, without a collective: one symmetric allocation
-    holds the aperture cube + geometry of the feeding rank and ``depth`` full [S][G] images on every rank.
+    holds, per image slot (``depth`` of them), the aperture cube + geometry of the feeding rank and a full [S][G] image on
+    every rank.
 
-        ex.put_inputs(aperture, positions)      # rank ``src`` only: into its symmetric region; then every rank:
-        ex.inputs_ready()                       # cross-rank barrier on the current stream
-        ap, po = ex.inputs()                    # this rank's copy, pulled from rank src's region by one peer copy each (1.5 MB)
+        ex.put_inputs(k, aperture, positions)   # rank ``src`` only: into slot k of its symmetric region; then every rank:
+        ex.inputs_ready(k)                      # cross-rank barrier on the slot's stream
+        ap, po = ex.inputs(k)                   # this rank's copy, pulled from rank src's region by one peer copy each (1.5 MB)
         ex.arm(k)                               # radar_sar_image also stores its cells into image k of EVERY rank, at this rank's columns
-        engine.sar_image(ap, po, dirs, lam, lo, hi, out=ex.tile)
+        engine_k.sar_image(ap, po, dirs, lam, lo, hi, out=tile_k)
         ex.finish(k)                            # cross-rank barrier: all tiles of image k have landed everywhere
         img = ex.image(k)                       # [S][G] complex64 view of this rank's image k
 
-    The all-gather of the tiles is the store stream of the range-FFT kernel (``radar_ctx_set_image_mirrors``), the
-    broadcast is a pull by the copy engines (kernels that load the cube straight from the peer run 1.5x longer: the small
-    preparation kernels are latency chains); ``finish(k)`` also fences the inputs (rank src may overwrite them afterwards) and
-    the reader must be done with image k before ``arm`` of step k + depth."""
+    (``run(k, ...)`` is that sequence.)  The all-gather of the tiles is the store stream of the range-FFT kernel
+    (``radar_ctx_set_image_mirrors``), the broadcast is a pull by the copy engines (kernels that load the cube straight
+    from the peer run 1.5x longer: the small preparation kernels are latency chains).  ``finish(k)`` also fences slot k's
+    inputs; the reader must be done with image k before ``run`` of step k + depth.
 
-    def __init__(self, engine, num_samples: int, n_elems: int, n_dirs: int, depth: int = 2, src: int = 0):
+    ``pipelined=True`` gives every slot its own stream and its own ``RadarEngine`` (the scratch of a context serves one
+    image at a time), so consecutive images overlap: the peer stores and barriers of image k run under the GEMM of image
+    k + 1.  ``image(k)`` is then valid once ``streams[k % depth]`` has reached the end of ``run(k)``."""
+
+    def __init__(self, engine, num_samples: int, n_elems: int, n_dirs: int, depth: int = 2, src: int = 0,
+                 pipelined: bool = False):
         import torch.distributed._symmetric_memory as symm
-        self.engine, self.s, self.n, self.g, self.depth, self.src = engine, int(num_samples), int(n_elems), int(n_dirs), int(depth), int(src)
+        self.s, self.n, self.g, self.depth, self.src = int(num_samples), int(n_elems), int(n_dirs), int(depth), int(src)
         self.world, self.rank = world_size(), dist.get_rank()
         up = lambda v: (v + 255) // 256 * 256                                  # noqa: E731
         self.ap_bytes, self.pos_bytes, self.img_bytes = self.s * self.n * 8, 3 * self.n * 8, self.s * self.g * 8
         self.pos_off = up(self.ap_bytes)
         self.img_off = self.pos_off + up(self.pos_bytes)
-        self.img_slot = up(self.img_bytes)
+        self.slot = self.img_off + up(self.img_bytes)                          # bytes of one slot: inputs | image
         dev = engine.device
-        self.buf = symm.empty((self.img_off + self.depth * self.img_slot,), dtype=torch.uint8, device=dev)
+        self.engines = [engine]
+        self.streams = [None] * self.depth
+        if pipelined:
+            from .engine import RadarEngine
+            self.engines += [RadarEngine(engine.R, engine.S, engine.cpl, engine.L, device=dev) for _ in range(self.depth - 1)]
+            self.streams = [torch.cuda.Stream(device=dev) for _ in range(self.depth)]
+        self.pipelined = bool(pipelined)
+        self.buf = symm.empty((self.depth * self.slot,), dtype=torch.uint8, device=dev)
         self.buf.zero_()
         self.hdl = symm.rendezvous(self.buf, dist.group.WORLD)
         self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
         self.src_buf = self.hdl.get_buffer(self.src, self.buf.shape, torch.uint8)
         self.lo, self.hi = shard_range(self.g, self.rank, self.world)
-        self.tile = torch.empty((self.s, self.hi - self.lo), dtype=torch.complex64, device=dev)
-        self.ap_local = torch.zeros((self.s, self.n), dtype=torch.complex64, device=dev)
-        self.pos_local = torch.zeros((3, self.n), dtype=torch.float64, device=dev)
+        self.tiles = [torch.empty((self.s, self.hi - self.lo), dtype=torch.complex64, device=dev) for _ in range(self.depth)]
+        self.ap_local = [torch.zeros((self.s, self.n), dtype=torch.complex64, device=dev) for _ in range(self.depth)]
+        self.pos_local = [torch.zeros((3, self.n), dtype=torch.float64, device=dev) for _ in range(self.depth)]
         torch.cuda.synchronize(dev)
         self.hdl.barrier(channel=0)
+        torch.cuda.synchronize(dev)
 
-    def put_inputs(self, aperture: torch.Tensor, positions: torch.Tensor):
+    def engine_of(self, k: int):
+        return self.engines[(k % self.depth) % len(self.engines)]
+
+    def stream_of(self, k: int):
+        st = self.streams[k % self.depth]
+        return torch.cuda.current_stream() if st is None else st
+
+    def _views(self, base: torch.Tensor, k: int):
+        off = (k % self.depth) * self.slot
+        return (base[off:off + self.ap_bytes].view(torch.complex64).view(self.s, self.n),
+                base[off + self.pos_off:off + self.pos_off + self.pos_bytes].view(torch.float64).view(3, self.n))
+
+    def put_inputs(self, k: int, aperture: torch.Tensor, positions: torch.Tensor):
         if self.rank != self.src:
             return
-        self.buf[:self.ap_bytes].view(torch.complex64).view(self.s, self.n).copy_(aperture, non_blocking=True)
-        self.buf[self.pos_off:self.pos_off + self.pos_bytes].view(torch.float64).view(3, self.n).copy_(positions, non_blocking=True)
+        ap, po = self._views(self.buf, k)
+        ap.copy_(aperture, non_blocking=True)
+        po.copy_(positions, non_blocking=True)
 
-    def inputs_ready(self):
-        self.hdl.barrier(channel=1)
+    def inputs_ready(self, k: int):
+        self.hdl.barrier(channel=1 + (k % self.depth))
 
-    def inputs(self):
-        """After ``inputs_ready``: pull rank src's aperture cube + geometry into this rank's memory (rank src uses its own
-        region in place) -> (aperture [S, N] c64, positions [3, N] f64)."""
-        b = self.src_buf if self.rank != self.src else self.buf
-        ap = b[:self.ap_bytes].view(torch.complex64).view(self.s, self.n)
-        po = b[self.pos_off:self.pos_off + self.pos_bytes].view(torch.float64).view(3, self.n)
+    def inputs(self, k: int):
+        """After ``inputs_ready(k)``: pull rank src's aperture cube + geometry of slot k into this rank's memory (rank src
+        uses its own region in place) -> (aperture [S, N] c64, positions [3, N] f64)."""
         if self.rank == self.src:
-            return ap, po
-        self.ap_local.copy_(ap, non_blocking=True)
-        self.pos_local.copy_(po, non_blocking=True)
-        return self.ap_local, self.pos_local
+            return self._views(self.buf, k)
+        ap, po = self._views(self.src_buf, k)
+        self.ap_local[k % self.depth].copy_(ap, non_blocking=True)
+        self.pos_local[k % self.depth].copy_(po, non_blocking=True)
+        return self.ap_local[k % self.depth], self.pos_local[k % self.depth]
 
     def arm(self, k: int):
-        off = self.img_off + (k % self.depth) * self.img_slot
-        self.engine.set_image_mirrors([p + off for p in self.ptrs], self.g, self.lo)
+        off = (k % self.depth) * self.slot + self.img_off
+        self.engine_of(k).set_image_mirrors([p + off for p in self.ptrs], self.g, self.lo)
 
     def disarm(self):
-        self.engine.set_image_mirrors([], 0, 0)
+        for e in self.engines:
+            e.set_image_mirrors([], 0, 0)
 
     def finish(self, k: int):
-        self.hdl.barrier(channel=2 + (k % self.depth))
+        self.hdl.barrier(channel=1 + self.depth + (k % self.depth))
 
     def image(self, k: int) -> torch.Tensor:
-        off = self.img_off + (k % self.depth) * self.img_slot
+        off = (k % self.depth) * self.slot + self.img_off
         return self.buf[off:off + self.img_bytes].view(torch.complex64).view(self.s, self.g)
+
+    def _run_on_current_stream(self, k: int, dirs, lambda_m, aperture, positions):
+        if aperture is not None:
+            self.put_inputs(k, aperture, positions)
+        self.inputs_ready(k)
+        ap, po = self.inputs(k)
+        self.arm(k)
+        self.engine_of(k).sar_image(ap, po, dirs, lambda_m, self.lo, self.hi, out=self.tiles[k % self.depth])
+        self.finish(k)
 
     def run(self, k: int, dirs: torch.Tensor, lambda_m: float, aperture: Optional[torch.Tensor] = None,
             positions: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """One image: rank ``src`` passes the aperture cube + geometry, the others None."""
-        if aperture is not None:
-            self.put_inputs(aperture, positions)
-        self.inputs_ready()
-        ap, po = self.inputs()
-        self.arm(k)
-        self.engine.sar_image(ap, po, dirs, lambda_m, self.lo, self.hi, out=self.tile)
-        self.finish(k)
+        """One image: rank ``src`` passes the aperture cube + geometry, the others None.  Pipelined: the work is queued on
+        the slot's stream after whatever the current stream has queued so far (the inputs)."""
+        st = self.streams[k % self.depth]
+        if st is None:
+            self._run_on_current_stream(k, dirs, lambda_m, aperture, positions)
+        else:
+            st.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(st):
+                self._run_on_current_stream(k, dirs, lambda_m, aperture, positions)
         return self.image(k)
+
+    def wait(self, k: int):
+        """Make the current stream wait for image k (pipelined mode; a no-op otherwise)."""
+        st = self.streams[k % self.depth]
+        if st is not None:
+            torch.cuda.current_stream().wait_stream(st)
 
     def capture(self, dirs: torch.Tensor, lambda_m: float, aperture: Optional[torch.Tensor] = None,
                 positions: Optional[torch.Tensor] = None):
         """CUDA graphs of ``run`` for the ``depth`` image slots (one image is ten short launches: at these sizes the host
         would otherwise set the pace).  Call after a few eager ``run`` calls (scratch sized, symmetric memory warm) with the
         tensors that will hold the inputs of every later image; returns ``replay(k) -> image k``.  Every rank must capture
-        and replay in step."""
+        and replay in step.  Pipelined: slot k's graph is replayed on its stream (after what the current stream has
+        queued), so consecutive replays overlap; ``wait(k)`` joins."""
+        torch.cuda.synchronize()
         graphs = []
         for k in range(self.depth):
             gr = torch.cuda.CUDAGraph()
             with torch.cuda.graph(gr):
-                self.run(k, dirs, lambda_m, aperture, positions)
+                self._run_on_current_stream(k, dirs, lambda_m, aperture, positions)
             graphs.append(gr)
 
         def replay(k: int) -> torch.Tensor:
-            graphs[k % self.depth].replay()
+            st = self.streams[k % self.depth]
+            if st is None:
+                graphs[k % self.depth].replay()
+            else:
+                st.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(st):
+                    graphs[k % self.depth].replay()
             return self.image(k)
         return replay

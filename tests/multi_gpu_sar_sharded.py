@@ -63,6 +63,21 @@ def main():
                 assert e3 < 2e-6, (rank, k, e3)
             dist.barrier()
         ex.disarm()
+        # two images in flight: one stream and one context per image slot, consecutive images overlap
+        exp = rdist.PeerImageExchange(eng, s, n, g, depth=2, src=0, pipelined=True)
+        for pair in range(2):
+            keep = []                                           # inputs stay alive until their images are done
+            for k in (2 * pair, 2 * pair + 1):
+                scale = float(2 ** (k % 3))
+                xin = xs * scale if rank == 0 else None
+                keep.append(xin)
+                exp.run(k, ds, lam, xin, ps if rank == 0 else None)
+            for k in (2 * pair, 2 * pair + 1):
+                exp.wait(k)
+                torch.cuda.synchronize()
+                assert torch.equal(exp.image(k), img * float(2 ** (k % 3))), (rank, s, n, g, k, "pipelined exchange differs")
+            dist.barrier()
+        exp.disarm()
         after = eng.sar_image(xs, ps, ds, lam, lo, hi)      # mirrors off again: a plain call
         assert torch.equal(after, img[:, lo:hi])
         dist.barrier()
