@@ -477,11 +477,18 @@ def run_sar(a):
     fused = world > 1 and os.environ.get("RADAR_B200_SAR_EXCHANGE", "peer") != "nccl"
     # RADAR_B200_SAR_PIPELINE=0: one image at a time; default: the two image slots run on their own streams and contexts, so the
     # peer stores and barriers of image k overlap the GEMM of image k + 1
-    pipelined = fused and os.environ.get("RADAR_B200_SAR_PIPELINE", "1") != "0"
+    want_pipe = os.environ.get("RADAR_B200_SAR_PIPELINE", "1") != "0"
+    pipelined = fused and want_pipe
     ex = rdist.PeerImageExchange(eng, s, n, g, depth=2, src=0, pipelined=pipelined) if fused else None
+    # N = 1: the same two slots on one GPU (LocalImagePipeline): the small kernels of one image run under the GEMM of the next
+    local = rdist.LocalImagePipeline(eng, g, depth=2) if (world == 1 and want_pipe) else None
     step_no = [0]
 
     def step():
+        if local is not None:
+            k = step_no[0]
+            step_no[0] += 1
+            return local.run(k, xs, ps, ds, lam)
         if ex is not None:
             k = step_no[0]
             step_no[0] += 1
@@ -495,6 +502,12 @@ def run_sar(a):
         img = step()
     torch.cuda.synchronize()
     graphed = False
+    if local is not None and os.environ.get("RADAR_B200_SAR_GRAPH", "1") != "0":
+        local.capture(xs, ps, ds, lam)
+        graphed = True
+        for _ in range(4):
+            img = step()
+        torch.cuda.synchronize()
     if ex is not None and os.environ.get("RADAR_B200_SAR_GRAPH", "1") != "0":
         # one image is ten short launches per rank: replay them as a CUDA graph per image slot so the host does not set the pace
         ok = torch.ones(1, device=dev)
@@ -526,9 +539,9 @@ def run_sar(a):
     e0.record()
     for _ in range(a.steps):
         img = step()
-    if ex is not None:
+    if ex is not None or local is not None:
         for kk in range(max(0, step_no[0] - 2), step_no[0]):     # pipelined: the last images are still on their own streams
-            ex.wait(kk)
+            (ex or local).wait(kk)
     e1.record()
     torch.cuda.synchronize()
     if world > 1:
@@ -539,9 +552,22 @@ def run_sar(a):
         ex.disarm()
     lo, hi = rdist.shard_range(g, rank, world)
     kx, kp = ex.inputs(0) if ex is not None else (xs, ps)     # the fused variant: this rank's pulled copy of rank 0's cube
+    kt = torch.empty((s, hi - lo), dtype=torch.complex64, device=dev)
+    eng.sar_image(kx, kp, ds, lam, lo, hi, out=kt)
+    torch.cuda.synchronize()
+    try:                                                       # the launches of one image as a graph: device time, not the host's pace
+        gk = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gk):
+            eng.sar_image(kx, kp, ds, lam, lo, hi, out=kt)
+        one_image = gk.replay
+    except Exception:  # noqa: BLE001
+        one_image = lambda: eng.sar_image(kx, kp, ds, lam, lo, hi, out=kt)   # noqa: E731
+    for _ in range(3):
+        one_image()
+    torch.cuda.synchronize()
     k0.record()
     for _ in range(a.steps):
-        eng.sar_image(kx, kp, ds, lam, lo, hi)
+        one_image()
     k1.record()
     torch.cuda.synchronize()
     k_ms = k0.elapsed_time(k1) / a.steps
@@ -562,8 +588,8 @@ def run_sar(a):
             xs.copy_(xh, non_blocking=True)
             ps.copy_(ph, non_blocking=True)
         img = step()
-        if ex is not None:
-            ex.wait(step_no[0] - 1)                              # the image's stream -> the stream of the read-back
+        if ex is not None or local is not None:
+            (ex or local).wait(step_no[0] - 1)                   # the image's stream -> the stream of the read-back
         ih.copy_(img, non_blocking=True)
     e1.record()
     torch.cuda.synchronize()
@@ -592,6 +618,8 @@ def run_sar(a):
                                            "image (symmetric memory, radar_ctx_set_image_mirrors); two device barriers per image, no collective"
                                            + ("; two images in flight (one stream + one context per image slot)" if pipelined else "")
                                            if fused else
+                                           "one GPU, two images in flight (one stream + one context per image slot, CUDA-graph replay): the max / prep / "
+                                           "range-FFT kernels of one image run under the GEMM of the next" if local is not None else
                                            f"voxel-sharded x{world}: NCCL broadcast of aperture cube + geometry, "
                                            "radar_sar_image(g_begin, g_end) per rank, NCCL all-gather of the image tiles"),
                            "l2_policy": "operands (1.4 MB) are L2-resident by design; output tiles are written once"},

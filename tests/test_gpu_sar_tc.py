@@ -170,3 +170,32 @@ def test_split_k_does_not_change_a_bit(torch_cuda):
     for ks in (2, 3, 7, 0):
         np.testing.assert_array_equal(outs[ks], outs[1])
     assert rel_l2(outs[1][:, :64], sar_direct(x, pos, dirs, lam, np.arange(64))) < TOL
+
+
+def test_two_images_in_flight_on_one_gpu(torch_cuda):
+    """distributed.LocalImagePipeline: two contexts / streams / CUDA graphs, consecutive images overlap; every image must be
+    the plain call's image bit for bit, also after the inputs changed between replays."""
+    torch = torch_cuda
+    from mmwave_radar_processing_b200.distributed import LocalImagePipeline
+    from mmwave_radar_processing_b200.engine import RadarEngine
+    s, n, g = 90, 700, 1500
+    x, pos, dirs, lam = sar_case(s, n, g, seed=21)
+    xs, ps, ds = torch.from_numpy(x).cuda(), torch.from_numpy(pos).cuda(), torch.from_numpy(dirs).cuda()
+    eng = RadarEngine(1, s, 1, 1)
+    want = eng.sar_image(xs, ps, ds, lam).clone()
+    pipe = LocalImagePipeline(eng, g, depth=2)
+    for k in range(3):                                       # eager first (sizes the scratch of both contexts)
+        img = pipe.run(k, xs, ps, ds, lam)
+        pipe.wait(k)
+        assert torch.equal(img, want)
+    pipe.capture(xs, ps, ds, lam)
+    imgs = [pipe.run(k, xs, ps, ds, lam) for k in (0, 1)]    # both in flight
+    for k in (0, 1):
+        pipe.wait(k)
+    torch.cuda.synchronize()
+    assert torch.equal(imgs[0], want) and torch.equal(imgs[1], want)
+    xs.mul_(2.0)                                             # new input in the captured tensor: exact power-of-two scale
+    img = pipe.run(2, xs, ps, ds, lam)
+    pipe.wait(2)
+    torch.cuda.synchronize()
+    assert torch.equal(img, want * 2.0)
