@@ -80,6 +80,7 @@ __global__ void __launch_bounds__(C::NT, 1) rd_reg_kernel(const __grid_constant_
             rd_reg_doppler_load<C>(a, ring + st * C::RAW_STAGE_W, shift + colc, h, v);
             mb::arrive(raw_empty + st);
             rd_reg_doppler_finish<C>(ws, v);
+            rd_reg_doppler_twiddle<C>(a, h, v);
             mb::wait(tile_empty + tb, (tround & 1) ^ 1);
             if (active) rd_reg_store_row<C>(v, tiles + (size_t)tb * C::TILE + (size_t)col * C::P, h);
             mb::arrive(tile_full + tb);
@@ -244,6 +245,7 @@ __global__ void __launch_bounds__(C::NT, 1) rd_reg_dbs_kernel(const __grid_const
                 rd_reg_doppler_load<C>(a, ring + st * C::RAW_STAGE_W, shift + colc, h, v);
                 mb::arrive(raw_empty + st);
                 rd_reg_doppler_finish<C>(ws, v);
+                rd_reg_doppler_twiddle<C>(a, h, v);
                 mb::wait(tile_empty + tb, (tround & 1) ^ 1);
                 if (active) rd_reg_store_row<C>(v, tiles + (size_t)tb * C::TILE + (size_t)col * C::P, h);
                 mb::arrive(tile_full + tb);
@@ -267,7 +269,7 @@ __global__ void __launch_bounds__(C::NT, 1) rd_reg_dbs_kernel(const __grid_const
             if (C::DF == 2) {
                 const int k = (d + C::L - C::L / 2) % C::L;
                 pos[q] = k % C::LH;
-                cw[q] = C::TW ? a.twL[k] : cmake((k & 1) ? -1.0f : 1.0f, 0.0f);
+                cw[q] = cmake((C::TW ? k >= C::LH : (k & 1)) ? -1.0f : 1.0f, 0.0f);
             }
         }
         unsigned j = 0;
@@ -294,8 +296,7 @@ __global__ void __launch_bounds__(C::NT, 1) rd_reg_dbs_kernel(const __grid_const
                                 cf x = row[pos[q]];
                                 if (C::DF == 2) {                           // the Doppler combine of RdRegColumn::value
                                     const cf o = row[pos[q] + C::HP];
-                                    if (C::TW) x = cmake(fmaf(cw[q].x, o.x, fmaf(-cw[q].y, o.y, x.x)), fmaf(cw[q].x, o.y, fmaf(cw[q].y, o.x, x.y)));
-                                    else x = cfma(cw[q].x, o, x);
+                                    x = cfma(cw[q].x, o, x);
                                 }
                                 cf c = first ? cmake(0.f, 0.f) : zrow[32 * q];
                                 c.x = fmaf(x.x, w[q].x, fmaf(-x.y, w[q].y, c.x));

@@ -197,6 +197,17 @@ RB_HD void rd_reg_doppler_finish(float ws, cf (&v)[C::LH]) {
 #pragma unroll
     for (int k = 0; k < C::LH; ++k) v[k] = cscale(v[k], ws);
 }
+// Twiddle mode of the Doppler split (L = 100: even / odd samples): X[k] = E[k mod LH] + W_L^k O[k mod LH] and
+// W_L^(m + LH) = -W_L^m, so the odd class multiplies its LH partial bins by W_L^m HERE, once, and phase B only adds or
+// subtracts (bins k < LH / k >= LH).  Folding in phase B instead cost four FMAs per value, for every range sample of every
+// column and again in every output class of the range split: four times the multiplies.
+template <class C>
+RB_HD void rd_reg_doppler_twiddle(const RdRegParams<C>& a, int h, cf (&v)[C::LH]) {
+    if (C::TW && h) {
+#pragma unroll
+        for (int m = 0; m < C::LH; ++m) v[m] = cmul(v[m], a.twL[m]);
+    }
+}
 // DF == 1: tile row in fftshifted order (frequency bin k lands at d = (k + L/2) mod L); DF == 2: the class's LH partial
 // bins in natural order at row + h*HP (the combine and the shift happen in phase B's addressing)
 template <class C>
@@ -218,27 +229,24 @@ RB_HD void rd_reg_store_row(const cf (&v)[C::LH], cf* row, int h) {
 }
 
 // ---- phase B: range transform of column (antenna g, Doppler position d), output class (a, ODD) ------------------------------
-// DF == 2: position d holds frequency bin k = (d + L - L/2) mod L = Y0[k mod LH] + (-1)^k Y1[k mod LH]
+// DF == 2: position d holds frequency bin k = (d + L - L/2) mod L = Y0[k mod LH] + sign Y1[k mod LH]; coprime halves:
+// sign = (-1)^k; twiddle mode (Y1 already carries W_L^(k mod LH), rd_reg_doppler_twiddle): sign = -1 for k >= LH
 template <class C>
 struct RdRegColumn {                      // one tile column as phase B sees it: value(s) applies the Doppler combine
     const cf* p;
     float sign;
-    cf w;
-    RB_HD RdRegColumn(const cf* tile, int g, int d, const cf* twL) {
-        sign = 1.0f; w = cmake(1.0f, 0.0f);
+    RB_HD RdRegColumn(const cf* tile, int g, int d, const cf*) {
+        sign = 1.0f;
         if (C::DF == 1) p = tile + (size_t)g * C::S * C::P + d;
         else {
             const int k = (d + C::L - C::L / 2) % C::L;
-            sign = (k & 1) ? -1.0f : 1.0f;
-            if (C::TW) w = twL[k];
+            sign = (C::TW ? k >= C::LH : (k & 1)) ? -1.0f : 1.0f;
             p = tile + (size_t)g * C::S * C::P + k % C::LH;
         }
     }
     RB_HD cf value(int s) const {
         if (C::DF == 1) return p[s * C::P];
-        const cf e = p[s * C::P], o = p[s * C::P + C::HP];
-        if (C::TW) return cmake(fmaf(w.x, o.x, fmaf(-w.y, o.y, e.x)), fmaf(w.x, o.y, fmaf(w.y, o.x, e.y)));
-        return cfma(sign, o, e);
+        return cfma(sign, p[s * C::P + C::HP], p[s * C::P]);
     }
 };
 // sigma = +1 for a = 0, -1 for a = 1.  Input m of class k_BF: sum_q x[(SH*q + BF*m) mod S] * W_BF^(q*k_BF)

@@ -45,6 +45,7 @@ static double check(int n_frames) {
                 cf v[C::LH];
                 rd_reg_doppler_load<C>(a, stage.data(), shift + col, h, v);
                 rd_reg_doppler_finish<C>(a.winS[col % S], v);
+                rd_reg_doppler_twiddle<C>(a, h, v);
                 rd_reg_store_row<C>(v, tile.data() + (size_t)col * C::P, h);
             }
         for (int cls = 0; cls < C::BF; ++cls)
