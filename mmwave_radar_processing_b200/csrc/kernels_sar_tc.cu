@@ -743,15 +743,15 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
     const size_t fsmem = arena_bytes((size_t)S * (kTcFftDirs | 1), sizeof(cf)) + arena_bytes(S, sizeof(cf)) + arena_bytes(S, 4) + arena_bytes(S, 2);
     if (fsmem > (size_t)ctx->max_smem_optin) return 1;          // the range FFT of the beams keeps S x 33 cells in shared memory
     for (int t = 0; t < n_tiles; ++t) {
-    const int s_base = t * ST, S_t = (S - s_base < ST) ? S - s_base : ST, SP_t = (S_t + 7) & ~7, NB_t = 2 * SP_t;
-    SarPrepArgs p{aperture + (size_t)s_base * N, S_t, N, SP_t, NB_t, n_chunks, positions, 1.0 / lambda_m, bblk, posl, posf, stepf, lin, max_bits, hamf};
-    sar_tc_prep_kernel<<<dim3((unsigned)n_chunks, kTcPrepSplit), 256, 0, st>>>(p);
-    RB_CUDA_OK(ctx, cudaGetLastError());
+        const int s_base = t * ST, S_t = (S - s_base < ST) ? S - s_base : ST, SP_t = (S_t + 7) & ~7, NB_t = 2 * SP_t;
+        SarPrepArgs p{aperture + (size_t)s_base * N, S_t, N, SP_t, NB_t, n_chunks, positions, 1.0 / lambda_m, bblk, posl, posf, stepf, lin, max_bits, hamf};
+        sar_tc_prep_kernel<<<dim3((unsigned)n_chunks, kTcPrepSplit), 256, 0, st>>>(p);
+        RB_CUDA_OK(ctx, cudaGetLastError());
 
-    SarTcArgs a{bblk, posl, posf, stepf, (ctx->sar_dbg & 32) ? nullptr : lin, dirs, npad, n_chunks, seg_chunks, G, S_t, SP_t, NB_t, g_begin, g_end,
-                beams + (size_t)s_base * width, ksplit, segs_per_split, n_part > 1 ? 1 : 0, (size_t)S * width, (ctx->sar_dbg & 64) ? 1 : 0};
-    const int tpr = ctx->sar_tpr > 0 ? ctx->sar_tpr : (mt == 2 ? 1 : 2);      // measured: 0.443 / 0.450 ms (2 tiles), 0.550 / 0.503 ms (1 tile)
-    const int unr = ctx->sar_dbg & 15, cs = !(ctx->sar_dbg & 16);      // RADAR_B200_SAR_DBG: unroll of the element loop (0 = default), +16 = sincospif
+        SarTcArgs a{bblk, posl, posf, stepf, (ctx->sar_dbg & 32) ? nullptr : lin, dirs, npad, n_chunks, seg_chunks, G, S_t, SP_t, NB_t, g_begin, g_end,
+                    beams + (size_t)s_base * width, ksplit, segs_per_split, n_part > 1 ? 1 : 0, (size_t)S * width, (ctx->sar_dbg & 64) ? 1 : 0};
+        const int tpr = ctx->sar_tpr > 0 ? ctx->sar_tpr : (mt == 2 ? 1 : 2);      // measured: 0.443 / 0.450 ms (2 tiles), 0.550 / 0.503 ms (1 tile)
+        const int unr = ctx->sar_dbg & 15, cs = !(ctx->sar_dbg & 16);      // RADAR_B200_SAR_DBG: unroll of the element loop (0 = default), +16 = sincospif
 #define RB_SAR_TC_LAUNCH(MT_, TPR_, UNR_, CS_)                                                                               \
     do {                                                                                                                     \
         RB_CUDA_OK(ctx, cudaFuncSetAttribute(sar_tc_kernel<MT_, TPR_, UNR_, CS_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
@@ -762,13 +762,13 @@ int launch_sar_image_tc(radar_ctx* ctx, const cf* aperture, int S, int N, const 
         if (cs) { if (unr == 1) RB_SAR_TC_LAUNCH(MT_, TPR_, 1, true); else if (unr == 2) RB_SAR_TC_LAUNCH(MT_, TPR_, 2, true); else RB_SAR_TC_LAUNCH(MT_, TPR_, 16, true); } \
         else { if (unr == 1) RB_SAR_TC_LAUNCH(MT_, TPR_, 1, false); else if (unr == 2) RB_SAR_TC_LAUNCH(MT_, TPR_, 2, false); else RB_SAR_TC_LAUNCH(MT_, TPR_, 16, false); } \
     } while (0)
-    if (mt == 2 && tpr == 2) RB_SAR_TC_VARIANTS(2, 2);
-    else if (mt == 2) RB_SAR_TC_VARIANTS(2, 1);
-    else if (tpr == 2) RB_SAR_TC_VARIANTS(1, 2);
-    else RB_SAR_TC_VARIANTS(1, 1);
+        if (mt == 2 && tpr == 2) RB_SAR_TC_VARIANTS(2, 2);
+        else if (mt == 2) RB_SAR_TC_VARIANTS(2, 1);
+        else if (tpr == 2) RB_SAR_TC_VARIANTS(1, 2);
+        else RB_SAR_TC_VARIANTS(1, 1);
 #undef RB_SAR_TC_VARIANTS
 #undef RB_SAR_TC_LAUNCH
-    RB_CUDA_OK(ctx, cudaGetLastError());
+        RB_CUDA_OK(ctx, cudaGetLastError());
     }
 
     SarFftArgs f{beams, n_part, S, width, ctx->fftS.hann, ctx->fftS.tw, ctx->fftS.pos, out, ctx->fftS.plan, make_fastdiv(kTcFftDirs), max_bits, {nullptr}, ctx->n_image_mirrors, ctx->image_row_stride, ctx->image_col0};
