@@ -52,6 +52,10 @@ def test_cabi_host_only_entry_points():
     assert rc == -1 and not ctx.value
     assert b">= 1" in lib.radar_last_error(None)
     assert lib.radar_ctx_destroy(None) == 0          # like free(NULL)
+    assert lib.radar_chirp_zoom_static_capacity() == 65536    # the stated limit of the allocation-free entry point
+    # null contexts are refused before anything touches a device
+    assert lib.radar_chirp_zoom_static(None, None, 0, 1, 0, 1, None, 1, None, None) == -1
+    assert lib.radar_ctx_set_image_mirrors(None, None, 0, 0, 0) == -1
 
 
 def _native_check(name, extra=()):
