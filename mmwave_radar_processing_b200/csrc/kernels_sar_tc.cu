@@ -61,7 +61,7 @@ __device__ __forceinline__ int sar_scale_exp(float mx) {
     if (!(mx > 0.0f) || mx > 3.0e38f) return 0;             // empty / all-zero / non-finite input: no scaling
     int e;
     frexpf(mx, &e);                                          // mx = m 2^e, m in [1/2, 1)
-    e = e < -100 ? -100 : (e > 100 ? 100 : e);
+    e = e < -110 ? -110 : e;                                 // keeps both 2^(15 - e) and its inverse 2^(e - 28) exact floats (e <= 128)
     return 15 - e;
 }
 

@@ -199,3 +199,19 @@ def test_two_images_in_flight_on_one_gpu(torch_cuda):
     pipe.wait(2)
     torch.cuda.synchronize()
     assert torch.equal(img, want * 2.0)
+
+
+def test_input_scale_leaves_no_trace(torch_cuda):
+    """The FP16 operands are scaled by exact powers of two taken from the largest sample of the call and the range-FFT kernel
+    undoes them: an aperture cube scaled by 2^80 or 2^-80 must give the image scaled by exactly that, bit for bit."""
+    torch = torch_cuda
+    s, n, g = 90, 300, 200
+    x, pos, dirs, lam = sar_case(s, n, g, seed=33)
+    xs, ps, ds = torch.from_numpy(x).cuda(), torch.from_numpy(pos).cuda(), torch.from_numpy(dirs).cuda()
+    eng = engine_with_mode(0, s)
+    want = eng.sar_image(xs, ps, ds, lam).clone()
+    for p2 in (80, -80, 1, -7):
+        got = eng.sar_image(xs * (2.0 ** p2), ps, ds, lam)
+        assert torch.equal(got, want * (2.0 ** p2)), p2
+    zero = eng.sar_image(torch.zeros_like(xs), ps, ds, lam)
+    assert torch.count_nonzero(torch.view_as_real(zero)) == 0
